@@ -1,0 +1,149 @@
+"""Seeded synthetic FS-Mol-shaped tasks.  There is no network / dataset in the
+build or bench environment, so every test, the oracle and bench.py draw their inputs from here.
+
+Molecule: V = clip(round(N(26, 7)), 8, 60) atoms; bonds = random spanning tree (atom i -> uniform j < i)
+plus floor(V/6) extra random pairs (each bond stored once, as FS-Mol does); bond type in {0,1,2} w.p.
+(0.80, 0.19, 0.01); node features [V, 32] float32 = concatenated one-hot blocks; ECFP count fingerprint
+[2048] int32 with ~45 non-zeros of value 1..4; 42 phys-chem descriptors ~ N(0, 1).
+Each task is a handful of chemical series ("scaffolds") sharing fingerprint bits; the hidden score is
+a per-series effect plus noise -> numeric label exp(1 + score) (positive, like FS-Mol activity values)
+and bool label = score above the task median, so the features cluster and the GP fit has signal.  `task_rng = np.random.default_rng(1234 + task_id)`.
+"""
+import math
+from typing import List, Tuple
+
+import numpy as np
+
+from .fsmol_batcher import (NUM_EDGE_TYPES, NUM_NODE_FEATURES, FSMolTaskSample, GraphData,
+                            MoleculeDatapoint)
+
+FINGERPRINT_DIM = 2048
+PHYS_CHEM_DESCRIPTORS_DIM = 42
+_ONE_HOT_BLOCKS = (15, 6, 5, 4, 2)  # sums to NUM_NODE_FEATURES
+assert sum(_ONE_HOT_BLOCKS) == NUM_NODE_FEATURES
+
+
+def _random_molecule_graph(rng: np.random.Generator) -> GraphData:
+    v = int(np.clip(np.rint(rng.normal(26.0, 7.0)), 8, 60))
+    # spanning tree + a few ring-closing bonds
+    src = np.arange(1, v, dtype=np.int64)
+    tgt = (rng.random(v - 1) * src).astype(np.int64)  # uniform j < i
+    n_extra = v // 6
+    ex_a = rng.integers(0, v, size=n_extra)
+    ex_b = rng.integers(0, v, size=n_extra)
+    keep = ex_a != ex_b
+    src = np.concatenate([src, ex_a[keep]])
+    tgt = np.concatenate([tgt, ex_b[keep]])
+    btype = rng.choice(NUM_EDGE_TYPES, size=src.shape[0], p=(0.80, 0.19, 0.01))
+    adjacency = [np.stack([src[btype == t], tgt[btype == t]], axis=1).astype(np.int64)
+                 for t in range(NUM_EDGE_TYPES)]
+    feats = np.zeros((v, NUM_NODE_FEATURES), dtype=np.float32)
+    col = 0
+    for width in _ONE_HOT_BLOCKS:
+        # skewed categorical so that some atom "types" dominate, as in real molecules
+        p = 0.5 ** np.arange(1, width + 1)
+        p /= p.sum()
+        pick = rng.choice(width, size=v, p=p)
+        feats[np.arange(v), col + pick] = 1.0
+        col += width
+    return GraphData(node_features=feats, adjacency_lists=adjacency, edge_features=[])
+
+
+def _random_fingerprint(rng: np.random.Generator, scaffold: np.ndarray) -> np.ndarray:
+    """Scaffold bits (shared by the molecules of one chemical series) + molecule-specific decoration."""
+    fp = np.zeros(FINGERPRINT_DIM, dtype=np.int32)
+    keep = scaffold[rng.random(scaffold.shape[0]) < 0.9]
+    fp[keep] = rng.integers(1, 5, size=keep.shape[0]).astype(np.int32)
+    n_own = int(np.clip(np.rint(rng.normal(12, 3)), 3, 40))
+    own = rng.choice(FINGERPRINT_DIM, size=n_own, replace=False)
+    fp[own] = rng.integers(1, 4, size=n_own).astype(np.int32)
+    return fp
+
+
+def make_task_molecules(task_id: int, num_molecules: int) -> List[MoleculeDatapoint]:
+    rng = np.random.default_rng(1234 + task_id)
+    name = f"SYNTH{task_id:06d}"
+    graphs = [_random_molecule_graph(rng) for _ in range(num_molecules)]
+    # a task = a handful of chemical series ("scaffolds"); activity depends on the series + noise
+    n_scaffolds = 4
+    scaffolds = [rng.choice(FINGERPRINT_DIM, size=int(rng.integers(28, 40)), replace=False)
+                 for _ in range(n_scaffolds)]
+    effect = rng.normal(size=n_scaffolds)
+    effect = (effect - effect.mean()) / (effect.std() + 1e-12)
+    member = rng.integers(0, n_scaffolds, size=num_molecules)
+    fps = [_random_fingerprint(rng, scaffolds[k]) for k in member]
+    descs = rng.normal(size=(num_molecules, PHYS_CHEM_DESCRIPTORS_DIM)).astype(np.float32)
+    score = effect[member] + 0.5 * rng.normal(size=num_molecules)
+    numeric = np.exp(1.0 + score)
+    thresh = np.median(score)
+    out = []
+    for i in range(num_molecules):
+        out.append(MoleculeDatapoint(task_name=name, smiles=f"SYN{task_id}_{i}", graph=graphs[i],
+                                     numeric_label=float(numeric[i]), bool_label=bool(score[i] > thresh),
+                                     fingerprint=fps[i], descriptors=descs[i]))
+    return out
+
+
+def make_task_sample(task_id: int, support_size: int, query_size: int) -> FSMolTaskSample:
+    """One few-shot task: `support_size` train molecules (>=1 of each class) and `query_size` test
+    molecules.  Deterministic in (task_id, support_size, query_size)."""
+    mols = make_task_molecules(task_id, support_size + query_size)
+    support, query = mols[:support_size], mols[support_size:]
+    labels = [m.bool_label for m in support]
+    if support_size >= 2 and (all(labels) or not any(labels)):
+        # force both classes into the support set by swapping with a query molecule
+        want = not labels[0]
+        for j, q in enumerate(query):
+            if q.bool_label == want:
+                support[-1], query[j] = query[j], support[-1]
+                break
+    return FSMolTaskSample(name=mols[0].task_name, train_samples=support, valid_samples=[],
+                           test_samples=query)
+
+
+def make_task_samples(first_task_id: int, num_tasks: int, support_size: int,
+                      query_size: int) -> List[FSMolTaskSample]:
+    return [make_task_sample(first_task_id + t, support_size, query_size) for t in range(num_tasks)]
+
+
+def trained_like_(model, alpha: float = 0.5, seed: int = 0) -> None:
+    """Make a freshly initialised feature extractor behave like a trained one for numerics tests:
+    the ReZero gates `alpha` are 1e-7 at init (fs_mol/modules/gnn.py:405-406), which would make every
+    GNN test vacuous; set them to `alpha`."""
+    import torch
+    with torch.no_grad():
+        for name, p in model.named_parameters():
+            if name.endswith(".alpha"):
+                p.fill_(alpha)
+
+
+def deterministic_init_(module_or_state, seed: int = 0, alpha: float = 0.5, gain: float = 1.0) -> None:
+    """Fill every non-GP tensor of a model (nn.Module or state-dict mapping) with values that depend
+    only on (tensor name, shape, seed) -- NOT on module construction order -- so that the reference
+    model (authoring container), the CPU oracle and the CUDA product get bit-identical weights and
+    the golden fixtures need not store 100 MB of parameters.  Linear weights ~ U(+-gain/sqrt(fan_in)),
+    biases ~ U(+-0.05), LayerNorm weight 1 +- 0.1, ReZero alpha = `alpha` (trained-like)."""
+    import zlib
+
+    import torch
+
+    state = module_or_state.state_dict() if hasattr(module_or_state, "state_dict") else module_or_state
+    with torch.no_grad():
+        for name in sorted(state.keys()):
+            t = state[name]
+            if name.startswith("gp_") or name.startswith("mll.") or not torch.is_floating_point(t):
+                continue
+            g = torch.Generator(device="cpu")
+            g.manual_seed((zlib.crc32(name.encode()) ^ (seed * 2654435761)) & 0x7FFFFFFF)
+            u = torch.rand(t.shape, generator=g, dtype=torch.float64) * 2.0 - 1.0
+            if name.endswith(".alpha"):
+                val = torch.full(t.shape, float(alpha), dtype=torch.float64)
+            elif "norm_layer.weight" in name:
+                val = 1.0 + 0.1 * u
+            elif "norm_layer.bias" in name:
+                val = 0.1 * u
+            elif t.dim() == 2:
+                val = u * (gain / math.sqrt(t.shape[1]))
+            else:
+                val = 0.05 * u
+            t.copy_(val.to(t.dtype))

@@ -1,0 +1,202 @@
+"""Generates tests/golden/*.npz by running the reference's OWN files (unmodified, /root/reference)
+through oracle/shims.py on the seeded synthetic tasks.  Authoring container only:
+
+    python tests/golden/make_golden.py
+
+Everything stored is small (features, predictions, phi, per-tensor gradient norms and probe dots); the
+25 M model weights are NOT stored -- they are regenerated from tensor names by
+adkf_ift_b200.synthetic.deterministic_init_.
+
+Third-party maths (gpytorch / botorch / torch_scatter) is restated (oracle/gpytorch_lite etc.), so GP
+numerics are "parity unpinned" at that boundary; everything else below is the reference's own code.
+"""
+import os
+import sys
+import zlib
+
+import numpy as np
+import torch
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(os.path.dirname(HERE))
+sys.path.insert(0, ROOT)
+
+from oracle import ref_runner as rr  # noqa: E402
+
+REPORT = rr.install()
+
+from adkf_ift_b200 import synthetic  # noqa: E402
+from oracle import adkf_oracle as orc  # noqa: E402
+
+
+def probe_vector(name, shape):
+    g = torch.Generator().manual_seed(zlib.crc32(("probe:" + name).encode()) & 0x7FFFFFFF)
+    return torch.randn(shape, generator=g, dtype=torch.float64)
+
+
+def flat(ps):
+    return np.concatenate([p.detach().reshape(-1).double().numpy() for p in ps])
+
+
+def model_task_fixture(path, task_id, n_s, n_q, use_numeric, kernel="matern", num_layers=10):
+    torch.manual_seed(0)
+    cfg = rr.reference_config(num_layers=num_layers, gp_kernel=kernel, use_numeric_labels=use_numeric)
+    model = rr.build_reference_model(cfg)
+    ts = synthetic.make_task_sample(task_id, n_s, n_q)
+    host, dev = rr.reference_dkt_sample(ts, use_numeric)
+    batch = dev.batches[0]
+    out = {}
+    with torch.no_grad():
+        gs = model.graph_feature_extractor(batch.support_features)
+        gq = model.graph_feature_extractor(batch.query_features)
+        zs = model.fc(torch.cat([gs, batch.support_features.fingerprints.float()], 1))
+        zq = model.fc(torch.cat([gq, batch.query_features.fingerprints.float()], 1))
+    out.update(gnn_support=gs.numpy(), gnn_query=gq.numpy(), z_support=zs.numpy(), z_query=zq.numpy())
+    # ---- meta-test (run_on_batches, train=False) -------------------------------------------
+    mt = rr.reference_meta_test(model, dev)[0]
+    out.update(test_phi_init=flat(mt["phi_init"]), test_phi_star=flat(mt["phi_star"]),
+               test_mean=mt["mean"].numpy(), test_variance=mt["variance"].numpy())
+    # ---- one meta-training task (reference cauchy_hypergradient on the whole model) -----------
+    tr = rr.reference_meta_train_task(model, batch)
+    names = [n for n, _ in model.named_parameters() if not n.startswith("gp_")]
+    out.update(train_F=tr["F"].numpy(), train_phi_star=flat(tr["phi_star"]), train_dF_dphi=flat(tr["gp_grads"]),
+               grad_norms=np.array([tr["grads"][n].double().norm().item() for n in names]),
+               grad_dots=np.array([(tr["grads"][n].double() * probe_vector(n, tr["grads"][n].shape)).sum().item()
+                                   for n in names]),
+               grad_names=np.array(names))
+    # a few small tensors in full
+    for n in ("fc.2.bias", "graph_feature_extractor.gnn.gnn_blocks.0.alpha",
+              "graph_feature_extractor.init_node_proj.weight"):
+        out["grad::" + n] = tr["grads"][n].numpy()
+    # ---- fixed-phi quantities at the reference's phi* (oracle autograd; fp32 and fp64) --------
+    ocfg = orc.OracleConfig(num_layers=num_layers, gp_kernel=kernel, use_numeric_labels=use_numeric)
+    for dt, tag in ((torch.float32, "f32"), (torch.float64, "f64")):
+        z_s, z_q = zs.to(dt), zq.to(dt)
+        y_s = orc.convert_labels(batch, "support", ocfg, dt)
+        y_q = orc.convert_labels(batch, "query", ocfg, dt)
+        tail = orc.GPTail(ocfg, dt)
+        tail.reinit(z_s)
+        with torch.no_grad():
+            for p, v in zip(tail.params(), tr["phi_star"]):
+                p.copy_(v.to(dt).view(p.shape))
+        hb = orc.hypergrad_wrt_features(tail, z_s, y_s, z_q, y_q)
+        pm = orc.predict(tail, z_s, y_s, z_q)
+        prior_locs = np.array([tail.likelihood.noise_covar.noise_prior.loc.item(),
+                               tail.model.covar_module.base_kernel.lengthscale_prior.loc.item()])
+        out.update({f"fixed_{tag}_{k}": v.detach().double().numpy() for k, v in hb.items()})
+        out.update({f"fixed_{tag}_mean": pm.mean.double().numpy(), f"fixed_{tag}_variance": pm.variance.double().numpy(),
+                    f"fixed_{tag}_prior_locs": prior_locs})
+    out["y_support"] = orc.convert_labels(batch, "support", ocfg, torch.float64).numpy()
+    out["y_query"] = orc.convert_labels(batch, "query", ocfg, torch.float64).numpy()
+    out["meta"] = np.array([task_id, n_s, n_q, int(use_numeric), num_layers])
+    out.pop("gnn_query")
+    # big float64 arrays are stored as float32 (6e-8 relative rounding << any tolerance used)
+    out = {k: (v.astype(np.float32) if isinstance(v, np.ndarray) and v.dtype == np.float64 and v.size > 512 else v)
+           for k, v in out.items()}
+    np.savez_compressed(path, **out)
+    print("wrote", path, {k: getattr(v, "shape", None) for k, v in list(out.items())[:6]})
+
+
+def batcher_fixture(path, task_id=3, n_s=16, n_q=40, max_graphs=36):
+    """Integer collation path of the reference (fsmol_batcher.py / dkt.py) incl. a query split into
+    two batches and the bidirectional expansion of gnn.py:540-544."""
+    ts = synthetic.make_task_sample(task_id, n_s, n_q)
+    host, dev = rr.reference_dkt_sample(ts, True, max_num_graphs=max_graphs)
+    out = {"num_batches": np.array(len(host.batches))}
+    for bi, b in enumerate(host.batches):
+        for side in ("support", "query"):
+            f = getattr(b, side + "_features")
+            for t, a in enumerate(f.adjacency_lists):
+                out[f"b{bi}_{side}_adj{t}"] = a
+                out[f"b{bi}_{side}_bidir{t}"] = np.concatenate([a, a[:, ::-1]], axis=0)
+            out[f"b{bi}_{side}_node_to_graph"] = f.node_to_graph
+            out[f"b{bi}_{side}_counts"] = np.array([f.num_graphs, f.num_nodes, f.num_edges])
+            out[f"b{bi}_{side}_node_features"] = f.node_features
+            out[f"b{bi}_{side}_fingerprints"] = f.fingerprints
+            out[f"b{bi}_{side}_labels"] = getattr(b, side + "_labels")
+            out[f"b{bi}_{side}_numeric_labels"] = getattr(b, side + "_numeric_labels")
+    out["meta"] = np.array([task_id, n_s, n_q, max_graphs])
+    np.savez_compressed(path, **out)
+    print("wrote", path)
+
+
+def gp_kernels_fixture(path):
+    """GP-only fixtures through the reference's ExactGPLayer / ExactTanimotoGP (fs_mol/utils/gp_utils.py)
+    at fixed hyper-parameters and after fit_gpytorch_scipy, on small random features."""
+    import gpytorch
+    from botorch.optim.fit import fit_gpytorch_scipy
+    from fs_mol.utils.gp_utils import ExactGPLayer, ExactTanimotoGP
+    out = {}
+    rng = np.random.default_rng(7)
+    n, m, d = 24, 40, 64
+    centers = rng.normal(size=(3, d))
+    lab = rng.integers(0, 3, size=n + m)
+    X = (centers[lab] + 0.6 * rng.normal(size=(n + m, d))).astype(np.float32)
+    y = (np.array([1.0, -1.0, 0.3])[lab] + 0.2 * rng.normal(size=n + m)).astype(np.float32)
+    out.update(X=X, y=y, n=np.array(n))
+    xs, xq = torch.from_numpy(X[:n]), torch.from_numpy(X[n:])
+    ys, yq = torch.from_numpy(y[:n]), torch.from_numpy(y[n:])
+    for kern in ("matern", "rbf", "linear", "cossim", "poli1", "poli2"):
+        lik = gpytorch.likelihoods.GaussianLikelihood(
+            noise_prior=gpytorch.priors.LogNormalPrior(loc=np.log(0.1) + 0.0625, scale=0.25))
+        xs_k, xq_k = xs, xq
+        if kern == "cossim":
+            xs_k = torch.nn.functional.normalize(xs, p=2, dim=1)
+            xq_k = torch.nn.functional.normalize(xq, p=2, dim=1)
+        gp = ExactGPLayer(xs_k, ys, lik, kern)
+        mll = gpytorch.mlls.ExactMarginalLogLikelihood(lik, gp)
+        if kern in ("matern", "rbf"):
+            gp.covar_module.base_kernel.lengthscale = 6.0
+        gp.covar_module.outputscale = 0.8
+        gp.train(); lik.train()
+        params = [p for p in mll.parameters() if p.requires_grad]
+        loss = -mll(gp(xs_k), ys)
+        grads = torch.autograd.grad(loss, params)
+        out[f"{kern}_phi"] = flat(params)
+        out[f"{kern}_loss"] = loss.detach().numpy()
+        out[f"{kern}_grad"] = flat(grads)
+        gp.eval(); lik.eval()
+        with torch.no_grad():
+            mvn = lik(gp(xq_k))
+            out[f"{kern}_mean"] = mvn.mean.numpy()
+            out[f"{kern}_var"] = mvn.variance.numpy()
+            out[f"{kern}_nll"] = (-mvn.log_prob(yq)).numpy()
+        gp.train(); lik.train()
+        fit_gpytorch_scipy(mll)
+        out[f"{kern}_phi_fit"] = flat(params)
+        out[f"{kern}_loss_fit"] = (-mll(gp(xs_k), ys)).detach().numpy()
+        gp.eval(); lik.eval()
+        with torch.no_grad():
+            mvn = lik(gp(xq_k))
+            out[f"{kern}_mean_fit"] = mvn.mean.numpy()
+            out[f"{kern}_var_fit"] = mvn.variance.numpy()
+    # Tanimoto on count fingerprints (GP-ST / bayes_opt gpst)
+    fp = (rng.random((n + m, 256)) < 0.12).astype(np.float32) * rng.integers(1, 4, size=(n + m, 256)).astype(np.float32)
+    out["fp"] = fp
+    fs, fq = torch.from_numpy(fp[:n]), torch.from_numpy(fp[n:])
+    lik = gpytorch.likelihoods.GaussianLikelihood()
+    gp = ExactTanimotoGP(fs, ys, lik, use_numeric_labels=True)
+    mll = gpytorch.mlls.ExactMarginalLogLikelihood(lik, gp)
+    gp.train(); lik.train()
+    params = [p for p in mll.parameters() if p.requires_grad]
+    loss = -mll(gp(fs), ys)
+    out["tanimoto_phi"] = flat(params)
+    out["tanimoto_loss"] = loss.detach().numpy()
+    out["tanimoto_grad"] = flat(torch.autograd.grad(loss, params))
+    gp.eval(); lik.eval()
+    with torch.no_grad():
+        mvn = lik(gp(fq))
+        out["tanimoto_mean"] = mvn.mean.numpy()
+        out["tanimoto_var"] = mvn.variance.numpy()
+    np.savez_compressed(path, **out)
+    print("wrote", path)
+
+
+if __name__ == "__main__":
+    print(REPORT)
+    batcher_fixture(os.path.join(HERE, "batcher.npz"))
+    gp_kernels_fixture(os.path.join(HERE, "gp_kernels.npz"))
+    model_task_fixture(os.path.join(HERE, "c1_classification.npz"), task_id=0, n_s=16, n_q=32, use_numeric=False)
+    model_task_fixture(os.path.join(HERE, "c1_regression.npz"), task_id=5, n_s=16, n_q=32, use_numeric=True)
+    model_task_fixture(os.path.join(HERE, "s64_rbf_l2.npz"), task_id=9, n_s=64, n_q=64, use_numeric=False,
+                       kernel="rbf", num_layers=2)
