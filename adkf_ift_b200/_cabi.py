@@ -1,0 +1,85 @@
+"""ctypes binding of libadkf_b200.so (the C-ABI declared in include/adkf_b200.h).
+
+PyTorch is only used here for device memory and streams: tensors are passed as raw device pointers
+(`data_ptr()`), work is enqueued on torch's current CUDA stream.  There is NO CPU fallback: every wrapper
+raises if a tensor is not a contiguous CUDA tensor of the declared dtype, and importing the library
+fails loudly if the shared object has not been built (run `python -m adkf_ift_b200.build`).
+"""
+import ctypes
+import os
+from ctypes import c_float, c_int32, c_int64, c_void_p
+
+import torch
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libadkf_b200.so")
+
+# every exported symbol of include/adkf_b200.h with its ctypes signature
+_P = c_void_p
+SIGNATURES = {
+    "adkf_version": ([], ctypes.c_int),
+    "adkf_graph_csr_build": ([_P, c_int64, _P, c_int64, _P, c_int64, c_int32, _P, _P, _P, _P, _P, _P, _P, _P, _P], ctypes.c_int),
+    "adkf_mp_pna_fwd": ([_P, _P, _P, _P, _P, _P, c_int32, _P, _P, _P, _P], ctypes.c_int),
+    "adkf_mp_pna_bwd": ([_P, _P, _P, _P, _P, _P, _P, _P, c_int32, c_int32, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P,
+                         c_int32, _P], ctypes.c_int),
+    "adkf_readout_weighted_fwd": ([_P, _P, _P, c_int32, c_int32, c_int32, c_int32, _P, _P, _P], ctypes.c_int),
+    "adkf_readout_weighted_bwd": ([_P, _P, _P, c_int32, c_int32, c_int32, c_int32, _P, _P, _P, _P], ctypes.c_int),
+    "adkf_readout_max_fwd": ([_P, _P, c_int32, c_int32, _P, _P, _P], ctypes.c_int),
+    "adkf_readout_max_bwd": ([_P, _P, _P, c_int32, c_int32, _P, _P], ctypes.c_int),
+    "adkf_ecfp_linear_fwd": ([_P, c_int32, c_int32, _P, c_int32, _P, _P], ctypes.c_int),
+    "adkf_ecfp_linear_bwd": ([_P, c_int32, c_int32, _P, c_int32, _P, _P], ctypes.c_int),
+    "adkf_gram_sqdist": ([_P, c_int32, c_int32, _P, _P, _P, c_int32, c_int32, _P, _P, _P, _P], ctypes.c_int),
+    "adkf_gram_sqdist_bwd": ([_P, c_int32, c_int32, _P, _P, c_int32, _P, _P, c_float, _P, _P], ctypes.c_int),
+    "adkf_gp_fit": ([c_int32, _P, _P, _P, _P, _P, c_int32, c_float, c_float, c_int32, c_int32, c_int32, c_float,
+                     _P, _P, _P, _P, c_int64, _P], ctypes.c_int),
+    "adkf_gp_predict": ([c_int32, _P, _P, _P, _P, _P, c_int32, _P, _P, _P, _P, _P, c_int64, _P], ctypes.c_int),
+    "adkf_gp_ift": ([c_int32, _P, _P, _P, _P, _P, c_int32, c_float, c_int32, c_int32, _P, _P, _P, _P, _P, c_int64,
+                     _P], ctypes.c_int),
+    "adkf_gp_ws_floats": ([c_int32, _P, _P, c_int32], c_int64),
+}
+
+_lib = None
+
+
+def load():
+    """dlopen the in-tree shared library (never silently falls back)."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise RuntimeError(
+            f"{LIB_PATH} is missing: the CUDA extension has not been built. Run `python -m adkf_ift_b200.build` "
+            "(needs nvcc; cross-compiles for sm_100a without a GPU). There is no CPU fallback.")
+    lib = ctypes.CDLL(LIB_PATH)
+    for name, (argtypes, restype) in SIGNATURES.items():
+        fn = getattr(lib, name)  # AttributeError if the symbol is not exported
+        fn.argtypes = argtypes
+        fn.restype = restype
+    _lib = lib
+    return lib
+
+
+def stream_ptr():
+    return c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def dptr(t, dtype=None, allow_none=False):
+    """Raw device pointer of a contiguous CUDA tensor (raises instead of falling back)."""
+    if t is None:
+        if allow_none:
+            return c_void_p(0)
+        raise ValueError("required tensor is None")
+    if not t.is_cuda:
+        raise RuntimeError("adkf_ift_b200 kernels need CUDA tensors (no CPU fallback)")
+    if not t.is_contiguous():
+        raise RuntimeError("adkf_ift_b200 kernels need contiguous tensors")
+    if dtype is not None and t.dtype != dtype:
+        raise TypeError(f"expected {dtype}, got {t.dtype}")
+    return c_void_p(t.data_ptr())
+
+
+def check(rc, what):
+    if rc != 0:
+        if rc < 0:
+            raise ValueError(f"{what}: argument error {rc}")
+        raise RuntimeError(f"{what}: CUDA launch failed with cudaError {rc}")

@@ -1,0 +1,59 @@
+// common.cuh -- shared device helpers for the ADKF-IFT B200 kernels (sm_100a).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <math.h>
+
+#define ADKF_LAUNCH_CHECK()                         \
+    do {                                            \
+        cudaError_t e__ = cudaGetLastError();       \
+        if (e__ != cudaSuccess) return (int)e__;    \
+    } while (0)
+
+namespace adkf {
+
+constexpr int kWarp = 32;
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+__device__ __forceinline__ double warp_sum(double v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+    return v;
+}
+
+// Block-wide sum of K per-thread partials; the cross-thread part runs in fp64.  Result is broadcast to
+// every thread through `out` (shared, >= K doubles).  `scratch` is shared, >= K * 32 doubles.
+// Contains __syncthreads(): must be called by all threads of the block.
+template <int K>
+__device__ __forceinline__ void block_sum_multi(const float (&part)[K], double* scratch, double* out) {
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, nw = (blockDim.x + 31) >> 5;
+#pragma unroll
+    for (int k = 0; k < K; ++k) {
+        double v = warp_sum((double)part[k]);
+        if (lane == 0) scratch[k * 32 + wid] = v;
+    }
+    __syncthreads();
+    if (wid == 0) {
+#pragma unroll
+        for (int k = 0; k < K; ++k) {
+            double v = (lane < nw) ? scratch[k * 32 + lane] : 0.0;
+            v = warp_sum(v);
+            if (lane == 0) out[k] = v;
+        }
+    }
+    __syncthreads();
+}
+
+__device__ __forceinline__ float softplusf(float x) { return (x > 20.f) ? x : log1pf(expf(x)); }
+__device__ __forceinline__ float sigmoidf_(float x) { return 1.f / (1.f + expf(-x)); }
+
+}  // namespace adkf

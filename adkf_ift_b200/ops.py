@@ -1,0 +1,359 @@
+"""Host-side operator layer over the C-ABI: device graph index, autograd Functions for the fused graph
+kernels, and the batched GP entry points.  Every function here launches hand-written sm_100a kernels from
+libadkf_b200.so; nothing falls back to torch ops or to the CPU."""
+import ctypes
+from dataclasses import dataclass
+from typing import List, Optional, Sequence
+
+import torch
+
+from . import _cabi
+from ._cabi import check, dptr, stream_ptr
+
+KERNEL_IDS = {"matern": 0, "rbf": 1, "RBF": 1}
+AUX = 32
+AUX_F, AUX_G, AUX_H, AUX_L0, AUX_LS_LOC, AUX_ITERS, AUX_FOUTER, AUX_DF_DPHI, AUX_V, AUX_JITTER, AUX_NFEV = (
+    0, 1, 4, 13, 14, 15, 16, 17, 20, 23, 24)
+ST_JITTER, ST_NOT_PD, ST_NOT_CONVERGED, ST_HESS_DAMPED = 1, 2, 4, 8
+MP_PARTIALS = 64
+
+
+# --------------------------------------------------------------------------------------------------
+# graph index
+# --------------------------------------------------------------------------------------------------
+@dataclass
+class GraphIndex:
+    """CSR over target nodes of the bidirectional edge set (device, int32) + per-graph node ranges."""
+    num_nodes: int
+    num_edges: int  # directed (= 2 x bonds)
+    rowptr: torch.Tensor
+    col_src: torch.Tensor
+    col_type: torch.Tensor
+    col_tgt: torch.Tensor
+    col_eid: torch.Tensor
+    rev_pos: torch.Tensor
+    degree: torch.Tensor
+    graph_ptr: Optional[torch.Tensor] = None  # [G+1] int32
+    num_graphs: int = 0
+
+
+def build_graph_index(adjacency_lists: Sequence[torch.Tensor], num_nodes: int,
+                      node_to_graph: Optional[torch.Tensor] = None, num_graphs: int = 0) -> GraphIndex:
+    """adjacency_lists: 3 x [E_t, 2] int64 CUDA tensors exactly as the reference batcher emits them."""
+    lib = _cabi.load()
+    assert len(adjacency_lists) == 3, "FS-Mol has 3 edge types"
+    dev = adjacency_lists[0].device
+    adjs = [a.contiguous() for a in adjacency_lists]
+    es = [int(a.shape[0]) for a in adjs]
+    etot = 2 * sum(es)
+    i32 = dict(dtype=torch.int32, device=dev)
+    rowptr = torch.empty(num_nodes + 1, **i32)
+    degree = torch.empty(max(num_nodes, 1), **i32)
+    n = max(etot, 1)
+    col_src, col_tgt, col_eid, rev_pos, scratch = (torch.empty(n, **i32) for _ in range(5))
+    col_type = torch.empty(n, dtype=torch.uint8, device=dev)
+    rc = lib.adkf_graph_csr_build(dptr(adjs[0], torch.int64), es[0], dptr(adjs[1], torch.int64), es[1],
+                                  dptr(adjs[2], torch.int64), es[2], num_nodes, dptr(rowptr), dptr(col_src),
+                                  dptr(col_type), dptr(col_tgt), dptr(col_eid), dptr(rev_pos), dptr(degree),
+                                  dptr(scratch), stream_ptr())
+    check(rc, "adkf_graph_csr_build")
+    graph_ptr = None
+    if node_to_graph is not None:
+        # nodes of a graph are contiguous (fsmol_batcher.py:200-202): counts -> exclusive scan
+        counts = torch.bincount(node_to_graph, minlength=num_graphs)
+        graph_ptr = torch.zeros(num_graphs + 1, **i32)
+        graph_ptr[1:] = torch.cumsum(counts, 0).to(torch.int32)
+    return GraphIndex(num_nodes, etot, rowptr, col_src[:etot], col_type[:etot], col_tgt[:etot], col_eid[:etot],
+                      rev_pos[:etot], degree[:num_nodes], graph_ptr, num_graphs)
+
+
+# --------------------------------------------------------------------------------------------------
+# PNA message passing
+# --------------------------------------------------------------------------------------------------
+class _PNAMessagePassing(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, h, W, b, gi: GraphIndex):
+        lib = _cabi.load()
+        h = h.contiguous()
+        W = W.contiguous()
+        b = b.contiguous()
+        V = gi.num_nodes
+        out = torch.empty(V, 4 * 768, dtype=torch.float32, device=h.device)
+        aux_cnt = torch.empty(V, 4, 64, dtype=torch.uint8, device=h.device)
+        aux_arg = torch.empty(V, 4, 64, dtype=torch.uint8, device=h.device)
+        rc = lib.adkf_mp_pna_fwd(dptr(h, torch.float32), dptr(W, torch.float32), dptr(b, torch.float32),
+                                 dptr(gi.rowptr), dptr(gi.col_src), dptr(gi.col_type), V, dptr(out),
+                                 dptr(aux_cnt), dptr(aux_arg), stream_ptr())
+        check(rc, "adkf_mp_pna_fwd")
+        ctx.gi = gi
+        ctx.save_for_backward(h, W, b, out, aux_cnt, aux_arg)
+        return out
+
+    @staticmethod
+    def backward(ctx, d_out):
+        lib = _cabi.load()
+        h, W, b, out, aux_cnt, aux_arg = ctx.saved_tensors
+        gi = ctx.gi
+        V, E = gi.num_nodes, gi.num_edges
+        dev = h.device
+        d_out = d_out.contiguous()
+        f32 = dict(dtype=torch.float32, device=dev)
+        d_pre = torch.empty(max(E, 1), 4, 192, **f32)
+        d_xs = torch.empty(max(E, 1), 128, **f32)
+        d_xt = torch.empty(V, 128, **f32)
+        d_h = torch.empty(V, 128, **f32)
+        d_W = torch.empty_like(W)
+        d_b = torch.empty_like(b)
+        partials = torch.empty(MP_PARTIALS, 12, 192 * 64 + 192, **f32)
+        rc = lib.adkf_mp_pna_bwd(dptr(h), dptr(W), dptr(b), dptr(gi.rowptr), dptr(gi.col_src), dptr(gi.col_tgt),
+                                 dptr(gi.col_type), dptr(gi.rev_pos), V, E, dptr(out), dptr(aux_cnt), dptr(aux_arg),
+                                 dptr(d_out, torch.float32), dptr(d_pre), dptr(d_xs), dptr(d_xt), dptr(d_h),
+                                 dptr(d_W), dptr(d_b), dptr(partials), MP_PARTIALS, stream_ptr())
+        check(rc, "adkf_mp_pna_bwd")
+        return d_h, d_W, d_b, None
+
+
+def pna_message_passing(h, W, b, gi: GraphIndex):
+    """h [V,128], W [4,3,192,64], b [4,3,192] -> aggregated messages [V, 3072] (all 4 towers)."""
+    return _PNAMessagePassing.apply(h, W, b, gi)
+
+
+# --------------------------------------------------------------------------------------------------
+# readout
+# --------------------------------------------------------------------------------------------------
+class _ReadoutWeighted(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, scores, values, graph_ptr, num_graphs, heads, head_dim, mode):
+        lib = _cabi.load()
+        scores = scores.contiguous()
+        values = values.contiguous()
+        weights = torch.empty_like(scores)
+        out = torch.empty(num_graphs, heads * head_dim, dtype=torch.float32, device=scores.device)
+        rc = lib.adkf_readout_weighted_fwd(dptr(scores, torch.float32), dptr(values, torch.float32),
+                                           dptr(graph_ptr, torch.int32), num_graphs, heads, head_dim, mode,
+                                           dptr(weights), dptr(out), stream_ptr())
+        check(rc, "adkf_readout_weighted_fwd")
+        ctx.save_for_backward(weights, values, graph_ptr)
+        ctx.meta = (num_graphs, heads, head_dim, mode)
+        return out
+
+    @staticmethod
+    def backward(ctx, d_out):
+        lib = _cabi.load()
+        weights, values, graph_ptr = ctx.saved_tensors
+        G, heads, head_dim, mode = ctx.meta
+        d_out = d_out.contiguous()
+        d_scores = torch.zeros_like(weights)
+        d_values = torch.zeros_like(values)
+        rc = lib.adkf_readout_weighted_bwd(dptr(weights), dptr(values), dptr(graph_ptr), G, heads, head_dim, mode,
+                                           dptr(d_out, torch.float32), dptr(d_scores), dptr(d_values), stream_ptr())
+        check(rc, "adkf_readout_weighted_bwd")
+        return d_scores, d_values, None, None, None, None, None
+
+
+def readout_weighted(scores, values, graph_ptr, num_graphs, heads, head_dim, mode):
+    """mode 0: per-graph softmax weights ("weighted_mean"); mode 1: sigmoid weights ("weighted_sum")."""
+    return _ReadoutWeighted.apply(scores, values, graph_ptr, num_graphs, heads, head_dim, mode)
+
+
+class _ReadoutMax(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, graph_ptr, num_graphs):
+        lib = _cabi.load()
+        x = x.contiguous()
+        dim = x.shape[1]
+        out = torch.empty(num_graphs, dim, dtype=torch.float32, device=x.device)
+        argmax = torch.empty(num_graphs, dim, dtype=torch.int32, device=x.device)
+        rc = lib.adkf_readout_max_fwd(dptr(x, torch.float32), dptr(graph_ptr, torch.int32), num_graphs, dim,
+                                      dptr(out), dptr(argmax), stream_ptr())
+        check(rc, "adkf_readout_max_fwd")
+        ctx.save_for_backward(argmax, graph_ptr)
+        ctx.meta = (num_graphs, dim, x.shape[0])
+        return out
+
+    @staticmethod
+    def backward(ctx, d_out):
+        lib = _cabi.load()
+        argmax, graph_ptr = ctx.saved_tensors
+        G, dim, V = ctx.meta
+        d_out = d_out.contiguous()
+        d_x = torch.zeros(V, dim, dtype=torch.float32, device=d_out.device)
+        rc = lib.adkf_readout_max_bwd(dptr(d_out, torch.float32), dptr(argmax), dptr(graph_ptr), G, dim, dptr(d_x),
+                                      stream_ptr())
+        check(rc, "adkf_readout_max_bwd")
+        return d_x, None, None
+
+
+def readout_max(x, graph_ptr, num_graphs):
+    return _ReadoutMax.apply(x, graph_ptr, num_graphs)
+
+
+# --------------------------------------------------------------------------------------------------
+# sparse ECFP branch of fc[0]
+# --------------------------------------------------------------------------------------------------
+class _EcfpLinear(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, base, fp, Wt):
+        lib = _cabi.load()
+        out = base.contiguous().clone()
+        Wt = Wt.contiguous()
+        fp = fp.contiguous()
+        G, fp_dim = fp.shape
+        rc = lib.adkf_ecfp_linear_fwd(dptr(fp, torch.int32), G, fp_dim, dptr(Wt, torch.float32), Wt.shape[1],
+                                      dptr(out, torch.float32), stream_ptr())
+        check(rc, "adkf_ecfp_linear_fwd")
+        ctx.save_for_backward(fp)
+        ctx.wshape = tuple(Wt.shape)
+        return out
+
+    @staticmethod
+    def backward(ctx, d_out):
+        lib = _cabi.load()
+        (fp,) = ctx.saved_tensors
+        d_out = d_out.contiguous()
+        d_Wt = None
+        if ctx.needs_input_grad[2]:
+            d_Wt = torch.zeros(ctx.wshape, dtype=torch.float32, device=d_out.device)
+            rc = lib.adkf_ecfp_linear_bwd(dptr(fp), fp.shape[0], fp.shape[1], dptr(d_out, torch.float32),
+                                          ctx.wshape[1], dptr(d_Wt), stream_ptr())
+            check(rc, "adkf_ecfp_linear_bwd")
+        return d_out, None, d_Wt
+
+
+def ecfp_linear(base, fp, Wt):
+    """base [G,out] (dense part + bias) + fp[G,2048] (int32 counts) @ Wt[2048,out] through the sparse kernel."""
+    return _EcfpLinear.apply(base, fp, Wt)
+
+
+# --------------------------------------------------------------------------------------------------
+# batched GP tail
+# --------------------------------------------------------------------------------------------------
+@dataclass
+class TaskLayout:
+    """Row layout of a batch of T tasks inside Z / y: task t owns rows [z_off[t], z_off[t+1]) with the
+    n_sup[t] support rows first; its N_t x N_t squared-distance matrix starts at d2_off[t]."""
+    T: int
+    n_sup_host: List[int]
+    n_rows_host: List[int]
+    z_off: torch.Tensor
+    n_sup: torch.Tensor
+    d2_off: torch.Tensor
+    max_n: int
+    total_rows: int
+    d2_total: int
+
+    @staticmethod
+    def build(n_sup: Sequence[int], n_query: Sequence[int], device) -> "TaskLayout":
+        T = len(n_sup)
+        rows = [int(a) + int(b) for a, b in zip(n_sup, n_query)]
+        z_off = [0]
+        d2_off = [0]
+        for r in rows:
+            z_off.append(z_off[-1] + r)
+            d2_off.append(d2_off[-1] + r * r)
+        return TaskLayout(T, [int(x) for x in n_sup], rows,
+                          torch.tensor(z_off, dtype=torch.int32, device=device),
+                          torch.tensor([int(x) for x in n_sup], dtype=torch.int32, device=device),
+                          torch.tensor(d2_off, dtype=torch.int64, device=device),
+                          max(rows) if rows else 0, z_off[-1], d2_off[-1])
+
+    def ws_floats(self, which: int) -> int:
+        lib = _cabi.load()
+        zo = [0]
+        for r in self.n_rows_host:
+            zo.append(zo[-1] + r)
+        a = (ctypes.c_int32 * (self.T + 1))(*zo)
+        b = (ctypes.c_int32 * max(self.T, 1))(*self.n_sup_host)
+        return int(lib.adkf_gp_ws_floats(self.T, ctypes.cast(a, ctypes.c_void_p), ctypes.cast(b, ctypes.c_void_p), which))
+
+
+@dataclass
+class SqDist:
+    D2: torch.Tensor
+    mu: torch.Tensor
+    nrm: torch.Tensor
+
+
+def gp_sqdist(Z: torch.Tensor, layout: TaskLayout, qq_block: bool) -> SqDist:
+    lib = _cabi.load()
+    Z = Z.contiguous()
+    d = Z.shape[1]
+    f32 = dict(dtype=torch.float32, device=Z.device)
+    D2 = torch.zeros(max(layout.d2_total, 1), **f32)
+    mu = torch.empty(max(layout.T, 1), d, **f32)
+    nrm = torch.empty(max(layout.total_rows, 1), **f32)
+    rc = lib.adkf_gram_sqdist(dptr(Z, torch.float32), d, layout.T, dptr(layout.z_off), dptr(layout.n_sup),
+                              dptr(layout.d2_off), layout.max_n, 1 if qq_block else 0, dptr(mu), dptr(nrm), dptr(D2),
+                              stream_ptr())
+    check(rc, "adkf_gram_sqdist")
+    return SqDist(D2, mu, nrm)
+
+
+def gp_sqdist_bwd(Z, layout: TaskLayout, Wm, mu, scale: float) -> torch.Tensor:
+    lib = _cabi.load()
+    Z = Z.contiguous()
+    dZ = torch.zeros_like(Z)
+    rc = lib.adkf_gram_sqdist_bwd(dptr(Z, torch.float32), Z.shape[1], layout.T, dptr(layout.z_off), dptr(layout.d2_off),
+                                  layout.max_n, dptr(Wm, torch.float32), dptr(mu), float(scale), dptr(dZ), stream_ptr())
+    check(rc, "adkf_gram_sqdist_bwd")
+    return dZ
+
+
+def gp_fit(layout: TaskLayout, D2, y, kernel: str, noise_init: float, noise_prior_loc: float, ls_prior: int = 1,
+           init_mode: int = 1, max_iter: int = 50, gtol: float = 2e-6, phi: Optional[torch.Tensor] = None,
+           aux: Optional[torch.Tensor] = None):
+    """Returns (phi [T,3] raw, aux [T,32], status [T] int32)."""
+    lib = _cabi.load()
+    dev = D2.device
+    if phi is None:
+        phi = torch.zeros(layout.T, 3, dtype=torch.float32, device=dev)
+    else:
+        phi = phi.contiguous().clone()
+    if aux is None:
+        aux = torch.zeros(layout.T, AUX, dtype=torch.float32, device=dev)
+    else:
+        aux = aux.contiguous().clone()
+    status = torch.zeros(layout.T, dtype=torch.int32, device=dev)
+    nws = layout.ws_floats(0)
+    ws = torch.empty(nws, dtype=torch.float32, device=dev)
+    rc = lib.adkf_gp_fit(layout.T, dptr(layout.z_off), dptr(layout.n_sup), dptr(layout.d2_off),
+                         dptr(D2, torch.float32), dptr(y, torch.float32), KERNEL_IDS[kernel], float(noise_init),
+                         float(noise_prior_loc), int(ls_prior), int(init_mode), int(max_iter), float(gtol),
+                         dptr(phi), dptr(aux), dptr(status), dptr(ws), nws, stream_ptr())
+    check(rc, "adkf_gp_fit")
+    return phi, aux, status
+
+
+def gp_predict(layout: TaskLayout, D2, y, kernel: str, phi):
+    """Returns (mean, var) aligned with the Z rows (only the query rows are written) and status."""
+    lib = _cabi.load()
+    dev = D2.device
+    mean = torch.zeros(layout.total_rows, dtype=torch.float32, device=dev)
+    var = torch.zeros(layout.total_rows, dtype=torch.float32, device=dev)
+    status = torch.zeros(layout.T, dtype=torch.int32, device=dev)
+    nws = layout.ws_floats(1)
+    ws = torch.empty(nws, dtype=torch.float32, device=dev)
+    rc = lib.adkf_gp_predict(layout.T, dptr(layout.z_off), dptr(layout.n_sup), dptr(layout.d2_off),
+                             dptr(D2, torch.float32), dptr(y, torch.float32), KERNEL_IDS[kernel],
+                             dptr(phi.contiguous(), torch.float32), dptr(mean), dptr(var), dptr(status), dptr(ws), nws,
+                             stream_ptr())
+    check(rc, "adkf_gp_predict")
+    return mean, var, status
+
+
+def gp_ift(layout: TaskLayout, D2, y, kernel: str, noise_prior_loc: float, ls_prior: int, phi, aux,
+           ignore_grad_correction: bool = False):
+    """Returns (Wm same layout as D2, aux updated, status)."""
+    lib = _cabi.load()
+    dev = D2.device
+    Wm = torch.zeros_like(D2)
+    aux = aux.contiguous().clone()
+    status = torch.zeros(layout.T, dtype=torch.int32, device=dev)
+    nws = layout.ws_floats(2)
+    ws = torch.empty(nws, dtype=torch.float32, device=dev)
+    rc = lib.adkf_gp_ift(layout.T, dptr(layout.z_off), dptr(layout.n_sup), dptr(layout.d2_off),
+                         dptr(D2, torch.float32), dptr(y, torch.float32), KERNEL_IDS[kernel], float(noise_prior_loc),
+                         int(ls_prior), 1 if ignore_grad_correction else 0, dptr(phi.contiguous(), torch.float32),
+                         dptr(aux), dptr(Wm), dptr(status), dptr(ws), nws, stream_ptr())
+    check(rc, "adkf_gp_ift")
+    return Wm, aux, status

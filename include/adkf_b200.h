@@ -1,0 +1,179 @@
+/* adkf_b200.h -- C-ABI of the B200-native ADKF-IFT hot path (libadkf_b200.so).
+ *
+ * The reference (Wenlin-Chen/ADKF-IFT) is pure Python and has NO native interface: these entry points
+ * are what a ctypes binding on the reference side would bind to replace the Python/gpytorch/torch_scatter
+ * code cited beside each function (paths relative to the reference root).  See INTEGRATION.md for the
+ * reference-side ctypes stub.
+ *
+ * Conventions
+ *   - every pointer is a DEVICE pointer into caller-owned, contiguous memory unless marked "host";
+ *   - `stream` is a cudaStream_t passed as void*; all work is stream-ordered, no host sync inside;
+ *   - return value: 0 = launched, <0 = argument error (ADKF_ERR_*), >0 = cudaError_t of the launch;
+ *   - numerical failures (non-PD after the jitter retries, fit not converged) never raise: they are
+ *     reported per task in an int32 `status[T]` array (bit flags ADKF_ST_*);
+ *   - tasks are batched: T tasks per call, ragged sizes through int32/int64 offset arrays;
+ *   - fp32 arithmetic (the reference dtype), fp64 only inside block-wide reductions.
+ */
+#ifndef ADKF_B200_H
+#define ADKF_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define ADKF_ERR_BADARG   (-1)
+#define ADKF_ERR_TOOLARGE (-2)
+
+/* per-task status bit flags */
+#define ADKF_ST_OK            0
+#define ADKF_ST_JITTER        1   /* Cholesky needed diagonal jitter (psd_safe_cholesky fallback) */
+#define ADKF_ST_NOT_PD        2   /* not positive definite after 3 jitter retries                 */
+#define ADKF_ST_NOT_CONVERGED 4   /* inner fit hit max_iter before |grad|_inf <= gtol             */
+#define ADKF_ST_HESS_DAMPED   8   /* inner Hessian was not PD at the optimum (IFT solve damped)    */
+
+/* GP kernel families (fs_mol/utils/gp_utils.py:22-43, :106-134) */
+#define ADKF_KERNEL_MATERN52 0
+#define ADKF_KERNEL_RBF      1
+
+/* layout of the per-task float32 `aux` record written by adkf_gp_fit / adkf_gp_ift (stride ADKF_AUX) */
+#define ADKF_AUX            32
+#define ADKF_AUX_F           0   /* f = -MLL at phi*                       */
+#define ADKF_AUX_G           1   /* d f / d raw phi            [3]          */
+#define ADKF_AUX_H           4   /* d2 f / d raw phi2          [9] row-major */
+#define ADKF_AUX_L0         13   /* median-heuristic lengthscale init       */
+#define ADKF_AUX_LS_LOC     14   /* LogNormal prior loc on the lengthscale  */
+#define ADKF_AUX_ITERS      15   /* Newton iterations used                  */
+#define ADKF_AUX_FOUTER     16   /* F = -log p(y_q | y_s) (sum, joint)      */
+#define ADKF_AUX_DF_DPHI    17   /* d F / d raw phi            [3]          */
+#define ADKF_AUX_V          20   /* v = H^-1 dF/dphi           [3]          */
+#define ADKF_AUX_JITTER     23   /* jitter finally added to diag(A)         */
+#define ADKF_AUX_NFEV       24   /* function evaluations used by the fit    */
+
+int adkf_version(void);
+
+/* ---------------------------------------------------------------------------------------------
+ * Graph indexing (integer path, bit-exact).  Replaces GNN.forward's bidirectional expansion
+ * (fs_mol/modules/gnn.py:540-544) + the implicit scatter index of torch_scatter (gnn.py:197-265).
+ * Input : adjacency lists as the reference batcher produces them (fs_mol/data/fsmol_batcher.py:197),
+ *         one [E_t, 2] int64 array per edge type, each bond stored once.
+ * Output: CSR over TARGET nodes of the bidirectional edge set: rowptr[V+1]; for every incoming edge its
+ *         source node, edge type and its index in the reference's concatenated message order
+ *         (type-major; within a type forward edges then flipped edges) -- sorted by that index inside
+ *         a row, so the layout is a deterministic, permutation-stable transform of the input.
+ * ------------------------------------------------------------------------------------------- */
+int adkf_graph_csr_build(const int64_t* adj0, int64_t e0, const int64_t* adj1, int64_t e1,
+                         const int64_t* adj2, int64_t e2, int32_t num_nodes,
+                         int32_t* rowptr /*[V+1]*/, int32_t* col_src /*[2E]*/, uint8_t* col_type /*[2E]*/,
+                         int32_t* col_tgt /*[2E]*/, int32_t* col_eid /*[2E]*/,
+                         int32_t* rev_pos /*[2E] CSR position of the reversed copy of each edge*/,
+                         int32_t* degree /*[V]*/, int32_t* scratch /*[2E]*/, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * PNA relational message passing, all 4 towers of one GNN block in one launch.
+ * Replaces RelationalMP.forward + RelationalMultiAggrMP._aggregate_messages (gnn.py:129-150, 197-265):
+ *   m_e   = relu(W[k][type_e] [h_src[k]; h_tgt[k]] + b[k][type_e])                 (192 per tower)
+ *   agg_t = [sum | mean | sqrt(sum relu(m^2 - mean^2) + 1e-7) | max] x {1, log(d+1)/1.1515, 1.1515/(log(d+1)+1e-7)}
+ * h [V,128] -> out [V, 4*768]; weights W [4][3][192][64], b [4][3][192].
+ * aux_cnt / aux_arg [V,4,64] uint8: per channel the number of edges with m^2 > mean^2 and the arg-max edge
+ * (index inside the CSR row), kept for the backward.
+ * ------------------------------------------------------------------------------------------- */
+int adkf_mp_pna_fwd(const float* h, const float* W, const float* b, const int32_t* rowptr,
+                    const int32_t* col_src, const uint8_t* col_type, int32_t num_nodes,
+                    float* out, uint8_t* aux_cnt, uint8_t* aux_arg, void* stream);
+/* backward: d_out [V,3072] -> d_h [V,128], d_W, d_b (deterministic: no float atomics).
+ * scratch: d_pre [2E,4,192], d_xs [2E,128], d_xt [V,128], partials [num_partials, 12, 192*64+192]. */
+int adkf_mp_pna_bwd(const float* h, const float* W, const float* b, const int32_t* rowptr,
+                    const int32_t* col_src, const int32_t* col_tgt, const uint8_t* col_type,
+                    const int32_t* rev_pos, int32_t num_nodes, int32_t num_edges, const float* fwd_out,
+                    const uint8_t* aux_cnt, const uint8_t* aux_arg, const float* d_out, float* d_pre,
+                    float* d_xs, float* d_xt, float* d_h, float* d_W, float* d_b, float* partials,
+                    int32_t num_partials, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * Graph readout segment kernels (fs_mol/modules/graph_readout.py:224-259, 286-296).  Nodes of a graph
+ * are contiguous: graph_ptr[G+1].
+ *   weighted pool : w = softmax over the graph's nodes (mode 0) or sigmoid (mode 1) of scores [V,heads];
+ *                   out[g, h*hd + c] = sum_v w[v,h] * values[v, h*hd + c]
+ *   max pool      : out[g, c] = max_v x[v, c]  (empty graph -> 0), argmax kept for the backward
+ * ------------------------------------------------------------------------------------------- */
+int adkf_readout_weighted_fwd(const float* scores, const float* values, const int32_t* graph_ptr,
+                              int32_t num_graphs, int32_t heads, int32_t head_dim, int32_t mode,
+                              float* weights /*[V,heads]*/, float* out /*[G,heads*head_dim]*/, void* stream);
+int adkf_readout_weighted_bwd(const float* weights, const float* values, const int32_t* graph_ptr,
+                              int32_t num_graphs, int32_t heads, int32_t head_dim, int32_t mode,
+                              const float* d_out, float* d_scores, float* d_values, void* stream);
+int adkf_readout_max_fwd(const float* x, const int32_t* graph_ptr, int32_t num_graphs, int32_t dim,
+                         float* out, int32_t* argmax, void* stream);
+int adkf_readout_max_bwd(const float* d_out, const int32_t* argmax, const int32_t* graph_ptr,
+                         int32_t num_graphs, int32_t dim, float* d_x, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * ECFP branch of the first FC layer (fs_mol/models/adaptive_dkt.py:145-146,158-160): the fingerprint
+ * arrives as int32 counts with ~2% non-zeros, so  fc0(cat(gnn, ecfp.float()))  is computed as
+ *   out[g,:] += sum_{j : fp[g,j] != 0} fp[g,j] * Wt[j,:]       (Wt = fc.0.weight[:, 512:].T, [2048,2048])
+ * instead of a dense [G,2048]x[2048,2048] GEMM.  `out` must already hold the dense gnn part + bias.
+ * ------------------------------------------------------------------------------------------- */
+int adkf_ecfp_linear_fwd(const int32_t* fp, int32_t num_graphs, int32_t fp_dim, const float* Wt,
+                         int32_t out_dim, float* out, void* stream);
+/* d_Wt[j,:] += sum_g fp[g,j] * d_out[g,:]  (deterministic: one CTA owns a weight row) */
+int adkf_ecfp_linear_bwd(const int32_t* fp, int32_t num_graphs, int32_t fp_dim, const float* d_out,
+                         int32_t out_dim, float* d_Wt, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * Batched GP tail.  Task t owns rows [z_off[t], z_off[t+1]) of Z [rows, d] (support rows first:
+ * n_sup[t] of them, then the query rows) and the N_t x N_t matrix at D2 + d2_off[t] (ld = N_t).
+ * ------------------------------------------------------------------------------------------- */
+
+/* Joint squared-distance matrix per task from the centred quadratic expansion (gpytorch sq_dist; call
+ * sites fs_mol/utils/gp_utils.py:28,31).  qq_block = 0 skips the query x query block (meta-test needs
+ * only diag(K_qq) = outputscale). */
+int adkf_gram_sqdist(const float* Z, int32_t d, int32_t T, const int32_t* z_off, const int32_t* n_sup,
+                     const int64_t* d2_off, int32_t max_n /*max rows of any task (grid sizing)*/,
+                     int32_t qq_block, float* mu_ws /*[T,d]*/, float* nrm_ws /*[rows]*/, float* D2, void* stream);
+
+/* dZ[a,:] = scale * 4 * sum_b Wm[a,b] (z_a - z_b)  for a symmetric per-task weight matrix Wm (same layout
+ * as D2): the chain rule of anything that depends on Z only through D2. */
+int adkf_gram_sqdist_bwd(const float* Z, int32_t d, int32_t T, const int32_t* z_off, const int64_t* d2_off,
+                         int32_t max_n, const float* Wm, const float* mu_ws, float scale, float* dZ, void* stream);
+
+/* Per-task inner fit of (raw_noise, raw_outputscale, raw_lengthscale) by minimising f = -MLL (with the
+ * LogNormal priors) on the support set.  Replaces reinit_gp_params + compute_median_lengthscale_init
+ * (fs_mol/models/adaptive_dkt.py:88-131) and botorch fit_gpytorch_scipy / SciPy L-BFGS-B
+ * (fs_mol/utils/adaptive_dkt_utils.py:91) with an on-device damped Newton iteration using the analytic
+ * 3x3 Hessian.  max_iter = 0 evaluates f, grad, Hessian at the given phi (fixed-phi mode, phi_io is input).
+ * init_mode: 1 = reference initialisation (noise_init, outputscale softplus(0), median lengthscale),
+ *            0 = start from phi_io.  ls_prior: 1 = LogNormal(lengthscale) prior with loc log(l0)+0.0625,
+ *            2 = use the loc already stored in aux[ADKF_AUX_LS_LOC], 0 = no lengthscale prior. */
+int adkf_gp_fit(int32_t T, const int32_t* z_off, const int32_t* n_sup, const int64_t* d2_off,
+                const float* D2, const float* y, int32_t kernel, float noise_init, float noise_prior_loc,
+                int32_t ls_prior, int32_t init_mode, int32_t max_iter, float gtol,
+                float* phi_io /*[T,3]*/, float* aux /*[T,ADKF_AUX]*/, int32_t* status /*[T]*/,
+                float* ws, int64_t ws_floats, void* stream);
+
+/* Posterior predictive of the query rows: mean = K_qs A^-1 y, variance = diag(K_qq - K_qs A^-1 K_sq) + noise
+ * (gpytorch ExactGP eval + GaussianLikelihood; call sites fs_mol/models/adaptive_dkt.py:198-203,
+ * bayes_opt/bo_utils.py:367-373).  mean/var are aligned with the Z rows (support rows are left untouched). */
+int adkf_gp_predict(int32_t T, const int32_t* z_off, const int32_t* n_sup, const int64_t* d2_off,
+                    const float* D2, const float* y, int32_t kernel, const float* phi,
+                    float* mean, float* var, int32_t* status, float* ws, int64_t ws_floats, void* stream);
+
+/* IFT hypergradient pieces for a meta-training task (fs_mol/utils/cauchy_hypergradient.py:5-164 with
+ * f_inner / f_outer of fs_mol/utils/adaptive_dkt_utils.py:383-395):
+ *   F = -log N(y_q | posterior(y_s) + noise)  (summed joint log-prob, adaptive_dkt.py:183-191),
+ *   H = d2f/dphi2 (3x3), v = H^-1 dF/dphi, and the symmetric weight matrix
+ *   Wm = dF/dD2 - d/deps [ df/dD2 (phi + eps v) ]   (SURVEY App. B), to be fed to adkf_gram_sqdist_bwd.
+ * ignore_grad_correction = 1 drops the second term (reference flag of the same name). */
+int adkf_gp_ift(int32_t T, const int32_t* z_off, const int32_t* n_sup, const int64_t* d2_off,
+                const float* D2, const float* y, int32_t kernel, float noise_prior_loc, int32_t ls_prior,
+                int32_t ignore_grad_correction, const float* phi, float* aux /*[T,ADKF_AUX] in/out*/,
+                float* Wm, int32_t* status, float* ws, int64_t ws_floats, void* stream);
+
+/* workspace sizes (floats) for the three GP entry points, host-side helper */
+int64_t adkf_gp_ws_floats(int32_t T, const int32_t* z_off_host, const int32_t* n_sup_host, int32_t which);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* ADKF_B200_H */

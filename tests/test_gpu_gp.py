@@ -1,0 +1,151 @@
+"""-m gpu parity tests of the batched GP kernels (through the C-ABI) against the CPU oracle and the golden
+fixtures generated from the reference.  Tolerances: 1e-4 relative (north_star) at FIXED phi."""
+import math
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import gp_closed_form as cf
+
+pytestmark = pytest.mark.gpu
+
+FIXTURES = [("c1_classification", "matern"), ("c1_regression", "matern"), ("s64_rbf_l2", "rbf")]
+
+
+def rel(a, b):
+    a = np.asarray(a, dtype=np.float64)
+    b = np.asarray(b, dtype=np.float64)
+    return float(np.abs(a - b).max() / max(np.abs(b).max(), 1e-30))
+
+
+def load_task(golden_dir, name):
+    g = np.load(os.path.join(golden_dir, name + ".npz"))
+    Zs, Zq = g["z_support"].astype(np.float32), g["z_query"].astype(np.float32)
+    Z = np.concatenate([Zs, Zq])
+    y = np.concatenate([g["y_support"], g["y_query"]]).astype(np.float32)
+    return g, Z, y, len(Zs), len(Zq)
+
+
+def stack_tasks(tasks, device):
+    from adkf_ift_b200 import ops
+    layout = ops.TaskLayout.build([t[2] for t in tasks], [t[3] for t in tasks], device)
+    Z = torch.from_numpy(np.concatenate([t[0] for t in tasks])).to(device)
+    y = torch.from_numpy(np.concatenate([t[1] for t in tasks])).to(device)
+    return layout, Z, y
+
+
+@pytest.mark.parametrize("name,kind", FIXTURES)
+def test_sqdist_matches_oracle(cuda_device, golden_dir, name, kind):
+    from adkf_ift_b200 import ops
+    g, Z, y, n, m = load_task(golden_dir, name)
+    layout, Zd, yd = stack_tasks([(Z, y, n, m)], cuda_device)
+    sq = ops.gp_sqdist(Zd, layout, qq_block=True)
+    D2 = sq.D2.cpu().numpy().reshape(n + m, n + m)
+    ref = cf.sq_dist_centered(Z.astype(np.float64), n)
+    assert rel(D2, ref) < 2e-6
+    assert np.all(np.diag(D2) == 0.0)
+    assert np.array_equal(D2, D2.T)
+
+
+@pytest.mark.parametrize("name,kind", FIXTURES)
+def test_fixed_phi_inner_and_ift(cuda_device, golden_dir, name, kind):
+    """f, grad, Hessian, F, dF/dphi, v and dL/dZ at the reference's phi* (golden: reference autograd)."""
+    from adkf_ift_b200 import ops
+    g, Z, y, n, m = load_task(golden_dir, name)
+    numeric = bool(g["meta"][3])
+    layout, Zd, yd = stack_tasks([(Z, y, n, m)], cuda_device)
+    sq = ops.gp_sqdist(Zd, layout, qq_block=True)
+    phi = torch.from_numpy(g["train_phi_star"].astype(np.float32)).view(1, 3).to(cuda_device)
+    locs = g["fixed_f64_prior_locs"]
+    phi_o, aux, st = ops.gp_fit(layout, sq.D2, yd, kind, 0.01 if numeric else 0.1, float(locs[0]), ls_prior=1,
+                                init_mode=0, max_iter=0, phi=phi)
+    a = aux.cpu().numpy()[0]
+    assert int(st.item()) & ops.ST_NOT_PD == 0
+    assert abs(a[ops.AUX_F] - g["fixed_f64_f"]) < 1e-4 * abs(g["fixed_f64_f"])
+    assert rel(a[ops.AUX_H:ops.AUX_H + 9].reshape(3, 3), g["fixed_f64_H"]) < 1e-3  # H in fp32: n^3 sums
+    assert abs(a[ops.AUX_LS_LOC] - locs[1]) < 1e-5
+    Wm, aux2, st2 = ops.gp_ift(layout, sq.D2, yd, kind, float(locs[0]), 1, phi, aux)
+    b = aux2.cpu().numpy()[0]
+    assert abs(b[ops.AUX_FOUTER] - g["fixed_f64_F"]) < 1e-4 * abs(g["fixed_f64_F"])
+    assert rel(b[ops.AUX_DF_DPHI:ops.AUX_DF_DPHI + 3], g["fixed_f64_dF_dphi"]) < 1e-3
+    dZ = ops.gp_sqdist_bwd(Zd, layout, Wm, sq.mu, 1.0).cpu().numpy()
+    ref = np.concatenate([g["fixed_f64_dL_dzs"], g["fixed_f64_dL_dzq"]])
+    ref32 = np.concatenate([g["fixed_f32_dL_dzs"], g["fixed_f32_dL_dzq"]])
+    err, base = rel(dZ, ref), rel(ref32, ref)
+    print(name, "dL/dZ rel err cuda", err, "reference-fp32-vs-fp64", base)
+    assert err < max(1e-4, 3 * base)
+
+
+@pytest.mark.parametrize("name,kind", FIXTURES)
+def test_predict_fixed_phi(cuda_device, golden_dir, name, kind):
+    from adkf_ift_b200 import ops
+    g, Z, y, n, m = load_task(golden_dir, name)
+    layout, Zd, yd = stack_tasks([(Z, y, n, m)], cuda_device)
+    sq = ops.gp_sqdist(Zd, layout, qq_block=False)
+    phi = torch.from_numpy(g["test_phi_star"].astype(np.float32)).view(1, 3).to(cuda_device)
+    mean, var, st = ops.gp_predict(layout, sq.D2, yd, kind, phi)
+    assert rel(mean.cpu().numpy()[n:], g["test_mean"]) < 1e-4
+    assert rel(var.cpu().numpy()[n:], g["test_variance"]) < 1e-4
+
+
+@pytest.mark.parametrize("name,kind", FIXTURES)
+def test_fit_reaches_reference_optimum(cuda_device, golden_dir, name, kind):
+    """After-fit parity at each side's own optimum: <=1e-3 on phi*, and a smaller inner gradient than SciPy."""
+    from adkf_ift_b200 import ops
+    g, Z, y, n, m = load_task(golden_dir, name)
+    numeric = bool(g["meta"][3])
+    layout, Zd, yd = stack_tasks([(Z, y, n, m)], cuda_device)
+    sq = ops.gp_sqdist(Zd, layout, qq_block=False)
+    locs = g["fixed_f64_prior_locs"]
+    phi, aux, st = ops.gp_fit(layout, sq.D2, yd, kind, 0.01 if numeric else 0.1, float(locs[0]))
+    a = aux.cpu().numpy()[0]
+    p = phi.cpu().numpy()[0]
+    print(name, "phi*", p, "ref", g["test_phi_star"], "iters", a[ops.AUX_ITERS], "nfev", a[ops.AUX_NFEV],
+          "|g|", np.abs(a[ops.AUX_G:ops.AUX_G + 3]).max(), "status", int(st.item()))
+    assert int(st.item()) & (ops.ST_NOT_PD | ops.ST_NOT_CONVERGED) == 0
+    assert np.abs(p - g["test_phi_star"]).max() < 2e-3
+    assert np.abs(a[ops.AUX_G:ops.AUX_G + 3]).max() < np.abs(g["fixed_f64_g_inner"]).max() + 5e-6
+    assert abs(a[ops.AUX_L0] - math.exp(locs[1] - 0.0625)) < 1e-5 * a[ops.AUX_L0]
+    mean, var, _ = ops.gp_predict(layout, sq.D2, yd, kind, phi)
+    assert rel(mean.cpu().numpy()[n:], g["test_mean"]) < 2e-3
+    assert rel(var.cpu().numpy()[n:], g["test_variance"]) < 2e-3
+
+
+def test_batched_ragged_tasks(cuda_device):
+    """T ragged tasks in one launch == the closed-form oracle per task (incl. n = 128 and a global-ws size)."""
+    from adkf_ift_b200 import ops
+    rng = np.random.default_rng(0)
+    sizes = [(16, 32), (64, 256), (128, 192), (200, 40), (24, 7)]
+    tasks = []
+    for (n, m) in sizes:
+        c = rng.normal(size=(3, 96))
+        lab = rng.integers(0, 3, size=n + m)
+        Z = (c[lab] + 0.7 * rng.normal(size=(n + m, 96))).astype(np.float32)
+        y = (np.array([1.0, -1.0, 0.2])[lab] + 0.3 * rng.normal(size=n + m)).astype(np.float32)
+        tasks.append((Z, y, n, m))
+    layout, Zd, yd = stack_tasks(tasks, cuda_device)
+    sq = ops.gp_sqdist(Zd, layout, qq_block=True)
+    noise_loc = math.log(0.1) + 0.0625
+    phi, aux, st = ops.gp_fit(layout, sq.D2, yd, "matern", 0.1, noise_loc)
+    Wm, aux2, st2 = ops.gp_ift(layout, sq.D2, yd, "matern", noise_loc, 1, phi, aux)
+    dZ = ops.gp_sqdist_bwd(Zd, layout, Wm, sq.mu, 1.0).cpu().numpy()
+    mean, var, _ = ops.gp_predict(layout, sq.D2, yd, "matern", phi)
+    phi_h, aux_h, mean_h, var_h = phi.cpu().numpy(), aux2.cpu().numpy(), mean.cpu().numpy(), var.cpu().numpy()
+    off = 0
+    for t, (Z, y, n, m) in enumerate(tasks):
+        assert int(st[t].item()) & (ops.ST_NOT_PD | ops.ST_NOT_CONVERGED) == 0, (t, int(st[t].item()))
+        D2 = cf.sq_dist_centered(Z.astype(np.float64), n)
+        p_ref, info = cf.newton_fit(D2[:n, :n], y[:n].astype(np.float64), "matern", 0.1, noise_loc)
+        assert np.abs(phi_h[t] - p_ref).max() < 2e-3, (t, phi_h[t], p_ref)
+        r = cf.ift_all(D2, n, y.astype(np.float64), phi_h[t].astype(np.float64), "matern", noise_loc, info["ls_loc"])
+        assert abs(aux_h[t, ops.AUX_FOUTER] - r["F"]) < 2e-4 * abs(r["F"]), (t, aux_h[t, ops.AUX_FOUTER], r["F"])
+        ref_dz = cf.dz_from_wm(Z.astype(np.float64), n, r["Wm"])
+        e = rel(dZ[off:off + n + m], ref_dz)
+        print("task", t, (n, m), "dZ rel", e, "H cond", np.linalg.cond(r["H"]))
+        assert e < 2e-3
+        mr, vr = cf.predict(D2, n, y[:n].astype(np.float64), phi_h[t].astype(np.float64), "matern")
+        assert rel(mean_h[off + n:off + n + m], mr) < 2e-4
+        assert rel(var_h[off + n:off + n + m], vr) < 2e-4
+        off += n + m
