@@ -18,6 +18,7 @@ LIB_PATH = os.path.join(_HERE, "libadkf_b200.so")
 _P = c_void_p
 SIGNATURES = {
     "adkf_version": ([], ctypes.c_int),
+    "adkf_launch_count": ([], c_int64),
     "adkf_graph_csr_build": ([_P, c_int64, _P, c_int64, _P, c_int64, c_int32, _P, _P, _P, _P, _P, _P, _P, _P, _P], ctypes.c_int),
     "adkf_mp_pna_fwd": ([_P, _P, _P, _P, _P, _P, c_int32, _P, _P, _P, _P], ctypes.c_int),
     "adkf_mp_pna_bwd": ([_P, _P, _P, _P, _P, _P, _P, _P, c_int32, c_int32, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P,

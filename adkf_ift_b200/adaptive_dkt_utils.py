@@ -1,0 +1,235 @@
+"""Task loops of ADKF-IFT on the batched B200 path -- surface of fs_mol/utils/adaptive_dkt_utils.py.
+
+  run_on_batches(model, batches, batch_labels, batch_numeric_labels, train)   reference semantics (:70-116),
+        one task, query batches looped; each step is the T=1 case of the batched kernels.
+  run_on_task_batch(model, task_batch, train)                                  NEW: T tasks per launch.
+        meta-test : embed -> sqdist -> fit -> predict                    (reference :87-104 per task)
+        meta-train: embed -> sqdist -> fit -> IFT -> sqdist_bwd -> ONE backward through the extractor,
+                    i.e. sum_t [dF_t/dtheta - v_t^T d2f_t/dphi dtheta] / T      (reference :361-404 + cauchy_hypergradient.py)
+  ADKTModelTrainer                                                              (:208-458) with `train_step`.
+
+Multi-GPU: one process per GPU; rank r takes tasks r::R of the meta-batch, the flat fp32 meta-gradient is
+all-reduced (sum) once per outer step over NCCL, then every rank applies the identical clip + Adam update
+(SURVEY.md 8(e)).  The reference has no distributed code.
+"""
+import math
+import os
+from dataclasses import dataclass
+from typing import Any, Dict, List, Optional, Sequence
+
+import numpy as np
+import torch
+
+from . import gp as gpk
+from . import ops
+from .adaptive_dkt import ADKTModel, ADKTModelTrainerConfig
+from .task_batch import DeviceTaskBatch, HostTaskBatch, collate_tasks, to_device
+
+
+def fit_gpytorch_scipy(mll, **_ignored):
+    """Name kept for call-site compatibility (adaptive_dkt_utils.py:91): runs the on-device Newton fit."""
+    return mll.fit()
+
+
+@dataclass
+class TaskBatchResult:
+    """Per-task outputs of one batched launch (device tensors; nothing is synced to the host here)."""
+    phi: torch.Tensor                 # [T,3]
+    status: torch.Tensor              # [T] int32
+    aux: torch.Tensor                 # [T,32]
+    mean: Optional[torch.Tensor] = None       # [rows] predictive mean (query rows valid)
+    variance: Optional[torch.Tensor] = None
+    preds: Optional[torch.Tensor] = None      # sigmoid(mean) | mean, query rows only, task-major
+    query_mask: Optional[torch.Tensor] = None
+    outer_loss: Optional[torch.Tensor] = None  # [T] F_t (training)
+    loss_per_sample: Optional[torch.Tensor] = None
+
+
+def _query_mask(layout: ops.TaskLayout, device) -> torch.Tensor:
+    m = np.zeros(layout.total_rows, dtype=bool)
+    off = 0
+    for ns, nr in zip(layout.n_sup_host, layout.n_rows_host):
+        m[off + ns:off + nr] = True
+        off += nr
+    return torch.from_numpy(m).to(device, non_blocking=True)
+
+
+def _fit_or_fixed(g: gpk.BatchedExactGP, phi: Optional[torch.Tensor], max_iter: int, gtol: float) -> gpk.FitResult:
+    if phi is None:
+        return g.fit(max_iter=max_iter, gtol=gtol)
+    init = g.init()   # median lengthscale -> prior loc, exactly as a fit would see it
+    return g.evaluate(phi.to(init.phi.device, torch.float32).view(-1, 3).contiguous(), init.aux)
+
+
+def run_on_task_batch(model: ADKTModel, tb: DeviceTaskBatch, train: bool = False, grad_scale: Optional[float] = None,
+                      fit_max_iter: int = 50, fit_gtol: float = 2e-6,
+                      phi: Optional[torch.Tensor] = None) -> TaskBatchResult:
+    """All T tasks of `tb` in one pass.  train=True accumulates the IFT hypergradient, scaled by `grad_scale`
+    (default 1/T = the reference's `/ tasks_per_batch`), into `.grad` of the feature-extractor parameters.
+    `phi` [T,3] skips the inner fit and evaluates at the given raw GP parameters (fixed-phi parity checks)."""
+    cfg = model.config
+    if train:
+        model.train()
+        Z = model.embed(tb)
+        g = gpk.BatchedExactGP(Z, tb.labels, tb.layout, cfg.gp_kernel, cfg.use_numeric_labels,
+                               cfg.use_lengthscale_prior, qq_block=True)
+        fit = _fit_or_fixed(g, phi, fit_max_iter, fit_gtol)
+        dZ, aux, status = g.hypergradient(fit, mode=1 if cfg.ignore_grad_correction else 0)
+        scale = (1.0 / tb.num_tasks) if grad_scale is None else grad_scale
+        Z.backward(dZ * scale)
+        F_t = aux[:, ops.AUX_FOUTER]
+        n_q = torch.tensor([r - s for r, s in zip(tb.layout.n_rows_host, tb.layout.n_sup_host)],
+                           dtype=torch.float32).to(Z.device, non_blocking=True)
+        return TaskBatchResult(phi=fit.phi, status=status | fit.status, aux=aux, outer_loss=F_t,
+                               loss_per_sample=F_t / n_q)
+    model.eval()
+    with torch.no_grad():
+        Z = model.embed(tb)
+        g = gpk.BatchedExactGP(Z, tb.labels, tb.layout, cfg.gp_kernel, cfg.use_numeric_labels,
+                               cfg.use_lengthscale_prior, qq_block=False)
+        fit = _fit_or_fixed(g, phi, fit_max_iter, fit_gtol)
+        mean, var, st = g.predict(fit.phi)
+        qm = _query_mask(tb.layout, Z.device)
+        mq = mean[qm]
+        preds = mq if cfg.use_numeric_labels else torch.sigmoid(mq)
+    return TaskBatchResult(phi=fit.phi, status=fit.status | st, aux=fit.aux, mean=mean, variance=var, preds=preds,
+                           query_mask=qm)
+
+
+def run_on_batches(model: ADKTModel, batches: Sequence, batch_labels: Sequence, batch_numeric_labels: Sequence,
+                   train: bool = False):
+    """Reference loop (adaptive_dkt_utils.py:70-116) over the query batches of ONE task.  The reference re-fits
+    the GP for every query batch on the same support set; the fit is deterministic, so it is done once.
+    Returns (predictions, labels) as numpy for the metric code (None, None when train=True)."""
+    if train:
+        assert len(batches) == 1
+    preds: List[np.ndarray] = []
+    labels: List[np.ndarray] = []
+    fitted = False
+    for feats, bl, bnl in zip(batches, batch_labels, batch_numeric_labels):
+        if not fitted:
+            model.train()
+            _ = model(feats, train_loss=True)
+            fit_gpytorch_scipy(model.mll)
+            fitted = True
+        if not train:
+            model.eval()
+            with torch.no_grad():
+                out = model(feats, train_loss=None)
+            if model.config.use_numeric_labels:
+                preds.append(out.mean.detach().cpu().numpy())
+                labels.append(torch.as_tensor(bnl).detach().cpu().numpy())
+            else:
+                preds.append(torch.sigmoid(out.mean).detach().cpu().numpy())
+                labels.append(torch.as_tensor(bl).detach().cpu().numpy())
+    if train:
+        return None, None
+    return np.concatenate(preds, axis=0), np.concatenate(labels, axis=0)
+
+
+# ----------------------------------------------------------------------------------------------------------
+# trainer
+# ----------------------------------------------------------------------------------------------------------
+class FlatParams:
+    """Feature-extractor parameters and gradients as views of two flat fp32 buffers, so that the NCCL
+    all-reduce, the gradient-norm clip and Adam each touch ONE contiguous 101 MB array."""
+
+    def __init__(self, params: List[torch.nn.Parameter]):
+        self.params = params
+        self.sizes = [p.numel() for p in params]
+        total = sum(self.sizes)
+        dev = params[0].device
+        self.total = total
+        self.flat = torch.empty(total, dtype=torch.float32, device=dev)
+        self.grad = torch.zeros(total, dtype=torch.float32, device=dev)
+        off = 0
+        for p, n in zip(params, self.sizes):
+            self.flat[off:off + n].copy_(p.data.reshape(-1))
+            p.data = self.flat[off:off + n].view_as(p.data)
+            p.grad = self.grad[off:off + n].view_as(p.data)
+            off += n
+
+    def zero_grad(self):
+        self.grad.zero_()
+        off = 0
+        for p, n in zip(self.params, self.sizes):   # re-attach views if something replaced .grad
+            if p.grad is None or p.grad.data_ptr() != self.grad[off:off + n].data_ptr():
+                p.grad = self.grad[off:off + n].view_as(p.data)
+            off += n
+
+
+class ADKTModelTrainer(ADKTModel):
+    def __init__(self, config: ADKTModelTrainerConfig):
+        super().__init__(config)
+        self.config = config
+        self.optimizer = torch.optim.Adam(self.feature_extractor_params(), config.learning_rate)
+        self.lr_scheduler = None
+        self._flat: Optional[FlatParams] = None
+        self._step = 0
+
+    # ---- checkpoints (adaptive_dkt_utils.py:221-259, 305-327) -----------------------------------------
+    def get_model_state(self) -> Dict[str, Any]:
+        return {"model_config": self.config, "model_state_dict": self.state_dict()}
+
+    def save_model(self, path: str, optimizer: Optional[torch.optim.Optimizer] = None, epoch: Optional[int] = None):
+        data = self.get_model_state()
+        if optimizer is not None:
+            data["optimizer_state_dict"] = optimizer.state_dict()
+        if epoch is not None:
+            data["epoch"] = epoch
+        torch.save(data, path)
+
+    def load_model_weights(self, path: str, quiet: bool = False, device: Optional[torch.device] = None):
+        """Copies tensors by key.  Reference checkpoints also carry gpytorch's `gp_*` / `mll.*` entries (several
+        aliases of the same three tensors plus prior buffers): they are re-initialised per task anyway, so keys
+        this model does not own are skipped."""
+        ckpt = torch.load(path, map_location=device, weights_only=False)
+        own = self.state_dict()
+        skipped = []
+        for name, value in ckpt["model_state_dict"].items():
+            if isinstance(value, torch.nn.Parameter):
+                value = value.data
+            if name in own and own[name].shape == value.shape:
+                own[name].copy_(value)
+            elif name.startswith("gp_") or name.startswith("mll."):
+                skipped.append(name)
+            else:
+                raise KeyError(f"checkpoint tensor {name} {tuple(value.shape)} has no counterpart in the model")
+        return skipped
+
+    @classmethod
+    def build_from_model_file(cls, model_file: str, config_overrides: Dict[str, Any] = {}, quiet: bool = False,
+                              device: Optional[torch.device] = None) -> "ADKTModelTrainer":
+        ckpt = torch.load(model_file, map_location=device, weights_only=False)
+        model = cls(ckpt["model_config"])
+        if device is not None:
+            model.to(device)
+        model.load_model_weights(model_file, quiet=quiet, device=device)
+        return model
+
+    # ---- one outer step -------------------------------------------------------------------------------
+    def _ensure_flat(self):
+        if self._flat is None:
+            self._flat = FlatParams(self.feature_extractor_params())
+            self.optimizer = torch.optim.Adam(self.feature_extractor_params(), self.config.learning_rate, fused=True)
+        return self._flat
+
+    def train_step(self, tb: DeviceTaskBatch, global_num_tasks: Optional[int] = None) -> TaskBatchResult:
+        """One outer step on this rank's share of the meta-batch (adaptive_dkt_utils.py:352-413): hypergradients of
+        the local tasks / global task count, all-reduce, clip, Adam."""
+        flat = self._ensure_flat()
+        flat.zero_grad()
+        world = torch.distributed.get_world_size() if torch.distributed.is_initialized() else 1
+        total_tasks = global_num_tasks if global_num_tasks is not None else tb.num_tasks * world
+        res = run_on_task_batch(self, tb, train=True, grad_scale=1.0 / total_tasks)
+        if world > 1:
+            torch.distributed.all_reduce(flat.grad, op=torch.distributed.ReduceOp.SUM)
+        if self.config.clip_value is not None:
+            # clip_grad_norm_ on the flat buffer: same global 2-norm, one reduction, no host sync
+            norm = torch.linalg.vector_norm(flat.grad)
+            flat.grad.mul_(torch.clamp(self.config.clip_value / (norm + 1e-6), max=1.0))
+        self.optimizer.step()
+        if self.lr_scheduler is not None:
+            self.lr_scheduler.step()
+        self._step += 1
+        return res

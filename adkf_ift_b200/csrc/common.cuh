@@ -10,6 +10,9 @@
         if (e__ != cudaSuccess) return (int)e__;    \
     } while (0)
 
+// number of kernel launches issued through the C-ABI since load (host-side counter, see capi.cu)
+extern "C" void adkf_count_launches(int n);
+
 namespace adkf {
 
 constexpr int kWarp = 32;

@@ -696,6 +696,26 @@ gp_ift_kernel(const int32_t* __restrict__ z_off, const int32_t* __restrict__ n_s
     }
     const float nll_inner = sh.nll;
 
+    if (ignore_corr == 2) {
+        // inner loss only: Wm_ss = df/dD2 = Gamma o Ku / n, zero elsewhere (first-order autograd of f = -MLL)
+        for (int idx = threadIdx.x; idx < N * N; idx += blockDim.x) {
+            const int a = idx / N, b = idx - a * N;
+            float w = 0.f;
+            if (a < n && b < n) {
+                const KParts kp = kernel_parts(D2t[idx], h.s, h.l, kind);
+                w = 0.5f * (cv.M1[(size_t)a * cv.ld + b] - alpha[a] * alpha[b]) * kp.Ku / n;
+            }
+            Wt[idx] = w;
+        }
+        if (threadIdx.x == 0) {
+            auxt[ADKF_AUX_F] = sh.f;
+            for (int i = 0; i < 3; ++i) auxt[ADKF_AUX_G + i] = sh.g[i];
+            for (int i = 0; i < 9; ++i) auxt[ADKF_AUX_H + i] = sh.H[i];
+            status[t] = (jit_inner > 0.f) ? ADKF_ST_JITTER : ADKF_ST_OK;
+        }
+        return;
+    }
+
     // ---- joint covariance J = K + sig2 I over support+query: Cholesky, inverse, beta --------------
     {
         GpProblem pj = pb;
@@ -753,7 +773,7 @@ gp_ift_kernel(const int32_t* __restrict__ z_off, const int32_t* __restrict__ n_s
     if (sh.flag) st |= ADKF_ST_HESS_DAMPED;
 
     // ---- IFT correction on the support block:  Wm_ss -= (1/n) [ Gamdot o Ku + Gam o Kudot ] ---------
-    if (!ignore_corr) {
+    if (ignore_corr == 0) {
         const float pd0 = sh.pd[0], pd1 = sh.pd[1], pd2 = sh.pd[2];
         // M2 <- Adot = pd0 I + pd1 K/s + pd2 S   (M2 currently holds S)
         for (int idx = threadIdx.x; idx < n * n; idx += blockDim.x) {
@@ -880,6 +900,7 @@ extern "C" int adkf_gp_fit(int32_t T, const int32_t* z_off, const int32_t* n_sup
     gp_fit_kernel<<<T, kGpThreads, gp_smem_bytes(), s>>>(z_off, n_sup, d2_off, D2, y, kernel, noise_init,
                                                         noise_prior_loc, ls_prior, init_mode, max_iter, gtol,
                                                         phi_io, aux, status, ws, off);
+    adkf_count_launches(2);
     ADKF_LAUNCH_CHECK();
     return 0;
 }
@@ -896,24 +917,27 @@ extern "C" int adkf_gp_predict(int32_t T, const int32_t* z_off, const int32_t* n
     gp_ws_offsets_kernel<<<1, 1, 0, s>>>(T, z_off, n_sup, 1, off);
     gp_predict_kernel<<<T, kGpThreads, gp_smem_bytes(), s>>>(z_off, n_sup, d2_off, D2, y, kernel, phi, mean, var,
                                                             status, ws, off);
+    adkf_count_launches(2);
     ADKF_LAUNCH_CHECK();
     return 0;
 }
 
 extern "C" int adkf_gp_ift(int32_t T, const int32_t* z_off, const int32_t* n_sup, const int64_t* d2_off,
                            const float* D2, const float* y, int32_t kernel, float noise_prior_loc,
-                           int32_t ls_prior, int32_t ignore_grad_correction, const float* phi, float* aux,
+                           int32_t ls_prior, int32_t mode, const float* phi, float* aux,
                            float* Wm, int32_t* status, float* ws, int64_t ws_floats, void* stream) {
     if (T <= 0) return 0;
     if (!z_off || !n_sup || !d2_off || !D2 || !y || !phi || !aux || !Wm || !status || !ws) return ADKF_ERR_BADARG;
+    if (mode < 0 || mode > 2) return ADKF_ERR_BADARG;
     cudaStream_t s = (cudaStream_t)stream;
     int e = set_smem_attr((const void*)gp_ift_kernel);
     if (e) return e;
     int64_t* off = reinterpret_cast<int64_t*>(ws);
     gp_ws_offsets_kernel<<<1, 1, 0, s>>>(T, z_off, n_sup, 2, off);
     gp_ift_kernel<<<T, kGpThreads, gp_smem_bytes(), s>>>(z_off, n_sup, d2_off, D2, y, kernel, noise_prior_loc,
-                                                        ls_prior, ignore_grad_correction, phi, aux, Wm, status,
+                                                        ls_prior, mode, phi, aux, Wm, status,
                                                         ws, off);
+    adkf_count_launches(2);
     ADKF_LAUNCH_CHECK();
     return 0;
 }

@@ -194,6 +194,7 @@ extern "C" int adkf_gram_sqdist(const float* Z, int32_t d, int32_t T, const int3
     row_norm_kernel<<<dim3((max_n + 7) / 8, T), 256, 0, s>>>(Z, d, z_off, mu_ws, nrm_ws);
     const int nt = (max_n + kTile - 1) / kTile;
     sqdist_tile_kernel<<<dim3(nt, nt, T), 256, 0, s>>>(Z, d, z_off, n_sup, d2_off, qq_block, mu_ws, nrm_ws, D2);
+    adkf_count_launches(3);
     ADKF_LAUNCH_CHECK();
     return 0;
 }
@@ -206,6 +207,7 @@ extern "C" int adkf_gram_sqdist_bwd(const float* Z, int32_t d, int32_t T, const 
     cudaStream_t s = (cudaStream_t)stream;
     sqdist_bwd_kernel<<<dim3((d + kTile - 1) / kTile, (max_n + kTile - 1) / kTile, T), 256, 0, s>>>(
         Z, d, z_off, d2_off, Wm, mu_ws, scale, dZ);
+    adkf_count_launches(1);
     ADKF_LAUNCH_CHECK();
     return 0;
 }

@@ -536,6 +536,7 @@ extern "C" int adkf_graph_csr_build(const int64_t* adj0, int64_t e0, const int64
                                                                 col_tgt, scratch);
         csr_reverse_kernel<<<min(eb, 4096), 256, 0, s>>>(A, etot, col_eid, scratch, rev_pos);
     }
+    adkf_count_launches(5);
     ADKF_LAUNCH_CHECK();
     return 0;
 }
@@ -557,6 +558,7 @@ extern "C" int adkf_mp_pna_fwd(const float* h, const float* W, const float* b, c
     if (e != cudaSuccess) return (int)e;
     pna_fwd_kernel<<<dim3(mp_grid_x(num_nodes), kTowers), kMpWarps * 32, kMpSmemFwd, s>>>(
         h, W, b, rowptr, col_src, col_type, num_nodes, out, aux_cnt, aux_arg);
+    adkf_count_launches(1);
     ADKF_LAUNCH_CHECK();
     return 0;
 }
@@ -585,6 +587,7 @@ extern "C" int adkf_mp_pna_bwd(const float* h, const float* W, const float* b, c
     pna_bwd_weights_kernel<<<dim3(num_partials, kTowers * kTypes), 256, 0, s>>>(h, col_src, col_tgt, col_type,
                                                                                num_edges, d_pre, partials);
     pna_bwd_reduce_kernel<<<148 * 2, 256, 0, s>>>(partials, num_partials, d_W, d_b);
+    adkf_count_launches(4);
     ADKF_LAUNCH_CHECK();
     return 0;
 }

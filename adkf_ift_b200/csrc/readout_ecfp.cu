@@ -258,6 +258,7 @@ extern "C" int adkf_readout_weighted_fwd(const float* scores, const float* value
     if (!scores || !values || !graph_ptr || !weights || !out || heads <= 0 || head_dim <= 0) return ADKF_ERR_BADARG;
     readout_weighted_fwd_kernel<<<num_graphs, 256, 0, (cudaStream_t)stream>>>(scores, values, graph_ptr, heads,
                                                                               head_dim, mode, weights, out);
+    adkf_count_launches(1);
     ADKF_LAUNCH_CHECK();
     return 0;
 }
@@ -269,6 +270,7 @@ extern "C" int adkf_readout_weighted_bwd(const float* weights, const float* valu
     if (!weights || !values || !graph_ptr || !d_out || !d_scores || !d_values) return ADKF_ERR_BADARG;
     readout_weighted_bwd_kernel<<<num_graphs, 256, 0, (cudaStream_t)stream>>>(weights, values, graph_ptr, heads,
                                                                               head_dim, mode, d_out, d_scores, d_values);
+    adkf_count_launches(1);
     ADKF_LAUNCH_CHECK();
     return 0;
 }
@@ -278,6 +280,7 @@ extern "C" int adkf_readout_max_fwd(const float* x, const int32_t* graph_ptr, in
     if (num_graphs <= 0) return 0;
     if (!x || !graph_ptr || !out || !argmax || dim <= 0) return ADKF_ERR_BADARG;
     readout_max_fwd_kernel<<<num_graphs, 256, 0, (cudaStream_t)stream>>>(x, graph_ptr, dim, out, argmax);
+    adkf_count_launches(1);
     ADKF_LAUNCH_CHECK();
     return 0;
 }
@@ -287,6 +290,7 @@ extern "C" int adkf_readout_max_bwd(const float* d_out, const int32_t* argmax, c
     if (num_graphs <= 0) return 0;
     if (!d_out || !argmax || !graph_ptr || !d_x || dim <= 0) return ADKF_ERR_BADARG;
     readout_max_bwd_kernel<<<num_graphs, 256, 0, (cudaStream_t)stream>>>(d_out, argmax, graph_ptr, dim, d_x);
+    adkf_count_launches(1);
     ADKF_LAUNCH_CHECK();
     return 0;
 }
@@ -296,6 +300,7 @@ extern "C" int adkf_ecfp_linear_fwd(const int32_t* fp, int32_t num_graphs, int32
     if (num_graphs <= 0) return 0;
     if (!fp || !Wt || !out || fp_dim <= 0 || out_dim <= 0 || (out_dim & 3)) return ADKF_ERR_BADARG;
     ecfp_linear_fwd_kernel<<<num_graphs, 256, 0, (cudaStream_t)stream>>>(fp, fp_dim, Wt, out_dim, out);
+    adkf_count_launches(1);
     ADKF_LAUNCH_CHECK();
     return 0;
 }
@@ -306,6 +311,7 @@ extern "C" int adkf_ecfp_linear_bwd(const int32_t* fp, int32_t num_graphs, int32
     if (!fp || !d_out || !d_Wt || fp_dim <= 0 || out_dim <= 0) return ADKF_ERR_BADARG;
     ecfp_linear_bwd_kernel<<<dim3((fp_dim + kEbJ - 1) / kEbJ, (out_dim + kEbC - 1) / kEbC), 256, 0,
                              (cudaStream_t)stream>>>(fp, num_graphs, fp_dim, d_out, out_dim, d_Wt);
+    adkf_count_launches(1);
     ADKF_LAUNCH_CHECK();
     return 0;
 }

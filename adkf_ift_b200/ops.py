@@ -342,10 +342,12 @@ def gp_predict(layout: TaskLayout, D2, y, kernel: str, phi):
 
 
 def gp_ift(layout: TaskLayout, D2, y, kernel: str, noise_prior_loc: float, ls_prior: int, phi, aux,
-           ignore_grad_correction: bool = False):
+           ignore_grad_correction: bool = False, mode=None):
     """Returns (Wm same layout as D2, aux updated, status)."""
     lib = _cabi.load()
     dev = D2.device
+    if mode is None:
+        mode = 1 if ignore_grad_correction else 0
     Wm = torch.zeros_like(D2)
     aux = aux.contiguous().clone()
     status = torch.zeros(layout.T, dtype=torch.int32, device=dev)
@@ -353,7 +355,7 @@ def gp_ift(layout: TaskLayout, D2, y, kernel: str, noise_prior_loc: float, ls_pr
     ws = torch.empty(nws, dtype=torch.float32, device=dev)
     rc = lib.adkf_gp_ift(layout.T, dptr(layout.z_off), dptr(layout.n_sup), dptr(layout.d2_off),
                          dptr(D2, torch.float32), dptr(y, torch.float32), KERNEL_IDS[kernel], float(noise_prior_loc),
-                         int(ls_prior), 1 if ignore_grad_correction else 0, dptr(phi.contiguous(), torch.float32),
+                         int(ls_prior), int(mode), dptr(phi.contiguous(), torch.float32),
                          dptr(aux), dptr(Wm), dptr(status), dptr(ws), nws, stream_ptr())
     check(rc, "adkf_gp_ift")
     return Wm, aux, status

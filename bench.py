@@ -1,0 +1,312 @@
+#!/usr/bin/env python
+"""bench.py -- FS-Mol-shaped tasks/sec (GP fit + IFT hypergradient) of the ADKF-IFT meta-training step.
+
+    python bench.py --gpus N --steps K --warmup W            # this repo's B200 path
+    python bench.py --impl reference --gpus N --steps K ...   # the reference's CPU path (oracle) on the host cores
+
+Workload (BASELINE.json configs[1]): ADKTModel meta-training step, 16 tasks per GPU per step, support 64, query 256,
+gnn+ecfp+fc features (PNA 10 layers, H=128; FC 2560->2048->2048), Matern-5/2 GP, inner fit + IFT hypergradient
++ one backward through the extractor, NCCL all-reduce of the flat 25.3 M-float meta-gradient, clip 1.0, Adam.
+Weak scaling: every rank processes its own 16 tasks per step (global meta-batch 16 N).
+
+One JSON line on rank 0 (contract in the task statement): value = device-resident tasks/s, e2e = the same step
+through to_device() from pinned host memory + a host read of the loss, roofline for the dominant own kernel
+(timed live with CUDA events), cpu_baseline = oracle on the host cores (N=1 only), clocks, gpu_launches.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+import numpy as np  # noqa: E402
+import torch  # noqa: E402
+
+TASKS_PER_GPU = 16
+SUPPORT, QUERY = 64, 256
+METRIC = "FS-Mol-shaped meta-training tasks/sec (GP fit + IFT hypergradient)"
+UNIT = "tasks/s"
+
+
+def workload_config(n_gpus):
+    return {"workload": "C2: ADKTModel meta-training step, 16 tasks/GPU/step, support 64, query 256, gnn+ecfp+fc, "
+                        "matern, IFT hypergradient, clip 1.0, Adam",
+            "tasks_per_step": TASKS_PER_GPU * n_gpus, "support": SUPPORT, "query": QUERY,
+            "parallelism": f"task-sharded dp{n_gpus}, one NCCL all-reduce of the 101 MB meta-gradient per step",
+            "l2": "inputs+weights (~160 MB) and ~20 GB of per-step activations exceed the 126 MB L2; no explicit flush"}
+
+
+def make_model(device, num_layers=10):
+    from adkf_ift_b200 import synthetic
+    from adkf_ift_b200.adaptive_dkt import ADKTModelTrainerConfig
+    from adkf_ift_b200.adaptive_dkt_utils import ADKTModelTrainer
+    from adkf_ift_b200.feature_extractor import cli_default_config
+    cfg = ADKTModelTrainerConfig(graph_feature_extractor_config=cli_default_config(num_layers), gp_kernel="matern",
+                                 tasks_per_batch=TASKS_PER_GPU, support_set_size=SUPPORT, query_set_size=QUERY,
+                                 learning_rate=1e-4, clip_value=1.0)
+    model = ADKTModelTrainer(cfg)
+    synthetic.deterministic_init_(model, seed=0, alpha=0.5)
+    return model.to(device)
+
+
+def host_tasks(first_task, num_tasks):
+    from adkf_ift_b200 import dkt, synthetic
+    out = []
+    for t in range(num_tasks):
+        s = synthetic.make_task_sample(first_task + t, SUPPORT, QUERY)
+        out.append(dkt.task_sample_to_dkt_task_sample(s, dkt.get_dkt_batcher(max_num_graphs=SUPPORT + QUERY), False).batches[0])
+    return out
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled every 200 ms while the timed region runs."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.rows, self.proc = index, [], None
+
+    def __enter__(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-i", str(self.index), "-lms", "200"], stdout=subprocess.PIPE, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except OSError:
+            self.proc = None
+        return self
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def __exit__(self, *a):
+        if self.proc is not None:
+            time.sleep(0.25)
+            self.proc.terminate()
+            self.thread.join(timeout=2)
+
+    def summary(self):
+        sm, mx, reasons = [], [], set()
+        for r in self.rows:
+            try:
+                sm.append(float(r[0])); mx.append(float(r[1]))
+            except (ValueError, IndexError):
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[2:6]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        return {"sm_mhz": float(np.median(sm)), "sm_max_mhz": float(max(mx)), "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+def timed_region(fn, steps, world, device):
+    """barrier + sync, K steps between CUDA events on the current stream, barrier + sync; max over ranks (ms)."""
+    if world > 1:
+        torch.distributed.barrier()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(steps):
+        fn(i)
+    e1.record()
+    torch.cuda.synchronize()
+    if world > 1:
+        torch.distributed.barrier()
+    ms = torch.tensor([e0.elapsed_time(e1)], device=device)
+    if world > 1:
+        torch.distributed.all_reduce(ms, op=torch.distributed.ReduceOp.MAX)
+    return float(ms.item())
+
+
+def dominant_kernel_roofline(model, tb, peaks):
+    """Times the dominant own kernel (the fused PNA message-passing forward of one GNN block over the whole
+    16-task graph batch) alone with CUDA events and relates its ALGORITHMIC bytes (4*H*V read of h,
+    4*3072*V write of the aggregate, 512 B/node of backward aux, 4 B/edge source index, 1 B/edge type,
+    4*(V+1) rowptr) to the measured HBM copy bandwidth."""
+    from adkf_ift_b200 import ops
+    gi = tb.graph_index
+    V, E = gi.num_nodes, gi.num_edges
+    blk = model.graph_feature_extractor.gnn.gnn_blocks[0]
+    with torch.no_grad():
+        W, b = blk.stacked_message_weights()
+        h = torch.randn(V, 128, device=W.device)
+        for _ in range(3):
+            ops.pna_message_passing(h, W, b, gi)
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        reps = 10
+        e0.record()
+        for _ in range(reps):
+            ops.pna_message_passing(h, W, b, gi)
+        e1.record()
+        torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / reps
+    alg_bytes = 4 * 128 * V + 4 * 3072 * V + 512 * V + 5 * E + 4 * (V + 1)
+    achieved = alg_bytes / (ms * 1e-3) / 1e9
+    peak = peaks.get("hbm_gbs")
+    src = "measured (MEASURED_PEAKS.json hbm_gbs)"
+    if peak is None:
+        peak, src = 6650.0, "fallback (B200_PROFILING.md)"
+    flops = 2 * 192 * 32 * 4 * (E + V * 1.3)   # source half per edge + target half per (node, type present)
+    return {"kernel": "pna_fwd_kernel", "bound": "hbm", "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s",
+            "frac": round(achieved / peak, 4), "traffic": None, "peak_source": src, "launch_ms": round(ms, 4),
+            "algorithmic_bytes": int(alg_bytes), "nodes": V, "directed_edges": E,
+            "fp32_tflops": round(flops / (ms * 1e-3) / 1e12, 2)}
+
+
+# ----------------------------------------------------------------------------------------------------------
+# CPU reference arm (oracle = the reference's algorithm restated on torch CPU + SciPy L-BFGS-B)
+# ----------------------------------------------------------------------------------------------------------
+def oracle_setup():
+    from adkf_ift_b200 import dkt, synthetic
+    from adkf_ift_b200.adaptive_dkt import ADKTModelTrainerConfig
+    from adkf_ift_b200.adaptive_dkt_utils import ADKTModelTrainer
+    from adkf_ift_b200.feature_extractor import cli_default_config
+    from oracle import adkf_oracle as orc
+    torch.set_num_threads(os.cpu_count() or 1)
+    model = ADKTModelTrainer(ADKTModelTrainerConfig(graph_feature_extractor_config=cli_default_config(10)))
+    synthetic.deterministic_init_(model, seed=0, alpha=0.5)
+    P = {n: p.detach().clone().requires_grad_(True) for n, p in model.named_parameters() if not n.startswith("gp_")}
+    names = list(P.keys())
+    ocfg = orc.OracleConfig(num_layers=10, gp_kernel="matern")
+
+    def run_task(task_id):
+        s = synthetic.make_task_sample(task_id, SUPPORT, QUERY)
+        host = dkt.task_sample_to_dkt_task_sample(s, dkt.get_dkt_batcher(max_num_graphs=SUPPORT + QUERY), False)
+        batch = dkt.torchify(host, torch.device("cpu")).batches[0]
+        t0 = time.perf_counter()
+        out = orc.meta_train_task(P, names, batch, ocfg)
+        return time.perf_counter() - t0, float(out["F"])
+
+    return run_task
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    run_task = oracle_setup()
+    for i in range(args.warmup):
+        run_task(9000 + i)
+    t = 0.0
+    for i in range(args.steps):
+        dt, _ = run_task(9100 + i)
+        t += dt
+    value = args.steps / t
+    cores = torch.get_num_threads()
+    sample = f"{args.steps} steps x 1 task (support {SUPPORT}, query {QUERY}) of the C2 meta-training step, sequential"
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": 1e3 * t / args.steps, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": workload_config(args.gpus),
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0}), flush=True)
+
+
+# ----------------------------------------------------------------------------------------------------------
+def run_b200(args):
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device (there is no CPU fallback for the product path)")
+    torch.cuda.set_device(local)
+    device = torch.device("cuda", local)
+    if world > 1:
+        torch.distributed.init_process_group("nccl", device_id=device)
+    from adkf_ift_b200 import _cabi, task_batch
+    lib = _cabi.load()
+    model = make_model(device)
+    n_distinct = 2
+    hbs = [task_batch.collate_tasks(host_tasks(1000 * (rank + 1) + 100 * j, TASKS_PER_GPU), False) for j in range(n_distinct)]
+    staged = [task_batch.to_device(hb, device, build_index=False) for hb in hbs]
+    losses = []
+
+    def step_resident(i):
+        from adkf_ift_b200 import ops
+        tb = staged[i % n_distinct]
+        tb.graph_index = ops.build_graph_index(tb.adjacency_lists, tb.num_nodes, tb.node_to_graph, tb.num_graphs)
+        res = model.train_step(tb)
+        losses.append(res.loss_per_sample)
+
+    def step_e2e(i):
+        tb = task_batch.to_device(hbs[i % n_distinct], device)
+        res = model.train_step(tb)
+        losses.append(float(res.loss_per_sample.mean().item()))   # D2H read of the step's loss
+
+    for i in range(args.warmup):
+        step_resident(i)
+    torch.cuda.synchronize()
+    l0 = lib.adkf_launch_count()
+    with ClockSampler(local) as clk:
+        ms = timed_region(step_resident, args.steps, world, device)
+    launches = lib.adkf_launch_count() - l0
+    status = None
+    for i in range(max(1, min(args.warmup, 2))):
+        step_e2e(i)
+    with ClockSampler(local) as clk2:
+        ms_e2e = timed_region(step_e2e, args.steps, world, device)
+    total_tasks = TASKS_PER_GPU * world * args.steps
+    value = total_tasks / (ms * 1e-3)
+    e2e = total_tasks / (ms_e2e * 1e-3)
+    if rank != 0:
+        if world > 1:
+            torch.distributed.destroy_process_group()
+        return
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except OSError:
+        pass
+    staged[0].graph_index = task_batch.ops.build_graph_index(staged[0].adjacency_lists, staged[0].num_nodes,
+                                                             staged[0].node_to_graph, staged[0].num_graphs)
+    roof = dominant_kernel_roofline(model, staged[0], peaks)
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f32", "data": "synthetic", "config": workload_config(world),
+        "e2e": {"value": e2e, "unit": UNIT, "h2d_bytes_per_step": hbs[0].nbytes(), "d2h_bytes_per_step": 4,
+                "ms_per_step": ms_e2e / args.steps},
+        "gpu_launches": int(launches), "clocks": clk.summary(), "clocks_e2e": clk2.summary(), "roofline": roof,
+        "last_loss_per_sample": losses[-1],
+    }
+    if world == 1 and not args.no_cpu_baseline:
+        run_task = oracle_setup()
+        run_task(9000)  # warm-up (thread pools, allocator)
+        n_cpu = args.cpu_tasks
+        t = sum(run_task(9100 + i)[0] for i in range(n_cpu))
+        line["cpu_baseline"] = {"value": n_cpu / t, "unit": UNIT, "cores": torch.get_num_threads(), "kind": "port",
+                                "sample": f"{n_cpu} tasks (support {SUPPORT}, query {QUERY}) of the same C2 step through the "
+                                          "CPU oracle (reference algorithm on torch CPU + SciPy L-BFGS-B), sequential"}
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        torch.distributed.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--cpu-tasks", type=int, default=2)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_b200(args)
+
+
+if __name__ == "__main__":
+    main()

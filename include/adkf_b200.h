@@ -52,6 +52,8 @@ extern "C" {
 #define ADKF_AUX_NFEV       24   /* function evaluations used by the fit    */
 
 int adkf_version(void);
+/* kernels launched through this library since it was loaded (bench.py's gpu_launches) */
+int64_t adkf_launch_count(void);
 
 /* ---------------------------------------------------------------------------------------------
  * Graph indexing (integer path, bit-exact).  Replaces GNN.forward's bidirectional expansion
@@ -164,10 +166,12 @@ int adkf_gp_predict(int32_t T, const int32_t* z_off, const int32_t* n_sup, const
  *   F = -log N(y_q | posterior(y_s) + noise)  (summed joint log-prob, adaptive_dkt.py:183-191),
  *   H = d2f/dphi2 (3x3), v = H^-1 dF/dphi, and the symmetric weight matrix
  *   Wm = dF/dD2 - d/deps [ df/dD2 (phi + eps v) ]   (SURVEY App. B), to be fed to adkf_gram_sqdist_bwd.
- * ignore_grad_correction = 1 drops the second term (reference flag of the same name). */
+ * mode: 0 = full hypergradient; 1 = drop the second term (the reference's ignore_grad_correction flag);
+ *       2 = inner loss only: Wm = df/dD2 on the support block (first-order gradient of f = -MLL w.r.t. Z_s,
+ *           the functional train-loss branch of adaptive_dkt.py:173-176), aux F/G/H refreshed. */
 int adkf_gp_ift(int32_t T, const int32_t* z_off, const int32_t* n_sup, const int64_t* d2_off,
                 const float* D2, const float* y, int32_t kernel, float noise_prior_loc, int32_t ls_prior,
-                int32_t ignore_grad_correction, const float* phi, float* aux /*[T,ADKF_AUX] in/out*/,
+                int32_t mode, const float* phi, float* aux /*[T,ADKF_AUX] in/out*/,
                 float* Wm, int32_t* status, float* ws, int64_t ws_floats, void* stream);
 
 /* workspace sizes (floats) for the three GP entry points, host-side helper */

@@ -1,0 +1,178 @@
+"""-m gpu end-to-end parity of the ADKTModel surface and the batched task path against the golden fixtures
+generated from the reference's own files (tests/golden/make_golden.py).
+
+Tolerances: <=1e-4 relative at FIXED phi (north_star; features, predictive mean/variance, F, hypergradient),
+<=2e-3 after each side's own inner fit (SciPy's L-BFGS-B stopping error alone moves the reference by 3-4e-4,
+SURVEY.md App. D)."""
+import os
+import zlib
+
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+CASES = [("c1_classification", "matern"), ("c1_regression", "matern"), ("s64_rbf_l2", "rbf")]
+
+
+def rel(a, b):
+    a = np.asarray(a, dtype=np.float64)
+    b = np.asarray(b, dtype=np.float64)
+    return float(np.abs(a - b).max() / max(np.abs(b).max(), 1e-30))
+
+
+def probe_vector(name, shape):
+    g = torch.Generator().manual_seed(zlib.crc32(("probe:" + name).encode()) & 0x7FFFFFFF)
+    return torch.randn(shape, generator=g, dtype=torch.float64)
+
+
+def build(golden_dir, name, kernel, device):
+    from adkf_ift_b200 import dkt, synthetic, task_batch
+    from adkf_ift_b200.adaptive_dkt import ADKTModelTrainerConfig
+    from adkf_ift_b200.adaptive_dkt_utils import ADKTModelTrainer
+    from adkf_ift_b200.feature_extractor import cli_default_config
+    g = np.load(os.path.join(golden_dir, name + ".npz"))
+    task_id, n_s, n_q, numeric, layers = (int(x) for x in g["meta"])
+    cfg = ADKTModelTrainerConfig(graph_feature_extractor_config=cli_default_config(layers), gp_kernel=kernel,
+                                 use_numeric_labels=bool(numeric))
+    model = ADKTModelTrainer(cfg)
+    synthetic.deterministic_init_(model, seed=0, alpha=0.5)
+    model.to(device)
+    sample = synthetic.make_task_sample(task_id, n_s, n_q)
+    host = dkt.task_sample_to_dkt_task_sample(sample, dkt.get_dkt_batcher(max_num_graphs=320), bool(numeric))
+    hb = task_batch.collate_tasks([host.batches[0]], bool(numeric))
+    return g, model, host, task_batch.to_device(hb, device)
+
+
+@pytest.mark.parametrize("name,kernel", CASES)
+def test_features_match_reference(cuda_device, golden_dir, name, kernel):
+    g, model, host, tb = build(golden_dir, name, kernel, cuda_device)
+    with torch.no_grad():
+        Z = model.embed(tb).cpu().numpy()
+    n = len(g["z_support"])
+    e_s, e_q = rel(Z[:n], g["z_support"]), rel(Z[n:], g["z_query"])
+    print(name, "feature rel err support", e_s, "query", e_q)
+    assert e_s < 1e-4 and e_q < 1e-4
+
+
+@pytest.mark.parametrize("name,kernel", CASES)
+def test_meta_test_fixed_phi_and_fitted(cuda_device, golden_dir, name, kernel):
+    from adkf_ift_b200.adaptive_dkt_utils import run_on_task_batch
+    g, model, host, tb = build(golden_dir, name, kernel, cuda_device)
+    n = len(g["z_support"])
+    phi_ref = torch.from_numpy(g["test_phi_star"].astype(np.float32)).view(1, 3)
+    fixed = run_on_task_batch(model, tb, train=False, phi=phi_ref)
+    assert rel(fixed.mean.cpu().numpy()[n:], g["test_mean"]) < 1e-4
+    assert rel(fixed.variance.cpu().numpy()[n:], g["test_variance"]) < 1e-4
+    fitted = run_on_task_batch(model, tb, train=False)
+    assert int(fitted.status.item()) & 6 == 0
+    assert np.abs(fitted.phi.cpu().numpy()[0] - g["test_phi_star"]).max() < 2e-3
+    assert rel(fitted.mean.cpu().numpy()[n:], g["test_mean"]) < 2e-3
+    assert rel(fitted.variance.cpu().numpy()[n:], g["test_variance"]) < 2e-3
+
+
+@pytest.mark.parametrize("name,kernel", CASES)
+def test_meta_train_hypergradient_matches_cauchy_hypergradient(cuda_device, golden_dir, name, kernel):
+    """theta-gradients of one training task vs the reference's cauchy_hypergradient on the whole model."""
+    from adkf_ift_b200.adaptive_dkt_utils import run_on_task_batch
+    g, model, host, tb = build(golden_dir, name, kernel, cuda_device)
+    names = [str(x) for x in g["grad_names"]]
+    params = dict(model.named_parameters())
+    for tag, phi, tol in (("fixed", torch.from_numpy(g["train_phi_star"].astype(np.float32)).view(1, 3), 2e-4),
+                          ("fitted", None, 3e-3)):
+        model.zero_grad(set_to_none=True)
+        res = run_on_task_batch(model, tb, train=True, grad_scale=1.0, phi=phi)
+        F = float(res.outer_loss.item())
+        assert abs(F - float(g["train_F"])) < tol * abs(float(g["train_F"])), (tag, F, float(g["train_F"]))
+        norms = np.array([params[n].grad.double().norm().item() if params[n].grad is not None else 0.0 for n in names])
+        dots = np.array([(params[n].grad.double().cpu() * probe_vector(n, params[n].shape)).sum().item()
+                         if params[n].grad is not None else 0.0 for n in names])
+        ref_n, ref_d = g["grad_norms"], g["grad_dots"]
+        big = ref_n > 1e-3 * ref_n.max()
+        e_norm = np.abs(norms - ref_n)[big] / ref_n[big]
+        e_dot = np.abs(dots - ref_d) / np.maximum(ref_n, 1e-3 * ref_n.max()) / np.sqrt([params[n].numel() for n in names])
+        print(name, tag, "F", F, "max rel grad-norm err", e_norm.max(), "max probe-dot err / (|g| sqrt(numel))", e_dot.max())
+        assert e_norm.max() < 5 * tol
+        assert e_dot.max() < 5 * tol
+        for n in ("fc.2.bias", "graph_feature_extractor.gnn.gnn_blocks.0.alpha",
+                  "graph_feature_extractor.init_node_proj.weight"):
+            # fc.2.bias shifts every feature row alike -> pairwise distances (hence F and f) do not depend on it:
+            # its true gradient is 0 and both sides hold rounding noise, so the error is measured against the
+            # largest per-tensor gradient norm as well
+            got, want = params[n].grad.cpu().numpy(), g["grad::" + n]
+            e = rel(got, want)
+            e_abs = float(np.abs(got - want).max() / ref_n.max())
+            print("   ", n, e, e_abs)
+            assert e < 5 * tol or e_abs < 1e-5
+        # unused parameters get zero gradients in the reference (cauchy_hypergradient.py:144-146)
+        assert float(ref_n[[i for i, n in enumerate(names) if "mp_norm_layer" in n]].max()) == 0.0
+
+
+def test_batched_tasks_equal_single_tasks(cuda_device):
+    """T=3 ragged tasks in one pass == each task alone (meta-test predictions and summed hypergradient)."""
+    from adkf_ift_b200 import dkt, synthetic, task_batch
+    from adkf_ift_b200.adaptive_dkt import ADKTModelTrainerConfig
+    from adkf_ift_b200.adaptive_dkt_utils import ADKTModelTrainer, run_on_task_batch
+    from adkf_ift_b200.feature_extractor import cli_default_config
+    cfg = ADKTModelTrainerConfig(graph_feature_extractor_config=cli_default_config(3))
+    model = ADKTModelTrainer(cfg)
+    synthetic.deterministic_init_(model, seed=1, alpha=0.5)
+    model.to(cuda_device)
+    sizes = [(16, 24), (32, 10), (20, 33)]
+    hosts = [dkt.task_sample_to_dkt_task_sample(synthetic.make_task_sample(40 + i, ns, nq),
+                                                dkt.get_dkt_batcher(max_num_graphs=320), False).batches[0]
+             for i, (ns, nq) in enumerate(sizes)]
+    tb_all = task_batch.to_device(task_batch.collate_tasks(hosts, False), cuda_device)
+    res_all = run_on_task_batch(model, tb_all, train=False)
+    model.zero_grad(set_to_none=True)
+    tr_all = run_on_task_batch(model, tb_all, train=True)
+    g_all = {n: p.grad.clone() for n, p in model.named_parameters() if p.grad is not None}
+    acc = None
+    off = 0
+    for i, h in enumerate(hosts):
+        tb = task_batch.to_device(task_batch.collate_tasks([h], False), cuda_device)
+        r = run_on_task_batch(model, tb, train=False)
+        ns, nq = sizes[i]
+        a = res_all.mean[off + ns: off + ns + nq].cpu().numpy()
+        assert rel(a, r.mean[ns:].cpu().numpy()) < 1e-4
+        assert rel(res_all.phi[i].cpu().numpy(), r.phi[0].cpu().numpy()) < 1e-4
+        model.zero_grad(set_to_none=True)
+        run_on_task_batch(model, tb, train=True, grad_scale=1.0 / len(hosts))
+        cur = {n: p.grad.clone() for n, p in model.named_parameters() if p.grad is not None}
+        acc = cur if acc is None else {n: acc[n] + cur[n] for n in acc}
+        off += ns + nq
+    # tensors whose true gradient is 0 (fc.2.bias: distances are shift-invariant; mp_norm_layer: unused) hold only
+    # rounding noise, so the error of every tensor is measured against max(own norm, 1e-4 x largest norm)
+    top = max(float(acc[n].norm()) for n in acc)
+    worst = max(float((g_all[n] - acc[n]).norm() / max(float(acc[n].norm()), 1e-4 * top)) for n in acc)
+    print("batched vs per-task summed hypergradient: worst rel l2", worst)
+    assert worst < 2e-3
+
+
+def test_single_task_surface(cuda_device, golden_dir):
+    """The reference's call sequence on ADKTModel (run_on_batches) + first-order autograd of the functional
+    losses, on the T=1 kernels."""
+    from adkf_ift_b200 import dkt
+    from adkf_ift_b200.adaptive_dkt_utils import run_on_batches
+    g, model, host, tb = build(golden_dir, "c1_classification", "matern", cuda_device)
+    dev = dkt.torchify(host, cuda_device)
+    preds, labels = run_on_batches(model, dev.batches, dev.batch_labels, dev.batch_numeric_labels, train=False)
+    ref = 1.0 / (1.0 + np.exp(-g["test_mean"].astype(np.float64)))
+    assert rel(preds, ref) < 2e-3
+    assert np.abs(np.array([p.item() for p in model.gp_params()]) - g["test_phi_star"]).max() < 2e-3
+    # functional losses: value + first-order gradients w.r.t. phi at the fitted optimum
+    model.train()
+    batch = dev.batches[0]
+    f = model(batch, train_loss=True, is_functional_call=True)
+    gphi = torch.autograd.grad(f, model.gp_params(), allow_unused=True)
+    assert max(abs(float(x)) for x in gphi) < 1e-4           # stationary point of the inner loss
+    F = model(batch, train_loss=False, predictive_val_loss=True, is_functional_call=True)
+    assert abs(float(F) - float(g["train_F"])) < 3e-3 * abs(float(g["train_F"]))
+    dF = torch.autograd.grad(F, model.gp_params())
+    assert rel(np.array([float(x) for x in dF]), g["train_dF_dphi"]) < 2e-2
+    model.eval()
+    with torch.no_grad():
+        mvn = model(batch, train_loss=None)
+    yq = (batch.query_labels.float() - 0.5) * 2.0
+    assert abs(float(-mvn.log_prob(yq)) - float(F)) < 1e-4 * abs(float(F))
