@@ -22,7 +22,9 @@ import torch
 
 from . import gp as gpk
 from . import ops
+from . import distributed
 from .adaptive_dkt import ADKTModel, ADKTModelTrainerConfig
+from .distributed import FlatParams
 from .task_batch import DeviceTaskBatch, HostTaskBatch, collate_tasks, to_device
 
 
@@ -130,34 +132,6 @@ def run_on_batches(model: ADKTModel, batches: Sequence, batch_labels: Sequence, 
 # ----------------------------------------------------------------------------------------------------------
 # trainer
 # ----------------------------------------------------------------------------------------------------------
-class FlatParams:
-    """Feature-extractor parameters and gradients as views of two flat fp32 buffers, so that the NCCL
-    all-reduce, the gradient-norm clip and Adam each touch ONE contiguous 101 MB array."""
-
-    def __init__(self, params: List[torch.nn.Parameter]):
-        self.params = params
-        self.sizes = [p.numel() for p in params]
-        total = sum(self.sizes)
-        dev = params[0].device
-        self.total = total
-        self.flat = torch.empty(total, dtype=torch.float32, device=dev)
-        self.grad = torch.zeros(total, dtype=torch.float32, device=dev)
-        off = 0
-        for p, n in zip(params, self.sizes):
-            self.flat[off:off + n].copy_(p.data.reshape(-1))
-            p.data = self.flat[off:off + n].view_as(p.data)
-            p.grad = self.grad[off:off + n].view_as(p.data)
-            off += n
-
-    def zero_grad(self):
-        self.grad.zero_()
-        off = 0
-        for p, n in zip(self.params, self.sizes):   # re-attach views if something replaced .grad
-            if p.grad is None or p.grad.data_ptr() != self.grad[off:off + n].data_ptr():
-                p.grad = self.grad[off:off + n].view_as(p.data)
-            off += n
-
-
 class ADKTModelTrainer(ADKTModel):
     def __init__(self, config: ADKTModelTrainerConfig):
         super().__init__(config)
@@ -208,28 +182,31 @@ class ADKTModelTrainer(ADKTModel):
         return model
 
     # ---- one outer step -------------------------------------------------------------------------------
-    def _ensure_flat(self):
+    def _ensure_flat(self) -> FlatParams:
         if self._flat is None:
-            self._flat = FlatParams(self.feature_extractor_params())
-            self.optimizer = torch.optim.Adam(self.feature_extractor_params(), self.config.learning_rate, fused=True)
+            params = self.feature_extractor_params()
+            self._flat = FlatParams(params)
+            self.optimizer = torch.optim.Adam(params, self.config.learning_rate, fused=params[0].is_cuda)
         return self._flat
+
+    def reduce_and_update(self):
+        """All-reduce (sum) of the flat meta-gradient over the ranks, then clip + Adam -- identical on every rank, so
+        the replicas stay bit-identical (adaptive_dkt_utils.py:406-413)."""
+        flat = self._ensure_flat()
+        distributed.allreduce_sum_(flat.grad)
+        if self.config.clip_value is not None:
+            flat.clip_(self.config.clip_value)
+        self.optimizer.step()
+        if self.lr_scheduler is not None:
+            self.lr_scheduler.step()
+        self._step += 1
 
     def train_step(self, tb: DeviceTaskBatch, global_num_tasks: Optional[int] = None) -> TaskBatchResult:
         """One outer step on this rank's share of the meta-batch (adaptive_dkt_utils.py:352-413): hypergradients of
         the local tasks / global task count, all-reduce, clip, Adam."""
         flat = self._ensure_flat()
         flat.zero_grad()
-        world = torch.distributed.get_world_size() if torch.distributed.is_initialized() else 1
-        total_tasks = global_num_tasks if global_num_tasks is not None else tb.num_tasks * world
-        res = run_on_task_batch(self, tb, train=True, grad_scale=1.0 / total_tasks)
-        if world > 1:
-            torch.distributed.all_reduce(flat.grad, op=torch.distributed.ReduceOp.SUM)
-        if self.config.clip_value is not None:
-            # clip_grad_norm_ on the flat buffer: same global 2-norm, one reduction, no host sync
-            norm = torch.linalg.vector_norm(flat.grad)
-            flat.grad.mul_(torch.clamp(self.config.clip_value / (norm + 1e-6), max=1.0))
-        self.optimizer.step()
-        if self.lr_scheduler is not None:
-            self.lr_scheduler.step()
-        self._step += 1
+        total = global_num_tasks if global_num_tasks is not None else tb.num_tasks * distributed.world_size()
+        res = run_on_task_batch(self, tb, train=True, grad_scale=1.0 / total)
+        self.reduce_and_update()
         return res

@@ -1,0 +1,135 @@
+"""Host-side logic on CPU: graph collation (bit-exact vs the reference's own batcher output), support/query DKT
+batching incl. regression label standardisation, multi-task collation, model surface / state-dict names,
+checkpoint loading."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from adkf_ift_b200 import dkt, synthetic, task_batch
+from adkf_ift_b200.adaptive_dkt import ADKTModelTrainerConfig
+from adkf_ift_b200.adaptive_dkt_utils import ADKTModelTrainer
+from adkf_ift_b200.feature_extractor import GNNConfig, GraphFeatureExtractorConfig, cli_default_config
+
+
+def test_batcher_bit_exact_vs_reference(golden_dir):
+    """fsmol_batcher.py:174-218 + dkt.py:84-138 run unmodified in the authoring container -> batcher.npz."""
+    g = np.load(os.path.join(golden_dir, "batcher.npz"))
+    task_id, n_s, n_q, max_graphs = (int(x) for x in g["meta"])
+    ts = synthetic.make_task_sample(task_id, n_s, n_q)
+    host = dkt.task_sample_to_dkt_task_sample(ts, dkt.get_dkt_batcher(max_num_graphs=max_graphs), True)
+    assert len(host.batches) == int(g["num_batches"]) == 2     # query split into two batches
+    for bi, b in enumerate(host.batches):
+        for side in ("support", "query"):
+            f = getattr(b, side + "_features")
+            for t in range(3):
+                a = f.adjacency_lists[t]
+                assert a.dtype == np.int64 and np.array_equal(a, g[f"b{bi}_{side}_adj{t}"])
+                assert np.array_equal(np.concatenate([a, a[:, ::-1]], 0), g[f"b{bi}_{side}_bidir{t}"])
+            assert np.array_equal(f.node_to_graph, g[f"b{bi}_{side}_node_to_graph"])
+            assert [f.num_graphs, f.num_nodes, f.num_edges] == list(g[f"b{bi}_{side}_counts"])
+            assert np.array_equal(f.node_features, g[f"b{bi}_{side}_node_features"])
+            assert np.array_equal(f.fingerprints, g[f"b{bi}_{side}_fingerprints"])
+            assert np.array_equal(getattr(b, side + "_labels"), g[f"b{bi}_{side}_labels"])
+            # regression labels: log(y) standardised with the SUPPORT mean / population std (dkt.py:91-95,110-113)
+            assert np.array_equal(getattr(b, side + "_numeric_labels"), g[f"b{bi}_{side}_numeric_labels"])
+
+
+def test_trailing_single_graph_batch_is_dropped():
+    ts = synthetic.make_task_sample(1, 4, 7)       # 7 query graphs, budget 3 per batch -> 3 + 3 + (1 dropped)
+    host = dkt.task_sample_to_dkt_task_sample(ts, dkt.get_dkt_batcher(max_num_graphs=7), False)
+    assert [b.query_features.num_graphs for b in host.batches] == [3, 3]
+    with pytest.raises(ValueError):
+        dkt.task_sample_to_dkt_task_sample(ts, dkt.get_dkt_batcher(max_num_graphs=3), False)  # support does not fit
+
+
+def test_multi_task_collation_layout():
+    sizes = [(5, 9), (8, 3), (4, 4)]
+    hosts = [dkt.task_sample_to_dkt_task_sample(synthetic.make_task_sample(10 + i, a, b),
+                                                dkt.get_dkt_batcher(max_num_graphs=64), False).batches[0]
+             for i, (a, b) in enumerate(sizes)]
+    hb = task_batch.collate_tasks(hosts, False, pin=False)
+    assert hb.n_sup == [5, 8, 4] and hb.n_query == [9, 3, 4] and hb.num_graphs == 33
+    n2g = hb.node_to_graph.numpy()
+    assert np.all(np.diff(n2g) >= 0) and n2g[-1] == 32 and len(n2g) == hb.num_nodes
+    # graph r of the merged batch == the r-th graph in (task0 support, task0 query, task1 support, ...) order
+    g_off = v_off = 0
+    fps = []
+    for h in hosts:
+        for f in (h.support_features, h.query_features):
+            for t in range(3):
+                rows = (hb.adjacency[t].numpy() >= v_off).all(1) & (hb.adjacency[t].numpy() < v_off + f.num_nodes).all(1)
+                assert np.array_equal(hb.adjacency[t].numpy()[rows] - v_off, f.adjacency_lists[t])
+            assert np.array_equal(n2g[v_off:v_off + f.num_nodes] - g_off, f.node_to_graph)
+            fps.append(f.fingerprints)
+            g_off += f.num_graphs
+            v_off += f.num_nodes
+    assert np.array_equal(hb.fingerprints.numpy(), np.concatenate(fps))
+    want = np.concatenate([np.concatenate([h.support_labels, h.query_labels]) for h in hosts])
+    assert np.array_equal(hb.labels.numpy(), (want.astype(np.float32) - 0.5) * 2)
+    assert hb.fingerprints.dtype == torch.int32 and hb.adjacency[0].dtype == torch.int64
+    # edges never cross graphs
+    for t in range(3):
+        a = hb.adjacency[t].numpy()
+        assert np.array_equal(n2g[a[:, 0]], n2g[a[:, 1]])
+
+
+def test_model_surface_and_state_dict_names(golden_dir):
+    g = np.load(os.path.join(golden_dir, "c1_classification.npz"))
+    model = ADKTModelTrainer(ADKTModelTrainerConfig())
+    fe = [n for n, _ in model.named_parameters() if not n.startswith("gp_")]
+    assert fe == [str(x) for x in g["grad_names"]]          # reference registration order, 375 tensors
+    assert sum(p.numel() for p in model.feature_extractor_params()) == 25_336_354
+    assert [n for n, _ in model.named_parameters() if n.startswith("gp_")] == [
+        "gp_likelihood.noise_covar.raw_noise", "gp_model.covar_module.raw_outputscale",
+        "gp_model.covar_module.base_kernel.raw_lengthscale"]
+    assert [tuple(p.shape) for p in model.gp_params()] == [(1,), (), (1, 1)]
+    sd = model.state_dict()
+    assert sd["graph_feature_extractor.gnn.gnn_blocks.0.mp_layers.0.message_fns.0._layers.0.weight"].shape == (192, 64)
+    assert sd["graph_feature_extractor.gnn.gnn_blocks.9.mp_norm_layer.weight"].shape == (128,)   # unused, kept
+    assert sd["fc.0.weight"].shape == (2048, 2560) and sd["fc.2.weight"].shape == (2048, 2048)
+    assert abs(float(model.gp_likelihood.noise) - 0.1) < 1e-6                       # gp_utils.py:16-17
+    assert abs(float(model.gp_model.covar_module.outputscale) - np.log(2.0)) < 1e-6  # softplus(0)
+    for attr in ("config", "use_fc", "fc", "fc_out_dim", "gp_likelihood", "gp_model", "mll", "normalizing_features"):
+        assert hasattr(model, attr)
+
+
+def test_unsupported_configurations_fail_loudly():
+    with pytest.raises(NotImplementedError):
+        ADKTModelTrainer(ADKTModelTrainerConfig(gp_kernel="cossim"))
+    with pytest.raises(NotImplementedError):
+        ADKTModelTrainer(ADKTModelTrainerConfig(use_ard=True))
+    with pytest.raises(NotImplementedError):
+        ADKTModelTrainer(ADKTModelTrainerConfig(graph_feature_extractor_config=GraphFeatureExtractorConfig(
+            gnn_config=GNNConfig(type="MultiHeadAttention", per_head_dim=64, intermediate_dim=1024, num_layers=2))))
+
+
+def test_checkpoint_roundtrip_and_reference_gp_keys(tmp_path):
+    cfg = ADKTModelTrainerConfig(graph_feature_extractor_config=cli_default_config(1))
+    a = ADKTModelTrainer(cfg)
+    synthetic.deterministic_init_(a, seed=3)
+    path = str(tmp_path / "best_validation.pt")
+    a.save_model(path)
+    # a reference checkpoint additionally carries gpytorch's own entries: tolerated and skipped
+    ck = torch.load(path, weights_only=False)
+    ck["model_state_dict"]["mll.likelihood.noise_covar.raw_noise"] = torch.zeros(1)
+    ck["model_state_dict"]["gp_model.likelihood.noise_covar.noise_prior.loc"] = torch.zeros(())
+    torch.save(ck, path)
+    b = ADKTModelTrainer.build_from_model_file(path)
+    for (n1, p1), (n2, p2) in zip(a.named_parameters(), b.named_parameters()):
+        assert n1 == n2 and torch.equal(p1, p2)
+    ck["model_state_dict"]["fc.9.weight"] = torch.zeros(3)
+    torch.save(ck, path)
+    with pytest.raises(KeyError):
+        ADKTModelTrainer.build_from_model_file(path)
+
+
+def test_synthetic_tasks_are_deterministic_and_well_formed():
+    a, b = synthetic.make_task_sample(7, 16, 32), synthetic.make_task_sample(7, 16, 32)
+    assert all(np.array_equal(x.fingerprint, y.fingerprint) for x, y in zip(a.train_samples, b.train_samples))
+    labels = [m.bool_label for m in a.train_samples]
+    assert any(labels) and not all(labels)
+    m = a.test_samples[0]
+    assert m.graph.node_features.shape[1] == 32 and m.fingerprint.dtype == np.int32 and m.fingerprint.shape == (2048,)
+    assert 8 <= len(m.graph.node_features) <= 60 and len(m.graph.adjacency_lists) == 3
