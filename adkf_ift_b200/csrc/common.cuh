@@ -56,6 +56,10 @@ __device__ __forceinline__ void block_sum_multi(const float (&part)[K], double* 
     __syncthreads();
 }
 
+// gram.cu: mu[t][:] = mean of the support rows, nrm[row] = |z_row - mu_t|^2 (two launches on `s`)
+void launch_center_stats(const float* Z, int d, int T, const int32_t* z_off, const int32_t* n_sup, int max_n,
+                         float* mu_ws, float* nrm_ws, cudaStream_t s);
+
 __device__ __forceinline__ float softplusf(float x) { return (x > 20.f) ? x : log1pf(expf(x)); }
 __device__ __forceinline__ float sigmoidf_(float x) { return 1.f / (1.f + expf(-x)); }
 

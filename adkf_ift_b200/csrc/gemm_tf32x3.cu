@@ -1,0 +1,458 @@
+// gemm_tf32x3.cu -- fp32-accurate GEMM on the 5th-generation tensor cores (sm_100a): tcgen05.mma kind::tf32 with the
+// 3xTF32 error-compensated split, operands staged by TMA, accumulator in TMEM.
+//
+//   D[M,N] = A[M,K] . B[N,K]^T          (both operands K-major, fp32 in HBM)
+//
+// Used for
+//   (1) the per-task Gram / squared-distance matrix of the GP inputs (gpytorch sq_dist inside MaternKernel / RBFKernel,
+//       call sites fs_mol/utils/gp_utils.py:28,31): A = B = Z_task - mean(support rows), epilogue
+//       D2 = |a|^2 + |b|^2 - 2 a.b, clamp_min(0), exact zero diagonal -- "the one dense contraction that goes on tensor
+//       cores" of the north star;
+//   (2) the dense layers of the extractor forward, y = act(x W^T + b) (nn.Linear in fs_mol/modules/gnn.py:79-95,
+//       477-515, graph_readout.py:224-259, fs_mol/models/adaptive_dkt.py:61-65).
+//
+// Why 3xTF32: the parity target is 1e-4 relative on GP outputs at d = 2048 (SURVEY section 7 hard part (b)); a single TF32
+// pass carries 2^-11 per operand.  Each fp32 value v is split as hi = rna_tf32(v), lo = v - hi (exact in fp32), and
+// a.b ~ hi.hi + lo.hi + hi.lo (fp32 accumulation in TMEM), which leaves ~2^-21 per product -- fp32-class accuracy at a third
+// of the TF32 rate.
+//
+// The tensor core adds into its fp32 accumulator with round-toward-zero (measured here: a 1408-long contraction kept in
+// ONE TMEM accumulator comes out 1e-5 low, biased toward zero, growing linearly with K).  So the accumulation is split:
+//   * the dominant hi.hi products go to a double-buffered TMEM accumulator that is DRAINED every kGroup k-blocks
+//     (16 MMAs) into fp32 registers with ordinary round-to-nearest adds (bias <~ 6e-7);
+//   * the two correction products lo.hi + hi.lo are 2^-11 smaller and stay in a third accumulator until the end.
+//
+// CTA = one 128 x 128 output tile, 16 warps:
+//   warp 0     TMA producer      cp.async.bulk.tensor.2d (SWIZZLE_128B boxes of 128 rows x 32 floats) -> smem ring, 3 stages
+//   warp 1     MMA issuer        one elected lane: 4 k-steps x 3 tcgen05.mma per stage, tcgen05.commit frees the stage
+//   warp 2     TMEM allocator    512 columns: big[2] x 128, small x 128
+//   warps 4-7  splitter          hi/lo split of the landed tiles in place (generic proxy -> fence.proxy.async)
+//   warps 8-15 drain + epilogue  tcgen05.ld of the accumulator rows (warp w owns TMEM lanes 32(w%4).., 64 columns each),
+//              RN accumulation in registers, fused epilogue, stores.
+// Every mbarrier wait is bounded (trap after ~2^28 polls) so that a protocol bug cannot hang the device.
+#include <cuda.h>
+#include "common.cuh"
+#include "../../include/adkf_b200.h"
+
+namespace adkf {
+
+constexpr int kBM = 128, kBN = 128, kBK = 32;        // tile; 32 floats = 128 B = one swizzle row
+constexpr int kStages = 3;
+constexpr int kTileBytes = kBM * kBK * 4;            // 16 KB
+constexpr int kStageBytes = 4 * kTileBytes;          // A_hi, B_hi, A_lo, B_lo
+constexpr int kGemmThreads = 512;
+constexpr int kTmemCols = 512;                       // big[0], big[1], small (128 fp32 columns each); power of two
+constexpr int kGroup = 4;                            // k-blocks accumulated in TMEM between two drains
+constexpr size_t kGemmSmem = (size_t)kStages * kStageBytes + 1024 /*align*/ + 256 /*barriers*/;
+
+// ---- PTX wrappers ---------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+    uint32_t done = 0, spins = 0;
+    while (true) {
+        asm volatile(
+            "{\n\t.reg .pred p;\n\t"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+            "selp.u32 %0, 1, 0, p;\n\t}"
+            : "=r"(done)
+            : "r"(bar), "r"(parity)
+            : "memory");
+        if (done) break;
+        if (++spins > (1u << 28)) __trap();   // never hang the GPU on a protocol error
+    }
+}
+__device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map, uint32_t bar, int c0, int c1) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+        ::"r"(dst), "l"(reinterpret_cast<uint64_t>(map)), "r"(bar), "r"(c0), "r"(c1)
+        : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+
+__device__ __forceinline__ void umma_tf32(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t acc) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}"
+        ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(acc)
+        : "memory");
+}
+__device__ __forceinline__ void umma_commit(uint32_t bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, float (&v)[16]) {
+    uint32_t r[16];
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+          "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+        : "r"(taddr)
+        : "memory");
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+    for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]);
+}
+
+// K-major, SWIZZLE_128B shared-memory matrix descriptor (cute::UMMA::SmemDescriptor): start address >> 4, leading byte
+// offset 1 (unused for swizzled K-major), stride byte offset 1024 B (one 8-row swizzle atom), version 1, layout 2.
+__device__ __forceinline__ uint64_t smem_desc_k128(uint32_t addr) {
+    return (uint64_t)((addr >> 4) & 0x3FFF) | (1ull << 16) | ((uint64_t)(1024 >> 4) << 32) | (1ull << 46) | (2ull << 61);
+}
+// instruction descriptor: D = f32 (1<<4), A = B = tf32 (2<<7, 2<<10), both K-major, N>>3 at bit 17, M>>4 at bit 24
+constexpr uint32_t kIdescTf32 = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(kBN >> 3) << 17) | ((uint32_t)(kBM >> 4) << 24);
+
+__device__ __forceinline__ uint32_t rna_tf32(float x) {
+    uint32_t u;
+    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(u) : "f"(x));
+    return u;
+}
+
+struct GemmEpilogue {
+    // mode 0: Y = act(acc + bias)       mode 1: per-task squared distances
+    int mode;
+    float* out;
+    int64_t ldo;
+    int64_t M;
+    int N, K;
+    const float* bias;
+    int act;              // 0 none, 1 relu, 2 leaky_relu(0.01)
+    // gram
+    const int32_t* z_off;
+    const int32_t* n_sup;
+    const int64_t* d2_off;
+    const float* mu;      // [T, d]
+    const float* nrm;     // [rows]
+    int qq_block;
+};
+
+__global__ void __launch_bounds__(kGemmThreads, 1)
+gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, GemmEpilogue ep) {
+    extern __shared__ unsigned char smem_raw[];
+    const uint32_t raw = smem_u32(smem_raw);
+    const uint32_t base = (raw + 1023u) & ~1023u;                  // SWIZZLE_128B tiles need 1024 B alignment
+    unsigned char* base_ptr = smem_raw + (base - raw);
+    const uint32_t bars = base + kStages * kStageBytes;            // full[S], conv[S], empty[S], accum, tmem slot
+    auto full_bar = [&](int s) { return bars + 8u * s; };
+    auto conv_bar = [&](int s) { return bars + 8u * (kStages + s); };
+    auto empty_bar = [&](int s) { return bars + 8u * (2 * kStages + s); };
+    auto accfull_bar = [&](int b) { return bars + 8u * (3 * kStages + b); };
+    auto accempty_bar = [&](int b) { return bars + 8u * (3 * kStages + 2 + b); };
+    volatile uint32_t* tmem_slot = reinterpret_cast<volatile uint32_t*>(base_ptr + kStages * kStageBytes + 8 * (3 * kStages + 4));
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+    // ---- tile coordinates ---------------------------------------------------------------------------------
+    int rowA0, rowB0, task = 0, Nt = 0, nsup = 0;
+    if (ep.mode == 1) {
+        task = blockIdx.z;
+        const int r0 = ep.z_off[task];
+        Nt = ep.z_off[task + 1] - r0;
+        nsup = ep.n_sup[task];
+        const int ti = blockIdx.y, tj = blockIdx.x;
+        if (tj > ti || ti * kBM >= Nt) return;                       // symmetric: lower tiles only (uniform exit)
+        if (!ep.qq_block && tj * kBN >= nsup) return;                // query x query block not needed for meta-test
+        rowA0 = r0 + ti * kBM;
+        rowB0 = r0 + tj * kBN;
+    } else {
+        rowA0 = blockIdx.y * kBM;
+        rowB0 = blockIdx.x * kBN;
+    }
+    const int nk = (ep.K + kBK - 1) / kBK;
+
+    // ---- one-time setup -----------------------------------------------------------------------------------
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < kStages; ++s) {
+            mbar_init(full_bar(s), 1);
+            mbar_init(conv_bar(s), 4);      // one arrive per splitter warp
+            mbar_init(empty_bar(s), 1);
+        }
+        for (int b = 0; b < 2; ++b) {
+            mbar_init(accfull_bar(b), 1);
+            mbar_init(accempty_bar(b), 8);  // one arrive per drain warp
+        }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 2) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32((const void*)tmem_slot)),
+                     "n"(kTmemCols)
+                     : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_acc = *tmem_slot;
+
+    if (warp == 0) {
+        // ===== TMA producer =====
+        if (lane == 0) {
+            for (int kb = 0; kb < nk; ++kb) {
+                const int s = kb % kStages;
+                const uint32_t ph = (kb / kStages) & 1;
+                mbar_wait(empty_bar(s), ph ^ 1);
+                mbar_expect_tx(full_bar(s), 2 * kTileBytes);
+                const uint32_t st = base + s * kStageBytes;
+                tma_load_2d(st, &tmA, full_bar(s), kb * kBK, rowA0);
+                tma_load_2d(st + kTileBytes, &tmB, full_bar(s), kb * kBK, rowB0);
+            }
+        }
+    } else if (warp == 1) {
+        // ===== MMA issuer =====
+        const int ngroups = (nk + kGroup - 1) / kGroup;
+        for (int kb = 0; kb < nk; ++kb) {
+            const int s = kb % kStages;
+            const uint32_t ph = (kb / kStages) & 1;
+            const int g = kb / kGroup, b = g & 1;
+            const bool group_first = (kb % kGroup) == 0;
+            const bool group_last = (kb % kGroup) == kGroup - 1 || kb == nk - 1;
+            if (group_first) mbar_wait(accempty_bar(b), ((g >> 1) & 1) ^ 1);   // drained two groups ago
+            mbar_wait(conv_bar(s), ph);
+            tc_fence_after();
+            if (lane == 0) {
+                const uint32_t st = base + s * kStageBytes;
+                const uint64_t a_hi = smem_desc_k128(st), b_hi = smem_desc_k128(st + kTileBytes);
+                const uint64_t a_lo = smem_desc_k128(st + 2 * kTileBytes), b_lo = smem_desc_k128(st + 3 * kTileBytes);
+                const uint32_t acc_big = tmem_acc + (uint32_t)(b * kBN), acc_small = tmem_acc + 2u * kBN;
+#pragma unroll
+                for (int k = 0; k < kBK / 8; ++k) {                   // UMMA_K = 8 tf32 = 32 B = +2 in the address field
+                    const uint64_t adv = (uint64_t)(2 * k);
+                    umma_tf32(acc_small, a_lo + adv, b_hi + adv, kIdescTf32, (kb | k) ? 1u : 0u);
+                    umma_tf32(acc_small, a_hi + adv, b_lo + adv, kIdescTf32, 1u);
+                    umma_tf32(acc_big, a_hi + adv, b_hi + adv, kIdescTf32, (group_first && k == 0) ? 0u : 1u);
+                }
+                umma_commit(empty_bar(s));                             // frees the stage when these MMAs retire
+                if (group_last) umma_commit(accfull_bar(b));
+            }
+            __syncwarp();
+        }
+        (void)ngroups;
+    } else if (warp >= 4 && warp < 8) {
+        // ===== splitter (hi/lo) =====
+        const int t = threadIdx.x - 128;                               // 0..127
+        const int chunk = (t & 7) ^ ((t >> 3) & 7);                    // logical 16 B chunk of this thread's float4 (see header)
+        for (int kb = 0; kb < nk; ++kb) {
+            const int s = kb % kStages;
+            const uint32_t ph = (kb / kStages) & 1;
+            float4 mu4 = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (ep.mode == 1) {
+                const int k = kb * kBK + chunk * 4;
+                if (k + 3 < ep.K) mu4 = *reinterpret_cast<const float4*>(ep.mu + (size_t)task * ep.K + k);
+            }
+            mbar_wait(full_bar(s), ph);
+            float4* tile = reinterpret_cast<float4*>(base_ptr + (size_t)s * kStageBytes);
+            float4* tile_lo = tile + 2 * (kTileBytes / 16);
+#pragma unroll 4
+            for (int i = 0; i < 2 * (kTileBytes / 16) / 128; ++i) {   // A then B: 2048 float4 / 128 threads = 16
+                const int p = i * 128 + t;
+                float4 v = tile[p];
+                v.x -= mu4.x; v.y -= mu4.y; v.z -= mu4.z; v.w -= mu4.w;
+                float4 hi, lo;
+                hi.x = __uint_as_float(rna_tf32(v.x)); lo.x = v.x - hi.x;
+                hi.y = __uint_as_float(rna_tf32(v.y)); lo.y = v.y - hi.y;
+                hi.z = __uint_as_float(rna_tf32(v.z)); lo.z = v.z - hi.z;
+                hi.w = __uint_as_float(rna_tf32(v.w)); lo.w = v.w - hi.w;
+                tile[p] = hi;
+                tile_lo[p] = lo;
+            }
+            fence_async_smem();                                        // generic-proxy writes -> visible to the MMA (async proxy)
+            __syncwarp();
+            if (lane == 0) mbar_arrive(conv_bar(s));
+        }
+    } else if (warp >= 8) {
+        // ===== drain (RN accumulation of the TMEM partial sums in registers), then epilogue =====
+        const int q = warp & 3;                                        // TMEM lane quarter this warp may access
+        const int half = (warp - 8) >> 2;                              // which 64 accumulator columns
+        const int r_local = q * 32 + lane;
+        const uint32_t trow = tmem_acc + ((uint32_t)(q * 32) << 16) + (uint32_t)(half * 64);
+        float acc[64];
+#pragma unroll
+        for (int j = 0; j < 64; ++j) acc[j] = 0.f;
+        const int ngroups = (nk + kGroup - 1) / kGroup;
+        for (int g = 0; g < ngroups; ++g) {
+            const int b = g & 1;
+            mbar_wait(accfull_bar(b), (g >> 1) & 1);
+            tc_fence_after();
+#pragma unroll
+            for (int c0 = 0; c0 < 64; c0 += 16) {
+                float v[16];
+                tmem_ld16(trow + (uint32_t)(b * kBN) + c0, v);
+#pragma unroll
+                for (int j = 0; j < 16; ++j) acc[c0 + j] += v[j];
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(accempty_bar(b));
+        }
+#pragma unroll
+        for (int c0 = 0; c0 < 64; c0 += 16) {                          // the small correction accumulator, once
+            float v[16];
+            tmem_ld16(trow + 2u * kBN + c0, v);
+#pragma unroll
+            for (int j = 0; j < 16; ++j) acc[c0 + j] += v[j];
+        }
+        const int colbase = half * 64;
+        if (ep.mode == 0) {
+            const int64_t r = (int64_t)rowA0 + r_local;
+            float* orow = ep.out + r * ep.ldo;
+            const bool vec_ok = (ep.ldo % 4 == 0) && ((reinterpret_cast<uintptr_t>(ep.out) & 15) == 0);
+#pragma unroll
+            for (int c0 = 0; c0 < 64; c0 += 16) {
+                float v[16];
+#pragma unroll
+                for (int j = 0; j < 16; ++j) v[j] = acc[c0 + j];
+                const int col0 = rowB0 + colbase + c0;
+                if (r < ep.M && col0 < ep.N) {
+#pragma unroll
+                    for (int j = 0; j < 16; ++j) {
+                        float x = v[j];
+                        if (ep.bias != nullptr && col0 + j < ep.N) x += ep.bias[col0 + j];
+                        if (ep.act == 1) x = fmaxf(x, 0.f);
+                        else if (ep.act == 2) x = (x > 0.f) ? x : 0.01f * x;
+                        v[j] = x;
+                    }
+                    if (vec_ok && col0 + 16 <= ep.N) {
+#pragma unroll
+                        for (int j = 0; j < 16; j += 4)
+                            *reinterpret_cast<float4*>(orow + col0 + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+                    } else {
+#pragma unroll
+                        for (int j = 0; j < 16; ++j)
+                            if (col0 + j < ep.N) orow[col0 + j] = v[j];
+                    }
+                }
+            }
+        } else {
+            const int r0 = ep.z_off[task];
+            const int ti = blockIdx.y, tj = blockIdx.x;
+            const int r = ti * kBM + r_local;                          // row inside the task
+            float* Dt = ep.out + ep.d2_off[task];
+            const float ni = (r < Nt) ? ep.nrm[r0 + r] : 0.f;
+#pragma unroll
+            for (int c0 = 0; c0 < 64; c0 += 16) {
+                float v[16];
+#pragma unroll
+                for (int j = 0; j < 16; ++j) v[j] = acc[c0 + j];
+                if (r < Nt) {
+#pragma unroll
+                    for (int j = 0; j < 16; ++j) {
+                        const int c = tj * kBN + colbase + c0 + j;
+                        if (c < Nt && (ti != tj || c <= r)) {
+                            float d = fmaxf(ni + ep.nrm[r0 + c] - 2.f * v[j], 0.f);
+                            if (r == c) d = 0.f;
+                            Dt[(size_t)r * Nt + c] = d;
+                            Dt[(size_t)c * Nt + r] = d;
+                        }
+                    }
+                }
+            }
+        }
+        tc_fence_before();
+    }
+
+    __syncthreads();
+    if (warp == 2) {
+        tc_fence_after();
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_acc), "n"(kTmemCols) : "memory");
+    }
+}
+
+}  // namespace adkf
+
+using namespace adkf;
+
+// ---- host: tensor maps through the driver entry point (no link-time dependency on libcuda) --------------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn encode_fn() {
+    static EncodeTiledFn fn = nullptr;
+    if (fn == nullptr) {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult qres;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres) == cudaSuccess &&
+            qres == cudaDriverEntryPointSuccess)
+            fn = reinterpret_cast<EncodeTiledFn>(p);
+    }
+    return fn;
+}
+
+// row-major [rows, cols] fp32 matrix with leading dimension ld (floats); box = 32 floats x 128 rows, 128 B swizzle
+static int make_map_2d(CUtensorMap* map, const float* ptr, int64_t rows, int64_t cols, int64_t ld) {
+    EncodeTiledFn fn = encode_fn();
+    if (fn == nullptr) return (int)cudaErrorNotSupported;
+    if ((reinterpret_cast<uintptr_t>(ptr) & 15) || (ld * 4) % 16) return ADKF_ERR_BADARG;
+    const cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+    const cuuint64_t strides[1] = {(cuuint64_t)ld * 4};
+    const cuuint32_t box[2] = {(cuuint32_t)kBK, (cuuint32_t)kBM};
+    const cuuint32_t estr[2] = {1, 1};
+    CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(ptr), dims, strides, box, estr,
+                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    return r == CUDA_SUCCESS ? 0 : (int)cudaErrorInvalidValue;
+}
+
+static int gemm_attr() {
+    static bool done = false;
+    if (!done) {
+        cudaError_t e = cudaFuncSetAttribute((const void*)gemm_tf32x3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                             (int)kGemmSmem);
+        if (e != cudaSuccess) return (int)e;
+        done = true;
+    }
+    return 0;
+}
+
+extern "C" int adkf_linear_tf32x3(const float* X, int64_t M, int32_t K, int64_t ldx, const float* W, int32_t N,
+                                  int64_t ldw, const float* bias, int32_t act, float* Y, int64_t ldy, void* stream) {
+    if (M <= 0 || N <= 0) return 0;
+    if (!X || !W || !Y || K <= 0 || act < 0 || act > 2) return ADKF_ERR_BADARG;
+    CUtensorMap ma, mb;
+    int rc = make_map_2d(&ma, X, M, K, ldx);
+    if (rc) return rc;
+    rc = make_map_2d(&mb, W, N, K, ldw);
+    if (rc) return rc;
+    rc = gemm_attr();
+    if (rc) return rc;
+    GemmEpilogue ep = {};
+    ep.mode = 0; ep.out = Y; ep.ldo = ldy; ep.M = M; ep.N = N; ep.K = K; ep.bias = bias; ep.act = act;
+    dim3 grid((N + kBN - 1) / kBN, (unsigned)((M + kBM - 1) / kBM), 1);
+    gemm_tf32x3_kernel<<<grid, kGemmThreads, kGemmSmem, (cudaStream_t)stream>>>(ma, mb, ep);
+    adkf_count_launches(1);
+    ADKF_LAUNCH_CHECK();
+    return 0;
+}
+
+extern "C" int adkf_gram_sqdist_tc(const float* Z, int32_t d, int32_t T, int64_t total_rows, const int32_t* z_off,
+                                   const int32_t* n_sup, const int64_t* d2_off, int32_t max_n, int32_t qq_block,
+                                   float* mu_ws, float* nrm_ws, float* D2, void* stream) {
+    if (T <= 0 || max_n <= 0) return 0;
+    if (!Z || !z_off || !n_sup || !d2_off || !mu_ws || !nrm_ws || !D2 || d <= 0 || d % 4) return ADKF_ERR_BADARG;
+    cudaStream_t s = (cudaStream_t)stream;
+    CUtensorMap mz;
+    int rc = make_map_2d(&mz, Z, total_rows, d, d);
+    if (rc) return rc;
+    rc = gemm_attr();
+    if (rc) return rc;
+    launch_center_stats(Z, d, T, z_off, n_sup, max_n, mu_ws, nrm_ws, s);
+    GemmEpilogue ep = {};
+    ep.mode = 1; ep.out = D2; ep.K = d; ep.z_off = z_off; ep.n_sup = n_sup; ep.d2_off = d2_off; ep.mu = mu_ws;
+    ep.nrm = nrm_ws; ep.qq_block = qq_block;
+    const int nt = (max_n + kBM - 1) / kBM;
+    gemm_tf32x3_kernel<<<dim3(nt, nt, T), kGemmThreads, kGemmSmem, s>>>(mz, mz, ep);
+    adkf_count_launches(3);
+    ADKF_LAUNCH_CHECK();
+    return 0;
+}

@@ -184,14 +184,20 @@ sqdist_bwd_kernel(const float* __restrict__ Z, int d, const int32_t* __restrict_
 
 using namespace adkf;
 
+// centring statistics shared with the tensor-core Gram (gemm_tf32x3.cu)
+void adkf::launch_center_stats(const float* Z, int d, int T, const int32_t* z_off, const int32_t* n_sup, int max_n,
+                               float* mu_ws, float* nrm_ws, cudaStream_t s) {
+    task_mean_kernel<<<dim3((d + 255) / 256, T), 256, 0, s>>>(Z, d, z_off, n_sup, mu_ws);
+    row_norm_kernel<<<dim3((max_n + 7) / 8, T), 256, 0, s>>>(Z, d, z_off, mu_ws, nrm_ws);
+}
+
 extern "C" int adkf_gram_sqdist(const float* Z, int32_t d, int32_t T, const int32_t* z_off,
                                 const int32_t* n_sup, const int64_t* d2_off, int32_t max_n, int32_t qq_block,
                                 float* mu_ws, float* nrm_ws, float* D2, void* stream) {
     if (T <= 0 || max_n <= 0) return 0;
     if (!Z || !z_off || !n_sup || !d2_off || !mu_ws || !nrm_ws || !D2 || d <= 0) return ADKF_ERR_BADARG;
     cudaStream_t s = (cudaStream_t)stream;
-    task_mean_kernel<<<dim3((d + 255) / 256, T), 256, 0, s>>>(Z, d, z_off, n_sup, mu_ws);
-    row_norm_kernel<<<dim3((max_n + 7) / 8, T), 256, 0, s>>>(Z, d, z_off, mu_ws, nrm_ws);
+    launch_center_stats(Z, d, T, z_off, n_sup, max_n, mu_ws, nrm_ws, s);
     const int nt = (max_n + kTile - 1) / kTile;
     sqdist_tile_kernel<<<dim3(nt, nt, T), 256, 0, s>>>(Z, d, z_off, n_sup, d2_off, qq_block, mu_ws, nrm_ws, D2);
     adkf_count_launches(3);

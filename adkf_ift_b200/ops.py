@@ -274,10 +274,22 @@ class SqDist:
     nrm: torch.Tensor
 
 
-def gp_sqdist(Z: torch.Tensor, layout: TaskLayout, qq_block: bool) -> SqDist:
+def gp_sqdist(Z: torch.Tensor, layout: TaskLayout, qq_block: bool, impl: str = "tcgen05") -> SqDist:
+    """Per-task centred squared distances.  impl="tcgen05": 3xTF32 tensor-core Gram (default, needs d % 4 == 0);
+    impl="simt": the fp32 CUDA-core tile kernel (any d)."""
     lib = _cabi.load()
     Z = Z.contiguous()
     d = Z.shape[1]
+    if impl == "tcgen05" and d % 4 == 0 and Z.data_ptr() % 16 == 0:
+        f32 = dict(dtype=torch.float32, device=Z.device)
+        D2 = torch.zeros(max(layout.d2_total, 1), **f32)
+        mu = torch.empty(max(layout.T, 1), d, **f32)
+        nrm = torch.empty(max(layout.total_rows, 1), **f32)
+        rc = lib.adkf_gram_sqdist_tc(dptr(Z, torch.float32), d, layout.T, Z.shape[0], dptr(layout.z_off),
+                                     dptr(layout.n_sup), dptr(layout.d2_off), layout.max_n, 1 if qq_block else 0,
+                                     dptr(mu), dptr(nrm), dptr(D2), stream_ptr())
+        check(rc, "adkf_gram_sqdist_tc")
+        return SqDist(D2, mu, nrm)
     f32 = dict(dtype=torch.float32, device=Z.device)
     D2 = torch.zeros(max(layout.d2_total, 1), **f32)
     mu = torch.empty(max(layout.T, 1), d, **f32)
@@ -359,3 +371,26 @@ def gp_ift(layout: TaskLayout, D2, y, kernel: str, noise_prior_loc: float, ls_pr
                          dptr(aux), dptr(Wm), dptr(status), dptr(ws), nws, stream_ptr())
     check(rc, "adkf_gp_ift")
     return Wm, aux, status
+
+
+# --------------------------------------------------------------------------------------------------
+# dense layer on the tcgen05 3xTF32 GEMM
+# --------------------------------------------------------------------------------------------------
+ACT_IDS = {None: 0, "none": 0, "relu": 1, "leaky_relu": 2}
+
+
+def linear_tf32x3_forward(x: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.Tensor], act=None) -> torch.Tensor:
+    """act(x @ weight.T + bias) with fp32-class accuracy on the tensor cores (no autograd; see _LinearTC)."""
+    lib = _cabi.load()
+    x = x.contiguous()
+    weight = weight.contiguous()
+    M, K = x.shape
+    N = weight.shape[0]
+    if K % 4 or x.data_ptr() % 16 or weight.data_ptr() % 16:
+        raise ValueError("adkf_linear_tf32x3 needs K % 4 == 0 and 16-byte aligned operands")
+    y = torch.empty(M, N, dtype=torch.float32, device=x.device)
+    rc = lib.adkf_linear_tf32x3(dptr(x, torch.float32), M, K, K, dptr(weight, torch.float32), N, K,
+                                dptr(bias.contiguous(), torch.float32) if bias is not None else ctypes.c_void_p(0),
+                                ACT_IDS[act], dptr(y), N, stream_ptr())
+    check(rc, "adkf_linear_tf32x3")
+    return y

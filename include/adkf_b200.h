@@ -135,6 +135,19 @@ int adkf_gram_sqdist(const float* Z, int32_t d, int32_t T, const int32_t* z_off,
                      const int64_t* d2_off, int32_t max_n /*max rows of any task (grid sizing)*/,
                      int32_t qq_block, float* mu_ws /*[T,d]*/, float* nrm_ws /*[rows]*/, float* D2, void* stream);
 
+/* Same result as adkf_gram_sqdist, computed on the 5th-generation tensor cores: tcgen05.mma kind::tf32 with the 3xTF32
+ * error-compensated split (fp32-class accuracy), TMA-staged operands, accumulator in TMEM (gemm_tf32x3.cu).
+ * Needs d % 4 == 0 and a 16-byte aligned Z; total_rows = number of rows of Z (bounds of the TMA tensor map). */
+int adkf_gram_sqdist_tc(const float* Z, int32_t d, int32_t T, int64_t total_rows, const int32_t* z_off,
+                        const int32_t* n_sup, const int64_t* d2_off, int32_t max_n, int32_t qq_block,
+                        float* mu_ws /*[T,d]*/, float* nrm_ws /*[rows]*/, float* D2, void* stream);
+
+/* Dense layer forward on the same tensor-core kernel:  Y[M,N] = act(X[M,K] W[N,K]^T + bias[N])  (torch.nn.Linear of the
+ * extractor: fs_mol/modules/gnn.py:79-95,477-515; graph_readout.py:224-259; fs_mol/models/adaptive_dkt.py:61-65).
+ * act: 0 none, 1 relu, 2 leaky_relu(0.01).  ld* in floats (multiples of 4), pointers 16-byte aligned, bias may be NULL. */
+int adkf_linear_tf32x3(const float* X, int64_t M, int32_t K, int64_t ldx, const float* W, int32_t N, int64_t ldw,
+                       const float* bias, int32_t act, float* Y, int64_t ldy, void* stream);
+
 /* dZ[a,:] = scale * 4 * sum_b Wm[a,b] (z_a - z_b)  for a symmetric per-task weight matrix Wm (same layout
  * as D2): the chain rule of anything that depends on Z only through D2. */
 int adkf_gram_sqdist_bwd(const float* Z, int32_t d, int32_t T, const int32_t* z_off, const int64_t* d2_off,
