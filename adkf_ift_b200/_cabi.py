@@ -32,6 +32,9 @@ SIGNATURES = {
     "adkf_gram_sqdist": ([_P, c_int32, c_int32, _P, _P, _P, c_int32, c_int32, _P, _P, _P, _P], ctypes.c_int),
     "adkf_gram_sqdist_tc": ([_P, c_int32, c_int32, c_int64, _P, _P, _P, c_int32, c_int32, _P, _P, _P, _P], ctypes.c_int),
     "adkf_linear_tf32x3": ([_P, c_int64, c_int32, c_int64, _P, c_int32, c_int64, _P, c_int32, _P, c_int64, _P], ctypes.c_int),
+    "adkf_gemm_tf32x3": ([_P, c_int32, c_int64, _P, c_int32, c_int64, c_int64, c_int32, c_int32, _P, c_int32, _P, c_int64,
+                          _P, c_int64, _P], ctypes.c_int),
+    "adkf_gemm_splitk_ws_floats": ([c_int64, c_int32, c_int32], c_int64),
     "adkf_gram_sqdist_bwd": ([_P, c_int32, c_int32, _P, _P, c_int32, _P, _P, c_float, _P, _P], ctypes.c_int),
     "adkf_gp_fit": ([c_int32, _P, _P, _P, _P, _P, c_int32, c_float, c_float, c_int32, c_int32, c_int32, c_float,
                      _P, _P, _P, _P, c_int64, _P], ctypes.c_int),

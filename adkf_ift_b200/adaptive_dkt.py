@@ -295,7 +295,7 @@ class ADKTModel(nn.Module):
         col = 0
         base = None
         if gnn_out is not None:
-            base = F.linear(gnn_out, w0[:, :self._gnn_dim], b0)
+            base = ops.linear_tc(gnn_out, w0[:, :self._gnn_dim], b0)
             col = self._gnn_dim
         fp_cols = None
         if fingerprints is not None:
@@ -308,7 +308,7 @@ class ADKTModel(nn.Module):
             base = b0.unsqueeze(0).expand(fingerprints.shape[0], -1)
         if fp_cols is not None:
             base = ops.ecfp_linear(base, fingerprints, w0[:, fp_cols[0]:fp_cols[1]].t().contiguous())
-        return self.fc[2](F.relu(base))
+        return ops.linear_tc(F.relu(base), self.fc[2].weight, self.fc[2].bias)
 
     def embed(self, batch) -> torch.Tensor:
         """GP inputs Z [G, d] for every graph of `batch` (an FSMolBatch-like with fingerprints/descriptors on the

@@ -22,11 +22,18 @@
 //     (16 MMAs) into fp32 registers with ordinary round-to-nearest adds (bias <~ 6e-7);
 //   * the two correction products lo.hi + hi.lo are 2^-11 smaller and stay in a third accumulator until the end.
 //
-// CTA = one 128 x 128 output tile, 16 warps:
-//   warp 0     TMA producer      cp.async.bulk.tensor.2d (SWIZZLE_128B boxes of 128 rows x 32 floats) -> smem ring, 3 stages
-//   warp 1     MMA issuer        one elected lane: 4 k-steps x 3 tcgen05.mma per stage, tcgen05.commit frees the stage
+// Operand layouts.  An operand is "K-major" when the contraction index is the contiguous one in HBM (x[M,K], W[N,K]) and
+// "transposed" when the contraction index is the slow one (dY^T in dW = dY^T x, W^T in dX = dY W).  The tensor core only
+// ever sees K-major SWIZZLE_128B tiles: a transposed operand is fetched by TMA as an un-swizzled [32 k][128 mn] box and the
+// splitter warps, which touch every element anyway, write hi/lo TRANSPOSED into the K-major tiles.  One MMA path, three
+// operand combinations (A,B) = (K,K) forward, (K,T) input gradient, (T,T) weight gradient (split-K over the node dimension,
+// deterministic two-pass reduction).
+//
+// CTA = one 128 x 128 output tile, 16 warps, two smem rings (raw: TMA -> splitter, 3 x 32 KB; split: splitter -> MMA, 2 x 64 KB):
+//   warp 0     TMA producer      cp.async.bulk.tensor.2d -> raw ring
+//   warp 1     MMA issuer        one elected lane: 4 k-steps x 3 tcgen05.mma per k-block, tcgen05.commit frees the split stage
 //   warp 2     TMEM allocator    512 columns: big[2] x 128, small x 128
-//   warps 4-7  splitter          hi/lo split of the landed tiles in place (generic proxy -> fence.proxy.async)
+//   warps 4-7  splitter          raw tile -> hi/lo K-major tiles (generic proxy -> fence.proxy.async)
 //   warps 8-15 drain + epilogue  tcgen05.ld of the accumulator rows (warp w owns TMEM lanes 32(w%4).., 64 columns each),
 //              RN accumulation in registers, fused epilogue, stores.
 // Every mbarrier wait is bounded (trap after ~2^28 polls) so that a protocol bug cannot hang the device.
@@ -37,13 +44,16 @@
 namespace adkf {
 
 constexpr int kBM = 128, kBN = 128, kBK = 32;        // tile; 32 floats = 128 B = one swizzle row
-constexpr int kStages = 3;
+constexpr int kRaw = 3;                              // raw ring depth (TMA destination: A_raw, B_raw)
+constexpr int kSplit = 2;                            // split ring depth (MMA source: A_hi, B_hi, A_lo, B_lo)
 constexpr int kTileBytes = kBM * kBK * 4;            // 16 KB
-constexpr int kStageBytes = 4 * kTileBytes;          // A_hi, B_hi, A_lo, B_lo
+constexpr int kRawBytes = 2 * kTileBytes;
+constexpr int kSplitBytes = 4 * kTileBytes;
+constexpr int kRingBytes = kRaw * kRawBytes + kSplit * kSplitBytes;   // 224 KB
 constexpr int kGemmThreads = 512;
 constexpr int kTmemCols = 512;                       // big[0], big[1], small (128 fp32 columns each); power of two
 constexpr int kGroup = 4;                            // k-blocks accumulated in TMEM between two drains
-constexpr size_t kGemmSmem = (size_t)kStages * kStageBytes + 1024 /*align*/ + 256 /*barriers*/;
+constexpr size_t kGemmSmem = (size_t)kRingBytes + 1024 /*align*/ + 256 /*barriers*/;
 
 // ---- PTX wrappers ---------------------------------------------------------------------------------------
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -120,7 +130,7 @@ __device__ __forceinline__ uint32_t rna_tf32(float x) {
 }
 
 struct GemmEpilogue {
-    // mode 0: Y = act(acc + bias)       mode 1: per-task squared distances
+    // mode 0: Y = act(acc + bias) (or a split-K partial)       mode 1: per-task squared distances
     int mode;
     float* out;
     int64_t ldo;
@@ -128,6 +138,9 @@ struct GemmEpilogue {
     int N, K;
     const float* bias;
     int act;              // 0 none, 1 relu, 2 leaky_relu(0.01)
+    // split-K (mode 0): CTA z handles k-blocks [z * kb_per_split, ...) and writes to out + z * split_stride
+    int kb_per_split;
+    int64_t split_stride;
     // gram
     const int32_t* z_off;
     const int32_t* n_sup;
@@ -137,24 +150,81 @@ struct GemmEpilogue {
     int qq_block;
 };
 
+__device__ __forceinline__ void split4(const float4 v, float4& hi, float4& lo) {
+    hi.x = __uint_as_float(rna_tf32(v.x)); lo.x = v.x - hi.x;
+    hi.y = __uint_as_float(rna_tf32(v.y)); lo.y = v.y - hi.y;
+    hi.z = __uint_as_float(rna_tf32(v.z)); lo.z = v.z - hi.z;
+    hi.w = __uint_as_float(rna_tf32(v.w)); lo.w = v.w - hi.w;
+}
+
+// One operand tile, raw -> (hi, lo) in the K-major SWIZZLE_128B layout the MMA descriptors describe (row r = 128 B, its
+// logical 16 B chunk j stored at chunk j ^ (r & 7)).  t = 0..127 (the four splitter warps).
+//   TR = false: the raw tile already has that layout (TMA SWIZZLE_128B box of 128 rows x 32 floats); float4 p of the tile
+//               is row p / 8, physical chunk p % 8.  `mu4` (gram centring) is the slice of the task mean for this thread's
+//               logical chunk, which is the same for all its rows: (t & 7) ^ ((t >> 3) & 7).
+//   TR = true : the raw tile is [32 k][128 mn] floats, un-swizzled; thread t owns output row mn = t and gathers 4
+//               consecutive k per store (reads are conflict-free: a warp reads 32 consecutive floats).
+template <bool TR>
+__device__ __forceinline__ void split_tile(const unsigned char* raw, unsigned char* hi_t, unsigned char* lo_t, int t,
+                                           const float4 mu4) {
+    float4* hi4 = reinterpret_cast<float4*>(hi_t);
+    float4* lo4 = reinterpret_cast<float4*>(lo_t);
+    if (!TR) {
+        const float4* r4 = reinterpret_cast<const float4*>(raw);
+#pragma unroll 4
+        for (int i = 0; i < (kTileBytes / 16) / 128; ++i) {            // 1024 float4 / 128 threads = 8
+            const int p = i * 128 + t;
+            float4 v = r4[p];
+            v.x -= mu4.x; v.y -= mu4.y; v.z -= mu4.z; v.w -= mu4.w;
+            float4 hi, lo;
+            split4(v, hi, lo);
+            hi4[p] = hi;
+            lo4[p] = lo;
+        }
+    } else {
+        const float* rf = reinterpret_cast<const float*>(raw);
+#pragma unroll 4
+        for (int c = 0; c < kBK / 4; ++c) {
+            float4 v;
+            v.x = rf[(4 * c + 0) * kBM + t];
+            v.y = rf[(4 * c + 1) * kBM + t];
+            v.z = rf[(4 * c + 2) * kBM + t];
+            v.w = rf[(4 * c + 3) * kBM + t];
+            float4 hi, lo;
+            split4(v, hi, lo);
+            const int p = t * 8 + (c ^ (t & 7));
+            hi4[p] = hi;
+            lo4[p] = lo;
+        }
+    }
+}
+
+template <bool TA, bool TB>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, GemmEpilogue ep) {
     extern __shared__ unsigned char smem_raw[];
     const uint32_t raw = smem_u32(smem_raw);
     const uint32_t base = (raw + 1023u) & ~1023u;                  // SWIZZLE_128B tiles need 1024 B alignment
     unsigned char* base_ptr = smem_raw + (base - raw);
-    const uint32_t bars = base + kStages * kStageBytes;            // full[S], conv[S], empty[S], accum, tmem slot
-    auto full_bar = [&](int s) { return bars + 8u * s; };
-    auto conv_bar = [&](int s) { return bars + 8u * (kStages + s); };
-    auto empty_bar = [&](int s) { return bars + 8u * (2 * kStages + s); };
-    auto accfull_bar = [&](int b) { return bars + 8u * (3 * kStages + b); };
-    auto accempty_bar = [&](int b) { return bars + 8u * (3 * kStages + 2 + b); };
-    volatile uint32_t* tmem_slot = reinterpret_cast<volatile uint32_t*>(base_ptr + kStages * kStageBytes + 8 * (3 * kStages + 4));
+    const uint32_t split_base = base + kRaw * kRawBytes;
+    unsigned char* split_ptr = base_ptr + kRaw * kRawBytes;
+    const uint32_t bars = base + kRingBytes;
+    auto rawfull_bar = [&](int r) { return bars + 8u * r; };
+    auto rawempty_bar = [&](int r) { return bars + 8u * (kRaw + r); };
+    auto conv_bar = [&](int s) { return bars + 8u * (2 * kRaw + s); };              // split stage filled
+    auto empty_bar = [&](int s) { return bars + 8u * (2 * kRaw + kSplit + s); };    // split stage consumed by the MMAs
+    auto accfull_bar = [&](int b) { return bars + 8u * (2 * kRaw + 2 * kSplit + b); };
+    auto accempty_bar = [&](int b) { return bars + 8u * (2 * kRaw + 2 * kSplit + 2 + b); };
+    volatile uint32_t* tmem_slot =
+        reinterpret_cast<volatile uint32_t*>(base_ptr + kRingBytes + 8 * (2 * kRaw + 2 * kSplit + 4));
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
     // ---- tile coordinates ---------------------------------------------------------------------------------
     int rowA0, rowB0, task = 0, Nt = 0, nsup = 0;
+    int kb0 = 0;
+    int nk = (ep.K + kBK - 1) / kBK;
+    float* out = ep.out;
     if (ep.mode == 1) {
         task = blockIdx.z;
         const int r0 = ep.z_off[task];
@@ -168,15 +238,20 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
     } else {
         rowA0 = blockIdx.y * kBM;
         rowB0 = blockIdx.x * kBN;
+        kb0 = blockIdx.z * ep.kb_per_split;
+        nk = min(nk, kb0 + ep.kb_per_split) - kb0;                    // host guarantees >= 1
+        out += (int64_t)blockIdx.z * ep.split_stride;
     }
-    const int nk = (ep.K + kBK - 1) / kBK;
 
     // ---- one-time setup -----------------------------------------------------------------------------------
     if (threadIdx.x == 0) {
-        for (int s = 0; s < kStages; ++s) {
-            mbar_init(full_bar(s), 1);
+        for (int r = 0; r < kRaw; ++r) {
+            mbar_init(rawfull_bar(r), 1);
+            mbar_init(rawempty_bar(r), 4);  // one arrive per splitter warp
+        }
+        for (int s = 0; s < kSplit; ++s) {
             mbar_init(conv_bar(s), 4);      // one arrive per splitter warp
-            mbar_init(empty_bar(s), 1);
+            mbar_init(empty_bar(s), 1);     // tcgen05.commit
         }
         for (int b = 0; b < 2; ++b) {
             mbar_init(accfull_bar(b), 1);
@@ -198,77 +273,70 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
     if (warp == 0) {
         // ===== TMA producer =====
         if (lane == 0) {
-            for (int kb = 0; kb < nk; ++kb) {
-                const int s = kb % kStages;
-                const uint32_t ph = (kb / kStages) & 1;
-                mbar_wait(empty_bar(s), ph ^ 1);
-                mbar_expect_tx(full_bar(s), 2 * kTileBytes);
-                const uint32_t st = base + s * kStageBytes;
-                tma_load_2d(st, &tmA, full_bar(s), kb * kBK, rowA0);
-                tma_load_2d(st + kTileBytes, &tmB, full_bar(s), kb * kBK, rowB0);
+            for (int i = 0; i < nk; ++i) {
+                const int r = i % kRaw;
+                const uint32_t ph = (i / kRaw) & 1;
+                const int k = (kb0 + i) * kBK;
+                mbar_wait(rawempty_bar(r), ph ^ 1);
+                mbar_expect_tx(rawfull_bar(r), kRawBytes);
+                const uint32_t dst = base + r * kRawBytes;
+                if (TA) tma_load_2d(dst, &tmA, rawfull_bar(r), rowA0, k);
+                else    tma_load_2d(dst, &tmA, rawfull_bar(r), k, rowA0);
+                if (TB) tma_load_2d(dst + kTileBytes, &tmB, rawfull_bar(r), rowB0, k);
+                else    tma_load_2d(dst + kTileBytes, &tmB, rawfull_bar(r), k, rowB0);
             }
         }
     } else if (warp == 1) {
         // ===== MMA issuer =====
-        const int ngroups = (nk + kGroup - 1) / kGroup;
-        for (int kb = 0; kb < nk; ++kb) {
-            const int s = kb % kStages;
-            const uint32_t ph = (kb / kStages) & 1;
-            const int g = kb / kGroup, b = g & 1;
-            const bool group_first = (kb % kGroup) == 0;
-            const bool group_last = (kb % kGroup) == kGroup - 1 || kb == nk - 1;
+        for (int i = 0; i < nk; ++i) {
+            const int s = i % kSplit;
+            const uint32_t ph = (i / kSplit) & 1;
+            const int g = i / kGroup, b = g & 1;
+            const bool group_first = (i % kGroup) == 0;
+            const bool group_last = (i % kGroup) == kGroup - 1 || i == nk - 1;
             if (group_first) mbar_wait(accempty_bar(b), ((g >> 1) & 1) ^ 1);   // drained two groups ago
             mbar_wait(conv_bar(s), ph);
             tc_fence_after();
             if (lane == 0) {
-                const uint32_t st = base + s * kStageBytes;
+                const uint32_t st = split_base + s * kSplitBytes;
                 const uint64_t a_hi = smem_desc_k128(st), b_hi = smem_desc_k128(st + kTileBytes);
                 const uint64_t a_lo = smem_desc_k128(st + 2 * kTileBytes), b_lo = smem_desc_k128(st + 3 * kTileBytes);
                 const uint32_t acc_big = tmem_acc + (uint32_t)(b * kBN), acc_small = tmem_acc + 2u * kBN;
 #pragma unroll
                 for (int k = 0; k < kBK / 8; ++k) {                   // UMMA_K = 8 tf32 = 32 B = +2 in the address field
                     const uint64_t adv = (uint64_t)(2 * k);
-                    umma_tf32(acc_small, a_lo + adv, b_hi + adv, kIdescTf32, (kb | k) ? 1u : 0u);
+                    umma_tf32(acc_small, a_lo + adv, b_hi + adv, kIdescTf32, (i | k) ? 1u : 0u);
                     umma_tf32(acc_small, a_hi + adv, b_lo + adv, kIdescTf32, 1u);
                     umma_tf32(acc_big, a_hi + adv, b_hi + adv, kIdescTf32, (group_first && k == 0) ? 0u : 1u);
                 }
-                umma_commit(empty_bar(s));                             // frees the stage when these MMAs retire
+                umma_commit(empty_bar(s));                             // frees the split stage when these MMAs retire
                 if (group_last) umma_commit(accfull_bar(b));
             }
             __syncwarp();
         }
-        (void)ngroups;
     } else if (warp >= 4 && warp < 8) {
-        // ===== splitter (hi/lo) =====
+        // ===== splitter (hi/lo, transposing where the operand is not K-major) =====
         const int t = threadIdx.x - 128;                               // 0..127
-        const int chunk = (t & 7) ^ ((t >> 3) & 7);                    // logical 16 B chunk of this thread's float4 (see header)
-        for (int kb = 0; kb < nk; ++kb) {
-            const int s = kb % kStages;
-            const uint32_t ph = (kb / kStages) & 1;
+        const int chunk = (t & 7) ^ ((t >> 3) & 7);                    // logical 16 B chunk of this thread's float4s
+        for (int i = 0; i < nk; ++i) {
+            const int r = i % kRaw, s = i % kSplit;
             float4 mu4 = make_float4(0.f, 0.f, 0.f, 0.f);
             if (ep.mode == 1) {
-                const int k = kb * kBK + chunk * 4;
+                const int k = (kb0 + i) * kBK + chunk * 4;
                 if (k + 3 < ep.K) mu4 = *reinterpret_cast<const float4*>(ep.mu + (size_t)task * ep.K + k);
             }
-            mbar_wait(full_bar(s), ph);
-            float4* tile = reinterpret_cast<float4*>(base_ptr + (size_t)s * kStageBytes);
-            float4* tile_lo = tile + 2 * (kTileBytes / 16);
-#pragma unroll 4
-            for (int i = 0; i < 2 * (kTileBytes / 16) / 128; ++i) {   // A then B: 2048 float4 / 128 threads = 16
-                const int p = i * 128 + t;
-                float4 v = tile[p];
-                v.x -= mu4.x; v.y -= mu4.y; v.z -= mu4.z; v.w -= mu4.w;
-                float4 hi, lo;
-                hi.x = __uint_as_float(rna_tf32(v.x)); lo.x = v.x - hi.x;
-                hi.y = __uint_as_float(rna_tf32(v.y)); lo.y = v.y - hi.y;
-                hi.z = __uint_as_float(rna_tf32(v.z)); lo.z = v.z - hi.z;
-                hi.w = __uint_as_float(rna_tf32(v.w)); lo.w = v.w - hi.w;
-                tile[p] = hi;
-                tile_lo[p] = lo;
-            }
+            mbar_wait(rawfull_bar(r), (i / kRaw) & 1);
+            mbar_wait(empty_bar(s), ((i / kSplit) & 1) ^ 1);
+            const unsigned char* rw = base_ptr + (size_t)r * kRawBytes;
+            unsigned char* st = split_ptr + (size_t)s * kSplitBytes;
+            split_tile<TA>(rw, st, st + 2 * kTileBytes, t, mu4);
+            split_tile<TB>(rw + kTileBytes, st + kTileBytes, st + 3 * kTileBytes, t, mu4);
             fence_async_smem();                                        // generic-proxy writes -> visible to the MMA (async proxy)
             __syncwarp();
-            if (lane == 0) mbar_arrive(conv_bar(s));
+            if (lane == 0) {
+                mbar_arrive(conv_bar(s));
+                mbar_arrive(rawempty_bar(r));
+            }
         }
     } else if (warp >= 8) {
         // ===== drain (RN accumulation of the TMEM partial sums in registers), then epilogue =====
@@ -305,8 +373,8 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
         const int colbase = half * 64;
         if (ep.mode == 0) {
             const int64_t r = (int64_t)rowA0 + r_local;
-            float* orow = ep.out + r * ep.ldo;
-            const bool vec_ok = (ep.ldo % 4 == 0) && ((reinterpret_cast<uintptr_t>(ep.out) & 15) == 0);
+            float* orow = out + r * ep.ldo;
+            const bool vec_ok = (ep.ldo % 4 == 0) && ((reinterpret_cast<uintptr_t>(out) & 15) == 0);
 #pragma unroll
             for (int c0 = 0; c0 < 64; c0 += 16) {
                 float v[16];
@@ -337,7 +405,7 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
             const int r0 = ep.z_off[task];
             const int ti = blockIdx.y, tj = blockIdx.x;
             const int r = ti * kBM + r_local;                          // row inside the task
-            float* Dt = ep.out + ep.d2_off[task];
+            float* Dt = out + ep.d2_off[task];
             const float ni = (r < Nt) ? ep.nrm[r0 + r] : 0.f;
 #pragma unroll
             for (int c0 = 0; c0 < 64; c0 += 16) {
@@ -389,50 +457,116 @@ static EncodeTiledFn encode_fn() {
     return fn;
 }
 
-// row-major [rows, cols] fp32 matrix with leading dimension ld (floats); box = 32 floats x 128 rows, 128 B swizzle
-static int make_map_2d(CUtensorMap* map, const float* ptr, int64_t rows, int64_t cols, int64_t ld) {
+// An operand with `rows` indices on the output side and `kdim` contraction indices.
+//   transposed = 0: stored [rows, kdim] (ld floats per row)  -> box 32 k x 128 rows, SWIZZLE_128B (already K-major)
+//   transposed = 1: stored [kdim, rows]                      -> box 128 rows x 32 k, un-swizzled; the splitter transposes
+static int make_map_2d(CUtensorMap* map, const float* ptr, int64_t rows, int64_t kdim, int64_t ld, int transposed) {
     EncodeTiledFn fn = encode_fn();
     if (fn == nullptr) return (int)cudaErrorNotSupported;
     if ((reinterpret_cast<uintptr_t>(ptr) & 15) || (ld * 4) % 16) return ADKF_ERR_BADARG;
-    const cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+    const cuuint64_t dims[2] = {(cuuint64_t)(transposed ? rows : kdim), (cuuint64_t)(transposed ? kdim : rows)};
     const cuuint64_t strides[1] = {(cuuint64_t)ld * 4};
-    const cuuint32_t box[2] = {(cuuint32_t)kBK, (cuuint32_t)kBM};
+    const cuuint32_t box[2] = {(cuuint32_t)(transposed ? kBM : kBK), (cuuint32_t)(transposed ? kBK : kBM)};
     const cuuint32_t estr[2] = {1, 1};
-    CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(ptr), dims, strides, box, estr,
-                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-    return r == CUDA_SUCCESS ? 0 : (int)cudaErrorInvalidValue;
+    CUresult r = CUDA_SUCCESS;
+    for (int attempt = 0; attempt < 2; ++attempt) {
+        r = fn(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(ptr), dims, strides, box, estr,
+               CU_TENSOR_MAP_INTERLEAVE_NONE, transposed ? CU_TENSOR_MAP_SWIZZLE_NONE : CU_TENSOR_MAP_SWIZZLE_128B,
+               CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        if (r != CUDA_ERROR_INVALID_CONTEXT) break;
+        cudaFree(0);   // a host thread whose first CUDA call is this driver entry point (autograd workers) has no
+                       // current context yet: bind the primary context through the runtime and retry
+    }
+    return r == CUDA_SUCCESS ? 0 : -(1000 + (int)r);   // tensor-map encode failure: -(1000 + CUresult)
 }
 
+template <bool TA, bool TB>
 static int gemm_attr() {
     static bool done = false;
     if (!done) {
-        cudaError_t e = cudaFuncSetAttribute((const void*)gemm_tf32x3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                             (int)kGemmSmem);
+        cudaError_t e = cudaFuncSetAttribute((const void*)gemm_tf32x3_kernel<TA, TB>,
+                                             cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kGemmSmem);
         if (e != cudaSuccess) return (int)e;
         done = true;
     }
     return 0;
 }
 
-extern "C" int adkf_linear_tf32x3(const float* X, int64_t M, int32_t K, int64_t ldx, const float* W, int32_t N,
-                                  int64_t ldw, const float* bias, int32_t act, float* Y, int64_t ldy, void* stream) {
+namespace adkf {
+__global__ void splitk_reduce_kernel(const float* __restrict__ ws, int splits, int64_t n, float* __restrict__ out) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    float acc = 0.f;
+    for (int s = 0; s < splits; ++s) acc += ws[(int64_t)s * n + i];
+    out[i] = acc;
+}
+}  // namespace adkf
+
+// split-K plan: only when the output has too few 128 x 128 tiles to fill the 148 SMs; every split gets >= 8 k-blocks
+static int plan_splits(int64_t M, int32_t N, int32_t K) {
+    const int64_t tiles = ((M + kBM - 1) / kBM) * ((N + kBN - 1) / kBN);
+    const int nk = (K + kBK - 1) / kBK;
+    if (tiles >= 148 || nk < 16) return 1;
+    int splits = (int)((2 * 148 + tiles - 1) / tiles);
+    if (splits > nk / 8) splits = nk / 8;
+    if (splits < 1) splits = 1;
+    const int per = (nk + splits - 1) / splits;
+    return (nk + per - 1) / per;
+}
+
+extern "C" int64_t adkf_gemm_splitk_ws_floats(int64_t M, int32_t N, int32_t K) {
+    const int s = plan_splits(M, N, K);
+    return s > 1 ? (int64_t)s * M * N : 0;
+}
+
+extern "C" int adkf_gemm_tf32x3(const float* A, int32_t transA, int64_t lda, const float* B, int32_t transB, int64_t ldb,
+                                int64_t M, int32_t N, int32_t K, const float* bias, int32_t act, float* D, int64_t ldd,
+                                float* splitk_ws, int64_t splitk_ws_floats, void* stream) {
     if (M <= 0 || N <= 0) return 0;
-    if (!X || !W || !Y || K <= 0 || act < 0 || act > 2) return ADKF_ERR_BADARG;
+    if (!A || !B || !D || K <= 0 || act < 0 || act > 2) return ADKF_ERR_BADARG;
+    if (transA && !transB) return ADKF_ERR_BADARG;                  // (T,K) is not on the path
+    cudaStream_t s = (cudaStream_t)stream;
+    (void)cudaGetLastError();   // a stale error left in this host thread by someone else is not this launch's failure
     CUtensorMap ma, mb;
-    int rc = make_map_2d(&ma, X, M, K, ldx);
+    int rc = make_map_2d(&ma, A, M, K, lda, transA ? 1 : 0);
     if (rc) return rc;
-    rc = make_map_2d(&mb, W, N, K, ldw);
+    rc = make_map_2d(&mb, B, N, K, ldb, transB ? 1 : 0);
     if (rc) return rc;
-    rc = gemm_attr();
-    if (rc) return rc;
+    int splits = plan_splits(M, N, K);
+    if (splits > 1 && (splitk_ws == nullptr || splitk_ws_floats < (int64_t)splits * M * N || bias != nullptr || act != 0 ||
+                       ldd != N))
+        splits = 1;                                                  // no workspace (or fused epilogue): single pass
+    const int nk = (K + kBK - 1) / kBK;
     GemmEpilogue ep = {};
-    ep.mode = 0; ep.out = Y; ep.ldo = ldy; ep.M = M; ep.N = N; ep.K = K; ep.bias = bias; ep.act = act;
-    dim3 grid((N + kBN - 1) / kBN, (unsigned)((M + kBM - 1) / kBM), 1);
-    gemm_tf32x3_kernel<<<grid, kGemmThreads, kGemmSmem, (cudaStream_t)stream>>>(ma, mb, ep);
+    ep.mode = 0; ep.M = M; ep.N = N; ep.K = K; ep.bias = bias; ep.act = act;
+    ep.kb_per_split = (nk + splits - 1) / splits;
+    if (splits > 1) { ep.out = splitk_ws; ep.ldo = N; ep.split_stride = M * (int64_t)N; }
+    else            { ep.out = D; ep.ldo = ldd; ep.split_stride = 0; }
+    dim3 grid((N + kBN - 1) / kBN, (unsigned)((M + kBM - 1) / kBM), splits);
+    if (!transA && !transB) {
+        if ((rc = gemm_attr<false, false>())) return rc;
+        gemm_tf32x3_kernel<false, false><<<grid, kGemmThreads, kGemmSmem, s>>>(ma, mb, ep);
+    } else if (!transA && transB) {
+        if ((rc = gemm_attr<false, true>())) return rc;
+        gemm_tf32x3_kernel<false, true><<<grid, kGemmThreads, kGemmSmem, s>>>(ma, mb, ep);
+    } else {
+        if ((rc = gemm_attr<true, true>())) return rc;
+        gemm_tf32x3_kernel<true, true><<<grid, kGemmThreads, kGemmSmem, s>>>(ma, mb, ep);
+    }
     adkf_count_launches(1);
     ADKF_LAUNCH_CHECK();
+    if (splits > 1) {
+        const int64_t n = M * (int64_t)N;
+        splitk_reduce_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(splitk_ws, splits, n, D);
+        adkf_count_launches(1);
+        ADKF_LAUNCH_CHECK();
+    }
     return 0;
+}
+
+extern "C" int adkf_linear_tf32x3(const float* X, int64_t M, int32_t K, int64_t ldx, const float* W, int32_t N,
+                                  int64_t ldw, const float* bias, int32_t act, float* Y, int64_t ldy, void* stream) {
+    return adkf_gemm_tf32x3(X, 0, ldx, W, 0, ldw, M, N, K, bias, act, Y, ldy, nullptr, 0, stream);
 }
 
 extern "C" int adkf_gram_sqdist_tc(const float* Z, int32_t d, int32_t T, int64_t total_rows, const int32_t* z_off,
@@ -442,16 +576,16 @@ extern "C" int adkf_gram_sqdist_tc(const float* Z, int32_t d, int32_t T, int64_t
     if (!Z || !z_off || !n_sup || !d2_off || !mu_ws || !nrm_ws || !D2 || d <= 0 || d % 4) return ADKF_ERR_BADARG;
     cudaStream_t s = (cudaStream_t)stream;
     CUtensorMap mz;
-    int rc = make_map_2d(&mz, Z, total_rows, d, d);
+    int rc = make_map_2d(&mz, Z, total_rows, d, d, 0);
     if (rc) return rc;
-    rc = gemm_attr();
+    rc = gemm_attr<false, false>();
     if (rc) return rc;
     launch_center_stats(Z, d, T, z_off, n_sup, max_n, mu_ws, nrm_ws, s);
     GemmEpilogue ep = {};
     ep.mode = 1; ep.out = D2; ep.K = d; ep.z_off = z_off; ep.n_sup = n_sup; ep.d2_off = d2_off; ep.mu = mu_ws;
-    ep.nrm = nrm_ws; ep.qq_block = qq_block;
+    ep.nrm = nrm_ws; ep.qq_block = qq_block; ep.kb_per_split = (d + kBK - 1) / kBK;
     const int nt = (max_n + kBM - 1) / kBM;
-    gemm_tf32x3_kernel<<<dim3(nt, nt, T), kGemmThreads, kGemmSmem, s>>>(mz, mz, ep);
+    gemm_tf32x3_kernel<false, false><<<dim3(nt, nt, T), kGemmThreads, kGemmSmem, s>>>(mz, mz, ep);
     adkf_count_launches(3);
     ADKF_LAUNCH_CHECK();
     return 0;

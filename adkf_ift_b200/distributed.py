@@ -42,29 +42,34 @@ def allreduce_sum_(flat: torch.Tensor) -> torch.Tensor:
 
 class FlatParams:
     """Feature-extractor parameters and gradients as views of two flat fp32 buffers, so that the all-reduce, the
-    gradient-norm clip and Adam each touch ONE contiguous array (25.34 M floats = 101 MB for the CLI model)."""
+    gradient-norm clip and Adam each touch ONE contiguous array (25.34 M floats = 101 MB for the CLI model).
+    Every tensor starts on a 256-byte boundary (TMA tensor maps of the GEMM kernel need 16-byte aligned operands);
+    the padding floats stay zero in both buffers, so norms and the all-reduced sum are unaffected."""
+
+    ALIGN = 64  # floats
 
     def __init__(self, params: Sequence[torch.nn.Parameter]):
         self.params = list(params)
         self.sizes = [p.numel() for p in self.params]
-        self.total = sum(self.sizes)
-        dev = self.params[0].device
-        self.flat = torch.empty(self.total, dtype=torch.float32, device=dev)
-        self.grad = torch.zeros(self.total, dtype=torch.float32, device=dev)
+        self.offsets = []
         off = 0
-        for p, n in zip(self.params, self.sizes):
+        for n in self.sizes:
+            self.offsets.append(off)
+            off += -(-n // self.ALIGN) * self.ALIGN
+        self.total = off
+        dev = self.params[0].device
+        self.flat = torch.zeros(self.total, dtype=torch.float32, device=dev)
+        self.grad = torch.zeros(self.total, dtype=torch.float32, device=dev)
+        for p, n, off in zip(self.params, self.sizes, self.offsets):
             self.flat[off:off + n].copy_(p.data.reshape(-1))
             p.data = self.flat[off:off + n].view_as(p.data)
             p.grad = self.grad[off:off + n].view_as(p.data)
-            off += n
 
     def zero_grad(self):
         self.grad.zero_()
-        off = 0
-        for p, n in zip(self.params, self.sizes):   # re-attach the views if something replaced .grad
+        for p, n, off in zip(self.params, self.sizes, self.offsets):   # re-attach the views if something replaced .grad
             if p.grad is None or p.grad.data_ptr() != self.grad[off:off + n].data_ptr():
                 p.grad = self.grad[off:off + n].view_as(p.data)
-            off += n
 
     def clip_(self, max_norm: float) -> torch.Tensor:
         """torch.nn.utils.clip_grad_norm_ on the flat buffer: same global 2-norm, one reduction, no host sync."""

@@ -82,7 +82,13 @@ class MLP(nn.Module):
         self._layers = nn.Sequential(*mods)
 
     def forward(self, x):
-        return self._layers(x)
+        mods = list(self._layers)
+        i = 0
+        while i < len(mods):
+            fuse_relu = i + 1 < len(mods) and isinstance(mods[i + 1], nn.ReLU)
+            x = ops.linear_tc(x, mods[i].weight, mods[i].bias, "relu" if fuse_relu else None)
+            i += 2 if fuse_relu else 1
+        return x
 
 
 class _TowerMessageFns(nn.Module):
@@ -100,7 +106,8 @@ class BOOMLayer(nn.Module):
         self.linear2 = nn.Linear(intermediate_dim, inout_dim)
 
     def forward(self, x):
-        return self.linear2(F.leaky_relu(self.linear1(x), 0.01))
+        hid = ops.linear_tc(x, self.linear1.weight, self.linear1.bias, "leaky_relu")
+        return ops.linear_tc(hid, self.linear2.weight, self.linear2.bias)
 
 
 class GNNBlock(nn.Module):
@@ -135,7 +142,7 @@ class GNNBlock(nn.Module):
     def forward(self, h, gi: ops.GraphIndex):
         W, b = self.stacked_message_weights()
         agg = ops.pna_message_passing(h, W, b, gi)                     # [V, 3072]
-        h = h + self.alpha * self.msg_out_projection(agg)
+        h = h + self.alpha * ops.linear_tc(agg, self.msg_out_projection.weight, self.msg_out_projection.bias)
         return h + self.alpha * self.boom_layer(self.boom_norm_layer(h))
 
 
@@ -166,7 +173,7 @@ class _WeightedPooler(nn.Module):
     def forward(self, x, gi: ops.GraphIndex):
         pooled = ops.readout_weighted(self._scoring_module(x), self._transformation_mlp(x), gi.graph_ptr,
                                       gi.num_graphs, self._num_heads, self._head_dim, self._mode)
-        return self._combination_layer(pooled)
+        return ops.linear_tc(pooled, self._combination_layer.weight)
 
 
 class _MaxPooler(nn.Module):
@@ -175,7 +182,7 @@ class _MaxPooler(nn.Module):
         self._combination_layer = nn.Linear(node_dim, out_dim, bias=False)
 
     def forward(self, x, gi: ops.GraphIndex):
-        return self._combination_layer(ops.readout_max(x, gi.graph_ptr, gi.num_graphs))
+        return ops.linear_tc(ops.readout_max(x, gi.graph_ptr, gi.num_graphs), self._combination_layer.weight)
 
 
 class CombinedGraphReadout(nn.Module):
@@ -191,7 +198,7 @@ class CombinedGraphReadout(nn.Module):
     def forward(self, x, gi: ops.GraphIndex):
         raw = torch.cat((self._weighted_mean_pooler(x, gi), self._weighted_sum_pooler(x, gi),
                          self._max_pooler(x, gi)), dim=1)
-        return self._combination_layer(F.relu(raw))
+        return ops.linear_tc(F.relu(raw), self._combination_layer.weight)
 
 
 class GraphFeatureExtractor(nn.Module):

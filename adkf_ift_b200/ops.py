@@ -374,23 +374,92 @@ def gp_ift(layout: TaskLayout, D2, y, kernel: str, noise_prior_loc: float, ls_pr
 
 
 # --------------------------------------------------------------------------------------------------
-# dense layer on the tcgen05 3xTF32 GEMM
+# dense layers on the tcgen05 3xTF32 GEMM (forward, input gradient, weight gradient)
 # --------------------------------------------------------------------------------------------------
 ACT_IDS = {None: 0, "none": 0, "relu": 1, "leaky_relu": 2}
 
 
-def linear_tf32x3_forward(x: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.Tensor], act=None) -> torch.Tensor:
-    """act(x @ weight.T + bias) with fp32-class accuracy on the tensor cores (no autograd; see _LinearTC)."""
+def gemm_tf32x3(a: torch.Tensor, trans_a: bool, b: torch.Tensor, trans_b: bool, bias: Optional[torch.Tensor] = None,
+                act=None, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """D[M,N] = act(opA(a) @ opB(b).T + bias) on the tensor cores with fp32-class accuracy.
+    a is [M,K] (trans_a False) or [K,M]; b is [N,K] (trans_b False) or [K,N]; both may be row-strided views
+    (last dim contiguous, row stride a multiple of 4 floats, 16-byte aligned)."""
     lib = _cabi.load()
-    x = x.contiguous()
-    weight = weight.contiguous()
-    M, K = x.shape
-    N = weight.shape[0]
-    if K % 4 or x.data_ptr() % 16 or weight.data_ptr() % 16:
-        raise ValueError("adkf_linear_tf32x3 needs K % 4 == 0 and 16-byte aligned operands")
-    y = torch.empty(M, N, dtype=torch.float32, device=x.device)
-    rc = lib.adkf_linear_tf32x3(dptr(x, torch.float32), M, K, K, dptr(weight, torch.float32), N, K,
-                                dptr(bias.contiguous(), torch.float32) if bias is not None else ctypes.c_void_p(0),
-                                ACT_IDS[act], dptr(y), N, stream_ptr())
-    check(rc, "adkf_linear_tf32x3")
+    for t in (a, b):
+        if not t.is_cuda or t.dtype != torch.float32 or t.dim() != 2 or t.stride(1) != 1:
+            raise RuntimeError("gemm_tf32x3 needs 2-D fp32 CUDA operands with a contiguous last dimension (no CPU fallback)")
+        if t.stride(0) % 4 or t.data_ptr() % 16:
+            raise ValueError("gemm_tf32x3 needs row strides that are multiples of 4 floats and 16-byte aligned operands")
+    K, M = (a.shape if trans_a else a.shape[::-1])
+    Kb, N = (b.shape if trans_b else b.shape[::-1])
+    if K != Kb:
+        raise ValueError(f"contraction mismatch: {tuple(a.shape)} vs {tuple(b.shape)}")
+    if out is None:
+        out = torch.empty(M, N, dtype=torch.float32, device=a.device)
+    ws, nws = None, 0
+    if bias is None and ACT_IDS[act] == 0:
+        nws = int(lib.adkf_gemm_splitk_ws_floats(M, N, K))
+        if nws:
+            ws = torch.empty(nws, dtype=torch.float32, device=a.device)
+    rc = lib.adkf_gemm_tf32x3(ctypes.c_void_p(a.data_ptr()), 1 if trans_a else 0, a.stride(0),
+                              ctypes.c_void_p(b.data_ptr()), 1 if trans_b else 0, b.stride(0), M, N, K,
+                              dptr(bias.contiguous(), torch.float32) if bias is not None else ctypes.c_void_p(0),
+                              ACT_IDS[act], dptr(out, torch.float32), out.stride(0),
+                              dptr(ws) if ws is not None else ctypes.c_void_p(0), nws, stream_ptr())
+    check(rc, "adkf_gemm_tf32x3")
+    return out
+
+
+def linear_tf32x3_forward(x: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.Tensor], act=None) -> torch.Tensor:
+    """act(x @ weight.T + bias) with fp32-class accuracy on the tensor cores (no autograd; see linear_tc)."""
+    return gemm_tf32x3(x.contiguous(), False, weight.contiguous(), False, bias, act)
+
+
+def _tc_eligible(x, weight) -> bool:
+    K, N = weight.shape[1], weight.shape[0]
+    return (x.is_cuda and K % 4 == 0 and N % 4 == 0 and K >= 32 and N >= 32 and x.stride(-1) == 1 and weight.stride(1) == 1
+            and x.stride(0) % 4 == 0 and weight.stride(0) % 4 == 0 and x.data_ptr() % 16 == 0 and weight.data_ptr() % 16 == 0)
+
+
+class _LinearTC(torch.autograd.Function):
+    """nn.Linear (+ optional ReLU / LeakyReLU(0.01)) with all three GEMMs on the tcgen05 3xTF32 kernel."""
+
+    @staticmethod
+    def forward(ctx, x, weight, bias, act):
+        y = gemm_tf32x3(x, False, weight, False, bias, act)
+        ctx.act = ACT_IDS[act]
+        ctx.has_bias = bias is not None
+        ctx.save_for_backward(x, weight, y if ctx.act else None)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, weight, y = ctx.saved_tensors
+        dy = dy.contiguous()
+        if ctx.act == 1:
+            dy = dy * (y > 0)
+        elif ctx.act == 2:
+            dy = dy * torch.where(y > 0, 1.0, 0.01)
+        dx = dw = db = None
+        if ctx.needs_input_grad[0]:
+            dx = gemm_tf32x3(dy, False, weight, True)          # dX[M,K] = dY[M,N] W[N,K]
+        if ctx.needs_input_grad[1]:
+            dw = gemm_tf32x3(dy, True, x, True)                # dW[N,K] = dY^T[N,M] X[M,K]
+        if ctx.has_bias and ctx.needs_input_grad[2]:
+            db = dy.sum(0)
+        return dx, dw, db, None
+
+
+def linear_tc(x: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.Tensor] = None, act=None) -> torch.Tensor:
+    """Drop-in for F.linear(+activation) on [rows, K] inputs.  Shapes the tensor-core kernel does not take (K or N not a
+    multiple of 4, tiny layers such as the 12 attention scores or the 32-wide input projection) stay on cuBLAS."""
+    if not x.is_cuda:
+        raise RuntimeError("adkf_ift_b200 kernels need CUDA tensors (no CPU fallback)")
+    if x.dim() == 2 and _tc_eligible(x, weight):
+        return _LinearTC.apply(x, weight, bias, act)
+    y = torch.nn.functional.linear(x, weight, bias)
+    if ACT_IDS[act] == 1:
+        y = torch.relu(y)
+    elif ACT_IDS[act] == 2:
+        y = torch.nn.functional.leaky_relu(y, 0.01)
     return y

@@ -148,6 +148,19 @@ int adkf_gram_sqdist_tc(const float* Z, int32_t d, int32_t T, int64_t total_rows
 int adkf_linear_tf32x3(const float* X, int64_t M, int32_t K, int64_t ldx, const float* W, int32_t N, int64_t ldw,
                        const float* bias, int32_t act, float* Y, int64_t ldy, void* stream);
 
+/* General form of the same kernel, used by the backward of every dense layer (what autograd's mm backward does in the
+ * reference):   D[M,N] = act( opA(A)[M,K] . opB(B)[N,K]^T + bias[N] )
+ *   transA = 0: A stored [M,K] (lda floats per row);  transA = 1: A stored [K,M]  (contraction index is the slow one)
+ *   transB = 0: B stored [N,K];                       transB = 1: B stored [K,N]
+ * Supported combinations: (0,0) forward y = x W^T;  (0,1) input gradient dX = dY W;  (1,1) weight gradient dW = dY^T X.
+ * When the output has fewer than 148 tiles (weight gradients: K = number of nodes) and a workspace of
+ * adkf_gemm_splitk_ws_floats(M,N,K) floats is passed (bias NULL, act 0, ldd == N), the contraction is split over CTAs and
+ * reduced by a second, deterministic pass. */
+int adkf_gemm_tf32x3(const float* A, int32_t transA, int64_t lda, const float* B, int32_t transB, int64_t ldb,
+                     int64_t M, int32_t N, int32_t K, const float* bias, int32_t act, float* D, int64_t ldd,
+                     float* splitk_ws, int64_t splitk_ws_floats, void* stream);
+int64_t adkf_gemm_splitk_ws_floats(int64_t M, int32_t N, int32_t K);
+
 /* dZ[a,:] = scale * 4 * sum_b Wm[a,b] (z_a - z_b)  for a symmetric per-task weight matrix Wm (same layout
  * as D2): the chain rule of anything that depends on Z only through D2. */
 int adkf_gram_sqdist_bwd(const float* Z, int32_t d, int32_t T, const int32_t* z_off, const int64_t* d2_off,

@@ -74,3 +74,73 @@ def test_gram_tensor_core_matches_simt_and_oracle(cuda_device):
             if qq:
                 assert np.all(np.diag(a) == 0.0) and np.array_equal(a, a.T)
             off += N * N
+
+
+@pytest.mark.parametrize("M,N,K", [(1000, 3072, 128), (257, 1408, 768), (128, 128, 32), (5000, 132, 1024)])
+def test_input_gradient_form_kt(cuda_device, M, N, K):
+    """D[M,N] = A[M,K] . B  with B stored [K,N] (dX = dY W): the transposing splitter path for operand B."""
+    from adkf_ift_b200 import ops
+    g = torch.Generator().manual_seed(M * 7 + N)
+    a = torch.randn(M, K, generator=g)
+    b = torch.randn(K, N, generator=g) / K ** 0.5
+    ref = a.double() @ b.double()
+    ad, bd = a.to(cuda_device), b.to(cuda_device)
+    out = ops.gemm_tf32x3(ad, False, bd, True)
+    torch.cuda.synchronize()
+    e, e32 = rel(out, ref), rel(ad @ bd, ref)
+    print(f"KT M={M} N={N} K={K}: 3xTF32 {e:.3e} cuBLAS fp32 {e32:.3e}")
+    assert e < max(2e-6, 4 * e32)
+
+
+@pytest.mark.parametrize("M,N,K", [(128, 3072, 20000), (1024, 128, 33333), (768, 1408, 9000), (12 * 4, 768, 4100),
+                                   (2048, 512, 320)])
+def test_weight_gradient_form_tt_splitk(cuda_device, M, N, K):
+    """D[M,N] = A^T B with A stored [K,M], B stored [K,N] (dW = dY^T X): both operands transposed, split-K over the
+    (node) contraction with the deterministic second pass."""
+    from adkf_ift_b200 import ops
+    g = torch.Generator().manual_seed(M + N + K)
+    a = torch.randn(K, M, generator=g)
+    b = torch.randn(K, N, generator=g)
+    ref = a.double().t() @ b.double()
+    ad, bd = a.to(cuda_device), b.to(cuda_device)
+    out = ops.gemm_tf32x3(ad, True, bd, True)
+    out2 = ops.gemm_tf32x3(ad, True, bd, True)
+    torch.cuda.synchronize()
+    e, e32 = rel(out, ref), rel(ad.t() @ bd, ref)
+    print(f"TT M={M} N={N} K={K}: 3xTF32 {e:.3e} cuBLAS fp32 {e32:.3e}")
+    assert e < max(2e-6, 4 * e32)
+    assert torch.equal(out, out2), "split-K reduction must be deterministic"
+
+
+@pytest.mark.parametrize("act", [None, "relu", "leaky_relu"])
+def test_linear_tc_autograd(cuda_device, act):
+    """linear_tc (forward + both gradient GEMMs + bias gradient) against fp64 autograd, also on a strided weight view
+    (the fc[0] column block of adaptive_dkt.py:145-160)."""
+    from adkf_ift_b200 import ops
+    g = torch.Generator().manual_seed(5)
+    M, K, N = 700, 512, 2048
+    x = torch.randn(M, K, generator=g)
+    wfull = torch.randn(N, K + 2048, generator=g) / K ** 0.5
+    b = torch.randn(N, generator=g)
+    go = torch.randn(M, N, generator=g)
+
+    def run(x, wfull, b, go, fn):
+        x = x.clone().requires_grad_(True)
+        wfull = wfull.clone().requires_grad_(True)
+        b = b.clone().requires_grad_(True)
+        y = fn(x, wfull[:, :K], b)
+        y.backward(go)
+        return y.detach(), x.grad, wfull.grad, b.grad
+
+    def ref_fn(x, w, b):
+        y = torch.nn.functional.linear(x, w, b)
+        return y if act is None else (torch.relu(y) if act == "relu" else torch.nn.functional.leaky_relu(y, 0.01))
+
+    ref = run(x.double(), wfull.double(), b.double(), go.double(), ref_fn)
+    got = run(x.to(cuda_device), wfull.to(cuda_device), b.to(cuda_device), go.to(cuda_device),
+              lambda x, w, b: ops.linear_tc(x, w, b, act))
+    torch.cuda.synchronize()
+    for name, a, r in zip(("y", "dx", "dw", "db"), got, ref):
+        e = rel(a, r)
+        print(f"linear_tc act={act} {name}: rel err {e:.3e}")
+        assert e < 5e-6, name
