@@ -31,6 +31,10 @@ SIGNATURES = {
     "adkf_ecfp_linear_bwd": ([_P, c_int32, c_int32, _P, c_int32, _P, _P], ctypes.c_int),
     "adkf_gram_sqdist": ([_P, c_int32, c_int32, _P, _P, _P, c_int32, c_int32, _P, _P, _P, _P], ctypes.c_int),
     "adkf_gram_sqdist_tc": ([_P, c_int32, c_int32, c_int64, _P, _P, _P, c_int32, c_int32, _P, _P, _P, _P], ctypes.c_int),
+    "adkf_gram_pairstat": ([c_int32, _P, c_int32, c_int32, _P, _P, _P, c_int32, c_int32, _P, _P, _P, _P], ctypes.c_int),
+    "adkf_gram_pairstat_tc": ([c_int32, _P, c_int32, c_int32, c_int64, _P, _P, _P, c_int32, c_int32, _P, _P, _P, _P],
+                              ctypes.c_int),
+    "adkf_gram_pairstat_bwd": ([c_int32, _P, c_int32, c_int32, _P, _P, c_int32, _P, _P, c_float, _P, _P], ctypes.c_int),
     "adkf_linear_tf32x3": ([_P, c_int64, c_int32, c_int64, _P, c_int32, c_int64, _P, c_int32, _P, c_int64, _P], ctypes.c_int),
     "adkf_gemm_tf32x3": ([_P, c_int32, c_int64, _P, c_int32, c_int64, c_int64, c_int32, c_int32, _P, c_int32, _P, c_int64,
                           _P, c_int64, _P], ctypes.c_int),
@@ -41,6 +45,9 @@ SIGNATURES = {
     "adkf_gp_predict": ([c_int32, _P, _P, _P, _P, _P, c_int32, _P, _P, _P, _P, _P, c_int64, _P], ctypes.c_int),
     "adkf_gp_ift": ([c_int32, _P, _P, _P, _P, _P, c_int32, c_float, c_int32, c_int32, _P, _P, _P, _P, _P, c_int64,
                      _P], ctypes.c_int),
+    "adkf_chol_blocked_ws_floats": ([c_int32], c_int64),
+    "adkf_gp_joint_nll_blocked": ([_P, c_int32, c_int32, _P, c_int32, _P, c_float, _P, c_int64, _P, _P, _P], ctypes.c_int),
+    "adkf_ei_pool": ([_P, _P, c_int32, c_float, c_float, _P, _P, _P], ctypes.c_int),
     "adkf_gp_ws_floats": ([c_int32, _P, _P, c_int32], c_int64),
 }
 

@@ -320,9 +320,13 @@ class ADKTModel(nn.Module):
         if self.use_fc:
             if fp is not None and fp.dtype != torch.int32:
                 fp = fp.to(torch.int32)
-            return self._fc_forward(gnn_out, fp, desc)
-        parts = [p for p in (gnn_out, fp.float() if fp is not None else None, desc) if p is not None]
-        return torch.cat(parts, dim=1)
+            z = self._fc_forward(gnn_out, fp, desc)
+        else:
+            parts = [p for p in (gnn_out, fp.float() if fp is not None else None, desc) if p is not None]
+            z = torch.cat(parts, dim=1)
+        if self.normalizing_features:   # gp_kernel == "cossim" (adaptive_dkt.py:158-160)
+            z = F.normalize(z, p=2, dim=1)
+        return z
 
     # ---- the reference's forward ------------------------------------------------------------------------
     def _labels(self, batch, which: str) -> torch.Tensor:

@@ -56,9 +56,21 @@ __device__ __forceinline__ void block_sum_multi(const float (&part)[K], double* 
     __syncthreads();
 }
 
-// gram.cu: mu[t][:] = mean of the support rows, nrm[row] = |z_row - mu_t|^2 (two launches on `s`)
+// gram.cu: mu[t][:] = mean of the support rows (or 0 when center == 0), nrm[row] = |z_row - mu_t|^2
 void launch_center_stats(const float* Z, int d, int T, const int32_t* z_off, const int32_t* n_sup, int max_n,
-                         float* mu_ws, float* nrm_ws, cudaStream_t s);
+                         float* mu_ws, float* nrm_ws, cudaStream_t s, int center = 1);
+void launch_pairstat_diag(int stat, int T, const int32_t* z_off, const int64_t* d2_off, int max_n, const float* nrm,
+                          float* D2, cudaStream_t s);
+
+// pair statistic of two rows from their squared norms and dot product (stat: ADKF_STAT_* of adkf_b200.h)
+//   0 centred squared distance (gpytorch sq_dist: clamp_min 0, exact zero diagonal)
+//   1 dot product (diagonal = the row's squared norm)
+//   2 Tanimoto similarity (x.y + eps) / (eps + |x|^2 + |y|^2 - x.y), eps = 1e-6 (gp_utils.py:106-117); diagonal = 1
+__device__ __forceinline__ float pairstat_value(int stat, float ni, float nj, float dot, bool diag) {
+    if (stat == 0) return diag ? 0.f : fmaxf(ni + nj - 2.f * dot, 0.f);
+    if (stat == 1) return diag ? ni : dot;
+    return diag ? 1.f : (dot + 1e-6f) / (1e-6f + ni + nj - dot);
+}
 
 __device__ __forceinline__ float softplusf(float x) { return (x > 20.f) ? x : log1pf(expf(x)); }
 __device__ __forceinline__ float sigmoidf_(float x) { return 1.f / (1.f + expf(-x)); }

@@ -137,7 +137,7 @@ struct GemmEpilogue {
     int64_t M;
     int N, K;
     const float* bias;
-    int act;              // 0 none, 1 relu, 2 leaky_relu(0.01)
+    int act;              // 0 none, 1 relu, 2 leaky_relu(0.01), 3 subtract the product from what `out` holds
     // split-K (mode 0): CTA z handles k-blocks [z * kb_per_split, ...) and writes to out + z * split_stride
     int kb_per_split;
     int64_t split_stride;
@@ -148,6 +148,7 @@ struct GemmEpilogue {
     const float* mu;      // [T, d]
     const float* nrm;     // [rows]
     int qq_block;
+    int stat;             // ADKF_STAT_*
 };
 
 __device__ __forceinline__ void split4(const float4 v, float4& hi, float4& lo) {
@@ -388,6 +389,7 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
                         if (ep.bias != nullptr && col0 + j < ep.N) x += ep.bias[col0 + j];
                         if (ep.act == 1) x = fmaxf(x, 0.f);
                         else if (ep.act == 2) x = (x > 0.f) ? x : 0.01f * x;
+                        else if (ep.act == 3 && col0 + j < ep.N) x = orow[col0 + j] - x;   // D <- D - A.B^T (trailing update)
                         v[j] = x;
                     }
                     if (vec_ok && col0 + 16 <= ep.N) {
@@ -417,8 +419,7 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
                     for (int j = 0; j < 16; ++j) {
                         const int c = tj * kBN + colbase + c0 + j;
                         if (c < Nt && (ti != tj || c <= r)) {
-                            float d = fmaxf(ni + ep.nrm[r0 + c] - 2.f * v[j], 0.f);
-                            if (r == c) d = 0.f;
+                            const float d = pairstat_value(ep.stat, ni, ep.nrm[r0 + c], v[j], r == c);
                             Dt[(size_t)r * Nt + c] = d;
                             Dt[(size_t)c * Nt + r] = d;
                         }
@@ -523,7 +524,7 @@ extern "C" int adkf_gemm_tf32x3(const float* A, int32_t transA, int64_t lda, con
                                 int64_t M, int32_t N, int32_t K, const float* bias, int32_t act, float* D, int64_t ldd,
                                 float* splitk_ws, int64_t splitk_ws_floats, void* stream) {
     if (M <= 0 || N <= 0) return 0;
-    if (!A || !B || !D || K <= 0 || act < 0 || act > 2) return ADKF_ERR_BADARG;
+    if (!A || !B || !D || K <= 0 || act < 0 || act > 3) return ADKF_ERR_BADARG;
     if (transA && !transB) return ADKF_ERR_BADARG;                  // (T,K) is not on the path
     cudaStream_t s = (cudaStream_t)stream;
     (void)cudaGetLastError();   // a stale error left in this host thread by someone else is not this launch's failure
@@ -569,24 +570,34 @@ extern "C" int adkf_linear_tf32x3(const float* X, int64_t M, int32_t K, int64_t 
     return adkf_gemm_tf32x3(X, 0, ldx, W, 0, ldw, M, N, K, bias, act, Y, ldy, nullptr, 0, stream);
 }
 
-extern "C" int adkf_gram_sqdist_tc(const float* Z, int32_t d, int32_t T, int64_t total_rows, const int32_t* z_off,
-                                   const int32_t* n_sup, const int64_t* d2_off, int32_t max_n, int32_t qq_block,
-                                   float* mu_ws, float* nrm_ws, float* D2, void* stream) {
+extern "C" int adkf_gram_pairstat_tc(int32_t stat, const float* Z, int32_t d, int32_t T, int64_t total_rows,
+                                     const int32_t* z_off, const int32_t* n_sup, const int64_t* d2_off, int32_t max_n,
+                                     int32_t qq_block, float* mu_ws, float* nrm_ws, float* D2, void* stream) {
     if (T <= 0 || max_n <= 0) return 0;
     if (!Z || !z_off || !n_sup || !d2_off || !mu_ws || !nrm_ws || !D2 || d <= 0 || d % 4) return ADKF_ERR_BADARG;
+    if (stat < ADKF_STAT_SQDIST || stat > ADKF_STAT_TANIMOTO) return ADKF_ERR_BADARG;
     cudaStream_t s = (cudaStream_t)stream;
+    (void)cudaGetLastError();
     CUtensorMap mz;
     int rc = make_map_2d(&mz, Z, total_rows, d, d, 0);
     if (rc) return rc;
     rc = gemm_attr<false, false>();
     if (rc) return rc;
-    launch_center_stats(Z, d, T, z_off, n_sup, max_n, mu_ws, nrm_ws, s);
+    launch_center_stats(Z, d, T, z_off, n_sup, max_n, mu_ws, nrm_ws, s, stat == ADKF_STAT_SQDIST);
     GemmEpilogue ep = {};
     ep.mode = 1; ep.out = D2; ep.K = d; ep.z_off = z_off; ep.n_sup = n_sup; ep.d2_off = d2_off; ep.mu = mu_ws;
-    ep.nrm = nrm_ws; ep.qq_block = qq_block; ep.kb_per_split = (d + kBK - 1) / kBK;
+    ep.nrm = nrm_ws; ep.qq_block = qq_block; ep.kb_per_split = (d + kBK - 1) / kBK; ep.stat = stat;
     const int nt = (max_n + kBM - 1) / kBM;
     gemm_tf32x3_kernel<false, false><<<dim3(nt, nt, T), kGemmThreads, kGemmSmem, s>>>(mz, mz, ep);
+    if (stat != ADKF_STAT_SQDIST && !qq_block) launch_pairstat_diag(stat, T, z_off, d2_off, max_n, nrm_ws, D2, s);
     adkf_count_launches(3);
     ADKF_LAUNCH_CHECK();
     return 0;
+}
+
+extern "C" int adkf_gram_sqdist_tc(const float* Z, int32_t d, int32_t T, int64_t total_rows, const int32_t* z_off,
+                                   const int32_t* n_sup, const int64_t* d2_off, int32_t max_n, int32_t qq_block,
+                                   float* mu_ws, float* nrm_ws, float* D2, void* stream) {
+    return adkf_gram_pairstat_tc(ADKF_STAT_SQDIST, Z, d, T, total_rows, z_off, n_sup, d2_off, max_n, qq_block, mu_ws,
+                                 nrm_ws, D2, stream);
 }

@@ -25,7 +25,10 @@ constexpr int kSmemBudgetFloats = 50 * 1024;  // 200 KB of matrices+vectors in s
 
 struct KParts { float K, Ku, Kl, Kll, Kul; };
 
-// K = s k(u; l) and its partials w.r.t. u = squared distance and l (see oracle/gp_closed_form.py::kernel_parts)
+// K = s k(u; l) and its partials w.r.t. the pair statistic u and the third hyperparameter l (see
+// oracle/gp_closed_form.py::kernel_parts).  u is the squared distance for the stationary kernels, the plain dot
+// product for linear / polynomial / cossim (gpytorch LinearKernel: v x.x'; PolynomialKernel: (x.x' + c)^p;
+// fs_mol/utils/gp_utils.py:22-43) and the Tanimoto similarity itself for the Tanimoto kernel (gp_utils.py:106-134).
 __device__ __forceinline__ KParts kernel_parts(float u, float s, float l, int kind) {
     KParts p;
     if (kind == ADKF_KERNEL_MATERN52) {
@@ -39,7 +42,7 @@ __device__ __forceinline__ KParts kernel_parts(float u, float s, float l, int ki
         p.Kl = s * (5.f / 3.f) * (r2 / l) * h * e;
         p.Kll = -(5.f / 3.f) * s * il2 * e * r2 * (3.f + 3.f * kSqrt5 * r - 5.f * r2);
         p.Kul = (5.f / 6.f) * s * il2 / l * e * (2.f + 2.f * kSqrt5 * r - 5.f * r2);
-    } else {
+    } else if (kind == ADKF_KERNEL_RBF) {
         const float il2 = 1.f / (l * l);
         const float k = expf(-0.5f * u * il2);
         p.K = s * k;
@@ -47,6 +50,15 @@ __device__ __forceinline__ KParts kernel_parts(float u, float s, float l, int ki
         p.Kl = p.K * u * il2 / l;
         p.Kll = p.K * (u * u * il2 * il2 * il2 - 3.f * u * il2 * il2);
         p.Kul = (p.K * il2 / l) * (1.f - 0.5f * u * il2);
+    } else if (kind == ADKF_KERNEL_LINEAR) {          // K = s v u, l = v
+        p.K = s * l * u; p.Ku = s * l; p.Kl = s * u; p.Kll = 0.f; p.Kul = s;
+    } else if (kind == ADKF_KERNEL_POLY1) {           // K = s (u + c), l = c
+        p.K = s * (u + l); p.Ku = s; p.Kl = s; p.Kll = 0.f; p.Kul = 0.f;
+    } else if (kind == ADKF_KERNEL_POLY2) {           // K = s (u + c)^2
+        const float b = u + l;
+        p.K = s * b * b; p.Ku = 2.f * s * b; p.Kl = p.Ku; p.Kll = 2.f * s; p.Kul = 2.f * s;
+    } else {                                          // cossim (variance fixed to 1) and Tanimoto: K = s u, no third parameter
+        p.K = s * u; p.Ku = s; p.Kl = 0.f; p.Kll = 0.f; p.Kul = 0.f;
     }
     return p;
 }
@@ -55,7 +67,24 @@ __device__ __forceinline__ float kernel_only(float u, float s, float l, int kind
         const float r = sqrtf(fmaxf(u / (l * l), 1e-30f));
         return s * (1.f + kSqrt5 * r + (5.f / 3.f) * r * r) * expf(-kSqrt5 * r);
     }
-    return s * expf(-0.5f * u / (l * l));
+    if (kind == ADKF_KERNEL_RBF) return s * expf(-0.5f * u / (l * l));
+    if (kind == ADKF_KERNEL_LINEAR) return s * l * u;
+    if (kind == ADKF_KERNEL_POLY1) return s * (u + l);
+    if (kind == ADKF_KERNEL_POLY2) return s * (u + l) * (u + l);
+    return s * u;
+}
+__device__ __forceinline__ bool kind_is_stationary(int kind) { return kind == ADKF_KERNEL_MATERN52 || kind == ADKF_KERNEL_RBF; }
+// parameters the inner problem optimises: bit i <-> raw parameter i.  cossim / Tanimoto have no third parameter; the
+// caller can freeze more through the ADKF_KERNEL_FREEZE_* bits of the `kernel` argument (ExactTanimotoGP keeps the noise
+// fixed for classification, gp_utils.py:143).
+__device__ __forceinline__ int free_mask_of(int kernel_arg) {
+    const int kind = kernel_arg & 0xff;
+    int m = 7;
+    if (kind == ADKF_KERNEL_COSSIM || kind == ADKF_KERNEL_TANIMOTO) m &= ~4;
+    if (kernel_arg & ADKF_KERNEL_FREEZE_NOISE) m &= ~1;
+    if (kernel_arg & ADKF_KERNEL_FREEZE_OUTPUTSCALE) m &= ~2;
+    if (kernel_arg & ADKF_KERNEL_FREEZE_THIRD) m &= ~4;
+    return m;
 }
 
 struct Hyper { float sig2, s, l, t[3], c[3]; };
@@ -174,6 +203,7 @@ struct GpProblem {
     int kind;
     float noise_loc, ls_loc;
     int has_lsp;
+    int free_mask;   // bit i set: raw parameter i is optimised (frozen ones get g = 0, H row/col = identity)
 };
 
 // A (+ jitter) -> Cholesky in M1 with the psd_safe_cholesky retry policy.  Returns false if not PD after
@@ -217,8 +247,8 @@ __device__ bool gp_eval_f(const GpProblem& pb, const float* phi, float* M1, int 
     block_sum_multi<2>(part, sh.red, sh.sums);
     if (threadIdx.x == 0) {
         const float nll = 0.5f * (float)sh.sums[0] + (float)sh.sums[1] + n * kHalfLog2Pi;
-        float lp, d1, d2, lpl = 0.f;
-        lognormal_terms(h.sig2, pb.noise_loc, lp, d1, d2);
+        float lp = 0.f, d1, d2, lpl = 0.f;
+        if (!isnan(pb.noise_loc)) lognormal_terms(h.sig2, pb.noise_loc, lp, d1, d2);   // NaN loc = no noise prior
         if (pb.has_lsp) { float a, b; lognormal_terms(h.l, pb.ls_loc, lpl, a, b); }
         sh.f_try = (nll - lp - lpl) / n;
     }
@@ -305,8 +335,8 @@ __device__ bool gp_eval_full(const GpProblem& pb, const float* phi, float* M1, f
         const double trPPS = S[7], trPSPS = S[8], wu = S[9], aSa = S[10], uPu = S[11];
         const double sig2 = h.sig2, s = h.s;
         const float nll = (float)(0.5 * ya + 0.5 * logdet + n * (double)kHalfLog2Pi);
-        float lp, d1n, d2n, lpl = 0.f, d1l = 0.f, d2l = 0.f;
-        lognormal_terms(h.sig2, pb.noise_loc, lp, d1n, d2n);
+        float lp = 0.f, d1n = 0.f, d2n = 0.f, lpl = 0.f, d1l = 0.f, d2l = 0.f;
+        if (!isnan(pb.noise_loc)) lognormal_terms(h.sig2, pb.noise_loc, lp, d1n, d2n);   // bo_utils.py:425-430: optional
         if (pb.has_lsp) lognormal_terms(h.l, pb.ls_loc, lpl, d1l, d2l);
         sh.nll = nll;
         sh.logdet = logdet;
@@ -330,6 +360,15 @@ __device__ bool gp_eval_full(const GpProblem& pb, const float* phi, float* M1, f
                     if (i == j) v += h.c[i] * gp[i];
                     sh.H[i * 3 + j] = (float)v;
                 }
+        }
+        for (int i = 0; i < 3; ++i) {
+            if (pb.free_mask & (1 << i)) continue;
+            sh.g[i] = 0.f;
+            sh.g_psi[i] = 0.f;
+            if (want_hess) {
+                for (int j = 0; j < 3; ++j) sh.H[i * 3 + j] = sh.H[j * 3 + i] = 0.f;
+                sh.H[i * 3 + i] = 1.f;
+            }
         }
     }
     __syncthreads();
@@ -466,21 +505,27 @@ gp_fit_kernel(const int32_t* __restrict__ z_off, const int32_t* __restrict__ n_s
     pb.ldd = N;
     pb.D2 = D2 + d2_off[t];
     pb.y = y + z_off[t];
-    pb.kind = kind;
+    pb.kind = kind & 0xff;
+    pb.free_mask = free_mask_of(kind);
     pb.noise_loc = noise_prior_loc;
     bool in_smem;
     Carve cv = carve_workspace(pb.n, smem_f, ws + ws_off[t], in_smem);
     float* auxt = aux + (size_t)t * ADKF_AUX;
     int st = ADKF_ST_OK;
+    const bool stationary = kind_is_stationary(pb.kind);
+    if (!stationary) ls_prior = 0;   // the lengthscale prior / median initialisation only exist for matern and rbf
 
-    median_lengthscale(pb, sh);
+    if (stationary) median_lengthscale(pb, sh);   // (adaptive_dkt.py:92-101)
+    else if (threadIdx.x == 0) sh.l0 = 0.6931471805599453f;   // softplus(0): gpytorch's default variance / offset
+    __syncthreads();
     if (threadIdx.x == 0) {
         if (ls_prior == 2) sh.ls_loc = auxt[ADKF_AUX_LS_LOC];
         else sh.ls_loc = logf(sh.l0) + kTau * kTau;
         if (init_mode == 1) {
             sh.phi[0] = inv_softplusf(noise_init - 1e-4f);
             sh.phi[1] = 0.f;
-            sh.phi[2] = inv_softplusf(sh.l0);
+            sh.phi[2] = stationary ? inv_softplusf(sh.l0) : 0.f;
+            if (pb.kind == ADKF_KERNEL_COSSIM || pb.kind == ADKF_KERNEL_TANIMOTO) sh.phi[2] = 0.5413248546129181f;  // softplus^-1(1)
         } else {
             for (int i = 0; i < 3; ++i) sh.phi[i] = phi_io[t * 3 + i];
         }
@@ -577,7 +622,9 @@ gp_predict_kernel(const int32_t* __restrict__ z_off, const int32_t* __restrict__
     pb.ldd = N;
     pb.D2 = D2 + d2_off[t];
     pb.y = y + z_off[t];
+    kind &= 0xff;
     pb.kind = kind;
+    pb.free_mask = 7;
     const int n = pb.n, m = N - n;
     bool in_smem;
     Carve cv = carve_workspace(n, smem_f, ws + ws_off[t], in_smem);
@@ -636,7 +683,8 @@ gp_predict_kernel(const int32_t* __restrict__ z_off, const int32_t* __restrict__
         q = warp_sum(q);
         if (lane == 0) {
             mean[z_off[t] + n + j] = mu;
-            var[z_off[t] + n + j] = h.s + h.sig2 - q;
+            // prior variance k(x*, x*) from the diagonal of the pair statistic (0 -> s for the stationary kernels)
+            var[z_off[t] + n + j] = kernel_only(d2row[n + j], h.s, h.l, kind) + h.sig2 - q;
         }
         __syncwarp();
     }
@@ -665,9 +713,12 @@ gp_ift_kernel(const int32_t* __restrict__ z_off, const int32_t* __restrict__ n_s
     pb.ldd = N;
     pb.D2 = D2t;
     pb.y = yt;
+    pb.free_mask = free_mask_of(kind);
+    kind &= 0xff;
     pb.kind = kind;
     pb.noise_loc = noise_prior_loc;
     float* auxt = aux + (size_t)t * ADKF_AUX;
+    if (!kind_is_stationary(kind)) ls_prior = 0;
     pb.has_lsp = ls_prior != 0;
     pb.ls_loc = auxt[ADKF_AUX_LS_LOC];
     const int n = pb.n;
@@ -757,6 +808,7 @@ gp_ift_kernel(const int32_t* __restrict__ z_off, const int32_t* __restrict__ n_s
         sh.dF[0] = h.t[0] * (float)sh.sums[1];
         sh.dF[1] = h.t[1] * (float)(sh.sums[2] / h.s);
         sh.dF[2] = h.t[2] * (float)sh.sums[3];
+        for (int i = 0; i < 3; ++i) if (!(pb.free_mask & (1 << i))) sh.dF[i] = 0.f;   // frozen: not an inner variable
         bool solved = solve3_general(sh.H, sh.dF, sh.v);
         sh.flag = 0;
         if (!solved) { sh.v[0] = sh.v[1] = sh.v[2] = 0.f; sh.flag = 1; }
@@ -891,7 +943,7 @@ extern "C" int adkf_gp_fit(int32_t T, const int32_t* z_off, const int32_t* n_sup
                            int64_t ws_floats, void* stream) {
     if (T <= 0) return 0;
     if (!z_off || !n_sup || !d2_off || !D2 || !y || !phi_io || !aux || !status || !ws) return ADKF_ERR_BADARG;
-    if (kernel != ADKF_KERNEL_MATERN52 && kernel != ADKF_KERNEL_RBF) return ADKF_ERR_BADARG;
+    if ((kernel & 0xff) < 0 || (kernel & 0xff) > ADKF_KERNEL_TANIMOTO) return ADKF_ERR_BADARG;
     cudaStream_t s = (cudaStream_t)stream;
     int e = set_smem_attr((const void*)gp_fit_kernel);
     if (e) return e;

@@ -15,6 +15,16 @@
 
 namespace adkf {
 
+// rows of stat != SQDIST that the tile kernels skip (query x query block in meta-test mode) still need their diagonal:
+// the predictive variance reads k(x*, x*) from it.  dot: |z|^2, Tanimoto: 1.
+__global__ void pairstat_diag_kernel(int stat, const int32_t* __restrict__ z_off, const int64_t* __restrict__ d2_off,
+                                     const float* __restrict__ nrm, float* __restrict__ D2) {
+    const int t = blockIdx.y;
+    const int r0 = z_off[t], N = z_off[t + 1] - r0;
+    for (int r = blockIdx.x * blockDim.x + threadIdx.x; r < N; r += gridDim.x * blockDim.x)
+        D2[d2_off[t] + (size_t)r * N + r] = (stat == ADKF_STAT_DOT) ? nrm[r0 + r] : 1.f;
+}
+
 constexpr int kTile = 64;
 constexpr int kBK = 16;
 constexpr int kPad = 4;
@@ -51,7 +61,7 @@ __global__ void row_norm_kernel(const float* __restrict__ Z, int d, const int32_
 __global__ void __launch_bounds__(256)
 sqdist_tile_kernel(const float* __restrict__ Z, int d, const int32_t* __restrict__ z_off,
                    const int32_t* __restrict__ n_sup, const int64_t* __restrict__ d2_off, int qq_block,
-                   const float* __restrict__ mu, const float* __restrict__ nrm, float* __restrict__ D2) {
+                   const float* __restrict__ mu, const float* __restrict__ nrm, float* __restrict__ D2, int stat) {
     const int t = blockIdx.z;
     const int r0 = z_off[t], N = z_off[t + 1] - r0, n = n_sup[t];
     const int ti = blockIdx.y, tj = blockIdx.x;
@@ -107,8 +117,7 @@ sqdist_tile_kernel(const float* __restrict__ Z, int d, const int32_t* __restrict
         for (int j = 0; j < 4; ++j) {
             const int c = col0 + tx * 4 + j;
             if (c >= N) continue;
-            float v = fmaxf(ni + nrm[r0 + c] - 2.f * acc[i][j], 0.f);
-            if (r == c) v = 0.f;
+            const float v = pairstat_value(stat, ni, nrm[r0 + c], acc[i][j], r == c);
             Dt[(size_t)r * N + c] = v;
             if (ti != tj) Dt[(size_t)c * N + r] = v;
         }
@@ -119,7 +128,7 @@ sqdist_tile_kernel(const float* __restrict__ Z, int d, const int32_t* __restrict
 __global__ void __launch_bounds__(256)
 sqdist_bwd_kernel(const float* __restrict__ Z, int d, const int32_t* __restrict__ z_off,
                   const int64_t* __restrict__ d2_off, const float* __restrict__ Wm, const float* __restrict__ mu,
-                  float scale, float* __restrict__ dZ) {
+                  float scale, float* __restrict__ dZ, int stat) {
     const int t = blockIdx.z;
     const int r0 = z_off[t], N = z_off[t + 1] - r0;
     const int row0 = blockIdx.y * kTile, c0 = blockIdx.x * kTile;
@@ -175,7 +184,9 @@ sqdist_bwd_kernel(const float* __restrict__ Z, int d, const int32_t* __restrict_
             const int c = c0 + tx * 4 + j;
             if (c >= d) continue;
             const float zac = Z[(size_t)(r0 + a) * d + c] - m[c];
-            dZ[(size_t)(r0 + a) * d + c] = scale * 4.f * (rs[i] * zac - acc[i][j]);
+            // sqdist: du_ab = 2 (z_a - z_b).(dz_a - dz_b);  dot: du_ab = z_b.dz_a + z_a.dz_b   (Wm symmetric)
+            dZ[(size_t)(r0 + a) * d + c] = (stat == ADKF_STAT_SQDIST) ? scale * 4.f * (rs[i] * zac - acc[i][j])
+                                                                      : scale * 2.f * acc[i][j];
         }
     }
 }
@@ -184,23 +195,51 @@ sqdist_bwd_kernel(const float* __restrict__ Z, int d, const int32_t* __restrict_
 
 using namespace adkf;
 
-// centring statistics shared with the tensor-core Gram (gemm_tf32x3.cu)
+// centring statistics shared with the tensor-core Gram (gemm_tf32x3.cu); center = 0 -> mu = 0, nrm = |z|^2
 void adkf::launch_center_stats(const float* Z, int d, int T, const int32_t* z_off, const int32_t* n_sup, int max_n,
-                               float* mu_ws, float* nrm_ws, cudaStream_t s) {
-    task_mean_kernel<<<dim3((d + 255) / 256, T), 256, 0, s>>>(Z, d, z_off, n_sup, mu_ws);
+                               float* mu_ws, float* nrm_ws, cudaStream_t s, int center) {
+    if (center) task_mean_kernel<<<dim3((d + 255) / 256, T), 256, 0, s>>>(Z, d, z_off, n_sup, mu_ws);
+    else cudaMemsetAsync(mu_ws, 0, sizeof(float) * (size_t)T * d, s);
     row_norm_kernel<<<dim3((max_n + 7) / 8, T), 256, 0, s>>>(Z, d, z_off, mu_ws, nrm_ws);
+}
+
+void adkf::launch_pairstat_diag(int stat, int T, const int32_t* z_off, const int64_t* d2_off, int max_n, const float* nrm,
+                                float* D2, cudaStream_t s) {
+    pairstat_diag_kernel<<<dim3((max_n + 255) / 256, T), 256, 0, s>>>(stat, z_off, d2_off, nrm, D2);
+}
+
+extern "C" int adkf_gram_pairstat(int32_t stat, const float* Z, int32_t d, int32_t T, const int32_t* z_off,
+                                  const int32_t* n_sup, const int64_t* d2_off, int32_t max_n, int32_t qq_block,
+                                  float* mu_ws, float* nrm_ws, float* D2, void* stream) {
+    if (T <= 0 || max_n <= 0) return 0;
+    if (!Z || !z_off || !n_sup || !d2_off || !mu_ws || !nrm_ws || !D2 || d <= 0) return ADKF_ERR_BADARG;
+    if (stat < ADKF_STAT_SQDIST || stat > ADKF_STAT_TANIMOTO) return ADKF_ERR_BADARG;
+    cudaStream_t s = (cudaStream_t)stream;
+    launch_center_stats(Z, d, T, z_off, n_sup, max_n, mu_ws, nrm_ws, s, stat == ADKF_STAT_SQDIST);
+    const int nt = (max_n + kTile - 1) / kTile;
+    sqdist_tile_kernel<<<dim3(nt, nt, T), 256, 0, s>>>(Z, d, z_off, n_sup, d2_off, qq_block, mu_ws, nrm_ws, D2, stat);
+    if (stat != ADKF_STAT_SQDIST && !qq_block) launch_pairstat_diag(stat, T, z_off, d2_off, max_n, nrm_ws, D2, s);
+    adkf_count_launches(3);
+    ADKF_LAUNCH_CHECK();
+    return 0;
 }
 
 extern "C" int adkf_gram_sqdist(const float* Z, int32_t d, int32_t T, const int32_t* z_off,
                                 const int32_t* n_sup, const int64_t* d2_off, int32_t max_n, int32_t qq_block,
                                 float* mu_ws, float* nrm_ws, float* D2, void* stream) {
+    return adkf_gram_pairstat(ADKF_STAT_SQDIST, Z, d, T, z_off, n_sup, d2_off, max_n, qq_block, mu_ws, nrm_ws, D2, stream);
+}
+
+extern "C" int adkf_gram_pairstat_bwd(int32_t stat, const float* Z, int32_t d, int32_t T, const int32_t* z_off,
+                                      const int64_t* d2_off, int32_t max_n, const float* Wm, const float* mu_ws,
+                                      float scale, float* dZ, void* stream) {
     if (T <= 0 || max_n <= 0) return 0;
-    if (!Z || !z_off || !n_sup || !d2_off || !mu_ws || !nrm_ws || !D2 || d <= 0) return ADKF_ERR_BADARG;
+    if (!Z || !z_off || !d2_off || !Wm || !mu_ws || !dZ || d <= 0) return ADKF_ERR_BADARG;
+    if (stat != ADKF_STAT_SQDIST && stat != ADKF_STAT_DOT) return ADKF_ERR_BADARG;   // Tanimoto inputs are fixed fingerprints
     cudaStream_t s = (cudaStream_t)stream;
-    launch_center_stats(Z, d, T, z_off, n_sup, max_n, mu_ws, nrm_ws, s);
-    const int nt = (max_n + kTile - 1) / kTile;
-    sqdist_tile_kernel<<<dim3(nt, nt, T), 256, 0, s>>>(Z, d, z_off, n_sup, d2_off, qq_block, mu_ws, nrm_ws, D2);
-    adkf_count_launches(3);
+    sqdist_bwd_kernel<<<dim3((d + kTile - 1) / kTile, (max_n + kTile - 1) / kTile, T), 256, 0, s>>>(
+        Z, d, z_off, d2_off, Wm, mu_ws, scale, dZ, stat);
+    adkf_count_launches(1);
     ADKF_LAUNCH_CHECK();
     return 0;
 }
@@ -208,12 +247,5 @@ extern "C" int adkf_gram_sqdist(const float* Z, int32_t d, int32_t T, const int3
 extern "C" int adkf_gram_sqdist_bwd(const float* Z, int32_t d, int32_t T, const int32_t* z_off,
                                     const int64_t* d2_off, int32_t max_n, const float* Wm, const float* mu_ws,
                                     float scale, float* dZ, void* stream) {
-    if (T <= 0 || max_n <= 0) return 0;
-    if (!Z || !z_off || !d2_off || !Wm || !mu_ws || !dZ || d <= 0) return ADKF_ERR_BADARG;
-    cudaStream_t s = (cudaStream_t)stream;
-    sqdist_bwd_kernel<<<dim3((d + kTile - 1) / kTile, (max_n + kTile - 1) / kTile, T), 256, 0, s>>>(
-        Z, d, z_off, d2_off, Wm, mu_ws, scale, dZ);
-    adkf_count_launches(1);
-    ADKF_LAUNCH_CHECK();
-    return 0;
+    return adkf_gram_pairstat_bwd(ADKF_STAT_SQDIST, Z, d, T, z_off, d2_off, max_n, Wm, mu_ws, scale, dZ, stream);
 }

@@ -19,7 +19,7 @@ from . import ops
 
 NOISE_FLOOR = 1e-4            # gpytorch GreaterThan(1e-4) on the likelihood noise
 PRIOR_SCALE = 0.25            # LogNormal scale used for both priors (adaptive_dkt.py:96,111-119)
-SUPPORTED_KERNELS = ("matern", "rbf", "RBF")
+SUPPORTED_KERNELS = ("matern", "rbf", "RBF", "linear", "poli1", "poli2", "cossim", "tanimoto")
 
 
 def noise_init(use_numeric_labels: bool) -> float:
@@ -35,8 +35,8 @@ def noise_prior_loc(use_numeric_labels: bool) -> float:
 def check_kernel(kernel: str) -> str:
     if kernel not in SUPPORTED_KERNELS:
         raise NotImplementedError(
-            f"gp_kernel={kernel!r}: the sm_100a GP kernels implement 'matern' (nu=2.5) and 'rbf'; there is no "
-            "gpytorch / CPU fallback")
+            f"gp_kernel={kernel!r}: the sm_100a GP kernels implement {SUPPORTED_KERNELS}; there is no gpytorch / CPU "
+            "fallback")
     return kernel
 
 
@@ -52,39 +52,42 @@ class BatchedExactGP:
     of a one-CTA-per-task kernel.  `Z` is read as-is (detach before passing if it carries a graph)."""
 
     def __init__(self, Z: torch.Tensor, y: torch.Tensor, layout: ops.TaskLayout, kernel: str = "matern",
-                 use_numeric_labels: bool = False, use_lengthscale_prior: bool = True, qq_block: bool = False):
+                 use_numeric_labels: bool = False, use_lengthscale_prior: bool = True, qq_block: bool = False,
+                 freeze: int = 0):
         self.kernel = check_kernel(kernel)
+        self.stat = ops.KERNEL_STATS[kernel]
+        self.karg = ops.kernel_arg(kernel, freeze)      # family id | ADKF_KERNEL_FREEZE_* bits
         self.Z, self.y, self.layout = Z.detach().contiguous(), y.contiguous(), layout
         self.noise_init = noise_init(use_numeric_labels)
         self.noise_loc = noise_prior_loc(use_numeric_labels)
-        self.ls_prior = 1 if use_lengthscale_prior else 0
+        self.ls_prior = 1 if (use_lengthscale_prior and self.stat == ops.STAT_SQDIST) else 0
         self.qq_block = qq_block
-        self.sq = ops.gp_sqdist(self.Z, layout, qq_block=qq_block)
+        self.sq = ops.gp_sqdist(self.Z, layout, qq_block=qq_block, stat=self.stat)
 
     # reinit_gp_params: phi0 = (inv_softplus(noise_init - 1e-4), 0, inv_softplus(l0)), prior loc from l0
     def init(self) -> FitResult:
-        return FitResult(*ops.gp_fit(self.layout, self.sq.D2, self.y, self.kernel, self.noise_init, self.noise_loc,
+        return FitResult(*ops.gp_fit(self.layout, self.sq.D2, self.y, self.karg, self.noise_init, self.noise_loc,
                                      ls_prior=self.ls_prior, init_mode=1, max_iter=0))
 
     def fit(self, start: Optional[FitResult] = None, max_iter: int = 50, gtol: float = 2e-6) -> FitResult:
         """Inner fit of phi on the support sets.  start=None: reference initialisation."""
         if start is None:
-            return FitResult(*ops.gp_fit(self.layout, self.sq.D2, self.y, self.kernel, self.noise_init,
+            return FitResult(*ops.gp_fit(self.layout, self.sq.D2, self.y, self.karg, self.noise_init,
                                          self.noise_loc, ls_prior=self.ls_prior, init_mode=1, max_iter=max_iter,
                                          gtol=gtol))
-        return FitResult(*ops.gp_fit(self.layout, self.sq.D2, self.y, self.kernel, self.noise_init, self.noise_loc,
+        return FitResult(*ops.gp_fit(self.layout, self.sq.D2, self.y, self.karg, self.noise_init, self.noise_loc,
                                      ls_prior=2 if self.ls_prior else 0, init_mode=0, max_iter=max_iter, gtol=gtol,
                                      phi=start.phi, aux=start.aux))
 
     def evaluate(self, phi: torch.Tensor, aux: Optional[torch.Tensor] = None) -> FitResult:
         """f = -MLL, its gradient and Hessian at fixed phi (aux F / G / H)."""
-        return FitResult(*ops.gp_fit(self.layout, self.sq.D2, self.y, self.kernel, self.noise_init, self.noise_loc,
+        return FitResult(*ops.gp_fit(self.layout, self.sq.D2, self.y, self.karg, self.noise_init, self.noise_loc,
                                      ls_prior=(2 if aux is not None else 1) if self.ls_prior else 0, init_mode=0,
                                      max_iter=0, phi=phi, aux=aux))
 
     def predict(self, phi: torch.Tensor):
         """(mean, variance, status): rows aligned with Z; only query rows are written (likelihood noise included)."""
-        return ops.gp_predict(self.layout, self.sq.D2, self.y, self.kernel, phi)
+        return ops.gp_predict(self.layout, self.sq.D2, self.y, self.karg, phi)
 
     def hypergradient(self, fit: FitResult, mode: int = 0):
         """IFT hypergradient w.r.t. the features.  mode 0: dL/dZ = dF/dZ - d/deps df/dZ(phi + eps v)
@@ -92,9 +95,11 @@ class BatchedExactGP:
         Returns (dZ [rows,d], aux with F / dF/dphi / H / v, status)."""
         if not self.qq_block:
             raise RuntimeError("hypergradient needs the query x query block: construct with qq_block=True")
-        Wm, aux, status = ops.gp_ift(self.layout, self.sq.D2, self.y, self.kernel, self.noise_loc, self.ls_prior,
+        Wm, aux, status = ops.gp_ift(self.layout, self.sq.D2, self.y, self.karg, self.noise_loc, self.ls_prior,
                                      fit.phi, fit.aux, mode=mode)
-        dZ = ops.gp_sqdist_bwd(self.Z, self.layout, Wm, self.sq.mu, 1.0)
+        if self.stat == ops.STAT_TANIMOTO:
+            raise NotImplementedError("the Tanimoto kernel acts on fixed fingerprints: there is no feature gradient")
+        dZ = ops.gp_sqdist_bwd(self.Z, self.layout, Wm, self.sq.mu, 1.0, stat=self.stat)
         return dZ, aux, status
 
 

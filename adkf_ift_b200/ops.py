@@ -10,7 +10,15 @@ import torch
 from . import _cabi
 from ._cabi import check, dptr, stream_ptr
 
-KERNEL_IDS = {"matern": 0, "rbf": 1, "RBF": 1}
+KERNEL_IDS = {"matern": 0, "rbf": 1, "RBF": 1, "linear": 2, "poli1": 3, "poli2": 4, "cossim": 5, "tanimoto": 6}
+STAT_SQDIST, STAT_DOT, STAT_TANIMOTO = 0, 1, 2
+KERNEL_STATS = {"matern": 0, "rbf": 0, "RBF": 0, "linear": 1, "poli1": 1, "poli2": 1, "cossim": 1, "tanimoto": 2}
+FREEZE_NOISE, FREEZE_OUTPUTSCALE, FREEZE_THIRD = 0x100, 0x200, 0x400
+
+
+def kernel_arg(kernel, freeze: int = 0) -> int:
+    """`kernel` argument of adkf_gp_fit / adkf_gp_ift: family id | ADKF_KERNEL_FREEZE_* bits."""
+    return (KERNEL_IDS[kernel] if isinstance(kernel, str) else int(kernel)) | int(freeze)
 AUX = 32
 AUX_F, AUX_G, AUX_H, AUX_L0, AUX_LS_LOC, AUX_ITERS, AUX_FOUTER, AUX_DF_DPHI, AUX_V, AUX_JITTER, AUX_NFEV = (
     0, 1, 4, 13, 14, 15, 16, 17, 20, 23, 24)
@@ -274,44 +282,42 @@ class SqDist:
     nrm: torch.Tensor
 
 
-def gp_sqdist(Z: torch.Tensor, layout: TaskLayout, qq_block: bool, impl: str = "tcgen05") -> SqDist:
-    """Per-task centred squared distances.  impl="tcgen05": 3xTF32 tensor-core Gram (default, needs d % 4 == 0);
-    impl="simt": the fp32 CUDA-core tile kernel (any d)."""
+def gp_sqdist(Z: torch.Tensor, layout: TaskLayout, qq_block: bool, impl: str = "tcgen05", stat: int = STAT_SQDIST) -> SqDist:
+    """Per-task pair statistics (stat 0: centred squared distances, 1: dot products, 2: Tanimoto similarities).
+    impl="tcgen05": 3xTF32 tensor-core Gram (default, needs d % 4 == 0); impl="simt": the fp32 CUDA-core tile
+    kernel (any d)."""
     lib = _cabi.load()
     Z = Z.contiguous()
     d = Z.shape[1]
-    if impl == "tcgen05" and d % 4 == 0 and Z.data_ptr() % 16 == 0:
-        f32 = dict(dtype=torch.float32, device=Z.device)
-        D2 = torch.zeros(max(layout.d2_total, 1), **f32)
-        mu = torch.empty(max(layout.T, 1), d, **f32)
-        nrm = torch.empty(max(layout.total_rows, 1), **f32)
-        rc = lib.adkf_gram_sqdist_tc(dptr(Z, torch.float32), d, layout.T, Z.shape[0], dptr(layout.z_off),
-                                     dptr(layout.n_sup), dptr(layout.d2_off), layout.max_n, 1 if qq_block else 0,
-                                     dptr(mu), dptr(nrm), dptr(D2), stream_ptr())
-        check(rc, "adkf_gram_sqdist_tc")
-        return SqDist(D2, mu, nrm)
     f32 = dict(dtype=torch.float32, device=Z.device)
     D2 = torch.zeros(max(layout.d2_total, 1), **f32)
     mu = torch.empty(max(layout.T, 1), d, **f32)
     nrm = torch.empty(max(layout.total_rows, 1), **f32)
-    rc = lib.adkf_gram_sqdist(dptr(Z, torch.float32), d, layout.T, dptr(layout.z_off), dptr(layout.n_sup),
-                              dptr(layout.d2_off), layout.max_n, 1 if qq_block else 0, dptr(mu), dptr(nrm), dptr(D2),
-                              stream_ptr())
-    check(rc, "adkf_gram_sqdist")
+    if impl == "tcgen05" and d % 4 == 0 and Z.data_ptr() % 16 == 0:
+        rc = lib.adkf_gram_pairstat_tc(int(stat), dptr(Z, torch.float32), d, layout.T, Z.shape[0], dptr(layout.z_off),
+                                       dptr(layout.n_sup), dptr(layout.d2_off), layout.max_n, 1 if qq_block else 0,
+                                       dptr(mu), dptr(nrm), dptr(D2), stream_ptr())
+        check(rc, "adkf_gram_pairstat_tc")
+        return SqDist(D2, mu, nrm)
+    rc = lib.adkf_gram_pairstat(int(stat), dptr(Z, torch.float32), d, layout.T, dptr(layout.z_off), dptr(layout.n_sup),
+                                dptr(layout.d2_off), layout.max_n, 1 if qq_block else 0, dptr(mu), dptr(nrm), dptr(D2),
+                                stream_ptr())
+    check(rc, "adkf_gram_pairstat")
     return SqDist(D2, mu, nrm)
 
 
-def gp_sqdist_bwd(Z, layout: TaskLayout, Wm, mu, scale: float) -> torch.Tensor:
+def gp_sqdist_bwd(Z, layout: TaskLayout, Wm, mu, scale: float, stat: int = STAT_SQDIST) -> torch.Tensor:
     lib = _cabi.load()
     Z = Z.contiguous()
     dZ = torch.zeros_like(Z)
-    rc = lib.adkf_gram_sqdist_bwd(dptr(Z, torch.float32), Z.shape[1], layout.T, dptr(layout.z_off), dptr(layout.d2_off),
-                                  layout.max_n, dptr(Wm, torch.float32), dptr(mu), float(scale), dptr(dZ), stream_ptr())
-    check(rc, "adkf_gram_sqdist_bwd")
+    rc = lib.adkf_gram_pairstat_bwd(int(stat), dptr(Z, torch.float32), Z.shape[1], layout.T, dptr(layout.z_off),
+                                    dptr(layout.d2_off), layout.max_n, dptr(Wm, torch.float32), dptr(mu), float(scale),
+                                    dptr(dZ), stream_ptr())
+    check(rc, "adkf_gram_pairstat_bwd")
     return dZ
 
 
-def gp_fit(layout: TaskLayout, D2, y, kernel: str, noise_init: float, noise_prior_loc: float, ls_prior: int = 1,
+def gp_fit(layout: TaskLayout, D2, y, kernel, noise_init: float, noise_prior_loc: float, ls_prior: int = 1,
            init_mode: int = 1, max_iter: int = 50, gtol: float = 2e-6, phi: Optional[torch.Tensor] = None,
            aux: Optional[torch.Tensor] = None):
     """Returns (phi [T,3] raw, aux [T,32], status [T] int32)."""
@@ -329,14 +335,14 @@ def gp_fit(layout: TaskLayout, D2, y, kernel: str, noise_init: float, noise_prio
     nws = layout.ws_floats(0)
     ws = torch.empty(nws, dtype=torch.float32, device=dev)
     rc = lib.adkf_gp_fit(layout.T, dptr(layout.z_off), dptr(layout.n_sup), dptr(layout.d2_off),
-                         dptr(D2, torch.float32), dptr(y, torch.float32), KERNEL_IDS[kernel], float(noise_init),
+                         dptr(D2, torch.float32), dptr(y, torch.float32), kernel_arg(kernel), float(noise_init),
                          float(noise_prior_loc), int(ls_prior), int(init_mode), int(max_iter), float(gtol),
                          dptr(phi), dptr(aux), dptr(status), dptr(ws), nws, stream_ptr())
     check(rc, "adkf_gp_fit")
     return phi, aux, status
 
 
-def gp_predict(layout: TaskLayout, D2, y, kernel: str, phi):
+def gp_predict(layout: TaskLayout, D2, y, kernel, phi):
     """Returns (mean, var) aligned with the Z rows (only the query rows are written) and status."""
     lib = _cabi.load()
     dev = D2.device
@@ -346,14 +352,14 @@ def gp_predict(layout: TaskLayout, D2, y, kernel: str, phi):
     nws = layout.ws_floats(1)
     ws = torch.empty(nws, dtype=torch.float32, device=dev)
     rc = lib.adkf_gp_predict(layout.T, dptr(layout.z_off), dptr(layout.n_sup), dptr(layout.d2_off),
-                             dptr(D2, torch.float32), dptr(y, torch.float32), KERNEL_IDS[kernel],
+                             dptr(D2, torch.float32), dptr(y, torch.float32), kernel_arg(kernel) & 0xff,
                              dptr(phi.contiguous(), torch.float32), dptr(mean), dptr(var), dptr(status), dptr(ws), nws,
                              stream_ptr())
     check(rc, "adkf_gp_predict")
     return mean, var, status
 
 
-def gp_ift(layout: TaskLayout, D2, y, kernel: str, noise_prior_loc: float, ls_prior: int, phi, aux,
+def gp_ift(layout: TaskLayout, D2, y, kernel, noise_prior_loc: float, ls_prior: int, phi, aux,
            ignore_grad_correction: bool = False, mode=None):
     """Returns (Wm same layout as D2, aux updated, status)."""
     lib = _cabi.load()
@@ -366,7 +372,7 @@ def gp_ift(layout: TaskLayout, D2, y, kernel: str, noise_prior_loc: float, ls_pr
     nws = layout.ws_floats(2)
     ws = torch.empty(nws, dtype=torch.float32, device=dev)
     rc = lib.adkf_gp_ift(layout.T, dptr(layout.z_off), dptr(layout.n_sup), dptr(layout.d2_off),
-                         dptr(D2, torch.float32), dptr(y, torch.float32), KERNEL_IDS[kernel], float(noise_prior_loc),
+                         dptr(D2, torch.float32), dptr(y, torch.float32), kernel_arg(kernel), float(noise_prior_loc),
                          int(ls_prior), int(mode), dptr(phi.contiguous(), torch.float32),
                          dptr(aux), dptr(Wm), dptr(status), dptr(ws), nws, stream_ptr())
     check(rc, "adkf_gp_ift")
@@ -463,3 +469,42 @@ def linear_tc(x: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.Tensor
     elif ACT_IDS[act] == 2:
         y = torch.nn.functional.leaky_relu(y, 0.01)
     return y
+
+
+# --------------------------------------------------------------------------------------------------
+# large-pool GP path: blocked Cholesky joint NLL, expected improvement over a pool
+# --------------------------------------------------------------------------------------------------
+def gp_joint_nll_blocked(U: torch.Tensor, N: int, n_sup: int, y: torch.Tensor, kernel, phi: torch.Tensor):
+    """(out4, status): out4 = [NLL(all N rows), NLL(support rows), F = -log p(y_q | y_s), log det J] for ONE task whose
+    pair statistics U [N*N] came from gp_sqdist(..., qq_block=True).  Follows psd_safe_cholesky's jitter ladder
+    (0, 1e-6, 1e-5, 1e-4): the status word is read back between attempts (evaluation path, not the training loop)."""
+    lib = _cabi.load()
+    dev = U.device
+    nws = int(lib.adkf_chol_blocked_ws_floats(N))
+    ws = torch.empty(nws, dtype=torch.float32, device=dev)
+    out = torch.zeros(4, dtype=torch.float32, device=dev)
+    status = torch.zeros(1, dtype=torch.int32, device=dev)
+    phi = phi.contiguous().view(-1)[:3]
+    for jitter in (0.0, 1e-6, 1e-5, 1e-4):
+        rc = lib.adkf_gp_joint_nll_blocked(dptr(U, torch.float32), int(N), int(n_sup), dptr(y.contiguous(), torch.float32),
+                                           kernel_arg(kernel) & 0xff, dptr(phi, torch.float32), float(jitter), dptr(ws), nws,
+                                           dptr(out), dptr(status), stream_ptr())
+        check(rc, "adkf_gp_joint_nll_blocked")
+        if int(status.item()) & ST_NOT_PD == 0:
+            if jitter > 0.0:
+                status |= ST_JITTER
+            break
+    return out, status
+
+
+def ei_pool(mean: torch.Tensor, var: torch.Tensor, noise: float, best_f: float,
+            exclude: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """Expected improvement (minimisation) of every pool molecule from the NOISY predictive mean / variance."""
+    lib = _cabi.load()
+    m = mean.numel()
+    ei = torch.empty(m, dtype=torch.float32, device=mean.device)
+    rc = lib.adkf_ei_pool(dptr(mean.contiguous(), torch.float32), dptr(var.contiguous(), torch.float32), m, float(noise),
+                          float(best_f), dptr(exclude.contiguous(), torch.uint8) if exclude is not None else ctypes.c_void_p(0),
+                          dptr(ei), stream_ptr())
+    check(rc, "adkf_ei_pool")
+    return ei

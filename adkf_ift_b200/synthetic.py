@@ -147,3 +147,21 @@ def deterministic_init_(module_or_state, seed: int = 0, alpha: float = 0.5, gain
             else:
                 val = 0.05 * u
             t.copy_(val.to(t.dtype))
+
+
+def bo_pool(seed: int = 5, pool: int = 2312, dim: int = 64, binary: bool = False):
+    """dockstring-shaped candidate pool of BASELINE config 5: `pool` molecules with `dim` features and
+    docking-score-like targets y ~ N(-8, 1.5) SORTED ascending (bo_utils.py:341 expects that order).  Features carry
+    signal about y (a smooth function of three latent coordinates) so that the GP fit is non-degenerate; binary=True
+    gives fingerprint-like 0/1 features for the Tanimoto kernel.  Returns (x [pool, dim] f32, y [pool] f32)."""
+    rng = np.random.default_rng(seed)
+    lat = rng.normal(size=(pool, 3))
+    score = lat[:, 0] + 0.5 * np.sin(2.0 * lat[:, 1]) + 0.3 * lat[:, 2] ** 2
+    order = np.argsort(score)
+    lat = lat[order]
+    y = np.sort(rng.normal(-8.0, 1.5, size=pool))
+    proj = rng.normal(size=(3, dim)) / np.sqrt(3.0)
+    x = np.tanh(lat @ proj) + 0.15 * rng.normal(size=(pool, dim))
+    if binary:
+        x = (x > 0.6).astype(np.float32)
+    return x.astype(np.float32), y.astype(np.float32)

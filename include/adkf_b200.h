@@ -34,8 +34,21 @@ extern "C" {
 #define ADKF_ST_HESS_DAMPED   8   /* inner Hessian was not PD at the optimum (IFT solve damped)    */
 
 /* GP kernel families (fs_mol/utils/gp_utils.py:22-43, :106-134) */
-#define ADKF_KERNEL_MATERN52 0
+#define ADKF_KERNEL_MATERN52 0   /* pair statistic u = centred squared distance, third parameter = lengthscale */
 #define ADKF_KERNEL_RBF      1
+#define ADKF_KERNEL_LINEAR   2   /* u = x.x',  K = s v u,       third parameter = variance v (gpytorch LinearKernel)   */
+#define ADKF_KERNEL_POLY1    3   /* u = x.x',  K = s (u + c),   third parameter = offset c (PolynomialKernel power 1)  */
+#define ADKF_KERNEL_POLY2    4   /* u = x.x',  K = s (u + c)^2                                                        */
+#define ADKF_KERNEL_COSSIM   5   /* u = x.x' of L2-normalised features, K = s u (variance fixed to 1), 2 parameters   */
+#define ADKF_KERNEL_TANIMOTO 6   /* u = Tanimoto similarity (gp_utils.py:106-117), K = s u, 2 parameters              */
+/* OR-ed into the `kernel` argument of adkf_gp_fit / adkf_gp_ift: keep that raw parameter fixed in the inner problem */
+#define ADKF_KERNEL_FREEZE_NOISE        0x100   /* ExactTanimotoGP for classification (gp_utils.py:143) */
+#define ADKF_KERNEL_FREEZE_OUTPUTSCALE  0x200
+#define ADKF_KERNEL_FREEZE_THIRD        0x400
+/* pair statistics produced by adkf_gram_pairstat* */
+#define ADKF_STAT_SQDIST   0
+#define ADKF_STAT_DOT      1
+#define ADKF_STAT_TANIMOTO 2
 
 /* layout of the per-task float32 `aux` record written by adkf_gp_fit / adkf_gp_ift (stride ADKF_AUX) */
 #define ADKF_AUX            32
@@ -142,6 +155,21 @@ int adkf_gram_sqdist_tc(const float* Z, int32_t d, int32_t T, int64_t total_rows
                         const int32_t* n_sup, const int64_t* d2_off, int32_t max_n, int32_t qq_block,
                         float* mu_ws /*[T,d]*/, float* nrm_ws /*[rows]*/, float* D2, void* stream);
 
+/* Generalisation of the two entry points above to the other kernel families' pair statistics (ADKF_STAT_*):
+ * dot products for linear / polynomial / cossim (gpytorch LinearKernel / PolynomialKernel behind
+ * fs_mol/utils/gp_utils.py:22-43) and the Tanimoto similarity (batch_tanimoto_sim, gp_utils.py:106-117).  For these the
+ * inputs are NOT centred; the diagonal (|z|^2 resp. 1) is always written because the predictive variance needs k(x*,x*).
+ * The backward exists for SQDIST and DOT (Tanimoto inputs are fixed fingerprints). */
+int adkf_gram_pairstat(int32_t stat, const float* Z, int32_t d, int32_t T, const int32_t* z_off, const int32_t* n_sup,
+                       const int64_t* d2_off, int32_t max_n, int32_t qq_block, float* mu_ws, float* nrm_ws, float* D2,
+                       void* stream);
+int adkf_gram_pairstat_tc(int32_t stat, const float* Z, int32_t d, int32_t T, int64_t total_rows, const int32_t* z_off,
+                          const int32_t* n_sup, const int64_t* d2_off, int32_t max_n, int32_t qq_block, float* mu_ws,
+                          float* nrm_ws, float* D2, void* stream);
+int adkf_gram_pairstat_bwd(int32_t stat, const float* Z, int32_t d, int32_t T, const int32_t* z_off,
+                           const int64_t* d2_off, int32_t max_n, const float* Wm, const float* mu_ws, float scale,
+                           float* dZ, void* stream);
+
 /* Dense layer forward on the same tensor-core kernel:  Y[M,N] = act(X[M,K] W[N,K]^T + bias[N])  (torch.nn.Linear of the
  * extractor: fs_mol/modules/gnn.py:79-95,477-515; graph_readout.py:224-259; fs_mol/models/adaptive_dkt.py:61-65).
  * act: 0 none, 1 relu, 2 leaky_relu(0.01).  ld* in floats (multiples of 4), pointers 16-byte aligned, bias may be NULL. */
@@ -155,7 +183,9 @@ int adkf_linear_tf32x3(const float* X, int64_t M, int32_t K, int64_t ldx, const 
  * Supported combinations: (0,0) forward y = x W^T;  (0,1) input gradient dX = dY W;  (1,1) weight gradient dW = dY^T X.
  * When the output has fewer than 148 tiles (weight gradients: K = number of nodes) and a workspace of
  * adkf_gemm_splitk_ws_floats(M,N,K) floats is passed (bias NULL, act 0, ldd == N), the contraction is split over CTAs and
- * reduced by a second, deterministic pass. */
+ * reduced by a second, deterministic pass.  act = 3 (ADKF_EPI_SUB_FROM_D): D <- D - opA(A) opB(B)^T, the trailing update
+ * of the blocked Cholesky below. */
+#define ADKF_EPI_SUB_FROM_D 3
 int adkf_gemm_tf32x3(const float* A, int32_t transA, int64_t lda, const float* B, int32_t transB, int64_t ldb,
                      int64_t M, int32_t N, int32_t K, const float* bias, int32_t act, float* D, int64_t ldd,
                      float* splitk_ws, int64_t splitk_ws_floats, void* stream);
@@ -199,6 +229,25 @@ int adkf_gp_ift(int32_t T, const int32_t* z_off, const int32_t* n_sup, const int
                 const float* D2, const float* y, int32_t kernel, float noise_prior_loc, int32_t ls_prior,
                 int32_t mode, const float* phi, float* aux /*[T,ADKF_AUX] in/out*/,
                 float* Wm, int32_t* status, float* ws, int64_t ws_floats, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * Large-pool path (bayes_opt / predictive_performance: fit on <= 64 molecules, evaluate on ~2.25k):
+ * joint predictive NLL of ONE task's query rows through a blocked Cholesky of the (support + query) covariance, trailing
+ * updates on the tensor-core GEMM (chol_blocked.cu).  Replaces likelihood(model(x_test)).log_prob(y_test)
+ * (bayes_opt/predictive_performance/adkt.py:93-96; gpytorch would switch to CG/Lanczos above 800 rows).
+ *   U [N,N] pair statistics (adkf_gram_pairstat* with qq_block = 1), support rows first; phi [3] raw parameters (device).
+ *   out4 = { NLL of all N rows, NLL of the n_sup support rows, their difference F = -log p(y_q | y_s), log det J }.
+ *   status[0] gets ADKF_ST_NOT_PD if a pivot fails (retry with a larger `jitter`, psd_safe_cholesky policy, on the host).
+ * ------------------------------------------------------------------------------------------- */
+int64_t adkf_chol_blocked_ws_floats(int32_t N);
+int adkf_gp_joint_nll_blocked(const float* U, int32_t N, int32_t n_sup, const float* y, int32_t kernel, const float* phi,
+                              float jitter, float* ws, int64_t ws_floats, float* out4, int32_t* status, void* stream);
+
+/* Analytic expected improvement for MINIMISATION over a candidate pool, on the latent posterior (variance minus noise):
+ * botorch ExpectedImprovement(model, best_f, maximize=False) evaluated per molecule in bayes_opt/bo_utils.py:368-378.
+ * exclude[i] != 0 (already queried) -> -inf. */
+int adkf_ei_pool(const float* mean, const float* var, int32_t m, float noise, float best_f, const uint8_t* exclude,
+                 float* ei, void* stream);
 
 /* workspace sizes (floats) for the three GP entry points, host-side helper */
 int64_t adkf_gp_ws_floats(int32_t T, const int32_t* z_off_host, const int32_t* n_sup_host, int32_t which);
