@@ -202,7 +202,8 @@ class ADKTModel(nn.Module):
         self.config = config
         if getattr(config, "use_ard", False):
             raise NotImplementedError("--use-ard has no sm_100a kernel yet (SURVEY 8(f4))")
-        gpk.check_kernel(config.gp_kernel)
+        if gpk.check_kernel(config.gp_kernel) == "tanimoto":   # ExactGPLayer has no Tanimoto branch (gp_utils.py:22-45)
+            raise ValueError("[ERROR] the kernel 'tanimoto' is not supported! (use gp_utils.ExactTanimotoGP)")
         if config.used_features.startswith("gnn"):
             self.graph_feature_extractor = GraphFeatureExtractor(config.graph_feature_extractor_config)
         self.use_fc = config.used_features.endswith("+fc")

@@ -33,10 +33,9 @@ def noise_prior_loc(use_numeric_labels: bool) -> float:
 
 
 def check_kernel(kernel: str) -> str:
-    if kernel not in SUPPORTED_KERNELS:
-        raise NotImplementedError(
-            f"gp_kernel={kernel!r}: the sm_100a GP kernels implement {SUPPORTED_KERNELS}; there is no gpytorch / CPU "
-            "fallback")
+    if kernel not in SUPPORTED_KERNELS:   # gp_utils.py:44-45 raises ValueError with this message
+        raise ValueError(f"[ERROR] the kernel '{kernel}' is not supported! (sm_100a kernels: {SUPPORTED_KERNELS}; there is "
+                         "no gpytorch / CPU fallback)")
     return kernel
 
 

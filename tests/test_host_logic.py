@@ -96,8 +96,11 @@ def test_model_surface_and_state_dict_names(golden_dir):
 
 
 def test_unsupported_configurations_fail_loudly():
-    with pytest.raises(NotImplementedError):
-        ADKTModelTrainer(ADKTModelTrainerConfig(gp_kernel="cossim"))
+    for bad in ("tanimoto", "spectral"):        # gp_utils.py:44-45: ValueError for kernels ExactGPLayer does not know
+        with pytest.raises(ValueError):
+            ADKTModelTrainer(ADKTModelTrainerConfig(gp_kernel=bad))
+    assert ADKTModelTrainer(ADKTModelTrainerConfig(gp_kernel="cossim", graph_feature_extractor_config=cli_default_config(1))
+                            ).normalizing_features
     with pytest.raises(NotImplementedError):
         ADKTModelTrainer(ADKTModelTrainerConfig(use_ard=True))
     with pytest.raises(NotImplementedError):
