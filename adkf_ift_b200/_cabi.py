@@ -7,7 +7,7 @@ fails loudly if the shared object has not been built (run `python -m adkf_ift_b2
 """
 import ctypes
 import os
-from ctypes import c_float, c_int32, c_int64, c_void_p
+from ctypes import c_float, c_int32, c_int64, c_uint64, c_void_p
 
 import torch
 
@@ -48,6 +48,15 @@ SIGNATURES = {
     "adkf_chol_blocked_ws_floats": ([c_int32], c_int64),
     "adkf_gp_joint_nll_blocked": ([_P, c_int32, c_int32, _P, c_int32, _P, c_float, _P, c_int64, _P, _P, _P], ctypes.c_int),
     "adkf_ei_pool": ([_P, _P, c_int32, c_float, c_float, _P, _P, _P], ctypes.c_int),
+    "adkf_csr_from_edge_index": ([_P, c_int64, c_int32, c_int32, _P, _P, _P, _P, _P], ctypes.c_int),
+    "adkf_embed_sum2": ([_P, c_int64, c_int32, _P, _P, _P, _P], ctypes.c_int),
+    "adkf_gin_gather": ([_P, c_int32, c_int32, _P, _P, _P, _P, _P, _P, _P, _P], ctypes.c_int),
+    "adkf_seg_bn_fwd": ([_P, c_int32, _P, c_int32, _P, _P, _P, _P, c_float, c_int32, c_int32, c_float, c_uint64, _P, _P, _P,
+                         _P, _P], ctypes.c_int),
+    "adkf_seg_bn_bwd": ([_P, _P, c_int32, _P, c_int32, _P, _P, _P, _P, c_int32, c_float, c_uint64, _P, _P, _P, _P],
+                        ctypes.c_int),
+    "adkf_seg_mean_fwd": ([_P, c_int32, _P, c_int32, _P, _P], ctypes.c_int),
+    "adkf_seg_mean_bwd": ([_P, c_int32, _P, c_int32, _P, _P], ctypes.c_int),
     "adkf_gp_ws_floats": ([c_int32, _P, _P, c_int32], c_int64),
 }
 

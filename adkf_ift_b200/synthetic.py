@@ -138,10 +138,16 @@ def deterministic_init_(module_or_state, seed: int = 0, alpha: float = 0.5, gain
             u = torch.rand(t.shape, generator=g, dtype=torch.float64) * 2.0 - 1.0
             if name.endswith(".alpha"):
                 val = torch.full(t.shape, float(alpha), dtype=torch.float64)
-            elif "norm_layer.weight" in name:
+            elif "norm_layer.weight" in name or ("batch_norms" in name and name.endswith(".weight")):
                 val = 1.0 + 0.1 * u
-            elif "norm_layer.bias" in name:
+            elif "norm_layer.bias" in name or ("batch_norms" in name and name.endswith(".bias")):
                 val = 0.1 * u
+            elif name.endswith("running_mean"):
+                val = torch.zeros(t.shape, dtype=torch.float64)
+            elif name.endswith("running_var"):
+                val = torch.ones(t.shape, dtype=torch.float64)
+            elif "embedding" in name:            # MoleculeNet atom / bond embedding tables
+                val = 0.5 * u
             elif t.dim() == 2:
                 val = u * (gain / math.sqrt(t.shape[1]))
             else:
@@ -165,3 +171,32 @@ def bo_pool(seed: int = 5, pool: int = 2312, dim: int = 64, binary: bool = False
     if binary:
         x = (x > 0.6).astype(np.float32)
     return x.astype(np.float32), y.astype(np.float32)
+
+
+def make_mol_graphs(seed: int, num_graphs: int):
+    """MoleculeNet-shaped graphs in the PyG layout of MoleculeNet/chem_lib: atom type U{0..118},
+    chirality U{0..2}; random spanning tree + V//6 extra bonds, every bond stored in both directions with the same
+    attributes (bond type U{0..3}, direction U{0..2}); labels Bernoulli(0.5) with both classes present.
+    Returns dict(x [V,2], edge_index [2,E], edge_attr [E,2], batch [V], y [G]) of int64 numpy arrays."""
+    rng = np.random.default_rng(77_000 + seed)
+    xs, srcs, tgts, attrs, batch = [], [], [], [], []
+    v_off = 0
+    for g in range(num_graphs):
+        V = int(np.clip(round(rng.normal(24, 6)), 6, 50))
+        xs.append(np.stack([rng.integers(0, 119, size=V), rng.integers(0, 3, size=V)], 1))
+        bonds = [(i, int(rng.integers(0, i))) for i in range(1, V)]
+        have = set(bonds)
+        for _ in range(V // 6):
+            a, b = (int(v) for v in rng.integers(0, V, size=2))
+            if a != b and (a, b) not in have and (b, a) not in have:
+                bonds.append((a, b)); have.add((a, b))
+        for (a, b) in bonds:
+            at = (int(rng.integers(0, 4)), int(rng.integers(0, 3)))
+            srcs += [a + v_off, b + v_off]; tgts += [b + v_off, a + v_off]; attrs += [at, at]
+        batch += [g] * V
+        v_off += V
+    y = rng.integers(0, 2, size=num_graphs)
+    y[0], y[1 % num_graphs] = 1, 0
+    return dict(x=np.concatenate(xs).astype(np.int64), edge_index=np.array([srcs, tgts], dtype=np.int64),
+                edge_attr=np.array(attrs, dtype=np.int64).reshape(-1, 2), batch=np.array(batch, dtype=np.int64),
+                y=y.astype(np.int64))

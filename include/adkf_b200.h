@@ -249,6 +249,36 @@ int adkf_gp_joint_nll_blocked(const float* U, int32_t N, int32_t n_sup, const fl
 int adkf_ei_pool(const float* mean, const float* var, int32_t m, float noise, float best_f, const uint8_t* exclude,
                  float* ei, void* stream);
 
+/* ---------------------------------------------------------------------------------------------
+ * MoleculeNet branch (config 4): GIN molecule encoder, MoleculeNet/chem_lib/models/encoder.py (gin.cu).
+ * Graphs arrive in the PyG layout of the reference: x [V,2] int64 (atom type, chirality), edge_index [2,E] int64
+ * (row 0 source j, row 1 target i; both directions present), edge_attr [E,2] int64 (bond type, direction).
+ * ------------------------------------------------------------------------------------------- */
+/* CSR of edge_index by target (by_source = 0) or by source (1): rowptr [V+1], col_other [E] = the other endpoint,
+ * col_eid [E] = edge id; rows sorted by edge id (deterministic).  scratch: V int32. */
+int adkf_csr_from_edge_index(const int64_t* edge_index, int64_t E, int32_t V, int32_t by_source, int32_t* rowptr,
+                             int32_t* col_other, int32_t* col_eid, int32_t* scratch, void* stream);
+/* out[r] = T1[idx[r,0]] + T2[idx[r,1]]  (x_embedding1 + x_embedding2, encoder.py:269) */
+int adkf_embed_sum2(const int64_t* idx, int64_t rows, int32_t D, const float* T1, const float* T2, float* out, void* stream);
+/* GINConv propagate (encoder.py:40-58): out[i] = x[i] + E1[4] + E2[0] + sum_{p in row i} (x[col[p]] + E1[attr[eid[p],0]] +
+ * E2[attr[eid[p],1]]).  With edge_attr == NULL the edge terms are dropped: out[i] = x[i] + sum x[col[p]] -- the transpose
+ * used by the backward on the by-source CSR. */
+int adkf_gin_gather(const float* x, int32_t V, int32_t D, const int32_t* rowptr, const int32_t* col, const int32_t* col_eid,
+                    const int64_t* edge_attr, const float* E1, const float* E2, float* out, void* stream);
+/* BatchNorm1d (+ReLU when act = 1, + inverted dropout when keep < 1) with the statistics taken PER SEGMENT of rows
+ * seg_ptr[S+1]: one segment = one encoder call of the reference (support or query molecules of one task), so that merging
+ * T tasks into one launch leaves the train-mode statistics of encoder.py:273-281 unchanged.  mode 0 = batch statistics
+ * (saved: mean, rstd, unbiased variance, each [S,D]); mode 1 = running statistics. */
+int adkf_seg_bn_fwd(const float* x, int32_t D, const int32_t* seg_ptr, int32_t S, const float* gamma, const float* beta,
+                    const float* run_mean, const float* run_var, float eps, int32_t mode, int32_t act, float keep,
+                    uint64_t seed, float* y, float* save_mean, float* save_rstd, float* save_uvar, void* stream);
+int adkf_seg_bn_bwd(const float* x, const float* dy, int32_t D, const int32_t* seg_ptr, int32_t S, const float* gamma,
+                    const float* beta, const float* save_mean, const float* save_rstd, int32_t act, float keep, uint64_t seed,
+                    float* dx, float* dgamma_part /*[S,D]*/, float* dbeta_part /*[S,D]*/, void* stream);
+/* global_mean_pool (encoder.py:325): nodes of a graph are contiguous, graph_ptr[G+1] */
+int adkf_seg_mean_fwd(const float* x, int32_t D, const int32_t* graph_ptr, int32_t G, float* out, void* stream);
+int adkf_seg_mean_bwd(const float* dout, int32_t D, const int32_t* graph_ptr, int32_t G, float* dx, void* stream);
+
 /* workspace sizes (floats) for the three GP entry points, host-side helper */
 int64_t adkf_gp_ws_floats(int32_t T, const int32_t* z_off_host, const int32_t* n_sup_host, int32_t which);
 
