@@ -23,6 +23,10 @@ SIGNATURES = {
     "adkf_mp_pna_fwd": ([_P, _P, _P, _P, _P, _P, c_int32, _P, _P, _P, _P], ctypes.c_int),
     "adkf_mp_pna_bwd": ([_P, _P, _P, _P, _P, _P, _P, _P, c_int32, c_int32, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P,
                          c_int32, _P], ctypes.c_int),
+    "adkf_pna_gather_inputs": ([_P, _P, _P, c_int64, _P, _P], ctypes.c_int),
+    "adkf_pna_aggregate_fwd": ([_P, _P, c_int32, _P, _P, _P, _P], ctypes.c_int),
+    "adkf_pna_dpre": ([_P, _P, c_int32, _P, _P, _P, _P, _P, _P], ctypes.c_int),
+    "adkf_pna_dh_gather": ([_P, _P, _P, c_int32, _P, _P], ctypes.c_int),
     "adkf_readout_weighted_fwd": ([_P, _P, _P, c_int32, c_int32, c_int32, c_int32, _P, _P, _P], ctypes.c_int),
     "adkf_readout_weighted_bwd": ([_P, _P, _P, c_int32, c_int32, c_int32, c_int32, _P, _P, _P, _P], ctypes.c_int),
     "adkf_readout_max_fwd": ([_P, _P, c_int32, c_int32, _P, _P, _P], ctypes.c_int),
@@ -38,6 +42,10 @@ SIGNATURES = {
     "adkf_linear_tf32x3": ([_P, c_int64, c_int32, c_int64, _P, c_int32, c_int64, _P, c_int32, _P, c_int64, _P], ctypes.c_int),
     "adkf_gemm_tf32x3": ([_P, c_int32, c_int64, _P, c_int32, c_int64, c_int64, c_int32, c_int32, _P, c_int32, _P, c_int64,
                           _P, c_int64, _P], ctypes.c_int),
+    "adkf_gemm_tf32x3_batched": ([_P, c_int32, c_int64, c_int64, c_int64, c_int32, c_int32, _P, c_int32, c_int64, c_int64, c_int64,
+                                  c_int32, c_int32, c_int64, c_int32, c_int32, c_int32, _P, c_int64, c_int32, _P, c_int64,
+                                  c_int64, _P, c_int64, _P], ctypes.c_int),
+    "adkf_gemm_batched_splitk_ws_floats": ([c_int64, c_int32, c_int32, c_int32], c_int64),
     "adkf_gemm_splitk_ws_floats": ([c_int64, c_int32, c_int32], c_int64),
     "adkf_gram_sqdist_bwd": ([_P, c_int32, c_int32, _P, _P, c_int32, _P, _P, c_float, _P, _P], ctypes.c_int),
     "adkf_gp_fit": ([c_int32, _P, _P, _P, _P, _P, c_int32, c_float, c_float, c_int32, c_int32, c_int32, c_float,

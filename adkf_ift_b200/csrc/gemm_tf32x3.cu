@@ -38,6 +38,7 @@
 //              RN accumulation in registers, fused epilogue, stores.
 // Every mbarrier wait is bounded (trap after ~2^28 polls) so that a protocol bug cannot hang the device.
 #include <cuda.h>
+#include <cstdlib>
 #include "common.cuh"
 #include "../../include/adkf_b200.h"
 
@@ -141,6 +142,12 @@ struct GemmEpilogue {
     // split-K (mode 0): CTA z handles k-blocks [z * kb_per_split, ...) and writes to out + z * split_stride
     int kb_per_split;
     int64_t split_stride;
+    // batching (mode 0): blockIdx.z = batch * splits + split.  Batch b reads A at (mn + b*a_mn, k + b*a_k), B likewise,
+    // writes D + b*d_off (+ bias + b*bias_off): column blocks / row blocks of the SAME 2-D arrays, one tensor map each.
+    int splits;
+    int debug;            // development probe (ADKF_GEMM_DEBUG): 1 = splitter skips the split, 2 = MMA warp skips the MMAs
+    int a_mn, a_k, b_mn, b_k;
+    int64_t d_off, bias_off;
     // gram
     const int32_t* z_off;
     const int32_t* n_sup;
@@ -151,11 +158,14 @@ struct GemmEpilogue {
     int stat;             // ADKF_STAT_*
 };
 
+// hi = v rounded to tf32 (round-to-nearest, ties away: what cvt.rna.tf32.f32 does, written as two integer ops so that it
+// stays on the ALU pipe), lo = v - hi (exact in fp32)
+__device__ __forceinline__ float tf32_hi(float v) { return __uint_as_float((__float_as_uint(v) + 0x1000u) & 0xffffe000u); }
 __device__ __forceinline__ void split4(const float4 v, float4& hi, float4& lo) {
-    hi.x = __uint_as_float(rna_tf32(v.x)); lo.x = v.x - hi.x;
-    hi.y = __uint_as_float(rna_tf32(v.y)); lo.y = v.y - hi.y;
-    hi.z = __uint_as_float(rna_tf32(v.z)); lo.z = v.z - hi.z;
-    hi.w = __uint_as_float(rna_tf32(v.w)); lo.w = v.w - hi.w;
+    hi.x = tf32_hi(v.x); lo.x = v.x - hi.x;
+    hi.y = tf32_hi(v.y); lo.y = v.y - hi.y;
+    hi.z = tf32_hi(v.z); lo.z = v.z - hi.z;
+    hi.w = tf32_hi(v.w); lo.w = v.w - hi.w;
 }
 
 // One operand tile, raw -> (hi, lo) in the K-major SWIZZLE_128B layout the MMA descriptors describe (row r = 128 B, its
@@ -165,37 +175,51 @@ __device__ __forceinline__ void split4(const float4 v, float4& hi, float4& lo) {
 //               logical chunk, which is the same for all its rows: (t & 7) ^ ((t >> 3) & 7).
 //   TR = true : the raw tile is [32 k][128 mn] floats, un-swizzled; thread t owns output row mn = t and gathers 4
 //               consecutive k per store (reads are conflict-free: a warp reads 32 consecutive floats).
+// All loads of a tile are issued before the first store: the splitter runs one warp per scheduler, so its throughput is
+// set by how many shared-memory loads it keeps in flight (ncu r1b: a load -> convert -> store chain per float4 left the
+// splitter busy 76% of the time and the tensor pipe at 31%).
 template <bool TR>
-__device__ __forceinline__ void split_tile(const unsigned char* raw, unsigned char* hi_t, unsigned char* lo_t, int t,
-                                           const float4 mu4) {
-    float4* hi4 = reinterpret_cast<float4*>(hi_t);
-    float4* lo4 = reinterpret_cast<float4*>(lo_t);
+__device__ __forceinline__ void split_tile(const unsigned char* __restrict__ raw, unsigned char* __restrict__ hi_t,
+                                           unsigned char* __restrict__ lo_t, int t, const float4 mu4) {
+    float4* __restrict__ hi4 = reinterpret_cast<float4*>(hi_t);
+    float4* __restrict__ lo4 = reinterpret_cast<float4*>(lo_t);
     if (!TR) {
-        const float4* r4 = reinterpret_cast<const float4*>(raw);
-#pragma unroll 4
-        for (int i = 0; i < (kTileBytes / 16) / 128; ++i) {            // 1024 float4 / 128 threads = 8
-            const int p = i * 128 + t;
-            float4 v = r4[p];
-            v.x -= mu4.x; v.y -= mu4.y; v.z -= mu4.z; v.w -= mu4.w;
+        const float4* __restrict__ r4 = reinterpret_cast<const float4*>(raw);
+        constexpr int kPer = (kTileBytes / 16) / 128;                 // 1024 float4 / 128 threads = 8
+        float4 v[kPer];
+#pragma unroll
+        for (int i = 0; i < kPer; ++i) v[i] = r4[i * 128 + t];
+#pragma unroll
+        for (int i = 0; i < kPer; ++i) {
+            float4 x = v[i];
+            x.x -= mu4.x; x.y -= mu4.y; x.z -= mu4.z; x.w -= mu4.w;
             float4 hi, lo;
-            split4(v, hi, lo);
-            hi4[p] = hi;
-            lo4[p] = lo;
+            split4(x, hi, lo);
+            hi4[i * 128 + t] = hi;
+            lo4[i * 128 + t] = lo;
         }
     } else {
-        const float* rf = reinterpret_cast<const float*>(raw);
-#pragma unroll 4
-        for (int c = 0; c < kBK / 4; ++c) {
-            float4 v;
-            v.x = rf[(4 * c + 0) * kBM + t];
-            v.y = rf[(4 * c + 1) * kBM + t];
-            v.z = rf[(4 * c + 2) * kBM + t];
-            v.w = rf[(4 * c + 3) * kBM + t];
-            float4 hi, lo;
-            split4(v, hi, lo);
-            const int p = t * 8 + (c ^ (t & 7));
-            hi4[p] = hi;
-            lo4[p] = lo;
+        const float* __restrict__ rf = reinterpret_cast<const float*>(raw);
+#pragma unroll
+        for (int half = 0; half < 2; ++half) {
+            float4 v[4];
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                const int c = half * 4 + q;
+                v[q].x = rf[(4 * c + 0) * kBM + t];
+                v[q].y = rf[(4 * c + 1) * kBM + t];
+                v[q].z = rf[(4 * c + 2) * kBM + t];
+                v[q].w = rf[(4 * c + 3) * kBM + t];
+            }
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                const int c = half * 4 + q;
+                float4 hi, lo;
+                split4(v[q], hi, lo);
+                const int p = t * 8 + (c ^ (t & 7));
+                hi4[p] = hi;
+                lo4[p] = lo;
+            }
         }
     }
 }
@@ -223,9 +247,10 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
 
     // ---- tile coordinates ---------------------------------------------------------------------------------
     int rowA0, rowB0, task = 0, Nt = 0, nsup = 0;
-    int kb0 = 0;
+    int kb0 = 0, batch = 0;
     int nk = (ep.K + kBK - 1) / kBK;
     float* out = ep.out;
+    const float* bias = ep.bias;
     if (ep.mode == 1) {
         task = blockIdx.z;
         const int r0 = ep.z_off[task];
@@ -239,10 +264,15 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
     } else {
         rowA0 = blockIdx.y * kBM;
         rowB0 = blockIdx.x * kBN;
-        kb0 = blockIdx.z * ep.kb_per_split;
+        const int split = blockIdx.z % ep.splits;
+        batch = blockIdx.z / ep.splits;
+        kb0 = split * ep.kb_per_split;
         nk = min(nk, kb0 + ep.kb_per_split) - kb0;                    // host guarantees >= 1
-        out += (int64_t)blockIdx.z * ep.split_stride;
+        out += (int64_t)blockIdx.z * ep.split_stride + (int64_t)batch * ep.d_off;
+        if (bias != nullptr) bias += (int64_t)batch * ep.bias_off;
     }
+    const int a_mn0 = rowA0 + batch * ep.a_mn, b_mn0 = rowB0 + batch * ep.b_mn;   // TMA coordinates of this batch
+    const int a_k0 = batch * ep.a_k, b_k0 = batch * ep.b_k;
 
     // ---- one-time setup -----------------------------------------------------------------------------------
     if (threadIdx.x == 0) {
@@ -281,10 +311,10 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
                 mbar_wait(rawempty_bar(r), ph ^ 1);
                 mbar_expect_tx(rawfull_bar(r), kRawBytes);
                 const uint32_t dst = base + r * kRawBytes;
-                if (TA) tma_load_2d(dst, &tmA, rawfull_bar(r), rowA0, k);
-                else    tma_load_2d(dst, &tmA, rawfull_bar(r), k, rowA0);
-                if (TB) tma_load_2d(dst + kTileBytes, &tmB, rawfull_bar(r), rowB0, k);
-                else    tma_load_2d(dst + kTileBytes, &tmB, rawfull_bar(r), k, rowB0);
+                if (TA) tma_load_2d(dst, &tmA, rawfull_bar(r), a_mn0, k + a_k0);
+                else    tma_load_2d(dst, &tmA, rawfull_bar(r), k + a_k0, a_mn0);
+                if (TB) tma_load_2d(dst + kTileBytes, &tmB, rawfull_bar(r), b_mn0, k + b_k0);
+                else    tma_load_2d(dst + kTileBytes, &tmB, rawfull_bar(r), k + b_k0, b_mn0);
             }
         }
     } else if (warp == 1) {
@@ -304,7 +334,7 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
                 const uint64_t a_lo = smem_desc_k128(st + 2 * kTileBytes), b_lo = smem_desc_k128(st + 3 * kTileBytes);
                 const uint32_t acc_big = tmem_acc + (uint32_t)(b * kBN), acc_small = tmem_acc + 2u * kBN;
 #pragma unroll
-                for (int k = 0; k < kBK / 8; ++k) {                   // UMMA_K = 8 tf32 = 32 B = +2 in the address field
+                for (int k = 0; k < ((ep.debug & 2) ? 0 : kBK / 8); ++k) {   // UMMA_K = 8 tf32 = 32 B = +2 in the address field
                     const uint64_t adv = (uint64_t)(2 * k);
                     umma_tf32(acc_small, a_lo + adv, b_hi + adv, kIdescTf32, (i | k) ? 1u : 0u);
                     umma_tf32(acc_small, a_hi + adv, b_lo + adv, kIdescTf32, 1u);
@@ -330,8 +360,10 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
             mbar_wait(empty_bar(s), ((i / kSplit) & 1) ^ 1);
             const unsigned char* rw = base_ptr + (size_t)r * kRawBytes;
             unsigned char* st = split_ptr + (size_t)s * kSplitBytes;
-            split_tile<TA>(rw, st, st + 2 * kTileBytes, t, mu4);
-            split_tile<TB>(rw + kTileBytes, st + kTileBytes, st + 3 * kTileBytes, t, mu4);
+            if (!(ep.debug & 1)) {
+                split_tile<TA>(rw, st, st + 2 * kTileBytes, t, mu4);
+                split_tile<TB>(rw + kTileBytes, st + kTileBytes, st + 3 * kTileBytes, t, mu4);
+            }
             fence_async_smem();                                        // generic-proxy writes -> visible to the MMA (async proxy)
             __syncwarp();
             if (lane == 0) {
@@ -386,7 +418,7 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
 #pragma unroll
                     for (int j = 0; j < 16; ++j) {
                         float x = v[j];
-                        if (ep.bias != nullptr && col0 + j < ep.N) x += ep.bias[col0 + j];
+                        if (bias != nullptr && col0 + j < ep.N) x += bias[col0 + j];
                         if (ep.act == 1) x = fmaxf(x, 0.f);
                         else if (ep.act == 2) x = (x > 0.f) ? x : 0.01f * x;
                         else if (ep.act == 3 && col0 + j < ep.N) x = orow[col0 + j] - x;   // D <- D - A.B^T (trailing update)
@@ -494,12 +526,15 @@ static int gemm_attr() {
 }
 
 namespace adkf {
-__global__ void splitk_reduce_kernel(const float* __restrict__ ws, int splits, int64_t n, float* __restrict__ out) {
+__global__ void splitk_reduce_kernel(const float* __restrict__ ws, int splits, int64_t n, float* __restrict__ out,
+                                     int64_t d_off) {
     const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
+    const int b = blockIdx.y;                                  // batch: its `splits` slabs are consecutive in ws
+    const float* w = ws + (int64_t)b * splits * n;
     float acc = 0.f;
-    for (int s = 0; s < splits; ++s) acc += ws[(int64_t)s * n + i];
-    out[i] = acc;
+    for (int s = 0; s < splits; ++s) acc += w[(int64_t)s * n + i];
+    out[(int64_t)b * d_off + i] = acc;
 }
 }  // namespace adkf
 
@@ -520,30 +555,49 @@ extern "C" int64_t adkf_gemm_splitk_ws_floats(int64_t M, int32_t N, int32_t K) {
     return s > 1 ? (int64_t)s * M * N : 0;
 }
 
-extern "C" int adkf_gemm_tf32x3(const float* A, int32_t transA, int64_t lda, const float* B, int32_t transB, int64_t ldb,
-                                int64_t M, int32_t N, int32_t K, const float* bias, int32_t act, float* D, int64_t ldd,
-                                float* splitk_ws, int64_t splitk_ws_floats, void* stream) {
-    if (M <= 0 || N <= 0) return 0;
-    if (!A || !B || !D || K <= 0 || act < 0 || act > 3) return ADKF_ERR_BADARG;
-    if (transA && !transB) return ADKF_ERR_BADARG;                  // (T,K) is not on the path
-    cudaStream_t s = (cudaStream_t)stream;
+// batch > 1: batch b reads opA at (mn + b*a_mn, k + b*a_k) and opB at (mn + b*b_mn, k + b*b_k) of the SAME 2-D arrays
+// (a_rows / b_rows = number of rows of the underlying arrays along the slow dimension, for the tensor-map bounds) and
+// writes D + b*d_off.  Rows / columns past M / N of a batch are computed from whatever lies there and masked in the epilogue.
+static int gemm_launch(const float* A, int transA, int64_t lda, int64_t a_slow, int64_t a_fast, const float* B, int transB,
+                       int64_t ldb, int64_t b_slow, int64_t b_fast, int64_t M, int32_t N, int32_t K, const float* bias,
+                       int32_t act, float* D, int64_t ldd, float* splitk_ws, int64_t splitk_ws_floats, int batch, int a_mn,
+                       int a_k, int b_mn, int b_k, int64_t d_off, int64_t bias_off, cudaStream_t s) {
     (void)cudaGetLastError();   // a stale error left in this host thread by someone else is not this launch's failure
     CUtensorMap ma, mb;
-    int rc = make_map_2d(&ma, A, M, K, lda, transA ? 1 : 0);
+    // make_map_2d(ptr, rows (mn extent), kdim (k extent), ld, transposed): extents of the WHOLE array
+    int rc = make_map_2d(&ma, A, transA ? a_fast : a_slow, transA ? a_slow : a_fast, lda, transA ? 1 : 0);
     if (rc) return rc;
-    rc = make_map_2d(&mb, B, N, K, ldb, transB ? 1 : 0);
+    rc = make_map_2d(&mb, B, transB ? b_fast : b_slow, transB ? b_slow : b_fast, ldb, transB ? 1 : 0);
     if (rc) return rc;
-    int splits = plan_splits(M, N, K);
-    if (splits > 1 && (splitk_ws == nullptr || splitk_ws_floats < (int64_t)splits * M * N || bias != nullptr || act != 0 ||
-                       ldd != N))
+    int splits = (batch > 1) ? 1 : plan_splits(M, N, K);
+    if (batch > 1 && splitk_ws != nullptr) {        // batched split-K: same plan for every batch, ws = [batch][splits][M][N]
+        const int64_t tiles = ((M + kBM - 1) / kBM) * ((N + kBN - 1) / kBN) * batch;
+        const int nk0 = (K + kBK - 1) / kBK;
+        if (tiles < 148 && nk0 >= 16) {
+            splits = (int)((2 * 148 + tiles - 1) / tiles);
+            if (splits > nk0 / 8) splits = nk0 / 8;
+            if (splits < 1) splits = 1;
+            const int per = (nk0 + splits - 1) / splits;
+            splits = (nk0 + per - 1) / per;
+        }
+    }
+    if (splits > 1 && (splitk_ws == nullptr || splitk_ws_floats < (int64_t)splits * batch * M * N || bias != nullptr ||
+                       act != 0 || ldd != N))
         splits = 1;                                                  // no workspace (or fused epilogue): single pass
     const int nk = (K + kBK - 1) / kBK;
     GemmEpilogue ep = {};
     ep.mode = 0; ep.M = M; ep.N = N; ep.K = K; ep.bias = bias; ep.act = act;
     ep.kb_per_split = (nk + splits - 1) / splits;
-    if (splits > 1) { ep.out = splitk_ws; ep.ldo = N; ep.split_stride = M * (int64_t)N; }
-    else            { ep.out = D; ep.ldo = ldd; ep.split_stride = 0; }
-    dim3 grid((N + kBN - 1) / kBN, (unsigned)((M + kBM - 1) / kBM), splits);
+    static const int dbg = getenv("ADKF_GEMM_DEBUG") ? atoi(getenv("ADKF_GEMM_DEBUG")) : 0;
+    ep.debug = dbg;
+    ep.splits = splits; ep.a_mn = a_mn; ep.a_k = a_k; ep.b_mn = b_mn; ep.b_k = b_k; ep.bias_off = bias_off;
+    if (splits > 1) {
+        // blockIdx.z = b * splits + split  ->  out = ws + z * M*N ; the reduce pass sums `splits` consecutive slabs
+        ep.out = splitk_ws; ep.ldo = N; ep.split_stride = M * (int64_t)N; ep.d_off = 0;
+    } else {
+        ep.out = D; ep.ldo = ldd; ep.split_stride = 0; ep.d_off = d_off;
+    }
+    dim3 grid((N + kBN - 1) / kBN, (unsigned)((M + kBM - 1) / kBM), splits * batch);
     if (!transA && !transB) {
         if ((rc = gemm_attr<false, false>())) return rc;
         gemm_tf32x3_kernel<false, false><<<grid, kGemmThreads, kGemmSmem, s>>>(ma, mb, ep);
@@ -558,11 +612,48 @@ extern "C" int adkf_gemm_tf32x3(const float* A, int32_t transA, int64_t lda, con
     ADKF_LAUNCH_CHECK();
     if (splits > 1) {
         const int64_t n = M * (int64_t)N;
-        splitk_reduce_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(splitk_ws, splits, n, D);
+        splitk_reduce_kernel<<<dim3((unsigned)((n + 255) / 256), batch), 256, 0, s>>>(splitk_ws, splits, n, D, d_off);
         adkf_count_launches(1);
         ADKF_LAUNCH_CHECK();
     }
     return 0;
+}
+
+extern "C" int adkf_gemm_tf32x3(const float* A, int32_t transA, int64_t lda, const float* B, int32_t transB, int64_t ldb,
+                                int64_t M, int32_t N, int32_t K, const float* bias, int32_t act, float* D, int64_t ldd,
+                                float* splitk_ws, int64_t splitk_ws_floats, void* stream) {
+    if (M <= 0 || N <= 0) return 0;
+    if (!A || !B || !D || K <= 0 || act < 0 || act > 3) return ADKF_ERR_BADARG;
+    if (transA && !transB) return ADKF_ERR_BADARG;                  // (T,K) is not on the path
+    return gemm_launch(A, transA, lda, transA ? K : M, transA ? M : K, B, transB, ldb, transB ? K : N, transB ? N : K, M, N, K,
+                       bias, act, D, ldd, splitk_ws, splitk_ws_floats, 1, 0, 0, 0, 0, 0, 0, (cudaStream_t)stream);
+}
+
+extern "C" int64_t adkf_gemm_batched_splitk_ws_floats(int64_t M, int32_t N, int32_t K, int32_t batch) {
+    const int64_t tiles = ((M + kBM - 1) / kBM) * ((N + kBN - 1) / kBN) * batch;
+    const int nk0 = (K + kBK - 1) / kBK;
+    if (tiles >= 148 || nk0 < 16) return 0;
+    int splits = (int)((2 * 148 + tiles - 1) / tiles);
+    if (splits > nk0 / 8) splits = nk0 / 8;
+    if (splits < 1) splits = 1;
+    const int per = (nk0 + splits - 1) / splits;
+    splits = (nk0 + per - 1) / per;
+    return splits > 1 ? (int64_t)splits * batch * M * N : 0;
+}
+
+extern "C" int adkf_gemm_tf32x3_batched(const float* A, int32_t transA, int64_t lda, int64_t a_slow, int64_t a_fast,
+                                        int32_t a_mn_stride, int32_t a_k_stride, const float* B, int32_t transB, int64_t ldb,
+                                        int64_t b_slow, int64_t b_fast, int32_t b_mn_stride, int32_t b_k_stride, int64_t M,
+                                        int32_t N, int32_t K, int32_t batch, const float* bias, int64_t bias_stride,
+                                        int32_t act, float* D, int64_t ldd, int64_t d_stride, float* splitk_ws,
+                                        int64_t splitk_ws_floats, void* stream) {
+    if (M <= 0 || N <= 0 || batch <= 0) return 0;
+    if (!A || !B || !D || K <= 0 || act < 0 || act > 3) return ADKF_ERR_BADARG;
+    if (transA && !transB) return ADKF_ERR_BADARG;
+    if (batch > 1 && (a_k_stride || b_k_stride) && K % kBK) return ADKF_ERR_BADARG;   // a partial k-block would read the next batch
+    return gemm_launch(A, transA, lda, a_slow, a_fast, B, transB, ldb, b_slow, b_fast, M, N, K, bias, act, D, ldd, splitk_ws,
+                       splitk_ws_floats, batch, a_mn_stride, a_k_stride, b_mn_stride, b_k_stride, d_stride, bias_stride,
+                       (cudaStream_t)stream);
 }
 
 extern "C" int adkf_linear_tf32x3(const float* X, int64_t M, int32_t K, int64_t ldx, const float* W, int32_t N,

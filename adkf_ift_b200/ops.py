@@ -43,6 +43,7 @@ class GraphIndex:
     degree: torch.Tensor
     graph_ptr: Optional[torch.Tensor] = None  # [G+1] int32
     num_graphs: int = 0
+    type_sorted: Optional["TypeSortedEdges"] = None
 
 
 def build_graph_index(adjacency_lists: Sequence[torch.Tensor], num_nodes: int,
@@ -71,8 +72,11 @@ def build_graph_index(adjacency_lists: Sequence[torch.Tensor], num_nodes: int,
         counts = torch.bincount(node_to_graph, minlength=num_graphs)
         graph_ptr = torch.zeros(num_graphs + 1, **i32)
         graph_ptr[1:] = torch.cumsum(counts, 0).to(torch.int32)
-    return GraphIndex(num_nodes, etot, rowptr, col_src[:etot], col_type[:etot], col_tgt[:etot], col_eid[:etot],
-                      rev_pos[:etot], degree[:num_nodes], graph_ptr, num_graphs)
+    gi = GraphIndex(num_nodes, etot, rowptr, col_src[:etot], col_type[:etot], col_tgt[:etot], col_eid[:etot],
+                    rev_pos[:etot], degree[:num_nodes], graph_ptr, num_graphs)
+    if etot > 0:
+        gi.type_sorted = _type_sorted(gi, [2 * e for e in es])
+    return gi
 
 
 # --------------------------------------------------------------------------------------------------
@@ -121,8 +125,101 @@ class _PNAMessagePassing(torch.autograd.Function):
         return d_h, d_W, d_b, None
 
 
-def pna_message_passing(h, W, b, gi: GraphIndex):
-    """h [V,128], W [4,3,192,64], b [4,3,192] -> aggregated messages [V, 3072] (all 4 towers)."""
+@dataclass
+class TypeSortedEdges:
+    """Edges re-ordered by (type, target node, reference message index): the layout of the GEMM-based PNA path."""
+    src: torch.Tensor        # [E] int32 source node of sorted edge r
+    tgt: torch.Tensor        # [E] int32
+    rev: torch.Tensor        # [E] int32 sorted position of the reversed copy of edge r
+    tptr: torch.Tensor       # [3V+1] int32
+    type_off: List[int]      # host: first sorted position of every type (+ E at the end)
+
+
+def _type_sorted(gi: GraphIndex, edges_per_type: Sequence[int]) -> TypeSortedEdges:
+    """Derived from the CSR (target-major, type-major inside a row) by one stable sort on (type, target): integer work done
+    once per batch.  edges_per_type = directed edge counts per type (2 x bonds), known on the host from the tensor shapes."""
+    V, E = gi.num_nodes, gi.num_edges
+    key = gi.col_type.to(torch.int64) * V + gi.col_tgt.to(torch.int64)
+    perm = torch.argsort(key, stable=True)
+    inv = torch.empty_like(perm)
+    inv[perm] = torch.arange(E, device=perm.device)
+    tptr = torch.zeros(3 * V + 1, dtype=torch.int32, device=perm.device)
+    tptr[1:] = torch.cumsum(torch.bincount(key, minlength=3 * V), 0).to(torch.int32)
+    off = [0]
+    for e in edges_per_type:
+        off.append(off[-1] + int(e))
+    assert off[-1] == E
+    return TypeSortedEdges(gi.col_src[perm].contiguous(), gi.col_tgt[perm].contiguous(),
+                           inv[gi.rev_pos.to(torch.int64)[perm]].to(torch.int32).contiguous(), tptr, off)
+
+
+class _PNAMessagePassingTC(torch.autograd.Function):
+    """PNA block on the tensor cores: gather -> batched 3xTF32 GEMM (message MLP) -> aggregation kernel (pna_gemm.cu)."""
+
+    @staticmethod
+    def forward(ctx, h, W, b, gi: GraphIndex):
+        lib = _cabi.load()
+        ts: TypeSortedEdges = gi.type_sorted
+        h, W, b = h.contiguous(), W.contiguous(), b.contiguous()
+        V, E = gi.num_nodes, gi.num_edges
+        f32 = dict(dtype=torch.float32, device=h.device)
+        XG = torch.empty(max(E, 1), 256, **f32)
+        pre = torch.empty(max(E, 1), 768, **f32)
+        check(lib.adkf_pna_gather_inputs(dptr(h, torch.float32), dptr(ts.src), dptr(ts.tgt), E, dptr(XG), stream_ptr()),
+              "adkf_pna_gather_inputs")
+        W2, b1 = W.view(12 * 192, 64), b.view(-1)
+        for t in range(3):
+            e0, e1 = ts.type_off[t], ts.type_off[t + 1]
+            if e1 > e0:   # pre[e0:e1, 192k:192k+192] = XG[e0:e1, 64k:64k+64] @ W[k][t]^T + b[k][t]
+                gemm_tf32x3_batched(XG[e0:e1], False, 0, 64, W2[t * 192:], False, 3 * 192, 0, e1 - e0, 192, 64, 4, pre[e0:e1], 768,
+                                    192, bias=b1[t * 192:], bias_stride=3 * 192)
+        out = torch.empty(V, 4 * 768, **f32)
+        aux_cnt = torch.empty(V, 4, 64, dtype=torch.uint8, device=h.device)
+        aux_arg = torch.empty(V, 4, 64, dtype=torch.uint8, device=h.device)
+        check(lib.adkf_pna_aggregate_fwd(dptr(pre), dptr(ts.tptr), V, dptr(out), dptr(aux_cnt), dptr(aux_arg), stream_ptr()),
+              "adkf_pna_aggregate_fwd")
+        ctx.gi = gi
+        ctx.save_for_backward(W, XG, pre, out, aux_cnt, aux_arg)
+        return out
+
+    @staticmethod
+    def backward(ctx, d_out):
+        lib = _cabi.load()
+        W, XG, pre, out, aux_cnt, aux_arg = ctx.saved_tensors
+        gi = ctx.gi
+        ts: TypeSortedEdges = gi.type_sorted
+        V, E = gi.num_nodes, gi.num_edges
+        f32 = dict(dtype=torch.float32, device=W.device)
+        d_out = d_out.contiguous()
+        d_pre = torch.empty(max(E, 1), 768, **f32)
+        check(lib.adkf_pna_dpre(dptr(pre), dptr(ts.tptr), V, dptr(out), dptr(aux_cnt), dptr(aux_arg), dptr(d_out, torch.float32),
+                                dptr(d_pre), stream_ptr()), "adkf_pna_dpre")
+        dXG = torch.empty(max(E, 1), 256, **f32)
+        d_W = torch.zeros_like(W)
+        d_b = torch.zeros(4, 3, 192, **f32)
+        W2 = W.view(12 * 192, 64)
+        for t in range(3):
+            e0, e1 = ts.type_off[t], ts.type_off[t + 1]
+            if e1 <= e0:
+                continue
+            n = e1 - e0
+            # dXG[:, 64k:64k+64] = d_pre[:, 192k:192k+192] @ W[k][t]
+            gemm_tf32x3_batched(d_pre[e0:e1], False, 0, 192, W2[t * 192:], True, 0, 3 * 192, n, 64, 192, 4, dXG[e0:e1], 256, 64)
+            # dW[k][t] = d_pre[:, 192k:192k+192]^T @ XG[:, 64k:64k+64]   (split-K over the edges)
+            gemm_tf32x3_batched(d_pre[e0:e1], True, 192, 0, XG[e0:e1], True, 64, 0, 192, 64, n, 4,
+                                d_W.view(-1)[t * 192 * 64:], 64, 3 * 192 * 64, allow_splitk=True)
+            d_b[:, t] = d_pre[e0:e1].view(n, 4, 192).sum(0)
+        d_h = torch.empty(V, 128, **f32)
+        check(lib.adkf_pna_dh_gather(dptr(dXG), dptr(ts.tptr), dptr(ts.rev), V, dptr(d_h), stream_ptr()), "adkf_pna_dh_gather")
+        return d_h, d_W, d_b, None
+
+
+def pna_message_passing(h, W, b, gi: GraphIndex, impl: str = "tcgen05"):
+    """h [V,128], W [4,3,192,64], b [4,3,192] -> aggregated messages [V, 3072] (all 4 towers).
+    impl="tcgen05": gather + batched tensor-core GEMM + segment kernels (pna_gemm.cu; needs gi.type_sorted);
+    impl="simt": the fused fp32 CUDA-core kernels of graph.cu."""
+    if impl == "tcgen05" and getattr(gi, "type_sorted", None) is not None:
+        return _PNAMessagePassingTC.apply(h, W, b, gi)
     return _PNAMessagePassing.apply(h, W, b, gi)
 
 
@@ -508,3 +605,29 @@ def ei_pool(mean: torch.Tensor, var: torch.Tensor, noise: float, best_f: float,
                           dptr(ei), stream_ptr())
     check(rc, "adkf_ei_pool")
     return ei
+
+
+def gemm_tf32x3_batched(a: torch.Tensor, trans_a: bool, a_mn_stride: int, a_k_stride: int, b: torch.Tensor, trans_b: bool,
+                        b_mn_stride: int, b_k_stride: int, M: int, N: int, K: int, batch: int, out: torch.Tensor, ldd: int,
+                        d_stride: int, bias: Optional[torch.Tensor] = None, bias_stride: int = 0, act=None,
+                        allow_splitk: bool = False) -> torch.Tensor:
+    """`batch` products D_b[M,N] = act(opA_b @ opB_b^T + bias_b) in one launch, the operands being row / column blocks of the
+    2-D arrays `a` and `b` (see adkf_gemm_tf32x3_batched in include/adkf_b200.h).  `out` is written at element offsets
+    b*d_stride with leading dimension ldd."""
+    lib = _cabi.load()
+    for t in (a, b):
+        if not t.is_cuda or t.dtype != torch.float32 or t.dim() != 2 or t.stride(1) != 1 or t.stride(0) % 4 or t.data_ptr() % 16:
+            raise RuntimeError("gemm_tf32x3_batched needs aligned 2-D fp32 CUDA operands (no CPU fallback)")
+    ws, nws = None, 0
+    if allow_splitk and bias is None and ACT_IDS[act] == 0 and ldd == N:
+        nws = int(lib.adkf_gemm_batched_splitk_ws_floats(M, N, K, batch))
+        if nws:
+            ws = torch.empty(nws, dtype=torch.float32, device=a.device)
+    rc = lib.adkf_gemm_tf32x3_batched(
+        ctypes.c_void_p(a.data_ptr()), 1 if trans_a else 0, a.stride(0), a.shape[0], a.shape[1], int(a_mn_stride), int(a_k_stride),
+        ctypes.c_void_p(b.data_ptr()), 1 if trans_b else 0, b.stride(0), b.shape[0], b.shape[1], int(b_mn_stride), int(b_k_stride),
+        int(M), int(N), int(K), int(batch), dptr(bias, torch.float32) if bias is not None else ctypes.c_void_p(0),
+        int(bias_stride), ACT_IDS[act], ctypes.c_void_p(out.data_ptr()), int(ldd), int(d_stride),
+        dptr(ws) if ws is not None else ctypes.c_void_p(0), nws, stream_ptr())
+    check(rc, "adkf_gemm_tf32x3_batched")
+    return out

@@ -107,6 +107,22 @@ int adkf_mp_pna_bwd(const float* h, const float* W, const float* b, const int32_
                     int32_t num_partials, void* stream);
 
 /* ---------------------------------------------------------------------------------------------
+ * The same PNA block with its three dense products on the tensor cores (pna_gemm.cu; default path of the extractor):
+ *   XG [E,256]   = adkf_pna_gather_inputs(h)            [h_src | h_tgt] per tower, edges sorted by (type, target, message index)
+ *   pre [E,768]  = adkf_gemm_tf32x3_batched(XG, W, b)   message MLP pre-activations, 4 towers per launch, one launch per type
+ *   out [V,3072] = adkf_pna_aggregate_fwd(pre)          relu + sum | mean | pseudo-std | max x 3 degree scalers
+ * backward: d_pre = adkf_pna_dpre(d out); dXG, dW through the batched GEMM; d_h = adkf_pna_dh_gather(dXG).
+ * tptr [3V+1]: tptr[type*V + v] .. tptr[type*V + v + 1] = sorted positions of the type-`type` edges arriving at v;
+ * rev [E]: sorted position of the reversed copy of every edge.
+ * ------------------------------------------------------------------------------------------- */
+int adkf_pna_gather_inputs(const float* h, const int32_t* src, const int32_t* tgt, int64_t E, float* XG, void* stream);
+int adkf_pna_aggregate_fwd(const float* pre, const int32_t* tptr, int32_t V, float* out, uint8_t* aux_cnt, uint8_t* aux_arg,
+                           void* stream);
+int adkf_pna_dpre(const float* pre, const int32_t* tptr, int32_t V, const float* fwd_out, const uint8_t* aux_cnt,
+                  const uint8_t* aux_arg, const float* d_out, float* d_pre, void* stream);
+int adkf_pna_dh_gather(const float* dXG, const int32_t* tptr, const int32_t* rev, int32_t V, float* d_h, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
  * Graph readout segment kernels (fs_mol/modules/graph_readout.py:224-259, 286-296).  Nodes of a graph
  * are contiguous: graph_ptr[G+1].
  *   weighted pool : w = softmax over the graph's nodes (mode 0) or sigmoid (mode 1) of scores [V,heads];
@@ -190,6 +206,17 @@ int adkf_gemm_tf32x3(const float* A, int32_t transA, int64_t lda, const float* B
                      int64_t M, int32_t N, int32_t K, const float* bias, int32_t act, float* D, int64_t ldd,
                      float* splitk_ws, int64_t splitk_ws_floats, void* stream);
 int64_t adkf_gemm_splitk_ws_floats(int64_t M, int32_t N, int32_t K);
+/* Batched form: `batch` products in one launch whose operands are column / row blocks of the same 2-D arrays (one TMA tensor
+ * map per operand): batch b uses opA at (row + b*a_mn_stride, k + b*a_k_stride), opB likewise, writes D + b*d_stride and adds
+ * bias + b*bias_stride.  a_slow / a_fast (b_slow / b_fast) are the extents of the whole underlying arrays (slow = rows).
+ * Used by the PNA message passing: 4 towers x {message MLP, its input gradient, its weight gradient} per edge type
+ * (fs_mol/modules/gnn.py:129-150).  K must be a multiple of 32 when a k stride is used. */
+int adkf_gemm_tf32x3_batched(const float* A, int32_t transA, int64_t lda, int64_t a_slow, int64_t a_fast, int32_t a_mn_stride,
+                             int32_t a_k_stride, const float* B, int32_t transB, int64_t ldb, int64_t b_slow, int64_t b_fast,
+                             int32_t b_mn_stride, int32_t b_k_stride, int64_t M, int32_t N, int32_t K, int32_t batch,
+                             const float* bias, int64_t bias_stride, int32_t act, float* D, int64_t ldd, int64_t d_stride,
+                             float* splitk_ws, int64_t splitk_ws_floats, void* stream);
+int64_t adkf_gemm_batched_splitk_ws_floats(int64_t M, int32_t N, int32_t K, int32_t batch);
 
 /* dZ[a,:] = scale * 4 * sum_b Wm[a,b] (z_a - z_b)  for a symmetric per-task weight matrix Wm (same layout
  * as D2): the chain rule of anything that depends on Z only through D2. */

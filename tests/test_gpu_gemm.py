@@ -144,3 +144,37 @@ def test_linear_tc_autograd(cuda_device, act):
         e = rel(a, r)
         print(f"linear_tc act={act} {name}: rel err {e:.3e}")
         assert e < 5e-6, name
+
+
+def test_batched_forms_of_the_pna_message_mlp(cuda_device):
+    """The three batched products the PNA message passing issues per edge type (4 towers per launch): message MLP
+    (column blocks of the gathered inputs x row blocks of the stacked weights, bias), its input gradient, and its weight
+    gradient with batched split-K."""
+    from adkf_ift_b200 import ops
+    g = torch.Generator().manual_seed(11)
+    E, T = 5000, 4
+    XG = torch.randn(E, T * 64, generator=g).to(cuda_device)
+    W = (torch.randn(T, 3, 192, 64, generator=g) / 8).to(cuda_device)
+    b = torch.randn(T, 3, 192, generator=g).to(cuda_device)
+    tau = 1
+    W2 = W.view(T * 3 * 192, 64)
+    # forward: pre[:, k, :] = XG[:, 64k:64k+64] @ W[k][tau]^T + b[k][tau]
+    pre = torch.zeros(E, T * 192, device=cuda_device)
+    ops.gemm_tf32x3_batched(XG, False, 0, 64, W2[tau * 192:], False, 3 * 192, 0, E, 192, 64, T, pre, T * 192, 192,
+                            bias=b.view(-1)[tau * 192:], bias_stride=3 * 192)
+    ref = torch.stack([XG[:, 64 * k:64 * k + 64].double() @ W[k, tau].double().t() + b[k, tau].double() for k in range(T)], 1)
+    assert rel(pre.view(E, T, 192), ref) < 2e-6
+    # input gradient: dXG[:, 64k:64k+64] = dpre[:, k, :] @ W[k][tau]
+    dpre = torch.randn(E, T * 192, generator=g).to(cuda_device)
+    dXG = torch.zeros(E, T * 64, device=cuda_device)
+    ops.gemm_tf32x3_batched(dpre, False, 0, 192, W2[tau * 192:], True, 0, 3 * 192, E, 64, 192, T, dXG, T * 64, 64)
+    ref = torch.cat([dpre[:, 192 * k:192 * k + 192].double() @ W[k, tau].double() for k in range(T)], 1)
+    assert rel(dXG, ref) < 2e-6
+    # weight gradient: dW[k][tau] = dpre[:, k, :]^T @ XG[:, 64k:64k+64]   (split-K over the edges, batched)
+    dW = torch.zeros(T, 3, 192, 64, device=cuda_device)
+    out = dW.view(-1)[tau * 192 * 64:]
+    ops.gemm_tf32x3_batched(dpre, True, 192, 0, XG, True, 64, 0, 192, 64, E, T, out, 64, 3 * 192 * 64, allow_splitk=True)
+    torch.cuda.synchronize()
+    ref = torch.stack([dpre[:, 192 * k:192 * k + 192].double().t() @ XG[:, 64 * k:64 * k + 64].double() for k in range(T)])
+    assert rel(dW[:, tau], ref) < 2e-6
+    assert float(dW[:, 0].abs().max()) == 0.0 and float(dW[:, 2].abs().max()) == 0.0     # other types untouched

@@ -76,8 +76,9 @@ def test_csr_build_bit_exact(cuda_device, golden_dir):
 
 
 
+@pytest.mark.parametrize("impl", ["tcgen05", "simt"])
 @pytest.mark.parametrize("n_mol", [3, 24])
-def test_pna_fwd_bwd(cuda_device, n_mol):
+def test_pna_fwd_bwd(cuda_device, n_mol, impl):
     from adkf_ift_b200 import ops
     from oracle import adkf_oracle as orc
     b, _ = make_batch(2, n_mol)
@@ -103,7 +104,7 @@ def test_pna_fwd_bwd(cuda_device, n_mol):
     # CUDA
     gi = ops.build_graph_index([a.to(cuda_device) for a in adjs], V)
     hc, Wc, bc = (x.to(cuda_device).requires_grad_(True) for x in (h, W, bias))
-    out = ops.pna_message_passing(hc, Wc, bc, gi)
+    out = ops.pna_message_passing(hc, Wc, bc, gi, impl=impl)
     e, e32 = rel(out, ref), rel(ref32, ref)
     print("pna fwd rel err cuda", e, "oracle-fp32", e32)
     assert e < max(2e-5, 4 * e32)
@@ -118,11 +119,12 @@ def test_pna_fwd_bwd(cuda_device, n_mol):
         assert l2 < max(1e-4, 4 * l2_32)
         assert e < max(1e-4, 10 * e32)
     # run-to-run bit stability (no float atomics)
-    out2 = ops.pna_message_passing(hc.detach(), Wc.detach(), bc.detach(), gi)
+    out2 = ops.pna_message_passing(hc.detach(), Wc.detach(), bc.detach(), gi, impl=impl)
     assert torch.equal(out2, out.detach())
 
 
-def test_pna_isolated_and_high_degree_nodes(cuda_device):
+@pytest.mark.parametrize("impl", ["tcgen05", "simt"])
+def test_pna_isolated_and_high_degree_nodes(cuda_device, impl):
     """Edge cases: a node without edges (all aggregates 0) and a hub with in-degree 40 (> the 32-message buffer)."""
     from adkf_ift_b200 import ops
     from oracle import adkf_oracle as orc
@@ -138,7 +140,7 @@ def test_pna_isolated_and_high_degree_nodes(cuda_device):
     ref = torch.cat([orc.pna_tower(h.double()[:, 32 * k:32 * k + 32], bid, [W[k, t].double() for t in range(3)],
                                    [bias[k, t].double() for t in range(3)], 64) for k in range(4)], dim=1)
     gi = ops.build_graph_index([a.to(cuda_device) for a in adjs], V)
-    out = ops.pna_message_passing(h.to(cuda_device), W.to(cuda_device), bias.to(cuda_device), gi)
+    out = ops.pna_message_passing(h.to(cuda_device), W.to(cuda_device), bias.to(cuda_device), gi, impl=impl)
     assert rel(out, ref) < 1e-4
     assert float(out[43].abs().max()) == 0.0
 

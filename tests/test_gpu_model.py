@@ -176,3 +176,59 @@ def test_single_task_surface(cuda_device, golden_dir):
         mvn = model(batch, train_loss=None)
     yq = (batch.query_labels.float() - 0.5) * 2.0
     assert abs(float(-mvn.log_prob(yq)) - float(F)) < 1e-4 * abs(float(F))
+
+
+def test_c3_regression_256_task_meta_test(cuda_device):
+    """BASELINE config 3 at full size: 256 regression tasks (--use-numeric-labels), support 128, query 192, ONE pass
+    (81,920 molecules, ~2.1 M nodes).  8 distinct tasks are tiled 32x, which gives a size-independent property on top of
+    the oracle checks: a task's result must not depend on where it sits in the batch.  GP side of every distinct task is
+    checked against the closed-form fp64 oracle on the same features; one task end to end against the torch oracle."""
+    import math
+    from adkf_ift_b200 import dkt, synthetic, task_batch
+    from adkf_ift_b200.adaptive_dkt import ADKTModelTrainerConfig
+    from adkf_ift_b200.adaptive_dkt_utils import ADKTModelTrainer, run_on_task_batch
+    from adkf_ift_b200.feature_extractor import cli_default_config
+    from oracle import adkf_oracle as orc
+    from oracle import gp_closed_form as cf
+    n_s, n_q, distinct, copies = 128, 192, 8, 32
+    cfg = ADKTModelTrainerConfig(graph_feature_extractor_config=cli_default_config(10), use_numeric_labels=True)
+    model = ADKTModelTrainer(cfg)
+    synthetic.deterministic_init_(model, seed=0, alpha=0.5)
+    model.to(cuda_device)
+    hosts = [dkt.task_sample_to_dkt_task_sample(synthetic.make_task_sample(300 + i, n_s, n_q),
+                                                dkt.get_dkt_batcher(max_num_graphs=n_s + n_q), True) for i in range(distinct)]
+    hb = task_batch.collate_tasks([hosts[i % distinct].batches[0] for i in range(distinct * copies)], True)
+    tb = task_batch.to_device(hb, cuda_device)
+    assert tb.num_tasks == 256 and tb.num_graphs == 256 * 320
+    res = run_on_task_batch(model, tb, train=False)
+    torch.cuda.synchronize()
+    status = res.status.cpu().numpy()
+    assert (status & 6).max() == 0, status
+    N = n_s + n_q
+    mean = res.mean.view(256, N)[:, n_s:].cpu().numpy()
+    var = res.variance.view(256, N)[:, n_s:].cpu().numpy()
+    phi = res.phi.cpu().numpy()
+    assert np.isfinite(mean).all() and (var > 0).all()
+    # (a) position independence
+    for c in range(1, copies):
+        for i in range(distinct):
+            assert rel(mean[c * distinct + i], mean[i]) < 1e-5 and rel(phi[c * distinct + i], phi[i]) < 1e-5
+    print("tiled copies bit-identical:", bool(np.array_equal(mean[distinct:2 * distinct], mean[:distinct])))
+    # (b) GP side vs the closed-form oracle on the CUDA features
+    with torch.no_grad():
+        tb8 = task_batch.to_device(task_batch.collate_tasks([h.batches[0] for h in hosts], True), cuda_device)
+        Z = model.embed(tb8).double().cpu().numpy().reshape(distinct, N, -1)
+    y = tb8.labels.double().cpu().numpy().reshape(distinct, N)
+    noise_loc = math.log(0.01) + 0.0625
+    for i in range(distinct):
+        D2 = cf.sq_dist_centered(Z[i], n_s)
+        p_ref, info = cf.newton_fit(D2[:n_s, :n_s], y[i, :n_s], "matern", 0.01, noise_loc)
+        assert np.abs(phi[i] - p_ref).max() < 2e-3, (i, phi[i], p_ref)
+        mr, vr = cf.predict(D2, n_s, y[i, :n_s], phi[i].astype(np.float64), "matern")
+        assert rel(mean[i], mr) < 2e-4 and rel(var[i], vr) < 2e-4
+    # (c) one task end to end against the torch oracle (reference algorithm incl. SciPy L-BFGS-B)
+    P = {n: p.detach().cpu() for n, p in model.named_parameters() if not n.startswith("gp_")}
+    ocfg = orc.OracleConfig(num_layers=10, gp_kernel="matern", use_numeric_labels=True)
+    batch = dkt.torchify(hosts[0], torch.device("cpu")).batches[0]
+    ref = orc.meta_test_task(P, batch, ocfg)
+    assert rel(mean[0], ref["mean"].numpy()) < 2e-3 and rel(var[0], ref["variance"].numpy()) < 2e-3
