@@ -38,6 +38,7 @@
 //              RN accumulation in registers, fused epilogue, stores.
 // Every mbarrier wait is bounded (trap after ~2^28 polls) so that a protocol bug cannot hang the device.
 #include <cuda.h>
+#include <algorithm>
 #include <cstdlib>
 #include "common.cuh"
 #include "../../include/adkf_b200.h"
@@ -145,6 +146,7 @@ struct GemmEpilogue {
     // batching (mode 0): blockIdx.z = batch * splits + split.  Batch b reads A at (mn + b*a_mn, k + b*a_k), B likewise,
     // writes D + b*d_off (+ bias + b*bias_off): column blocks / row blocks of the SAME 2-D arrays, one tensor map each.
     int splits;
+    int gx, gy, ntiles;   // persistent tile walk: tile -> (bx = tile % gx, by = (tile / gx) % gy, bz = tile / (gx gy))
     int debug;            // development probe (ADKF_GEMM_DEBUG): 1 = splitter skips the split, 2 = MMA warp skips the MMAs
     int a_mn, a_k, b_mn, b_k;
     int64_t d_off, bias_off;
@@ -224,6 +226,48 @@ __device__ __forceinline__ void split_tile(const unsigned char* __restrict__ raw
     }
 }
 
+// One output tile of the persistent loop: everything a warp role needs, a pure function of the tile index (so every
+// role takes the same skip decisions without talking to the others).
+struct TileCoord {
+    int rowA0, rowB0;      // first output row / column (mode 1: absolute row of Z)
+    int task, Nt, nsup;    // mode 1
+    int ti, tj;            // mode 1 tile coordinates inside the task
+    int kb0, nk;           // first k-block and number of k-blocks
+    int batch;
+    int64_t zslab;         // blockIdx.z of the non-persistent formulation (split-K slab index)
+    bool skip;
+};
+
+__device__ __forceinline__ TileCoord tile_coord(const GemmEpilogue& ep, int tile) {
+    TileCoord c;
+    const int bx = tile % ep.gx, by = (tile / ep.gx) % ep.gy, bz = tile / (ep.gx * ep.gy);
+    c.task = 0; c.Nt = 0; c.nsup = 0; c.ti = by; c.tj = bx; c.kb0 = 0; c.batch = 0; c.zslab = bz; c.skip = false;
+    c.nk = (ep.K + kBK - 1) / kBK;
+    if (ep.mode == 1) {
+        c.task = bz;
+        const int r0 = ep.z_off[bz];
+        c.Nt = ep.z_off[bz + 1] - r0;
+        c.nsup = ep.n_sup[bz];
+        // symmetric: lower tiles only; the query x query block is not needed for meta-test
+        c.skip = (bx > by) || (by * kBM >= c.Nt) || (!ep.qq_block && bx * kBN >= c.nsup);
+        c.rowA0 = r0 + by * kBM;
+        c.rowB0 = r0 + bx * kBN;
+    } else {
+        c.rowA0 = by * kBM;
+        c.rowB0 = bx * kBN;
+        const int split = bz % ep.splits;
+        c.batch = bz / ep.splits;
+        c.kb0 = split * ep.kb_per_split;
+        c.nk = min(c.nk, c.kb0 + ep.kb_per_split) - c.kb0;              // host guarantees >= 1
+    }
+    return c;
+}
+
+// Persistent: gridDim.x = min(tiles, SMs); CTA b walks tiles b, b + gridDim.x, ...  The smem rings, the double-buffered
+// TMEM accumulators and all mbarrier phases run on across tiles, so the loads / splits / MMAs of tile t+1 overlap the
+// drain and the global stores of tile t (what makes the short-K GEMMs -- K = 64 message MLP, K = 128 BOOM / input
+// gradient -- store-bound instead of launch- and latency-bound: ncu r1c had them at 6-10% tensor-pipe utilisation with one
+// CTA per tile).
 template <bool TA, bool TB>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, GemmEpilogue ep) {
@@ -240,39 +284,12 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
     auto empty_bar = [&](int s) { return bars + 8u * (2 * kRaw + kSplit + s); };    // split stage consumed by the MMAs
     auto accfull_bar = [&](int b) { return bars + 8u * (2 * kRaw + 2 * kSplit + b); };
     auto accempty_bar = [&](int b) { return bars + 8u * (2 * kRaw + 2 * kSplit + 2 + b); };
+    auto tileempty_bar = [&](int b) { return bars + 8u * (2 * kRaw + 2 * kSplit + 4 + b); };   // small[b] drained
     volatile uint32_t* tmem_slot =
-        reinterpret_cast<volatile uint32_t*>(base_ptr + kRingBytes + 8 * (2 * kRaw + 2 * kSplit + 4));
+        reinterpret_cast<volatile uint32_t*>(base_ptr + kRingBytes + 8 * (2 * kRaw + 2 * kSplit + 6));
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-
-    // ---- tile coordinates ---------------------------------------------------------------------------------
-    int rowA0, rowB0, task = 0, Nt = 0, nsup = 0;
-    int kb0 = 0, batch = 0;
-    int nk = (ep.K + kBK - 1) / kBK;
-    float* out = ep.out;
-    const float* bias = ep.bias;
-    if (ep.mode == 1) {
-        task = blockIdx.z;
-        const int r0 = ep.z_off[task];
-        Nt = ep.z_off[task + 1] - r0;
-        nsup = ep.n_sup[task];
-        const int ti = blockIdx.y, tj = blockIdx.x;
-        if (tj > ti || ti * kBM >= Nt) return;                       // symmetric: lower tiles only (uniform exit)
-        if (!ep.qq_block && tj * kBN >= nsup) return;                // query x query block not needed for meta-test
-        rowA0 = r0 + ti * kBM;
-        rowB0 = r0 + tj * kBN;
-    } else {
-        rowA0 = blockIdx.y * kBM;
-        rowB0 = blockIdx.x * kBN;
-        const int split = blockIdx.z % ep.splits;
-        batch = blockIdx.z / ep.splits;
-        kb0 = split * ep.kb_per_split;
-        nk = min(nk, kb0 + ep.kb_per_split) - kb0;                    // host guarantees >= 1
-        out += (int64_t)blockIdx.z * ep.split_stride + (int64_t)batch * ep.d_off;
-        if (bias != nullptr) bias += (int64_t)batch * ep.bias_off;
-    }
-    const int a_mn0 = rowA0 + batch * ep.a_mn, b_mn0 = rowB0 + batch * ep.b_mn;   // TMA coordinates of this batch
-    const int a_k0 = batch * ep.a_k, b_k0 = batch * ep.b_k;
+    const int ntiles = ep.ntiles;
 
     // ---- one-time setup -----------------------------------------------------------------------------------
     if (threadIdx.x == 0) {
@@ -287,6 +304,7 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
         for (int b = 0; b < 2; ++b) {
             mbar_init(accfull_bar(b), 1);
             mbar_init(accempty_bar(b), 8);  // one arrive per drain warp
+            mbar_init(tileempty_bar(b), 8);
         }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
@@ -299,76 +317,98 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
-    const uint32_t tmem_acc = *tmem_slot;
+    const uint32_t tmem_acc = *tmem_slot;     // columns: big[0] 0..127, big[1] 128..255, small[0] 256..383, small[1] 384..511
 
     if (warp == 0) {
         // ===== TMA producer =====
         if (lane == 0) {
-            for (int i = 0; i < nk; ++i) {
-                const int r = i % kRaw;
-                const uint32_t ph = (i / kRaw) & 1;
-                const int k = (kb0 + i) * kBK;
-                mbar_wait(rawempty_bar(r), ph ^ 1);
-                mbar_expect_tx(rawfull_bar(r), kRawBytes);
-                const uint32_t dst = base + r * kRawBytes;
-                if (TA) tma_load_2d(dst, &tmA, rawfull_bar(r), a_mn0, k + a_k0);
-                else    tma_load_2d(dst, &tmA, rawfull_bar(r), k + a_k0, a_mn0);
-                if (TB) tma_load_2d(dst + kTileBytes, &tmB, rawfull_bar(r), b_mn0, k + b_k0);
-                else    tma_load_2d(dst + kTileBytes, &tmB, rawfull_bar(r), k + b_k0, b_mn0);
+            uint32_t it = 0;
+            for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+                const TileCoord c = tile_coord(ep, tile);
+                if (c.skip) continue;
+                const int a_mn0 = c.rowA0 + c.batch * ep.a_mn, b_mn0 = c.rowB0 + c.batch * ep.b_mn;
+                const int a_k0 = c.batch * ep.a_k, b_k0 = c.batch * ep.b_k;
+                for (int i = 0; i < c.nk; ++i, ++it) {
+                    const int r = it % kRaw;
+                    const uint32_t ph = (it / kRaw) & 1;
+                    const int k = (c.kb0 + i) * kBK;
+                    mbar_wait(rawempty_bar(r), ph ^ 1);
+                    mbar_expect_tx(rawfull_bar(r), kRawBytes);
+                    const uint32_t dst = base + r * kRawBytes;
+                    if (TA) tma_load_2d(dst, &tmA, rawfull_bar(r), a_mn0, k + a_k0);
+                    else    tma_load_2d(dst, &tmA, rawfull_bar(r), k + a_k0, a_mn0);
+                    if (TB) tma_load_2d(dst + kTileBytes, &tmB, rawfull_bar(r), b_mn0, k + b_k0);
+                    else    tma_load_2d(dst + kTileBytes, &tmB, rawfull_bar(r), k + b_k0, b_mn0);
+                }
             }
         }
     } else if (warp == 1) {
         // ===== MMA issuer =====
-        for (int i = 0; i < nk; ++i) {
-            const int s = i % kSplit;
-            const uint32_t ph = (i / kSplit) & 1;
-            const int g = i / kGroup, b = g & 1;
-            const bool group_first = (i % kGroup) == 0;
-            const bool group_last = (i % kGroup) == kGroup - 1 || i == nk - 1;
-            if (group_first) mbar_wait(accempty_bar(b), ((g >> 1) & 1) ^ 1);   // drained two groups ago
-            mbar_wait(conv_bar(s), ph);
-            tc_fence_after();
-            if (lane == 0) {
-                const uint32_t st = split_base + s * kSplitBytes;
-                const uint64_t a_hi = smem_desc_k128(st), b_hi = smem_desc_k128(st + kTileBytes);
-                const uint64_t a_lo = smem_desc_k128(st + 2 * kTileBytes), b_lo = smem_desc_k128(st + 3 * kTileBytes);
-                const uint32_t acc_big = tmem_acc + (uint32_t)(b * kBN), acc_small = tmem_acc + 2u * kBN;
+        uint32_t it = 0, gc = 0, tl = 0;
+        for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+            const TileCoord c = tile_coord(ep, tile);
+            if (c.skip) continue;
+            const int sb = tl & 1;
+            mbar_wait(tileempty_bar(sb), ((tl >> 1) & 1) ^ 1);             // small[sb] drained two tiles ago
+            for (int i = 0; i < c.nk; ++i, ++it) {
+                const int s = it % kSplit;
+                const uint32_t ph = (it / kSplit) & 1;
+                const uint32_t g = gc + i / kGroup;
+                const int b = g & 1;
+                const bool group_first = (i % kGroup) == 0;
+                const bool group_last = (i % kGroup) == kGroup - 1 || i == c.nk - 1;
+                if (group_first) mbar_wait(accempty_bar(b), ((g >> 1) & 1) ^ 1);   // drained two groups ago
+                mbar_wait(conv_bar(s), ph);
+                tc_fence_after();
+                if (lane == 0) {
+                    const uint32_t st = split_base + s * kSplitBytes;
+                    const uint64_t a_hi = smem_desc_k128(st), b_hi = smem_desc_k128(st + kTileBytes);
+                    const uint64_t a_lo = smem_desc_k128(st + 2 * kTileBytes), b_lo = smem_desc_k128(st + 3 * kTileBytes);
+                    const uint32_t acc_big = tmem_acc + (uint32_t)(b * kBN), acc_small = tmem_acc + (uint32_t)((2 + sb) * kBN);
 #pragma unroll
-                for (int k = 0; k < ((ep.debug & 2) ? 0 : kBK / 8); ++k) {   // UMMA_K = 8 tf32 = 32 B = +2 in the address field
-                    const uint64_t adv = (uint64_t)(2 * k);
-                    umma_tf32(acc_small, a_lo + adv, b_hi + adv, kIdescTf32, (i | k) ? 1u : 0u);
-                    umma_tf32(acc_small, a_hi + adv, b_lo + adv, kIdescTf32, 1u);
-                    umma_tf32(acc_big, a_hi + adv, b_hi + adv, kIdescTf32, (group_first && k == 0) ? 0u : 1u);
+                    for (int k = 0; k < ((ep.debug & 2) ? 0 : kBK / 8); ++k) {   // UMMA_K = 8 tf32 = 32 B = +2 in the address field
+                        const uint64_t adv = (uint64_t)(2 * k);
+                        umma_tf32(acc_small, a_lo + adv, b_hi + adv, kIdescTf32, (i | k) ? 1u : 0u);
+                        umma_tf32(acc_small, a_hi + adv, b_lo + adv, kIdescTf32, 1u);
+                        umma_tf32(acc_big, a_hi + adv, b_hi + adv, kIdescTf32, (group_first && k == 0) ? 0u : 1u);
+                    }
+                    umma_commit(empty_bar(s));                             // frees the split stage when these MMAs retire
+                    if (group_last) umma_commit(accfull_bar(b));
                 }
-                umma_commit(empty_bar(s));                             // frees the split stage when these MMAs retire
-                if (group_last) umma_commit(accfull_bar(b));
+                __syncwarp();
             }
-            __syncwarp();
+            gc += (uint32_t)((c.nk + kGroup - 1) / kGroup);
+            ++tl;
         }
     } else if (warp >= 4 && warp < 8) {
         // ===== splitter (hi/lo, transposing where the operand is not K-major) =====
         const int t = threadIdx.x - 128;                               // 0..127
         const int chunk = (t & 7) ^ ((t >> 3) & 7);                    // logical 16 B chunk of this thread's float4s
-        for (int i = 0; i < nk; ++i) {
-            const int r = i % kRaw, s = i % kSplit;
-            float4 mu4 = make_float4(0.f, 0.f, 0.f, 0.f);
-            if (ep.mode == 1) {
-                const int k = (kb0 + i) * kBK + chunk * 4;
-                if (k + 3 < ep.K) mu4 = *reinterpret_cast<const float4*>(ep.mu + (size_t)task * ep.K + k);
-            }
-            mbar_wait(rawfull_bar(r), (i / kRaw) & 1);
-            mbar_wait(empty_bar(s), ((i / kSplit) & 1) ^ 1);
-            const unsigned char* rw = base_ptr + (size_t)r * kRawBytes;
-            unsigned char* st = split_ptr + (size_t)s * kSplitBytes;
-            if (!(ep.debug & 1)) {
-                split_tile<TA>(rw, st, st + 2 * kTileBytes, t, mu4);
-                split_tile<TB>(rw + kTileBytes, st + kTileBytes, st + 3 * kTileBytes, t, mu4);
-            }
-            fence_async_smem();                                        // generic-proxy writes -> visible to the MMA (async proxy)
-            __syncwarp();
-            if (lane == 0) {
-                mbar_arrive(conv_bar(s));
-                mbar_arrive(rawempty_bar(r));
+        uint32_t it = 0;
+        for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+            const TileCoord c = tile_coord(ep, tile);
+            if (c.skip) continue;
+            for (int i = 0; i < c.nk; ++i, ++it) {
+                const int r = it % kRaw, s = it % kSplit;
+                float4 mu4 = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (ep.mode == 1) {
+                    const int k = (c.kb0 + i) * kBK + chunk * 4;
+                    if (k + 3 < ep.K) mu4 = *reinterpret_cast<const float4*>(ep.mu + (size_t)c.task * ep.K + k);
+                }
+                mbar_wait(rawfull_bar(r), (it / kRaw) & 1);
+                mbar_wait(empty_bar(s), ((it / kSplit) & 1) ^ 1);
+                const unsigned char* rw = base_ptr + (size_t)r * kRawBytes;
+                unsigned char* st = split_ptr + (size_t)s * kSplitBytes;
+                if (!(ep.debug & 1)) {
+                    split_tile<TA>(rw, st, st + 2 * kTileBytes, t, mu4);
+                    split_tile<TB>(rw + kTileBytes, st + kTileBytes, st + 3 * kTileBytes, t, mu4);
+                }
+                fence_async_smem();                                    // generic-proxy writes -> visible to the MMA (async proxy)
+                __syncwarp();
+                if (lane == 0) {
+                    mbar_arrive(conv_bar(s));
+                    mbar_arrive(rawempty_bar(r));
+                }
             }
         }
     } else if (warp >= 8) {
@@ -377,83 +417,97 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
         const int half = (warp - 8) >> 2;                              // which 64 accumulator columns
         const int r_local = q * 32 + lane;
         const uint32_t trow = tmem_acc + ((uint32_t)(q * 32) << 16) + (uint32_t)(half * 64);
-        float acc[64];
+        const int colbase = half * 64;
+        uint32_t gc = 0, tl = 0;
+        for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+            const TileCoord c = tile_coord(ep, tile);
+            if (c.skip) continue;
+            const int sb = tl & 1;
+            float acc[64];
 #pragma unroll
-        for (int j = 0; j < 64; ++j) acc[j] = 0.f;
-        const int ngroups = (nk + kGroup - 1) / kGroup;
-        for (int g = 0; g < ngroups; ++g) {
-            const int b = g & 1;
-            mbar_wait(accfull_bar(b), (g >> 1) & 1);
-            tc_fence_after();
+            for (int j = 0; j < 64; ++j) acc[j] = 0.f;
+            const int ngroups = (c.nk + kGroup - 1) / kGroup;
+            for (int gl = 0; gl < ngroups; ++gl) {
+                const uint32_t g = gc + gl;
+                const int b = g & 1;
+                mbar_wait(accfull_bar(b), (g >> 1) & 1);
+                tc_fence_after();
 #pragma unroll
-            for (int c0 = 0; c0 < 64; c0 += 16) {
+                for (int c0 = 0; c0 < 64; c0 += 16) {
+                    float v[16];
+                    tmem_ld16(trow + (uint32_t)(b * kBN) + c0, v);
+#pragma unroll
+                    for (int j = 0; j < 16; ++j) acc[c0 + j] += v[j];
+                }
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(accempty_bar(b));
+            }
+#pragma unroll
+            for (int c0 = 0; c0 < 64; c0 += 16) {                      // the small correction accumulator, once per tile
                 float v[16];
-                tmem_ld16(trow + (uint32_t)(b * kBN) + c0, v);
+                tmem_ld16(trow + (uint32_t)((2 + sb) * kBN) + c0, v);
 #pragma unroll
                 for (int j = 0; j < 16; ++j) acc[c0 + j] += v[j];
             }
             tc_fence_before();
             __syncwarp();
-            if (lane == 0) mbar_arrive(accempty_bar(b));
-        }
+            if (lane == 0) mbar_arrive(tileempty_bar(sb));
+            gc += (uint32_t)ngroups;
+            ++tl;
+
+            if (ep.mode == 0) {
+                float* out = ep.out + c.zslab * ep.split_stride + (int64_t)c.batch * ep.d_off;
+                const float* bias = (ep.bias != nullptr) ? ep.bias + (int64_t)c.batch * ep.bias_off : nullptr;
+                const int64_t r = (int64_t)c.rowA0 + r_local;
+                float* orow = out + r * ep.ldo;
+                const bool vec_ok = (ep.ldo % 4 == 0) && ((reinterpret_cast<uintptr_t>(out) & 15) == 0);
 #pragma unroll
-        for (int c0 = 0; c0 < 64; c0 += 16) {                          // the small correction accumulator, once
-            float v[16];
-            tmem_ld16(trow + 2u * kBN + c0, v);
+                for (int c0 = 0; c0 < 64; c0 += 16) {
+                    float v[16];
 #pragma unroll
-            for (int j = 0; j < 16; ++j) acc[c0 + j] += v[j];
-        }
-        const int colbase = half * 64;
-        if (ep.mode == 0) {
-            const int64_t r = (int64_t)rowA0 + r_local;
-            float* orow = out + r * ep.ldo;
-            const bool vec_ok = (ep.ldo % 4 == 0) && ((reinterpret_cast<uintptr_t>(out) & 15) == 0);
+                    for (int j = 0; j < 16; ++j) v[j] = acc[c0 + j];
+                    const int col0 = c.rowB0 + colbase + c0;
+                    if (r < ep.M && col0 < ep.N) {
 #pragma unroll
-            for (int c0 = 0; c0 < 64; c0 += 16) {
-                float v[16];
+                        for (int j = 0; j < 16; ++j) {
+                            float x = v[j];
+                            if (bias != nullptr && col0 + j < ep.N) x += bias[col0 + j];
+                            if (ep.act == 1) x = fmaxf(x, 0.f);
+                            else if (ep.act == 2) x = (x > 0.f) ? x : 0.01f * x;
+                            else if (ep.act == 3 && col0 + j < ep.N) x = orow[col0 + j] - x;   // D <- D - A.B^T (trailing update)
+                            v[j] = x;
+                        }
+                        if (vec_ok && col0 + 16 <= ep.N) {
 #pragma unroll
-                for (int j = 0; j < 16; ++j) v[j] = acc[c0 + j];
-                const int col0 = rowB0 + colbase + c0;
-                if (r < ep.M && col0 < ep.N) {
+                            for (int j = 0; j < 16; j += 4)
+                                *reinterpret_cast<float4*>(orow + col0 + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+                        } else {
 #pragma unroll
-                    for (int j = 0; j < 16; ++j) {
-                        float x = v[j];
-                        if (bias != nullptr && col0 + j < ep.N) x += bias[col0 + j];
-                        if (ep.act == 1) x = fmaxf(x, 0.f);
-                        else if (ep.act == 2) x = (x > 0.f) ? x : 0.01f * x;
-                        else if (ep.act == 3 && col0 + j < ep.N) x = orow[col0 + j] - x;   // D <- D - A.B^T (trailing update)
-                        v[j] = x;
-                    }
-                    if (vec_ok && col0 + 16 <= ep.N) {
-#pragma unroll
-                        for (int j = 0; j < 16; j += 4)
-                            *reinterpret_cast<float4*>(orow + col0 + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
-                    } else {
-#pragma unroll
-                        for (int j = 0; j < 16; ++j)
-                            if (col0 + j < ep.N) orow[col0 + j] = v[j];
+                            for (int j = 0; j < 16; ++j)
+                                if (col0 + j < ep.N) orow[col0 + j] = v[j];
+                        }
                     }
                 }
-            }
-        } else {
-            const int r0 = ep.z_off[task];
-            const int ti = blockIdx.y, tj = blockIdx.x;
-            const int r = ti * kBM + r_local;                          // row inside the task
-            float* Dt = out + ep.d2_off[task];
-            const float ni = (r < Nt) ? ep.nrm[r0 + r] : 0.f;
+            } else {
+                const int r0 = ep.z_off[c.task];
+                const int r = c.ti * kBM + r_local;                    // row inside the task
+                float* Dt = ep.out + ep.d2_off[c.task];
+                const float ni = (r < c.Nt) ? ep.nrm[r0 + r] : 0.f;
 #pragma unroll
-            for (int c0 = 0; c0 < 64; c0 += 16) {
-                float v[16];
+                for (int c0 = 0; c0 < 64; c0 += 16) {
+                    float v[16];
 #pragma unroll
-                for (int j = 0; j < 16; ++j) v[j] = acc[c0 + j];
-                if (r < Nt) {
+                    for (int j = 0; j < 16; ++j) v[j] = acc[c0 + j];
+                    if (r < c.Nt) {
 #pragma unroll
-                    for (int j = 0; j < 16; ++j) {
-                        const int c = tj * kBN + colbase + c0 + j;
-                        if (c < Nt && (ti != tj || c <= r)) {
-                            const float d = pairstat_value(ep.stat, ni, ep.nrm[r0 + c], v[j], r == c);
-                            Dt[(size_t)r * Nt + c] = d;
-                            Dt[(size_t)c * Nt + r] = d;
+                        for (int j = 0; j < 16; ++j) {
+                            const int cc = c.tj * kBN + colbase + c0 + j;
+                            if (cc < c.Nt && (c.ti != c.tj || cc <= r)) {
+                                const float d = pairstat_value(ep.stat, ni, ep.nrm[r0 + cc], v[j], r == cc);
+                                Dt[(size_t)r * c.Nt + cc] = d;
+                                Dt[(size_t)cc * c.Nt + r] = d;
+                            }
                         }
                     }
                 }
@@ -511,6 +565,16 @@ static int make_map_2d(CUtensorMap* map, const float* ptr, int64_t rows, int64_t
                        // current context yet: bind the primary context through the runtime and retry
     }
     return r == CUDA_SUCCESS ? 0 : -(1000 + (int)r);   // tensor-map encode failure: -(1000 + CUresult)
+}
+
+static int num_sms() {
+    static int n = 0;
+    if (n == 0) {
+        int dev = 0;
+        if (cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0)
+            n = 148;
+    }
+    return n;
 }
 
 template <bool TA, bool TB>
@@ -597,7 +661,11 @@ static int gemm_launch(const float* A, int transA, int64_t lda, int64_t a_slow, 
     } else {
         ep.out = D; ep.ldo = ldd; ep.split_stride = 0; ep.d_off = d_off;
     }
-    dim3 grid((N + kBN - 1) / kBN, (unsigned)((M + kBM - 1) / kBM), splits * batch);
+    ep.gx = (int)((N + kBN - 1) / kBN); ep.gy = (int)((M + kBM - 1) / kBM);
+    const int64_t ntiles64 = (int64_t)ep.gx * ep.gy * splits * batch;
+    if (ntiles64 > 0x7fffffff) return ADKF_ERR_BADARG;
+    ep.ntiles = (int)ntiles64;
+    dim3 grid((unsigned)std::min<int64_t>(ntiles64, num_sms()));
     if (!transA && !transB) {
         if ((rc = gemm_attr<false, false>())) return rc;
         gemm_tf32x3_kernel<false, false><<<grid, kGemmThreads, kGemmSmem, s>>>(ma, mb, ep);
@@ -679,7 +747,8 @@ extern "C" int adkf_gram_pairstat_tc(int32_t stat, const float* Z, int32_t d, in
     ep.mode = 1; ep.out = D2; ep.K = d; ep.z_off = z_off; ep.n_sup = n_sup; ep.d2_off = d2_off; ep.mu = mu_ws;
     ep.nrm = nrm_ws; ep.qq_block = qq_block; ep.kb_per_split = (d + kBK - 1) / kBK; ep.stat = stat;
     const int nt = (max_n + kBM - 1) / kBM;
-    gemm_tf32x3_kernel<false, false><<<dim3(nt, nt, T), kGemmThreads, kGemmSmem, s>>>(mz, mz, ep);
+    ep.gx = nt; ep.gy = nt; ep.ntiles = nt * nt * T;
+    gemm_tf32x3_kernel<false, false><<<dim3((unsigned)std::min(ep.ntiles, num_sms())), kGemmThreads, kGemmSmem, s>>>(mz, mz, ep);
     if (stat != ADKF_STAT_SQDIST && !qq_block) launch_pairstat_diag(stat, T, z_off, d2_off, max_n, nrm_ws, D2, s);
     adkf_count_launches(3);
     ADKF_LAUNCH_CHECK();

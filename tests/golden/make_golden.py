@@ -194,9 +194,16 @@ def gp_kernels_fixture(path):
 
 if __name__ == "__main__":
     print(REPORT)
+    if len(sys.argv) > 1 and sys.argv[1] == "s64":
+        # task 3: the smallest non-zero top-2 gap of the max-pool readout is 1.9e-5 (tests/golden/scan_ties.py), so the
+        # arg-max routing of the reference's gradient does not hinge on fp32 rounding (task 9, used at first, has a
+        # 1.9e-6 near-tie that two correct fp32 implementations resolve differently)
+        model_task_fixture(os.path.join(HERE, "s64_rbf_l2.npz"), task_id=3, n_s=64, n_q=64, use_numeric=False,
+                           kernel="rbf", num_layers=2)
+        sys.exit(0)
     batcher_fixture(os.path.join(HERE, "batcher.npz"))
     gp_kernels_fixture(os.path.join(HERE, "gp_kernels.npz"))
     model_task_fixture(os.path.join(HERE, "c1_classification.npz"), task_id=0, n_s=16, n_q=32, use_numeric=False)
     model_task_fixture(os.path.join(HERE, "c1_regression.npz"), task_id=5, n_s=16, n_q=32, use_numeric=True)
-    model_task_fixture(os.path.join(HERE, "s64_rbf_l2.npz"), task_id=9, n_s=64, n_q=64, use_numeric=False,
+    model_task_fixture(os.path.join(HERE, "s64_rbf_l2.npz"), task_id=3, n_s=64, n_q=64, use_numeric=False,
                        kernel="rbf", num_layers=2)
