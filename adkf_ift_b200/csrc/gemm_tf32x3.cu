@@ -29,7 +29,8 @@
 // operand combinations (A,B) = (K,K) forward, (K,T) input gradient, (T,T) weight gradient (split-K over the node dimension,
 // deterministic two-pass reduction).
 //
-// CTA = one 128 x 128 output tile, 16 warps, two smem rings (raw: TMA -> splitter, 3 x 32 KB; split: splitter -> MMA, 2 x 64 KB):
+// CTA = persistent over 128 x 128 output tiles, 16 warps, two smem rings (raw: TMA -> splitter, 2 x 32 KB; split: splitter -> MMA,
+// 2 x 64 KB) + 32 KB of epilogue staging:
 //   warp 0     TMA producer      cp.async.bulk.tensor.2d -> raw ring
 //   warp 1     MMA issuer        one elected lane: 4 k-steps x 3 tcgen05.mma per k-block, tcgen05.commit frees the split stage
 //   warp 2     TMEM allocator    512 columns: big[2] x 128, small x 128
@@ -46,16 +47,17 @@
 namespace adkf {
 
 constexpr int kBM = 128, kBN = 128, kBK = 32;        // tile; 32 floats = 128 B = one swizzle row
-constexpr int kRaw = 3;                              // raw ring depth (TMA destination: A_raw, B_raw)
+constexpr int kRaw = 2;                              // raw ring depth (TMA destination: A_raw, B_raw)
 constexpr int kSplit = 2;                            // split ring depth (MMA source: A_hi, B_hi, A_lo, B_lo)
 constexpr int kTileBytes = kBM * kBK * 4;            // 16 KB
 constexpr int kRawBytes = 2 * kTileBytes;
 constexpr int kSplitBytes = 4 * kTileBytes;
-constexpr int kRingBytes = kRaw * kRawBytes + kSplit * kSplitBytes;   // 224 KB
+constexpr int kRingBytes = kRaw * kRawBytes + kSplit * kSplitBytes;   // 192 KB
+constexpr int kStageBytes = 8 * 4096;                // epilogue staging: 8 drain warps x (32 rows x 32 columns) fp32
 constexpr int kGemmThreads = 512;
 constexpr int kTmemCols = 512;                       // big[0], big[1], small (128 fp32 columns each); power of two
 constexpr int kGroup = 4;                            // k-blocks accumulated in TMEM between two drains
-constexpr size_t kGemmSmem = (size_t)kRingBytes + 1024 /*align*/ + 256 /*barriers*/;
+constexpr size_t kGemmSmem = (size_t)kRingBytes + kStageBytes + 1024 /*align*/ + 256 /*barriers*/;
 
 // ---- PTX wrappers ---------------------------------------------------------------------------------------
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -277,7 +279,8 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
     unsigned char* base_ptr = smem_raw + (base - raw);
     const uint32_t split_base = base + kRaw * kRawBytes;
     unsigned char* split_ptr = base_ptr + kRaw * kRawBytes;
-    const uint32_t bars = base + kRingBytes;
+    const uint32_t bars = base + kRingBytes + kStageBytes;
+    unsigned char* stage_ptr = base_ptr + kRingBytes;
     auto rawfull_bar = [&](int r) { return bars + 8u * r; };
     auto rawempty_bar = [&](int r) { return bars + 8u * (kRaw + r); };
     auto conv_bar = [&](int s) { return bars + 8u * (2 * kRaw + s); };              // split stage filled
@@ -286,7 +289,7 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
     auto accempty_bar = [&](int b) { return bars + 8u * (2 * kRaw + 2 * kSplit + 2 + b); };
     auto tileempty_bar = [&](int b) { return bars + 8u * (2 * kRaw + 2 * kSplit + 4 + b); };   // small[b] drained
     volatile uint32_t* tmem_slot =
-        reinterpret_cast<volatile uint32_t*>(base_ptr + kRingBytes + 8 * (2 * kRaw + 2 * kSplit + 6));
+        reinterpret_cast<volatile uint32_t*>(base_ptr + kRingBytes + kStageBytes + 8 * (2 * kRaw + 2 * kSplit + 6));
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int ntiles = ep.ntiles;
@@ -333,6 +336,7 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
                     const uint32_t ph = (it / kRaw) & 1;
                     const int k = (c.kb0 + i) * kBK;
                     mbar_wait(rawempty_bar(r), ph ^ 1);
+                    if (ep.debug & 16) { mbar_arrive(rawfull_bar(r)); continue; }
                     mbar_expect_tx(rawfull_bar(r), kRawBytes);
                     const uint32_t dst = base + r * kRawBytes;
                     if (TA) tma_load_2d(dst, &tmA, rawfull_bar(r), a_mn0, k + a_k0);
@@ -433,7 +437,7 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
                 mbar_wait(accfull_bar(b), (g >> 1) & 1);
                 tc_fence_after();
 #pragma unroll
-                for (int c0 = 0; c0 < 64; c0 += 16) {
+                for (int c0 = 0; c0 < ((ep.debug & 32) ? 0 : 64); c0 += 16) {
                     float v[16];
                     tmem_ld16(trow + (uint32_t)(b * kBN) + c0, v);
 #pragma unroll
@@ -444,7 +448,7 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
                 if (lane == 0) mbar_arrive(accempty_bar(b));
             }
 #pragma unroll
-            for (int c0 = 0; c0 < 64; c0 += 16) {                      // the small correction accumulator, once per tile
+            for (int c0 = 0; c0 < ((ep.debug & 32) ? 0 : 64); c0 += 16) {   // the small correction accumulator, once per tile
                 float v[16];
                 tmem_ld16(trow + (uint32_t)((2 + sb) * kBN) + c0, v);
 #pragma unroll
@@ -456,38 +460,68 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
             gc += (uint32_t)ngroups;
             ++tl;
 
+            if (ep.debug & 64) continue;
             if (ep.mode == 0) {
+                // Through a warp-private swizzled smem tile (32 rows x 32 columns per pass) so that every global store
+                // instruction writes 4 rows x 128 contiguous bytes (the lane-per-row layout of tcgen05.ld would touch 32
+                // different lines with 16 bytes each).  Bias and activation are applied AFTER the transpose, where a lane
+                // owns 4 fixed columns: one float4 bias load per pass instead of 64 scalar loads per row.
                 float* out = ep.out + c.zslab * ep.split_stride + (int64_t)c.batch * ep.d_off;
-                const float* bias = (ep.bias != nullptr) ? ep.bias + (int64_t)c.batch * ep.bias_off : nullptr;
-                const int64_t r = (int64_t)c.rowA0 + r_local;
-                float* orow = out + r * ep.ldo;
+                const float* bias = (ep.bias != nullptr && !(ep.debug & 8)) ? ep.bias + (int64_t)c.batch * ep.bias_off : nullptr;
                 const bool vec_ok = (ep.ldo % 4 == 0) && ((reinterpret_cast<uintptr_t>(out) & 15) == 0);
+                float4* stg = reinterpret_cast<float4*>(stage_ptr + (size_t)(warp - 8) * 4096);
+                const int ch = lane & 7, rsub = lane >> 3;
+                const int act = ep.act;
 #pragma unroll
-                for (int c0 = 0; c0 < 64; c0 += 16) {
-                    float v[16];
+                for (int p = 0; p < 2; ++p) {
 #pragma unroll
-                    for (int j = 0; j < 16; ++j) v[j] = acc[c0 + j];
-                    const int col0 = c.rowB0 + colbase + c0;
-                    if (r < ep.M && col0 < ep.N) {
-#pragma unroll
-                        for (int j = 0; j < 16; ++j) {
-                            float x = v[j];
-                            if (bias != nullptr && col0 + j < ep.N) x += bias[col0 + j];
-                            if (ep.act == 1) x = fmaxf(x, 0.f);
-                            else if (ep.act == 2) x = (x > 0.f) ? x : 0.01f * x;
-                            else if (ep.act == 3 && col0 + j < ep.N) x = orow[col0 + j] - x;   // D <- D - A.B^T (trailing update)
-                            v[j] = x;
-                        }
-                        if (vec_ok && col0 + 16 <= ep.N) {
-#pragma unroll
-                            for (int j = 0; j < 16; j += 4)
-                                *reinterpret_cast<float4*>(orow + col0 + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+                    for (int j = 0; j < 8; ++j)
+                        stg[lane * 8 + (j ^ (lane & 7))] =
+                            make_float4(acc[p * 32 + 4 * j], acc[p * 32 + 4 * j + 1], acc[p * 32 + 4 * j + 2], acc[p * 32 + 4 * j + 3]);
+                    __syncwarp();
+                    const int col = c.rowB0 + colbase + p * 32 + ch * 4;
+                    const bool full = vec_ok && col + 4 <= ep.N;
+                    float4 b4 = make_float4(0.f, 0.f, 0.f, 0.f);
+                    if (bias != nullptr) {
+                        if (col + 4 <= ep.N && ((reinterpret_cast<uintptr_t>(bias + col) & 15) == 0)) {
+                            b4 = *reinterpret_cast<const float4*>(bias + col);
                         } else {
-#pragma unroll
-                            for (int j = 0; j < 16; ++j)
-                                if (col0 + j < ep.N) orow[col0 + j] = v[j];
+                            if (col < ep.N) b4.x = bias[col];
+                            if (col + 1 < ep.N) b4.y = bias[col + 1];
+                            if (col + 2 < ep.N) b4.z = bias[col + 2];
+                            if (col + 3 < ep.N) b4.w = bias[col + 3];
                         }
                     }
+                    const int64_t rbase = (int64_t)c.rowA0 + q * 32 + rsub;
+                    float* o = out + rbase * ep.ldo + col;
+                    const int64_t ostep = 4 * ep.ldo;
+#pragma unroll
+                    for (int jj = 0; jj < 8; ++jj, o += ostep) {
+                        const int rr = jj * 4 + rsub;
+                        float4 x = stg[rr * 8 + (ch ^ (rr & 7))];
+                        x.x += b4.x; x.y += b4.y; x.z += b4.z; x.w += b4.w;
+                        if (act == 1) {
+                            x.x = fmaxf(x.x, 0.f); x.y = fmaxf(x.y, 0.f); x.z = fmaxf(x.z, 0.f); x.w = fmaxf(x.w, 0.f);
+                        } else if (act == 2) {
+                            x.x = (x.x > 0.f) ? x.x : 0.01f * x.x; x.y = (x.y > 0.f) ? x.y : 0.01f * x.y;
+                            x.z = (x.z > 0.f) ? x.z : 0.01f * x.z; x.w = (x.w > 0.f) ? x.w : 0.01f * x.w;
+                        }
+                        if (rbase + jj * 4 < ep.M && col < ep.N && !(ep.debug & 4)) {
+                            if (full) {
+                                if (act == 3) {                                    // D <- D - A.B^T (trailing update)
+                                    const float4 old = *reinterpret_cast<const float4*>(o);
+                                    x = make_float4(old.x - x.x, old.y - x.y, old.z - x.z, old.w - x.w);
+                                }
+                                *reinterpret_cast<float4*>(o) = x;
+                            } else {
+                                const float xs[4] = {x.x, x.y, x.z, x.w};
+#pragma unroll
+                                for (int e = 0; e < 4; ++e)
+                                    if (col + e < ep.N) o[e] = (act == 3) ? o[e] - xs[e] : xs[e];
+                            }
+                        }
+                    }
+                    __syncwarp();
                 }
             } else {
                 const int r0 = ep.z_off[c.task];
