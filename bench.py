@@ -127,40 +127,67 @@ def timed_region(fn, steps, world, device):
     return float(ms.item())
 
 
+def _time_ms(fn, reps=10, warm=3):
+    for _ in range(warm):
+        fn()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(reps):
+        fn()
+    e1.record()
+    torch.cuda.synchronize()
+    return e0.elapsed_time(e1) / reps
+
+
 def dominant_kernel_roofline(model, tb, peaks):
-    """Times the dominant own kernel (the fused PNA message-passing forward of one GNN block over the whole
-    16-task graph batch) alone with CUDA events and relates its ALGORITHMIC bytes (4*H*V read of h,
-    4*3072*V write of the aggregate, 512 B/node of backward aux, 4 B/edge source index, 1 B/edge type,
-    4*(V+1) rowptr) to the measured HBM copy bandwidth."""
+    """The dominant kernel of the step is the tcgen05 3xTF32 GEMM (gemm_tf32x3_kernel, ~60% of the device time over its
+    three operand forms, profiles/r1c_*): timed here alone, with CUDA events, on its most expensive launch of the step --
+    the readout hidden layer over all V nodes of the 16-task batch (M = V, N = 768, K = 1408, bias + ReLU fused).
+    achieved = ALGORITHMIC flops 2 M N K (fp32-equivalent; the kernel issues 3 TF32 MMAs per product, reported beside it)
+    over the measured duration; peak = TF32 dense = half of the measured bf16 peak of MEASURED_PEAKS.json.
+    A second entry gives the HBM-bound PNA aggregation kernel (reads pre [E,768], writes the aggregate [V,3072])."""
     from adkf_ift_b200 import ops
     gi = tb.graph_index
     V, E = gi.num_nodes, gi.num_edges
+    dev = tb.node_features.device
+    M, N, K = V, 768, 1408
+    x, w, b = torch.randn(M, K, device=dev), torch.randn(N, K, device=dev) / K ** 0.5, torch.randn(N, device=dev)
+    ms = _time_ms(lambda: ops.gemm_tf32x3(x, False, w, False, b, "relu"))
+    flops = 2.0 * M * N * K
+    achieved = flops / (ms * 1e-3) / 1e12
+    bf16 = peaks.get("bf16_tflops")
+    src = "measured (MEASURED_PEAKS.json bf16_tflops / 2: TF32 runs at half the bf16 rate)"
+    if bf16 is None:
+        bf16, src = 2250.0 * 0.73, "fallback (B200_PROFILING.md nominal bf16 x 0.73) / 2"
+    peak = bf16 / 2.0
+    roof = {"kernel": "gemm_tf32x3_kernel<false,false> (readout hidden layer, M=V N=768 K=1408, bias+ReLU)", "bound": "tensor",
+            "achieved": round(achieved, 1), "peak": round(peak, 1), "unit": "TFLOP/s", "frac": round(achieved / peak, 4),
+            "traffic": 1.142e9, "traffic_source": "ncu --set full, profiles/r1d_gemm_probe_summary.md (dram read+write per launch)",
+            "peak_source": src, "launch_ms": round(ms, 4), "algorithmic_flops": flops,
+            "issued_tf32_tflops": round(3 * achieved, 1), "frac_issued": round(3 * achieved / peak, 4),
+            "algorithmic_bytes": 4.0 * (M * K + N * K + M * N), "M": M, "N": N, "K": K}
+    # secondary: the HBM-bound aggregation kernel of one GNN block
+    del x, w, b
     blk = model.graph_feature_extractor.gnn.gnn_blocks[0]
     with torch.no_grad():
-        W, b = blk.stacked_message_weights()
-        h = torch.randn(V, 128, device=W.device)
-        for _ in range(3):
-            ops.pna_message_passing(h, W, b, gi)
-        torch.cuda.synchronize()
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        reps = 10
-        e0.record()
-        for _ in range(reps):
-            ops.pna_message_passing(h, W, b, gi)
-        e1.record()
-        torch.cuda.synchronize()
-    ms = e0.elapsed_time(e1) / reps
-    alg_bytes = 4 * 128 * V + 4 * 3072 * V + 512 * V + 5 * E + 4 * (V + 1)
-    achieved = alg_bytes / (ms * 1e-3) / 1e9
-    peak = peaks.get("hbm_gbs")
-    src = "measured (MEASURED_PEAKS.json hbm_gbs)"
-    if peak is None:
-        peak, src = 6650.0, "fallback (B200_PROFILING.md)"
-    flops = 2 * 192 * 32 * 4 * (E + V * 1.3)   # source half per edge + target half per (node, type present)
-    return {"kernel": "pna_fwd_kernel", "bound": "hbm", "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s",
-            "frac": round(achieved / peak, 4), "traffic": None, "peak_source": src, "launch_ms": round(ms, 4),
-            "algorithmic_bytes": int(alg_bytes), "nodes": V, "directed_edges": E,
-            "fp32_tflops": round(flops / (ms * 1e-3) / 1e12, 2)}
+        W, bb = blk.stacked_message_weights()
+        h = torch.randn(V, 128, device=dev)
+        from adkf_ift_b200 import _cabi
+        lib = _cabi.load()
+        ts = gi.type_sorted
+        pre = torch.randn(max(E, 1), 768, device=dev)
+        out = torch.empty(V, 3072, device=dev)
+        cnt = torch.empty(V, 4, 64, dtype=torch.uint8, device=dev)
+        arg = torch.empty(V, 4, 64, dtype=torch.uint8, device=dev)
+        ms2 = _time_ms(lambda: ops.check(lib.adkf_pna_aggregate_fwd(ops.dptr(pre), ops.dptr(ts.tptr), V, ops.dptr(out), ops.dptr(cnt),
+                                                                    ops.dptr(arg), ops.stream_ptr()), "adkf_pna_aggregate_fwd"))
+    alg2 = 4.0 * 768 * E + 4.0 * 3072 * V + 512.0 * V + 4.0 * (V + 1)
+    hbm = peaks.get("hbm_gbs") or 6650.0
+    roof["hbm_kernel"] = {"kernel": "pna_aggregate_fwd_kernel", "bound": "hbm", "achieved": round(alg2 / (ms2 * 1e-3) / 1e9, 1),
+                          "peak": hbm, "unit": "GB/s", "frac": round(alg2 / (ms2 * 1e-3) / 1e9 / hbm, 4), "launch_ms": round(ms2, 4),
+                          "algorithmic_bytes": alg2, "nodes": V, "directed_edges": E}
+    return roof
 
 
 # ----------------------------------------------------------------------------------------------------------
