@@ -12,6 +12,7 @@
 // shared memory (row stride n|1 to keep column walks bank-conflict free) when they fit, else in an
 // L2-resident global workspace; the joint (n+m) x (n+m) matrices of the IFT stage always live in the
 // workspace.  All closed-form algebra follows SURVEY.md App. B and is mirrored in oracle/gp_closed_form.py.
+#include <cstdio>
 #include "common.cuh"
 #include "../../include/adkf_b200.h"
 
@@ -159,6 +160,40 @@ __device__ void tri_inverse(const float* L, float* X, int n, int ld) {
     }
 }
 
+// X <- L^-1 with one WARP per column (right-looking substitution): lane l keeps the residual entries of rows l, l+32, ...
+// in registers, every step broadcasts x_k by shuffle and updates all later rows at once, so the dependent chain per
+// column is n short steps instead of the n^2/2 serial multiply-adds of the thread-per-column version (clock64 probe:
+// 64 x 64 tile 100 k -> ~10 k cycles).  n <= 32 Q.
+template <int Q>
+__device__ void tri_inverse_cols(const float* L, float* X, int n, int ld) {
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, nw = blockDim.x >> 5;
+    for (int c = wid; c < n; c += nw) {
+        float r[Q];
+#pragma unroll
+        for (int q = 0; q < Q; ++q) r[q] = (lane + 32 * q == c) ? 1.f : 0.f;
+        for (int i = lane; i < c; i += 32) X[(size_t)i * ld + c] = 0.f;
+        for (int k = c; k < n; ++k) {
+            float rk = 0.f;
+#pragma unroll
+            for (int q = 0; q < Q; ++q) if (q == (k >> 5)) rk = r[q];
+            rk = __shfl_sync(0xffffffffu, rk, k & 31);
+            const float xk = rk / L[(size_t)k * ld + k];
+            if (lane == (k & 31)) X[(size_t)k * ld + c] = xk;
+#pragma unroll
+            for (int q = 0; q < Q; ++q) {
+                const int i = lane + 32 * q;
+                if (i > k && i < n) r[q] = fmaf(-L[(size_t)i * ld + k], xk, r[q]);
+            }
+        }
+    }
+}
+__device__ void tri_inverse_fast(const float* L, float* X, int n, int ld) {
+    if (n <= 64) tri_inverse_cols<2>(L, X, n, ld);
+    else if (n <= 128) tri_inverse_cols<4>(L, X, n, ld);
+    else if (n <= 256) tri_inverse_cols<8>(L, X, n, ld);
+    else tri_inverse(L, X, n, ld);
+}
+
 // P <- X^T X (full symmetric), X lower triangular.
 __device__ void xtx(const float* X, float* P, int n, int ld) {
     for (int idx = threadIdx.x; idx < n * n; idx += blockDim.x) {
@@ -271,7 +306,7 @@ __device__ bool gp_eval_full(const GpProblem& pb, const float* phi, float* M1, f
     for (int i = threadIdx.x; i < n; i += blockDim.x) part_ld[0] += logf(M1[(size_t)i * ld + i]);
     block_sum_multi<1>(part_ld, sh.red, sh.sums);
     const float logdet = 2.f * (float)sh.sums[0];
-    tri_inverse(M1, M2, n, ld);
+    tri_inverse_fast(M1, M2, n, ld);
     __syncthreads();
     xtx(M2, M1, n, ld);            // M1 <- P
     __syncthreads();
@@ -638,7 +673,7 @@ gp_predict_kernel(const int32_t* __restrict__ z_off, const int32_t* __restrict__
         if (threadIdx.x == 0) status[t] = ADKF_ST_NOT_PD;
         return;
     }
-    tri_inverse(cv.M1, cv.M2, n, cv.ld);     // M2 = X = L^-1
+    tri_inverse_fast(cv.M1, cv.M2, n, cv.ld);     // M2 = X = L^-1
     float* w = cv.vec;                       // w = X y
     float* alpha = cv.vec + n;               // alpha = X^T w
     __syncthreads();
@@ -691,6 +726,169 @@ gp_predict_kernel(const int32_t* __restrict__ z_off, const int32_t* __restrict__
     if (threadIdx.x == 0) status[t] = (sh.jitter > 0.f) ? ADKF_ST_JITTER : ADKF_ST_OK;
 }
 
+// ---------------------------------------------------------------------------------------------
+// Blocked dense kernels for the joint (support + query) covariance of gp_ift_kernel: N = n + m ~ 320 does not fit
+// in shared memory, so the matrix stays in the (L2-resident) global workspace and is processed in 64 x 64 tiles that
+// are staged in three shared-memory buffers.  Everything is built from one CTA-wide tile product
+// C = beta C + alpha A B^T (r1c ncu + in-kernel clock64 probe: the unblocked thread-per-column code spent 35 M cycles
+// = 18 ms per step in these three phases at ~1 FMA per clock).
+// ---------------------------------------------------------------------------------------------
+constexpr int kJb = 64;            // tile edge
+constexpr int kJld = kJb + 1;      // padded leading dimension of a tile in shared memory
+constexpr int kJTileFloats = kJb * kJld;
+
+// dst[r][c] (or dst[c][r] when TR) <- src[(r0 + r) * ld + c0 + c], zero outside the N x N matrix
+template <bool TR>
+__device__ __forceinline__ void jt_load(float* dst, const float* src, int ld, int r0, int c0, int N) {
+    for (int idx = threadIdx.x; idx < kJb * kJb; idx += blockDim.x) {
+        const int r = idx >> 6, c = idx & 63;
+        const float v = (r0 + r < N && c0 + c < N) ? src[(size_t)(r0 + r) * ld + c0 + c] : 0.f;
+        if (TR) dst[c * kJld + r] = v; else dst[r * kJld + c] = v;
+    }
+}
+// dst[(r0 + r) * ld + c0 + c] <- tile[r][c] (or tile[c][r] when TR), inside the N x N matrix only
+template <bool TR>
+__device__ __forceinline__ void jt_store(float* dst, int ld, int r0, int c0, int N, const float* tile) {
+    for (int idx = threadIdx.x; idx < kJb * kJb; idx += blockDim.x) {
+        const int r = idx >> 6, c = idx & 63;
+        if (r0 + r < N && c0 + c < N) dst[(size_t)(r0 + r) * ld + c0 + c] = TR ? tile[c * kJld + r] : tile[r * kJld + c];
+    }
+}
+// C = beta C + alpha A B^T on 64 x 64 shared-memory tiles, 512 threads: thread (ti, tj) owns rows 2ti, 2ti+1 and columns
+// tj, tj+16, tj+32, tj+48 (A reads are two broadcasts per warp, B reads hit 16 distinct banks).  Caller synchronises.
+__device__ __forceinline__ void jt_mma(float* C, const float* A, const float* B, float alpha, float beta) {
+    const int ti = threadIdx.x >> 4, tj = threadIdx.x & 15;
+    if (ti >= 32) return;
+    const float* a0 = A + (2 * ti) * kJld;
+    const float* a1 = a0 + kJld;
+    const float* b0 = B + tj * kJld;
+    float acc[2][4] = {{0.f, 0.f, 0.f, 0.f}, {0.f, 0.f, 0.f, 0.f}};
+#pragma unroll 8
+    for (int k = 0; k < kJb; ++k) {
+        const float x0 = a0[k], x1 = a1[k];
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+            const float bv = b0[c * 16 * kJld + k];
+            acc[0][c] = fmaf(x0, bv, acc[0][c]);
+            acc[1][c] = fmaf(x1, bv, acc[1][c]);
+        }
+    }
+#pragma unroll
+    for (int a = 0; a < 2; ++a)
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+            float* o = C + (2 * ti + a) * kJld + tj + 16 * c;
+            *o = (beta == 0.f) ? alpha * acc[a][c] : fmaf(beta, *o, alpha * acc[a][c]);
+        }
+}
+
+// In-place blocked Cholesky of the lower triangle of J1 (N x N, leading dimension ld); the inverses of the diagonal
+// tiles, needed for the panel solves anyway, are kept as the diagonal tiles of X = L^-1 in J2.  Returns false
+// (uniformly) on a non-positive pivot.
+__device__ bool joint_chol_blocked(float* J1, float* J2, int N, int ld, float* T0, float* T1, float* T2) {
+    const int nb = (N + kJb - 1) / kJb;
+    for (int p = 0; p < nb; ++p) {
+        const int r0 = p * kJb, nv = min(kJb, N - r0);
+        jt_load<false>(T0, J1, ld, r0, r0, N);
+        for (int idx = threadIdx.x; idx < kJTileFloats; idx += blockDim.x) T1[idx] = 0.f;
+        __syncthreads();
+        const bool ok = chol_lower(T0, nv, kJld);
+        __syncthreads();
+        if (!ok) return false;
+        tri_inverse_cols<2>(T0, T1, nv, kJld);
+        __syncthreads();
+        jt_store<false>(J1, ld, r0, r0, N, T0);
+        jt_store<false>(J2, ld, r0, r0, N, T1);
+        __syncthreads();
+        for (int i = p + 1; i < nb; ++i) {                 // panel: L[ip] = A[ip] L[pp]^-T
+            jt_load<false>(T2, J1, ld, i * kJb, r0, N);
+            __syncthreads();
+            jt_mma(T0, T2, T1, 1.f, 0.f);
+            __syncthreads();
+            jt_store<false>(J1, ld, i * kJb, r0, N, T0);
+            __syncthreads();
+        }
+        for (int i = p + 1; i < nb; ++i) {                 // trailing update: A[ij] -= L[ip] L[jp]^T
+            jt_load<false>(T0, J1, ld, i * kJb, r0, N);
+            for (int j = p + 1; j <= i; ++j) {
+                jt_load<false>(T1, J1, ld, j * kJb, r0, N);
+                jt_load<false>(T2, J1, ld, i * kJb, j * kJb, N);
+                __syncthreads();
+                jt_mma(T2, T0, T1, -1.f, 1.f);
+                __syncthreads();
+                jt_store<false>(J1, ld, i * kJb, j * kJb, N, T2);
+                __syncthreads();
+            }
+        }
+    }
+    return true;
+}
+
+// Off-diagonal tiles of X = L^-1 (lower): X[ij] = -X[ii] sum_{k=j}^{i-1} L[ik] X[kj]; L in J1, X in J2.
+__device__ void joint_trtri_blocked(const float* J1, float* J2, int N, int ld, float* T0, float* T1, float* T2) {
+    const int nb = (N + kJb - 1) / kJb;
+    for (int j = 0; j < nb; ++j) {
+        for (int i = j + 1; i < nb; ++i) {
+            for (int k = j; k < i; ++k) {                  // T2 = S^T = sum_k X[kj]^T L[ik]^T
+                jt_load<true>(T0, J2, ld, k * kJb, j * kJb, N);
+                jt_load<false>(T1, J1, ld, i * kJb, k * kJb, N);
+                __syncthreads();
+                jt_mma(T2, T0, T1, 1.f, k == j ? 0.f : 1.f);
+                __syncthreads();
+            }
+            jt_load<false>(T0, J2, ld, i * kJb, i * kJb, N);
+            __syncthreads();
+            jt_mma(T1, T0, T2, -1.f, 0.f);
+            __syncthreads();
+            jt_store<false>(J2, ld, i * kJb, j * kJb, N, T1);
+            __syncthreads();
+        }
+    }
+}
+
+// P = X^T X (full symmetric) into J1 from the lower-triangular X in J2: P[ij] = sum_{k >= i} X[ki]^T X[kj], i >= j.
+__device__ void joint_lauum_blocked(float* J1, const float* J2, int N, int ld, float* T0, float* T1, float* T2) {
+    const int nb = (N + kJb - 1) / kJb;
+    for (int i = 0; i < nb; ++i) {
+        for (int j = 0; j <= i; ++j) {
+            for (int k = i; k < nb; ++k) {
+                jt_load<true>(T0, J2, ld, k * kJb, i * kJb, N);
+                jt_load<true>(T1, J2, ld, k * kJb, j * kJb, N);
+                __syncthreads();
+                jt_mma(T2, T0, T1, 1.f, k == i ? 0.f : 1.f);
+                __syncthreads();
+            }
+            jt_store<false>(J1, ld, i * kJb, j * kJb, N, T2);
+            if (i != j) jt_store<true>(J1, ld, j * kJb, i * kJb, N, T2);
+            __syncthreads();
+        }
+    }
+}
+
+// build_and_factor for the joint matrix on the blocked path (same psd_safe_cholesky retry policy)
+__device__ bool build_and_factor_blocked(const GpProblem& pb, const Hyper& h, float* J1, float* J2, int ld, GpShared& sh,
+                                         float* T0, float* T1, float* T2) {
+    const int n = pb.n;
+    const float jit[4] = {0.f, 1e-6f, 1e-5f, 1e-4f};
+    for (int a = 0; a < 4; ++a) {
+        for (int idx = threadIdx.x; idx < n * n; idx += blockDim.x) {
+            const int i = idx / n, j = idx - i * n;
+            float k = kernel_only(pb.D2[(size_t)i * pb.ldd + j], h.s, h.l, pb.kind);
+            if (i == j) k += h.sig2 + jit[a];
+            J1[(size_t)i * ld + j] = k;
+        }
+        __syncthreads();
+        const bool ok = joint_chol_blocked(J1, J2, n, ld, T0, T1, T2);
+        __syncthreads();
+        if (ok) {
+            if (threadIdx.x == 0) sh.jitter = jit[a];
+            __syncthreads();
+            return true;
+        }
+    }
+    return false;
+}
+
 // =============================================================================================
 // kernel 3: IFT hypergradient pieces (F, dF/dphi, H, v, Wm)
 // =============================================================================================
@@ -704,6 +902,10 @@ gp_ift_kernel(const int32_t* __restrict__ z_off, const int32_t* __restrict__ n_s
     GpShared& sh = *reinterpret_cast<GpShared*>(smem_raw);
     float* smem_f = reinterpret_cast<float*>(smem_raw + ((sizeof(GpShared) + 15) / 16) * 16);
     const int t = blockIdx.x;
+    const bool prof = (ignore_corr & 256) != 0 && blockIdx.x == 0 && threadIdx.x == 0;   // development probe
+    ignore_corr &= 255;
+    long long tk[8];
+    if (prof) tk[0] = clock64();
     const int N = z_off[t + 1] - z_off[t];
     const float* D2t = D2 + d2_off[t];
     float* Wt = Wm + d2_off[t];
@@ -746,6 +948,7 @@ gp_ift_kernel(const int32_t* __restrict__ z_off, const int32_t* __restrict__ n_s
         return;
     }
     const float nll_inner = sh.nll;
+    if (prof) tk[1] = clock64();
 
     if (ignore_corr == 2) {
         // inner loss only: Wm_ss = df/dD2 = Gamma o Ku / n, zero elsewhere (first-order autograd of f = -MLL)
@@ -768,10 +971,18 @@ gp_ift_kernel(const int32_t* __restrict__ z_off, const int32_t* __restrict__ n_s
     }
 
     // ---- joint covariance J = K + sig2 I over support+query: Cholesky, inverse, beta --------------
+    // blocked path when three 64 x 64 tiles fit behind the inner problem's shared-memory working set
+    const size_t smem_used = in_smem ? ((size_t)2 * n * cv.ld + 4 * (size_t)n + (size_t)(blockDim.x >> 5) * n) : 0;
+    const bool blocked = smem_used + 3 * (size_t)kJTileFloats <= (size_t)(kSmemBudgetFloats + kGpThreads / 32 * 256);
+    float* T0 = smem_f + smem_used;
+    float* T1 = T0 + kJTileFloats;
+    float* T2 = T1 + kJTileFloats;
     {
         GpProblem pj = pb;
         pj.n = N;
-        if (!build_and_factor(pj, h, J1, ldN, sh)) {
+        const bool okj = blocked ? build_and_factor_blocked(pj, h, J1, J2, ldN, sh, T0, T1, T2)
+                                 : build_and_factor(pj, h, J1, ldN, sh);
+        if (!okj) {
             if (threadIdx.x == 0) status[t] = ADKF_ST_NOT_PD;
             for (int idx = threadIdx.x; idx < N * N; idx += blockDim.x) Wt[idx] = 0.f;
             return;
@@ -781,10 +992,15 @@ gp_ift_kernel(const int32_t* __restrict__ z_off, const int32_t* __restrict__ n_s
     for (int i = threadIdx.x; i < N; i += blockDim.x) part1[0] += logf(J1[(size_t)i * ldN + i]);
     block_sum_multi<1>(part1, sh.red, sh.sums);
     const float logdetJ = 2.f * (float)sh.sums[0];
-    tri_inverse(J1, J2, N, ldN);
+    if (prof) tk[2] = clock64();
+    if (blocked) joint_trtri_blocked(J1, J2, N, ldN, T0, T1, T2);
+    else tri_inverse(J1, J2, N, ldN);
     __syncthreads();
-    xtx(J2, J1, N, ldN);   // J1 <- J^-1
+    if (prof) tk[3] = clock64();
+    if (blocked) joint_lauum_blocked(J1, J2, N, ldN, T0, T1, T2);
+    else xtx(J2, J1, N, ldN);   // J1 <- J^-1
     __syncthreads();
+    if (prof) tk[4] = clock64();
     matvec(J1, N, ldN, yt, beta);
     __syncthreads();
 
@@ -823,6 +1039,7 @@ gp_ift_kernel(const int32_t* __restrict__ z_off, const int32_t* __restrict__ n_s
     }
     __syncthreads();
     if (sh.flag) st |= ADKF_ST_HESS_DAMPED;
+    if (prof) tk[5] = clock64();
 
     // ---- IFT correction on the support block:  Wm_ss -= (1/n) [ Gamdot o Ku + Gam o Kudot ] ---------
     if (ignore_corr == 0) {
@@ -880,6 +1097,12 @@ gp_ift_kernel(const int32_t* __restrict__ z_off, const int32_t* __restrict__ n_s
             }
             __syncwarp();
         }
+    }
+    if (prof) {
+        tk[6] = clock64();
+        printf("gp_ift n=%d N=%d kcycles: inner %lld  joint chol %lld  tri_inverse %lld  xtx %lld  G+sums %lld  ift corr %lld\n", n, N,
+               (tk[1] - tk[0]) / 1000, (tk[2] - tk[1]) / 1000, (tk[3] - tk[2]) / 1000, (tk[4] - tk[3]) / 1000,
+               (tk[5] - tk[4]) / 1000, (tk[6] - tk[5]) / 1000);
     }
     if (threadIdx.x == 0) {
         if (jit_inner > 0.f || sh.jitter > 0.f) st |= ADKF_ST_JITTER;
@@ -980,7 +1203,7 @@ extern "C" int adkf_gp_ift(int32_t T, const int32_t* z_off, const int32_t* n_sup
                            float* Wm, int32_t* status, float* ws, int64_t ws_floats, void* stream) {
     if (T <= 0) return 0;
     if (!z_off || !n_sup || !d2_off || !D2 || !y || !phi || !aux || !Wm || !status || !ws) return ADKF_ERR_BADARG;
-    if (mode < 0 || mode > 2) return ADKF_ERR_BADARG;
+    if ((mode & 255) < 0 || (mode & 255) > 2) return ADKF_ERR_BADARG;   // bit 8: development probe (phase timings)
     cudaStream_t s = (cudaStream_t)stream;
     int e = set_smem_attr((const void*)gp_ift_kernel);
     if (e) return e;

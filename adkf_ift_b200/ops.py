@@ -2,6 +2,7 @@
 kernels, and the batched GP entry points.  Every function here launches hand-written sm_100a kernels from
 libadkf_b200.so; nothing falls back to torch ops or to the CPU."""
 import ctypes
+import os
 from dataclasses import dataclass
 from typing import List, Optional, Sequence
 
@@ -463,6 +464,8 @@ def gp_ift(layout: TaskLayout, D2, y, kernel, noise_prior_loc: float, ls_prior: 
     dev = D2.device
     if mode is None:
         mode = 1 if ignore_grad_correction else 0
+    if os.environ.get("ADKF_GP_PROF"):      # development probe: phase timings of task 0 printed by the kernel
+        mode = int(mode) | 256
     Wm = torch.zeros_like(D2)
     aux = aux.contiguous().clone()
     status = torch.zeros(layout.T, dtype=torch.int32, device=dev)
