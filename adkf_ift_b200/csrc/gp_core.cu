@@ -785,18 +785,24 @@ __device__ __forceinline__ void jt_mma(float* C, const float* A, const float* B,
 // In-place blocked Cholesky of the lower triangle of J1 (N x N, leading dimension ld); the inverses of the diagonal
 // tiles, needed for the panel solves anyway, are kept as the diagonal tiles of X = L^-1 in J2.  Returns false
 // (uniformly) on a non-positive pivot.
+__device__ long long g_jprof[8];
+#define JP(i) do { if (blockIdx.x == 0 && threadIdx.x == 0) { long long c_ = clock64(); g_jprof[i] += c_ - jp0; jp0 = c_; } } while (0)
 __device__ bool joint_chol_blocked(float* J1, float* J2, int N, int ld, float* T0, float* T1, float* T2) {
     const int nb = (N + kJb - 1) / kJb;
+    long long jp0 = clock64();
     for (int p = 0; p < nb; ++p) {
         const int r0 = p * kJb, nv = min(kJb, N - r0);
         jt_load<false>(T0, J1, ld, r0, r0, N);
         for (int idx = threadIdx.x; idx < kJTileFloats; idx += blockDim.x) T1[idx] = 0.f;
         __syncthreads();
+        JP(0);
         const bool ok = chol_lower(T0, nv, kJld);
         __syncthreads();
+        JP(1);
         if (!ok) return false;
         tri_inverse_cols<2>(T0, T1, nv, kJld);
         __syncthreads();
+        JP(2);
         jt_store<false>(J1, ld, r0, r0, N, T0);
         jt_store<false>(J2, ld, r0, r0, N, T1);
         __syncthreads();
@@ -808,6 +814,7 @@ __device__ bool joint_chol_blocked(float* J1, float* J2, int N, int ld, float* T
             jt_store<false>(J1, ld, i * kJb, r0, N, T0);
             __syncthreads();
         }
+        JP(3);
         for (int i = p + 1; i < nb; ++i) {                 // trailing update: A[ij] -= L[ip] L[jp]^T
             jt_load<false>(T0, J1, ld, i * kJb, r0, N);
             for (int j = p + 1; j <= i; ++j) {
@@ -820,6 +827,7 @@ __device__ bool joint_chol_blocked(float* J1, float* J2, int N, int ld, float* T
                 __syncthreads();
             }
         }
+        JP(4);
     }
     return true;
 }
@@ -1100,6 +1108,9 @@ gp_ift_kernel(const int32_t* __restrict__ z_off, const int32_t* __restrict__ n_s
     }
     if (prof) {
         tk[6] = clock64();
+        printf("joint chol kcycles: load %lld chol_tile %lld inv_tile %lld store+panel %lld trailing %lld\n", g_jprof[0] / 1000,
+               g_jprof[1] / 1000, g_jprof[2] / 1000, g_jprof[3] / 1000, g_jprof[4] / 1000);
+        for (int i_ = 0; i_ < 8; ++i_) g_jprof[i_] = 0;
         printf("gp_ift n=%d N=%d kcycles: inner %lld  joint chol %lld  tri_inverse %lld  xtx %lld  G+sums %lld  ift corr %lld\n", n, N,
                (tk[1] - tk[0]) / 1000, (tk[2] - tk[1]) / 1000, (tk[3] - tk[2]) / 1000, (tk[4] - tk[3]) / 1000,
                (tk[5] - tk[4]) / 1000, (tk[6] - tk[5]) / 1000);

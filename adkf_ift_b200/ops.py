@@ -209,7 +209,7 @@ class _PNAMessagePassingTC(torch.autograd.Function):
             # dW[k][t] = d_pre[:, 192k:192k+192]^T @ XG[:, 64k:64k+64]   (split-K over the edges)
             gemm_tf32x3_batched(d_pre[e0:e1], True, 192, 0, XG[e0:e1], True, 64, 0, 192, 64, n, 4,
                                 d_W.view(-1)[t * 192 * 64:], 64, 3 * 192 * 64, allow_splitk=True)
-            d_b[:, t] = d_pre[e0:e1].view(n, 4, 192).sum(0)
+            d_b[:, t] = act_bwd_colsum(d_pre[e0:e1], None, 0, True)[1].view(4, 192)
         d_h = torch.empty(V, 128, **f32)
         check(lib.adkf_pna_dh_gather(dptr(dXG), dptr(ts.tptr), dptr(ts.rev), V, dptr(d_h), stream_ptr()), "adkf_pna_dh_gather")
         return d_h, d_W, d_b, None
@@ -527,6 +527,33 @@ def _tc_eligible(x, weight) -> bool:
             and x.stride(0) % 4 == 0 and weight.stride(0) % 4 == 0 and x.data_ptr() % 16 == 0 and weight.data_ptr() % 16 == 0)
 
 
+def act_bwd_colsum(dy: torch.Tensor, y: Optional[torch.Tensor], act: int, want_db: bool):
+    """(dZ, db): dZ = dy * act'(y) (act 0: dZ is dy itself), db = dZ.sum(0) when want_db -- one pass over dy
+    (adkf_act_bwd_colsum).  dy [M,N] fp32 CUDA, rows 16-byte aligned, N % 4 == 0."""
+    lib = _cabi.load()
+    if not dy.is_cuda or dy.dtype != torch.float32 or dy.dim() != 2 or dy.stride(1) != 1:
+        raise RuntimeError("act_bwd_colsum needs a 2-D fp32 CUDA tensor with a contiguous last dimension (no CPU fallback)")
+    M, N = dy.shape
+    if act == 0 and not want_db:
+        return dy, None
+    if M == 0:
+        return dy, (torch.zeros(N, dtype=torch.float32, device=dy.device) if want_db else None)
+    dz = torch.empty(M, N, dtype=torch.float32, device=dy.device) if act else dy
+    db = ws = None
+    nws = 0
+    if want_db:
+        db = torch.empty(N, dtype=torch.float32, device=dy.device)
+        nws = int(lib.adkf_act_bwd_colsum_ws_floats(M, N))
+        ws = torch.empty(nws, dtype=torch.float32, device=dy.device)
+    null = ctypes.c_void_p(0)
+    rc = lib.adkf_act_bwd_colsum(ctypes.c_void_p(dy.data_ptr()), dy.stride(0), ctypes.c_void_p(y.data_ptr()) if act else null,
+                                 y.stride(0) if act else 0, M, N, int(act), ctypes.c_void_p(dz.data_ptr()) if act else null,
+                                 dz.stride(0) if act else 0, dptr(db) if want_db else null, dptr(ws) if want_db else null, nws,
+                                 stream_ptr())
+    check(rc, "adkf_act_bwd_colsum")
+    return dz, db
+
+
 class _LinearTC(torch.autograd.Function):
     """nn.Linear (+ optional ReLU / LeakyReLU(0.01)) with all three GEMMs on the tcgen05 3xTF32 kernel."""
 
@@ -541,18 +568,13 @@ class _LinearTC(torch.autograd.Function):
     @staticmethod
     def backward(ctx, dy):
         x, weight, y = ctx.saved_tensors
-        dy = dy.contiguous()
-        if ctx.act == 1:
-            dy = dy * (y > 0)
-        elif ctx.act == 2:
-            dy = dy * torch.where(y > 0, 1.0, 0.01)
-        dx = dw = db = None
+        # one pass over dY: activation derivative + bias gradient (dense_bwd.cu)
+        dy, db = act_bwd_colsum(dy.contiguous(), y, ctx.act, ctx.has_bias and ctx.needs_input_grad[2])
+        dx = dw = None
         if ctx.needs_input_grad[0]:
             dx = gemm_tf32x3(dy, False, weight, True)          # dX[M,K] = dY[M,N] W[N,K]
         if ctx.needs_input_grad[1]:
             dw = gemm_tf32x3(dy, True, x, True)                # dW[N,K] = dY^T[N,M] X[M,K]
-        if ctx.has_bias and ctx.needs_input_grad[2]:
-            db = dy.sum(0)
         return dx, dw, db, None
 
 

@@ -107,6 +107,17 @@ int adkf_mp_pna_bwd(const float* h, const float* W, const float* b, const int32_
                     int32_t num_partials, void* stream);
 
 /* ---------------------------------------------------------------------------------------------
+ * Elementwise half of a dense layer's backward (autograd of nn.Linear + ReLU / LeakyReLU(0.01):
+ * fs_mol/modules/gnn.py:79-95, fs_mol/modules/mlp.py:6-22) in one pass over dY [M,N]:
+ *   dZ = dY * act'(Y)   (act 1 relu, 2 leaky_relu; Y = the saved activation OUTPUT; act 0: no dZ is written)
+ *   db[c] = sum_r dZ[r,c]   (db may be NULL; deterministic two-pass column sum, ws >= adkf_act_bwd_colsum_ws_floats)
+ * N % 4 == 0, 16-byte aligned rows.
+ * ------------------------------------------------------------------------------------------- */
+int64_t adkf_act_bwd_colsum_ws_floats(int64_t M, int32_t N);
+int adkf_act_bwd_colsum(const float* dY, int64_t ldy, const float* Y, int64_t ldyy, int64_t M, int32_t N, int32_t act,
+                        float* dZ, int64_t ldz, float* db, float* ws, int64_t ws_floats, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
  * The same PNA block with its three dense products on the tensor cores (pna_gemm.cu; default path of the extractor):
  *   XG [E,256]   = adkf_pna_gather_inputs(h)            [h_src | h_tgt] per tower, edges sorted by (type, target, message index)
  *   pre [E,768]  = adkf_gemm_tf32x3_batched(XG, W, b)   message MLP pre-activations, 4 towers per launch, one launch per type

@@ -178,3 +178,22 @@ def test_batched_forms_of_the_pna_message_mlp(cuda_device):
     ref = torch.stack([dpre[:, 192 * k:192 * k + 192].double().t() @ XG[:, 64 * k:64 * k + 64].double() for k in range(T)])
     assert rel(dW[:, tau], ref) < 2e-6
     assert float(dW[:, 0].abs().max()) == 0.0 and float(dW[:, 2].abs().max()) == 0.0     # other types untouched
+
+
+@pytest.mark.parametrize("M,N,act", [(1000, 128, 0), (5000, 1024, 2), (133, 768, 1), (70000, 128, 2), (64, 12 * 4, 1)])
+def test_act_bwd_colsum(cuda_device, M, N, act):
+    """dZ = dY * act'(Y) is bit-exact against torch; the fused bias gradient matches an fp64 column sum and is
+    deterministic (two-pass reduction)."""
+    from adkf_ift_b200 import ops
+    g = torch.Generator().manual_seed(M + N + act)
+    dy = torch.randn(M, N, generator=g).to(cuda_device)
+    y = torch.randn(M, N, generator=g).to(cuda_device)
+    if act == 1:
+        y = y.clamp_min(0)
+    dz, db = ops.act_bwd_colsum(dy, y if act else None, act, True)
+    dz2, db2 = ops.act_bwd_colsum(dy, y if act else None, act, True)
+    want = dy if act == 0 else dy * (y > 0) if act == 1 else dy * torch.where(y > 0, 1.0, 0.01)
+    assert torch.equal(dz, want)
+    ref = want.double().sum(0)
+    assert float((db.double() - ref).abs().max()) <= 2e-6 * float(want.double().abs().sum(0).max())
+    assert torch.equal(db, db2)
