@@ -190,6 +190,56 @@ def dominant_kernel_roofline(model, tb, peaks):
     return roof
 
 
+def meta_test_throughput(device, cpu_tasks=1):
+    """BASELINE config 3 (reported beside the headline, not the bench metric): 256 regression meta-test tasks
+    (--use-numeric-labels), support 128, query 192, ONE batched pass = extractor forward + GP fit + prediction; 8 distinct
+    synthetic tasks tiled 32x (positions are independent, tests/test_gpu_model.py::test_c3_*).  The CPU figure is the oracle
+    port of run_on_batches (reference algorithm, SciPy L-BFGS-B) on `cpu_tasks` of the same tasks."""
+    from adkf_ift_b200 import dkt, synthetic, task_batch
+    from adkf_ift_b200.adaptive_dkt import ADKTModelTrainerConfig
+    from adkf_ift_b200.adaptive_dkt_utils import ADKTModelTrainer, run_on_task_batch
+    from adkf_ift_b200.feature_extractor import cli_default_config
+    n_s, n_q, distinct, copies = 128, 192, 8, 32
+    cfg = ADKTModelTrainerConfig(graph_feature_extractor_config=cli_default_config(10), use_numeric_labels=True)
+    model = ADKTModelTrainer(cfg)
+    synthetic.deterministic_init_(model, seed=0, alpha=0.5)
+    model.to(device)
+    hosts = [dkt.task_sample_to_dkt_task_sample(synthetic.make_task_sample(300 + i, n_s, n_q),
+                                                dkt.get_dkt_batcher(max_num_graphs=n_s + n_q), True) for i in range(distinct)]
+    hb = task_batch.collate_tasks([hosts[i % distinct].batches[0] for i in range(distinct * copies)], True)
+    for _ in range(2):
+        res = run_on_task_batch(model, task_batch.to_device(hb, device), train=False)
+    torch.cuda.synchronize()
+    reps = 3
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(reps):
+        res = run_on_task_batch(model, task_batch.to_device(hb, device), train=False)
+        float(res.preds.mean().item())
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / reps
+    out = {"workload": "C3: 256 regression meta-test tasks, support 128, query 192, one batched pass incl. H2D of the tasks",
+           "value": 256 / (ms * 1e-3), "unit": UNIT, "ms_per_pass": ms, "h2d_bytes_per_pass": hb.nbytes()}
+    if cpu_tasks > 0:
+        from oracle import adkf_oracle as orc
+        torch.set_num_threads(os.cpu_count() or 1)
+        P = {n: p.detach().cpu() for n, p in model.named_parameters() if not n.startswith("gp_")}
+        ocfg = orc.OracleConfig(num_layers=10, gp_kernel="matern", use_numeric_labels=True)
+        t = 0.0
+        for i in range(cpu_tasks + 1):
+            batch = dkt.torchify(hosts[i % distinct], torch.device("cpu")).batches[0]
+            t0 = time.perf_counter()
+            orc.meta_test_task(P, batch, ocfg)
+            if i > 0:                      # first call warms the thread pools
+                t += time.perf_counter() - t0
+        out["cpu_baseline"] = {"value": cpu_tasks / t, "unit": UNIT, "cores": torch.get_num_threads(), "kind": "port",
+                               "sample": f"{cpu_tasks} task(s) of the same workload through the CPU oracle, sequential"}
+    del model
+    torch.cuda.empty_cache()
+    return out
+
+
 # ----------------------------------------------------------------------------------------------------------
 # CPU reference arm (oracle = the reference's algorithm restated on torch CPU + SciPy L-BFGS-B)
 # ----------------------------------------------------------------------------------------------------------
@@ -315,6 +365,10 @@ def run_b200(args):
         line["cpu_baseline"] = {"value": n_cpu / t, "unit": UNIT, "cores": torch.get_num_threads(), "kind": "port",
                                 "sample": f"{n_cpu} tasks (support {SUPPORT}, query {QUERY}) of the same C2 step through the "
                                           "CPU oracle (reference algorithm on torch CPU + SciPy L-BFGS-B), sequential"}
+    if world == 1 and not args.no_meta_test:
+        del model, staged
+        torch.cuda.empty_cache()
+        line["meta_test"] = meta_test_throughput(device, 0 if args.no_cpu_baseline else 1)
     print(json.dumps(line), flush=True)
     if world > 1:
         torch.distributed.destroy_process_group()
@@ -328,6 +382,7 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--cpu-tasks", type=int, default=2)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-meta-test", action="store_true", help="skip the C3 meta-test throughput reported beside the headline")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)
