@@ -9,5 +9,5 @@ python tools/step_breakdown.py 16 test > gpurun_out/breakdown_test.log 2>&1; hea
 python tools/one_step.py 16 train 1 > gpurun_out/plain.log 2>&1 &&
 ncu --metrics gpu__time_duration.sum --clock-control none --csv --log-file gpurun_out/launches_train.csv python tools/one_step.py 16 train 1 > gpurun_out/ncu_launch.log 2>&1
 python tools/one_step.py 16 train 1 > gpurun_out/plain2.log 2>&1 &&
-ncu --set full --clock-control none --import-source on -k regex:'pna_|gemm_tf32x3|gp_ift|gp_fit|splitk|split_hilo|readout_' -s 40 -c 24 -o gpurun_out/prof_r1c python tools/one_step.py 16 train 1 > gpurun_out/ncu_full.log 2>&1
+ncu --set full --clock-control none --import-source on -k regex:'gemm_tf32x3|pna_aggregate|pna_dpre|act_bwd|gp_ift|gp_fit' -s 60 -c 30 -o gpurun_out/prof_r1e python tools/one_step.py 16 train 1 > gpurun_out/ncu_full.log 2>&1
 tail -3 gpurun_out/ncu_full.log
