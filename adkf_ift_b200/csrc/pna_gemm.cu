@@ -36,6 +36,7 @@ __global__ void pna_gather_inputs_kernel(const float* __restrict__ h, const int3
 }
 
 // one warp per (node, tower); lane owns channels lane + 32 c, c = 0..5  (0,1 sum part | 2,3 mean/std part | 4,5 max part)
+template <bool SCALERS>
 __global__ void __launch_bounds__(256)
 pna_aggregate_fwd_kernel(const float* __restrict__ pre, const int32_t* __restrict__ tptr, int V, float* __restrict__ out,
                          uint8_t* __restrict__ aux_cnt, uint8_t* __restrict__ aux_arg) {
@@ -80,7 +81,8 @@ pna_aggregate_fwd_kernel(const float* __restrict__ pre, const int32_t* __restric
         }
     const float logd = logf((float)deg + 1.f);
     const float amp = logd / pDelta, att = pDelta / (logd + pSmall);
-    float* o = out + (size_t)node * (pTowers * pOutTower) + (size_t)k * pOutTower;
+    constexpr int OT = SCALERS ? pOutTower : 4 * pPmd;      // 768 with the three PNA degree scalers, 256 for "MultiAggr"
+    float* o = out + (size_t)node * (pTowers * OT) + (size_t)k * OT;
 #pragma unroll
     for (int j = 0; j < 2; ++j) {
         const float vals[4] = {sum[j], mean[j], sqrtf(ssum[j]), (deg > 0) ? mx[j] : 0.f};
@@ -88,8 +90,10 @@ pna_aggregate_fwd_kernel(const float* __restrict__ pre, const int32_t* __restric
         for (int a = 0; a < 4; ++a) {
             const int col = a * pPmd + j * 32 + lane;
             o[col] = vals[a];
-            o[256 + col] = amp * vals[a];
-            o[512 + col] = att * vals[a];
+            if (SCALERS) {
+                o[256 + col] = amp * vals[a];
+                o[512 + col] = att * vals[a];
+            }
         }
         aux_cnt[((size_t)node * pTowers + k) * pPmd + j * 32 + lane] = (uint8_t)min(cpos[j], 255);
         aux_arg[((size_t)node * pTowers + k) * pPmd + j * 32 + lane] = (uint8_t)min(arg[j], 255);
@@ -97,6 +101,7 @@ pna_aggregate_fwd_kernel(const float* __restrict__ pre, const int32_t* __restric
 }
 
 // d out [V,3072] -> d pre [E,768]; reads the saved pre-activations, the forward output (mean, std) and the aux bytes
+template <bool SCALERS>
 __global__ void __launch_bounds__(256)
 pna_dpre_kernel(const float* __restrict__ pre, const int32_t* __restrict__ tptr, int V, const float* __restrict__ fwd_out,
                 const uint8_t* __restrict__ aux_cnt, const uint8_t* __restrict__ aux_arg, const float* __restrict__ d_out,
@@ -114,17 +119,24 @@ pna_dpre_kernel(const float* __restrict__ pre, const int32_t* __restrict__ tptr,
     if (deg == 0) return;
     const float logd = logf((float)deg + 1.f);
     const float amp = logd / pDelta, att = pDelta / (logd + pSmall);
-    const float* go = d_out + (size_t)node * (pTowers * pOutTower) + (size_t)k * pOutTower;
-    const float* fo = fwd_out + (size_t)node * (pTowers * pOutTower) + (size_t)k * pOutTower;
+    constexpr int OT = SCALERS ? pOutTower : 4 * pPmd;
+    const float* go = d_out + (size_t)node * (pTowers * OT) + (size_t)k * OT;
+    const float* fo = fwd_out + (size_t)node * (pTowers * OT) + (size_t)k * OT;
     float g_sum[2], g_mean[2], g_std[2], g_max[2], mean[2], stdv[2], cpos[2];
     int arg[2];
 #pragma unroll
     for (int j = 0; j < 2; ++j) {
         const int col = j * 32 + lane;
-        g_sum[j] = go[col] + amp * go[256 + col] + att * go[512 + col];
-        g_mean[j] = go[pPmd + col] + amp * go[256 + pPmd + col] + att * go[512 + pPmd + col];
-        g_std[j] = go[2 * pPmd + col] + amp * go[256 + 2 * pPmd + col] + att * go[512 + 2 * pPmd + col];
-        g_max[j] = go[3 * pPmd + col] + amp * go[256 + 3 * pPmd + col] + att * go[512 + 3 * pPmd + col];
+        g_sum[j] = go[col];
+        g_mean[j] = go[pPmd + col];
+        g_std[j] = go[2 * pPmd + col];
+        g_max[j] = go[3 * pPmd + col];
+        if (SCALERS) {
+            g_sum[j] += amp * go[256 + col] + att * go[512 + col];
+            g_mean[j] += amp * go[256 + pPmd + col] + att * go[512 + pPmd + col];
+            g_std[j] += amp * go[256 + 2 * pPmd + col] + att * go[512 + 2 * pPmd + col];
+            g_max[j] += amp * go[256 + 3 * pPmd + col] + att * go[512 + 3 * pPmd + col];
+        }
         mean[j] = fo[pPmd + col];
         stdv[j] = fo[2 * pPmd + col];
         cpos[j] = (float)aux_cnt[((size_t)node * pTowers + k) * pPmd + col];
@@ -149,6 +161,50 @@ pna_dpre_kernel(const float* __restrict__ pre, const int32_t* __restrict__ tptr,
                 q[32 * (4 + j)] = (a_max > 0.f && (idx == arg[j] || (idx >= 255 && arg[j] == 255))) ? g_max[j] : 0.f;
             }
         }
+}
+
+// "Plain" relational message passing (gnn.py:152-165): out[v, 64k + c] = sum over incoming edges of relu(pre[e, 64k + c]);
+// pre [E, 256] (4 towers x 64), one warp per (node, tower), lane owns channels lane and lane + 32.
+__global__ void __launch_bounds__(256)
+plain_aggregate_fwd_kernel(const float* __restrict__ pre, const int32_t* __restrict__ tptr, int V, float* __restrict__ out) {
+    const int lane = threadIdx.x & 31;
+    const int64_t w = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
+    if (w >= (int64_t)V * pTowers) return;
+    const int node = (int)(w >> 2), k = (int)(w & 3);
+    float s0 = 0.f, s1 = 0.f;
+#pragma unroll
+    for (int t = 0; t < pTypes; ++t) {
+        const int beg = tptr[(size_t)t * V + node], end = tptr[(size_t)t * V + node + 1];
+        for (int r = beg; r < end; ++r) {
+            const float* p = pre + (size_t)r * (pTowers * pPmd) + k * pPmd + lane;
+            s0 += fmaxf(p[0], 0.f);
+            s1 += fmaxf(p[32], 0.f);
+        }
+    }
+    float* o = out + (size_t)node * (pTowers * pPmd) + k * pPmd + lane;
+    o[0] = s0;
+    o[32] = s1;
+}
+
+__global__ void __launch_bounds__(256)
+plain_dpre_kernel(const float* __restrict__ pre, const int32_t* __restrict__ tptr, int V, const float* __restrict__ d_out,
+                  float* __restrict__ d_pre) {
+    const int lane = threadIdx.x & 31;
+    const int64_t w = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
+    if (w >= (int64_t)V * pTowers) return;
+    const int node = (int)(w >> 2), k = (int)(w & 3);
+    const float* go = d_out + (size_t)node * (pTowers * pPmd) + k * pPmd + lane;
+    const float g0 = go[0], g1 = go[32];
+#pragma unroll
+    for (int t = 0; t < pTypes; ++t) {
+        const int beg = tptr[(size_t)t * V + node], end = tptr[(size_t)t * V + node + 1];
+        for (int r = beg; r < end; ++r) {
+            const float* p = pre + (size_t)r * (pTowers * pPmd) + k * pPmd + lane;
+            float* q = d_pre + (size_t)r * (pTowers * pPmd) + k * pPmd + lane;
+            q[0] = (p[0] > 0.f) ? g0 : 0.f;
+            q[32] = (p[32] > 0.f) ? g1 : 0.f;
+        }
+    }
 }
 
 __global__ void pna_dh_gather_kernel(const float* __restrict__ dXG, const int32_t* __restrict__ tptr,
@@ -190,28 +246,48 @@ extern "C" int adkf_pna_gather_inputs(const float* h, const int32_t* src, const 
     return 0;
 }
 
-extern "C" int adkf_pna_aggregate_fwd(const float* pre, const int32_t* tptr, int32_t V, float* out, uint8_t* aux_cnt,
-                                      uint8_t* aux_arg, void* stream) {
+// mode: ADKF_MP_PNA (sum|mean|std|max x 3 degree scalers, out [V,3072]), ADKF_MP_MULTIAGGR (no scalers, out [V,1024]),
+// ADKF_MP_PLAIN (relu + sum of 64-wide messages, pre [E,256], out [V,256]; aux arrays unused)
+extern "C" int adkf_mp_aggregate_fwd(const float* pre, const int32_t* tptr, int32_t V, int32_t mode, float* out, uint8_t* aux_cnt,
+                                     uint8_t* aux_arg, void* stream) {
     if (V <= 0) return 0;
-    if (!tptr || !out || !aux_cnt || !aux_arg) return ADKF_ERR_BADARG;
+    if (!tptr || !out || mode < ADKF_MP_PNA || mode > ADKF_MP_PLAIN) return ADKF_ERR_BADARG;
+    if (mode != ADKF_MP_PLAIN && (!aux_cnt || !aux_arg)) return ADKF_ERR_BADARG;
     const int64_t threads = (int64_t)V * pTowers * 32;
-    pna_aggregate_fwd_kernel<<<(unsigned)((threads + 255) / 256), 256, 0, (cudaStream_t)stream>>>(pre, tptr, V, out, aux_cnt,
-                                                                                                 aux_arg);
+    const unsigned grid = (unsigned)((threads + 255) / 256);
+    cudaStream_t s = (cudaStream_t)stream;
+    if (mode == ADKF_MP_PNA) pna_aggregate_fwd_kernel<true><<<grid, 256, 0, s>>>(pre, tptr, V, out, aux_cnt, aux_arg);
+    else if (mode == ADKF_MP_MULTIAGGR) pna_aggregate_fwd_kernel<false><<<grid, 256, 0, s>>>(pre, tptr, V, out, aux_cnt, aux_arg);
+    else plain_aggregate_fwd_kernel<<<grid, 256, 0, s>>>(pre, tptr, V, out);
     adkf_count_launches(1);
     ADKF_LAUNCH_CHECK();
     return 0;
 }
 
-extern "C" int adkf_pna_dpre(const float* pre, const int32_t* tptr, int32_t V, const float* fwd_out, const uint8_t* aux_cnt,
-                             const uint8_t* aux_arg, const float* d_out, float* d_pre, void* stream) {
+extern "C" int adkf_mp_dpre(const float* pre, const int32_t* tptr, int32_t V, int32_t mode, const float* fwd_out,
+                            const uint8_t* aux_cnt, const uint8_t* aux_arg, const float* d_out, float* d_pre, void* stream) {
     if (V <= 0) return 0;
-    if (!tptr || !fwd_out || !aux_cnt || !aux_arg || !d_out) return ADKF_ERR_BADARG;
+    if (!tptr || !d_out || mode < ADKF_MP_PNA || mode > ADKF_MP_PLAIN) return ADKF_ERR_BADARG;
+    if (mode != ADKF_MP_PLAIN && (!fwd_out || !aux_cnt || !aux_arg)) return ADKF_ERR_BADARG;
     const int64_t threads = (int64_t)V * pTowers * 32;
-    pna_dpre_kernel<<<(unsigned)((threads + 255) / 256), 256, 0, (cudaStream_t)stream>>>(pre, tptr, V, fwd_out, aux_cnt, aux_arg,
-                                                                                        d_out, d_pre);
+    const unsigned grid = (unsigned)((threads + 255) / 256);
+    cudaStream_t s = (cudaStream_t)stream;
+    if (mode == ADKF_MP_PNA) pna_dpre_kernel<true><<<grid, 256, 0, s>>>(pre, tptr, V, fwd_out, aux_cnt, aux_arg, d_out, d_pre);
+    else if (mode == ADKF_MP_MULTIAGGR) pna_dpre_kernel<false><<<grid, 256, 0, s>>>(pre, tptr, V, fwd_out, aux_cnt, aux_arg, d_out, d_pre);
+    else plain_dpre_kernel<<<grid, 256, 0, s>>>(pre, tptr, V, d_out, d_pre);
     adkf_count_launches(1);
     ADKF_LAUNCH_CHECK();
     return 0;
+}
+
+extern "C" int adkf_pna_aggregate_fwd(const float* pre, const int32_t* tptr, int32_t V, float* out, uint8_t* aux_cnt,
+                                      uint8_t* aux_arg, void* stream) {
+    return adkf_mp_aggregate_fwd(pre, tptr, V, ADKF_MP_PNA, out, aux_cnt, aux_arg, stream);
+}
+
+extern "C" int adkf_pna_dpre(const float* pre, const int32_t* tptr, int32_t V, const float* fwd_out, const uint8_t* aux_cnt,
+                             const uint8_t* aux_arg, const float* d_out, float* d_pre, void* stream) {
+    return adkf_mp_dpre(pre, tptr, V, ADKF_MP_PNA, fwd_out, aux_cnt, aux_arg, d_out, d_pre, stream);
 }
 
 extern "C" int adkf_pna_dh_gather(const float* dXG, const int32_t* tptr, const int32_t* rev, int32_t V, float* d_h, void* stream) {

@@ -60,10 +60,10 @@ class GraphFeatureExtractorConfig:
     output_norm: str = "off"
 
 
-def cli_default_config(num_layers: int = 10) -> GraphFeatureExtractorConfig:
-    """The configuration `adaptive_dkt_train.py` builds from its argparse defaults."""
+def cli_default_config(num_layers: int = 10, gnn_type: str = "PNA") -> GraphFeatureExtractorConfig:
+    """The configuration `adaptive_dkt_train.py` builds from its argparse defaults (`--gnn_type` PNA | MultiAggr | Plain)."""
     return GraphFeatureExtractorConfig(
-        gnn_config=GNNConfig(type="PNA", hidden_dim=128, num_heads=4, per_head_dim=64, intermediate_dim=1024,
+        gnn_config=GNNConfig(type=gnn_type, hidden_dim=128, num_heads=4, per_head_dim=64, intermediate_dim=1024,
                              num_layers=num_layers),
         readout_config=GraphReadoutConfig())
 
@@ -116,8 +116,12 @@ class GNNBlock(nn.Module):
 
     def __init__(self, config: GNNConfig):
         super().__init__()
-        if config.type.lower() != "pna":
-            raise NotImplementedError(f"gnn type {config.type!r}: only the default PNA path has sm_100a kernels")
+        kind = config.type.lower()
+        if kind == "multiheadattention":
+            raise NotImplementedError("gnn type 'MultiHeadAttention' has no sm_100a kernels yet (PNA, MultiAggr and Plain do)")
+        if kind not in ("pna", "multiaggr", "plain"):
+            raise ValueError(f"Unknown GNN type {config.type}.")          # gnn.py:447
+        self._mp_mode = {"pna": ops.MP_PNA, "multiaggr": ops.MP_MULTIAGGR, "plain": ops.MP_PLAIN}[kind]
         if (config.hidden_dim, config.num_heads, config.per_head_dim, config.num_edge_types) != (128, 4, 64, 3):
             raise NotImplementedError("the fused PNA kernel is specialised to hidden 128 / 4 towers / per-head 64 / 3 edge types")
         if config.message_function_depth != 1 or config.dropout_rate != 0.0 or not config.use_rezero_scaling:
@@ -127,9 +131,13 @@ class GNNBlock(nn.Module):
         self.config = config
         self.alpha = nn.Parameter(torch.full((1,), 1e-7))
         tower_in = config.hidden_dim // config.num_heads
-        self.mp_layers = nn.ModuleList(_TowerMessageFns(tower_in, 3 * config.per_head_dim, config.num_edge_types)
+        # gnn.py:421-447: PNA / MultiAggr towers emit 3 x per_head_dim messages aggregated as sum|mean|std|max (x 3 scalers for
+        # PNA); Plain towers emit per_head_dim messages aggregated by sum
+        msg_dim = config.per_head_dim if kind == "plain" else 3 * config.per_head_dim
+        tower_out = {"pna": 12, "multiaggr": 4, "plain": 1}[kind] * config.per_head_dim
+        self.mp_layers = nn.ModuleList(_TowerMessageFns(tower_in, msg_dim, config.num_edge_types)
                                        for _ in range(config.num_heads))
-        self.msg_out_projection = nn.Linear(config.num_heads * 12 * config.per_head_dim, config.hidden_dim)
+        self.msg_out_projection = nn.Linear(config.num_heads * tower_out, config.hidden_dim)
         self.mp_norm_layer = nn.LayerNorm(config.hidden_dim)
         self.boom_layer = BOOMLayer(config.hidden_dim, config.intermediate_dim)
         self.boom_norm_layer = nn.LayerNorm(config.hidden_dim)
@@ -141,7 +149,7 @@ class GNNBlock(nn.Module):
 
     def forward(self, h, gi: ops.GraphIndex):
         W, b = self.stacked_message_weights()
-        agg = ops.pna_message_passing(h, W, b, gi)                     # [V, 3072]
+        agg = ops.pna_message_passing(h, W, b, gi) if self._mp_mode == ops.MP_PNA else ops.mp_message_passing(h, W, b, gi, self._mp_mode)   # [V, 3072 | 1024 | 256]
         h = h + self.alpha * ops.linear_tc(agg, self.msg_out_projection.weight, self.msg_out_projection.bias)
         return h + self.alpha * self.boom_layer(self.boom_norm_layer(h))
 

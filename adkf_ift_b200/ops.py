@@ -154,32 +154,45 @@ def _type_sorted(gi: GraphIndex, edges_per_type: Sequence[int]) -> TypeSortedEdg
                            inv[gi.rev_pos.to(torch.int64)[perm]].to(torch.int32).contiguous(), tptr, off)
 
 
+MP_PNA, MP_MULTIAGGR, MP_PLAIN = 0, 1, 2          # ADKF_MP_* of include/adkf_b200.h
+_MP_OUT_WIDTH = {MP_PNA: 4 * 768, MP_MULTIAGGR: 4 * 256, MP_PLAIN: 4 * 64}
+
+
 class _PNAMessagePassingTC(torch.autograd.Function):
-    """PNA block on the tensor cores: gather -> batched 3xTF32 GEMM (message MLP) -> aggregation kernel (pna_gemm.cu)."""
+    """Tower-style relational message passing on the tensor cores: gather -> batched 3xTF32 GEMM (message MLP, all 4
+    towers per launch) -> aggregation kernel (pna_gemm.cu).  mode: MP_PNA / MP_MULTIAGGR (messages 192 wide) or MP_PLAIN
+    (messages 64 wide)."""
 
     @staticmethod
-    def forward(ctx, h, W, b, gi: GraphIndex):
+    def forward(ctx, h, W, b, gi: GraphIndex, mode: int = MP_PNA):
         lib = _cabi.load()
         ts: TypeSortedEdges = gi.type_sorted
         h, W, b = h.contiguous(), W.contiguous(), b.contiguous()
         V, E = gi.num_nodes, gi.num_edges
+        msg = W.shape[2]                                  # 192 (PNA / MultiAggr) or 64 (Plain)
+        if msg != (64 if mode == MP_PLAIN else 192):
+            raise ValueError(f"message width {msg} does not match message-passing mode {mode}")
         f32 = dict(dtype=torch.float32, device=h.device)
         XG = torch.empty(max(E, 1), 256, **f32)
-        pre = torch.empty(max(E, 1), 768, **f32)
+        pre = torch.empty(max(E, 1), 4 * msg, **f32)
         check(lib.adkf_pna_gather_inputs(dptr(h, torch.float32), dptr(ts.src), dptr(ts.tgt), E, dptr(XG), stream_ptr()),
               "adkf_pna_gather_inputs")
-        W2, b1 = W.view(12 * 192, 64), b.view(-1)
+        W2, b1 = W.view(12 * msg, 64), b.view(-1)
         for t in range(3):
             e0, e1 = ts.type_off[t], ts.type_off[t + 1]
-            if e1 > e0:   # pre[e0:e1, 192k:192k+192] = XG[e0:e1, 64k:64k+64] @ W[k][t]^T + b[k][t]
-                gemm_tf32x3_batched(XG[e0:e1], False, 0, 64, W2[t * 192:], False, 3 * 192, 0, e1 - e0, 192, 64, 4, pre[e0:e1], 768,
-                                    192, bias=b1[t * 192:], bias_stride=3 * 192)
-        out = torch.empty(V, 4 * 768, **f32)
-        aux_cnt = torch.empty(V, 4, 64, dtype=torch.uint8, device=h.device)
-        aux_arg = torch.empty(V, 4, 64, dtype=torch.uint8, device=h.device)
-        check(lib.adkf_pna_aggregate_fwd(dptr(pre), dptr(ts.tptr), V, dptr(out), dptr(aux_cnt), dptr(aux_arg), stream_ptr()),
-              "adkf_pna_aggregate_fwd")
-        ctx.gi = gi
+            if e1 > e0:   # pre[e0:e1, msg k : msg k + msg] = XG[e0:e1, 64k:64k+64] @ W[k][t]^T + b[k][t]
+                gemm_tf32x3_batched(XG[e0:e1], False, 0, 64, W2[t * msg:], False, 3 * msg, 0, e1 - e0, msg, 64, 4, pre[e0:e1], 4 * msg,
+                                    msg, bias=b1[t * msg:], bias_stride=3 * msg)
+        out = torch.empty(V, _MP_OUT_WIDTH[mode], **f32)
+        if mode == MP_PLAIN:
+            aux_cnt = aux_arg = torch.empty(0, dtype=torch.uint8, device=h.device)
+        else:
+            aux_cnt = torch.empty(V, 4, 64, dtype=torch.uint8, device=h.device)
+            aux_arg = torch.empty(V, 4, 64, dtype=torch.uint8, device=h.device)
+        null = ctypes.c_void_p(0)
+        check(lib.adkf_mp_aggregate_fwd(dptr(pre), dptr(ts.tptr), V, int(mode), dptr(out), dptr(aux_cnt) if mode != MP_PLAIN else null,
+                                        dptr(aux_arg) if mode != MP_PLAIN else null, stream_ptr()), "adkf_mp_aggregate_fwd")
+        ctx.gi, ctx.mode = gi, mode
         ctx.save_for_backward(W, XG, pre, out, aux_cnt, aux_arg)
         return out
 
@@ -187,32 +200,43 @@ class _PNAMessagePassingTC(torch.autograd.Function):
     def backward(ctx, d_out):
         lib = _cabi.load()
         W, XG, pre, out, aux_cnt, aux_arg = ctx.saved_tensors
-        gi = ctx.gi
+        gi, mode = ctx.gi, ctx.mode
         ts: TypeSortedEdges = gi.type_sorted
         V, E = gi.num_nodes, gi.num_edges
+        msg = W.shape[2]
         f32 = dict(dtype=torch.float32, device=W.device)
         d_out = d_out.contiguous()
-        d_pre = torch.empty(max(E, 1), 768, **f32)
-        check(lib.adkf_pna_dpre(dptr(pre), dptr(ts.tptr), V, dptr(out), dptr(aux_cnt), dptr(aux_arg), dptr(d_out, torch.float32),
-                                dptr(d_pre), stream_ptr()), "adkf_pna_dpre")
+        d_pre = torch.empty(max(E, 1), 4 * msg, **f32)
+        null = ctypes.c_void_p(0)
+        plain = mode == MP_PLAIN
+        check(lib.adkf_mp_dpre(dptr(pre), dptr(ts.tptr), V, int(mode), null if plain else dptr(out), null if plain else dptr(aux_cnt),
+                               null if plain else dptr(aux_arg), dptr(d_out, torch.float32), dptr(d_pre), stream_ptr()),
+              "adkf_mp_dpre")
         dXG = torch.empty(max(E, 1), 256, **f32)
         d_W = torch.zeros_like(W)
-        d_b = torch.zeros(4, 3, 192, **f32)
-        W2 = W.view(12 * 192, 64)
+        d_b = torch.zeros(4, 3, msg, **f32)
+        W2 = W.view(12 * msg, 64)
         for t in range(3):
             e0, e1 = ts.type_off[t], ts.type_off[t + 1]
             if e1 <= e0:
                 continue
             n = e1 - e0
-            # dXG[:, 64k:64k+64] = d_pre[:, 192k:192k+192] @ W[k][t]
-            gemm_tf32x3_batched(d_pre[e0:e1], False, 0, 192, W2[t * 192:], True, 0, 3 * 192, n, 64, 192, 4, dXG[e0:e1], 256, 64)
-            # dW[k][t] = d_pre[:, 192k:192k+192]^T @ XG[:, 64k:64k+64]   (split-K over the edges)
-            gemm_tf32x3_batched(d_pre[e0:e1], True, 192, 0, XG[e0:e1], True, 64, 0, 192, 64, n, 4,
-                                d_W.view(-1)[t * 192 * 64:], 64, 3 * 192 * 64, allow_splitk=True)
-            d_b[:, t] = act_bwd_colsum(d_pre[e0:e1], None, 0, True)[1].view(4, 192)
+            # dXG[:, 64k:64k+64] = d_pre[:, msg k : msg k + msg] @ W[k][t]
+            gemm_tf32x3_batched(d_pre[e0:e1], False, 0, msg, W2[t * msg:], True, 0, 3 * msg, n, 64, msg, 4, dXG[e0:e1], 256, 64)
+            # dW[k][t] = d_pre[:, msg k : msg k + msg]^T @ XG[:, 64k:64k+64]   (split-K over the edges)
+            gemm_tf32x3_batched(d_pre[e0:e1], True, msg, 0, XG[e0:e1], True, 64, 0, msg, 64, n, 4,
+                                d_W.view(-1)[t * msg * 64:], 64, 3 * msg * 64, allow_splitk=True)
+            d_b[:, t] = act_bwd_colsum(d_pre[e0:e1], None, 0, True)[1].view(4, msg)
         d_h = torch.empty(V, 128, **f32)
         check(lib.adkf_pna_dh_gather(dptr(dXG), dptr(ts.tptr), dptr(ts.rev), V, dptr(d_h), stream_ptr()), "adkf_pna_dh_gather")
-        return d_h, d_W, d_b, None
+        return d_h, d_W, d_b, None, None
+
+
+def mp_message_passing(h, W, b, gi: GraphIndex, mode: int):
+    """h [V,128], W [4,3,msg,64], b [4,3,msg] -> aggregated messages of all 4 towers for GNN types PNA / MultiAggr / Plain."""
+    if getattr(gi, "type_sorted", None) is None:
+        raise RuntimeError("mp_message_passing needs a GraphIndex built by build_graph_index (type-sorted edges)")
+    return _PNAMessagePassingTC.apply(h, W, b, gi, mode)
 
 
 def pna_message_passing(h, W, b, gi: GraphIndex, impl: str = "tcgen05"):
@@ -220,7 +244,7 @@ def pna_message_passing(h, W, b, gi: GraphIndex, impl: str = "tcgen05"):
     impl="tcgen05": gather + batched tensor-core GEMM + segment kernels (pna_gemm.cu; needs gi.type_sorted);
     impl="simt": the fused fp32 CUDA-core kernels of graph.cu."""
     if impl == "tcgen05" and getattr(gi, "type_sorted", None) is not None:
-        return _PNAMessagePassingTC.apply(h, W, b, gi)
+        return _PNAMessagePassingTC.apply(h, W, b, gi, MP_PNA)
     return _PNAMessagePassing.apply(h, W, b, gi)
 
 

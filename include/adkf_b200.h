@@ -132,6 +132,18 @@ int adkf_pna_aggregate_fwd(const float* pre, const int32_t* tptr, int32_t V, flo
 int adkf_pna_dpre(const float* pre, const int32_t* tptr, int32_t V, const float* fwd_out, const uint8_t* aux_cnt,
                   const uint8_t* aux_arg, const float* d_out, float* d_pre, void* stream);
 int adkf_pna_dh_gather(const float* dXG, const int32_t* tptr, const int32_t* rev, int32_t V, float* d_h, void* stream);
+/* The other two tower-style message-passing types of GNNBlock (fs_mol/modules/gnn.py:421-447), same edge layout:
+ *   ADKF_MP_MULTIAGGR  RelationalMultiAggrMP without PNA scalers: pre [E,768] -> out [V,1024]  (gnn.py:197-240)
+ *   ADKF_MP_PLAIN      RelationalMP: relu + scatter_sum of 64-wide messages, pre [E,256] -> out [V,256]  (gnn.py:152-165;
+ *                      fwd_out / aux arrays unused, may be NULL)
+ * ADKF_MP_PNA is what adkf_pna_aggregate_fwd / adkf_pna_dpre run. */
+#define ADKF_MP_PNA 0
+#define ADKF_MP_MULTIAGGR 1
+#define ADKF_MP_PLAIN 2
+int adkf_mp_aggregate_fwd(const float* pre, const int32_t* tptr, int32_t V, int32_t mode, float* out, uint8_t* aux_cnt,
+                          uint8_t* aux_arg, void* stream);
+int adkf_mp_dpre(const float* pre, const int32_t* tptr, int32_t V, int32_t mode, const float* fwd_out, const uint8_t* aux_cnt,
+                 const uint8_t* aux_arg, const float* d_out, float* d_pre, void* stream);
 
 /* ---------------------------------------------------------------------------------------------
  * Graph readout segment kernels (fs_mol/modules/graph_readout.py:224-259, 286-296).  Nodes of a graph

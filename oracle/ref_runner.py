@@ -18,7 +18,7 @@ def install():
 
 
 def reference_config(num_layers=10, used_features="gnn+ecfp+fc", gp_kernel="matern",
-                     use_numeric_labels=False, use_lengthscale_prior=True, **extra):
+                     use_numeric_labels=False, use_lengthscale_prior=True, gnn_type="PNA", **extra):
     """CLI-default model (fs_mol/adaptive_dkt_train.py + gnn.py:31-63) as an ADKTModelTrainerConfig."""
     from fs_mol.modules.gnn import GNNConfig
     from fs_mol.modules.graph_feature_extractor import GraphFeatureExtractorConfig
@@ -26,7 +26,7 @@ def reference_config(num_layers=10, used_features="gnn+ecfp+fc", gp_kernel="mate
     from fs_mol.utils.adaptive_dkt_utils import ADKTModelTrainerConfig
     return ADKTModelTrainerConfig(
         graph_feature_extractor_config=GraphFeatureExtractorConfig(
-            gnn_config=GNNConfig(type="PNA", hidden_dim=128, num_heads=4, per_head_dim=64,
+            gnn_config=GNNConfig(type=gnn_type, hidden_dim=128, num_heads=4, per_head_dim=64,
                                  intermediate_dim=1024, num_layers=num_layers),
             readout_config=GraphReadoutConfig()),
         used_features=used_features, gp_kernel=gp_kernel, use_numeric_labels=use_numeric_labels,
