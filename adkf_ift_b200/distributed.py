@@ -29,6 +29,10 @@ def world_size() -> int:
     return dist.get_world_size() if dist.is_available() and dist.is_initialized() else 1
 
 
+def rank() -> int:
+    return dist.get_rank() if dist.is_available() and dist.is_initialized() else 0
+
+
 def shard_tasks(num_tasks: int, rank: int, world: int) -> List[int]:
     """Round-robin task shard of one meta-batch: rank r owns tasks r, r+R, ... (balanced to within one task)."""
     return list(range(rank, num_tasks, world))

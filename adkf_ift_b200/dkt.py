@@ -142,3 +142,26 @@ def torchify(data, device: torch.device):
         new = {f.name: torchify(getattr(data, f.name), device) for f in dataclasses.fields(data)}
         return dataclasses.replace(data, **new)
     raise ValueError(f"Trying to torchify unknown value type {type(data)}!")
+
+
+def get_dkt_task_sample_iterable(dataset, data_fold, num_samples: int, support_size: int, query_size: Optional[int],
+                                 max_num_graphs: Optional[int] = None, max_num_nodes: Optional[int] = None,
+                                 max_num_edges: Optional[int] = None, repeat: bool = False,
+                                 filter_numeric_labels: bool = False):
+    """fs_mol/data/dkt.py:154-207: stratified (support, query) draws of every task of a fold, featurised into DKT batches.
+    `dataset` needs `get_task_reading_iterable(data_fold, repeat=...)` yielding tasks; the draw seed is task index + draw
+    index as in the reference's reader pipeline."""
+    from .eval_utils import StratifiedTaskSampler, numeric_task_is_filtered
+    sampler = StratifiedTaskSampler(train_size_or_ratio=support_size, test_size_or_ratio=query_size)
+    batcher = get_dkt_batcher(max_num_graphs=max_num_graphs, max_num_nodes=max_num_nodes, max_num_edges=max_num_edges)
+    for idx, task in enumerate(dataset.get_task_reading_iterable(data_fold, repeat=repeat)):
+        if filter_numeric_labels and numeric_task_is_filtered(task):
+            continue
+        drawn = 0
+        for _ in range(num_samples):
+            try:
+                sample = sampler.sample(task, seed=idx + drawn)
+                drawn += 1
+            except Exception:      # noqa: BLE001  (the reference skips any failed draw, dkt.py:191-196)
+                continue
+            yield task_sample_to_dkt_task_sample(sample, batcher, filter_numeric_labels)

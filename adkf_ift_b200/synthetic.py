@@ -200,3 +200,34 @@ def make_mol_graphs(seed: int, num_graphs: int):
     return dict(x=np.concatenate(xs).astype(np.int64), edge_index=np.array([srcs, tgts], dtype=np.int64),
                 edge_attr=np.array(attrs, dtype=np.int64).reshape(-1, 2), batch=np.array(batch, dtype=np.int64),
                 y=y.astype(np.int64))
+
+
+class SyntheticFSMolDataset:
+    """Stand-in for fs_mol.data.FSMolDataset (fsmol_dataset.py:30-142) over seeded synthetic tasks: the only method the task
+    loops use is `get_task_reading_iterable(data_fold)`.  `numeric_scale` > 5 pushes the numeric labels out of the
+    percentage range that `--use-numeric-labels` filters (test_utils.py:281-290)."""
+
+    def __init__(self, num_train_tasks: int = 8, num_valid_tasks: int = 2, num_test_tasks: int = 2, molecules_per_task: int = 96,
+                 first_task_id: int = 5000, numeric_scale: float = 1.0):
+        self._counts = (num_train_tasks, num_valid_tasks, num_test_tasks)
+        self._mols, self._first, self._scale = molecules_per_task, first_task_id, numeric_scale
+
+    def get_num_fold_tasks(self, data_fold) -> int:
+        return self._counts[int(data_fold)]
+
+    def _task(self, task_id: int):
+        import dataclasses
+        from .eval_utils import FSMolTask
+        mols = make_task_molecules(task_id, self._mols)
+        if self._scale != 1.0:
+            mols = [dataclasses.replace(m, numeric_label=m.numeric_label * self._scale) for m in mols]
+        return FSMolTask(name=mols[0].task_name, samples=mols)
+
+    def get_task_reading_iterable(self, data_fold, repeat: bool = False):
+        fold = int(data_fold)
+        start = self._first + sum(self._counts[:fold])
+        while True:
+            for i in range(self._counts[fold]):
+                yield self._task(start + i)
+            if not repeat:
+                return

@@ -154,10 +154,10 @@ def test_single_task_surface(cuda_device, golden_dir):
     """The reference's call sequence on ADKTModel (run_on_batches) + first-order autograd of the functional
     losses, on the T=1 kernels."""
     from adkf_ift_b200 import dkt
-    from adkf_ift_b200.adaptive_dkt_utils import run_on_batches
+    from adkf_ift_b200.adaptive_dkt_utils import run_on_batches_raw
     g, model, host, tb = build(golden_dir, "c1_classification", "matern", cuda_device)
     dev = dkt.torchify(host, cuda_device)
-    preds, labels = run_on_batches(model, dev.batches, dev.batch_labels, dev.batch_numeric_labels, train=False)
+    preds, labels = run_on_batches_raw(model, dev.batches, dev.batch_labels, dev.batch_numeric_labels, train=False)
     ref = 1.0 / (1.0 + np.exp(-g["test_mean"].astype(np.float64)))
     assert rel(preds, ref) < 2e-3
     assert np.abs(np.array([p.item() for p in model.gp_params()]) - g["test_phi_star"]).max() < 2e-3

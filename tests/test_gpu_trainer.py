@@ -1,0 +1,87 @@
+"""-m gpu tests of the trainer / evaluation surface around the hot path (fs_mol/utils/adaptive_dkt_utils.py:119-211, 261-303,
+329-458) on a small synthetic dataset: batched evaluation == the reference's per-sample protocol, train_loop runs, validates
+and checkpoints, GNN-only checkpoints load with the reference's two learning-rate groups."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+def small_model(device, **over):
+    from adkf_ift_b200 import synthetic
+    from adkf_ift_b200.adaptive_dkt import ADKTModelTrainerConfig
+    from adkf_ift_b200.adaptive_dkt_utils import ADKTModelTrainer
+    from adkf_ift_b200.feature_extractor import cli_default_config
+    kw = dict(graph_feature_extractor_config=cli_default_config(2), batch_size=96, tasks_per_batch=4, support_set_size=16,
+              query_set_size=32, num_train_steps=3, validate_every_num_steps=2, validation_support_set_sizes=(16,),
+              validation_query_set_size=32, validation_num_samples=1, learning_rate=1e-4, clip_value=1.0)
+    kw.update(over)
+    model = ADKTModelTrainer(ADKTModelTrainerConfig(**kw))
+    synthetic.deterministic_init_(model, seed=0, alpha=0.5)
+    return model.to(device)
+
+
+@pytest.mark.parametrize("numeric", [False, True])
+def test_batched_evaluation_matches_per_sample_protocol(cuda_device, tmp_path, numeric):
+    from adkf_ift_b200 import dkt, eval_utils as E, synthetic
+    from adkf_ift_b200.adaptive_dkt_utils import evaluate_adkt_model, run_on_batches
+    model = small_model(cuda_device, use_numeric_labels=numeric)
+    ds = synthetic.SyntheticFSMolDataset(2, 1, 3, molecules_per_task=72, numeric_scale=50.0 if numeric else 1.0)
+    batched = evaluate_adkt_model(model, ds, support_sizes=[16, 24], num_samples=2, seed=1, batch_size=96, query_size=None,
+                                  save_dir=str(tmp_path), tasks_per_launch=5)
+    batcher = dkt.get_dkt_batcher(max_num_graphs=96)
+
+    def per_sample(sample, tmp, seed):
+        dev = dkt.torchify(dkt.task_sample_to_dkt_task_sample(sample, batcher, numeric), cuda_device)
+        return run_on_batches(model, dev.batches, dev.batch_labels, dev.batch_numeric_labels, train=False)
+    single = E.eval_model(per_sample, ds, [16, 24], num_samples=2, seed=1, filter_numeric_labels=numeric)
+    assert sorted(batched) == sorted(single) and len(batched) == 3
+    keys = ("mse", "mae", "r2") if numeric else ("acc", "roc_auc", "avg_precision", "f1")
+    for name in batched:
+        assert len(batched[name]) == len(single[name]) == 4
+        for a, b in zip(batched[name], single[name]):
+            assert (a.seed, a.num_train, a.num_test) == (b.seed, b.num_train, b.num_test)
+            for k in keys:
+                assert abs(getattr(a, k) - getattr(b, k)) <= 2e-3 * max(1.0, abs(getattr(b, k))), (name, k, getattr(a, k), getattr(b, k))
+        assert os.path.exists(tmp_path / f"{name}_eval_results.csv")
+    # a query set larger than one batch goes through run_on_batches (several query batches per task)
+    multi = evaluate_adkt_model(model, ds, support_sizes=[16], num_samples=1, seed=1, batch_size=40, query_size=None)
+    assert all(len(v) == 1 and v[0].num_test == 56 for v in multi.values())
+
+
+def test_train_loop_and_checkpoints(cuda_device, tmp_path):
+    from adkf_ift_b200 import synthetic
+    from adkf_ift_b200.adaptive_dkt_utils import ADKTModelTrainer
+    model = small_model(cuda_device)
+    ds = synthetic.SyntheticFSMolDataset(5, 2, 1, molecules_per_task=64)
+    before = torch.cat([p.detach().reshape(-1).clone() for p in model.feature_extractor_params()])
+    losses = model.train_loop(str(tmp_path), ds, cuda_device)
+    after = torch.cat([p.detach().reshape(-1) for p in model.feature_extractor_params()])
+    assert len(losses) == 3 and np.isfinite(losses).all()
+    assert float((after - before).abs().max()) > 0.0
+    for f in ("best_validation.pt", "fully_trained.pt"):
+        assert os.path.exists(tmp_path / f)
+    again = ADKTModelTrainer.build_from_model_file(str(tmp_path / "fully_trained.pt"), device=cuda_device)
+    got = torch.cat([p.detach().reshape(-1) for p in again.feature_extractor_params()])
+    assert torch.equal(got, after)
+
+
+def test_load_model_gnn_weights(cuda_device, tmp_path):
+    model = small_model(cuda_device)
+    donor = small_model(cuda_device)
+    with torch.no_grad():
+        for p in donor.graph_feature_extractor.parameters():
+            p.add_(0.25)
+    # a GNNMultitask checkpoint names the extractor's tensors without the prefix
+    torch.save({"model_state_dict": {k: v.clone() for k, v in donor.graph_feature_extractor.state_dict().items()}}, tmp_path / "gnn.pt")
+    fc_before = model.fc[0].weight.detach().clone()
+    model.load_model_gnn_weights(str(tmp_path / "gnn.pt"), device=cuda_device)
+    for (n, a), (_, b) in zip(model.graph_feature_extractor.state_dict().items(), donor.graph_feature_extractor.state_dict().items()):
+        assert torch.equal(a, b), n
+    assert torch.equal(model.fc[0].weight, fc_before)
+    lrs = [g["lr"] for g in model.optimizer.param_groups]
+    assert len(lrs) == 2 and lrs[1] == 0.0 and abs(lrs[0] - 1e-4) < 1e-12          # warm-up: the loaded group starts at 0
+    assert sum(p.numel() for p in model.optimizer.param_groups[1]["params"]) == sum(p.numel() for p in model.graph_feature_extractor.parameters())

@@ -136,3 +136,74 @@ def test_synthetic_tasks_are_deterministic_and_well_formed():
     m = a.test_samples[0]
     assert m.graph.node_features.shape[1] == 32 and m.fingerprint.dtype == np.int32 and m.fingerprint.shape == (2048,)
     assert 8 <= len(m.graph.node_features) <= 60 and len(m.graph.adjacency_lists) == 3
+
+
+def test_metrics_match_scikit_learn():
+    """adkf_ift_b200.metrics restates fs_mol/utils/metrics.py without scikit-learn; scikit-learn is the checker here."""
+    import warnings
+    from sklearn import metrics as S
+    from adkf_ift_b200 import metrics as M
+    rng = np.random.default_rng(0)
+    for trial in range(120):
+        n = int(rng.integers(4, 60))
+        y = rng.integers(0, 2, n).astype(float)
+        if trial % 9 == 0:
+            y[:] = 1.0
+        p = np.round(rng.random(n), 1 if trial % 3 == 0 else 6)      # ties in the scores every third trial
+        m = M.compute_binary_task_metrics(p, y)
+        yh = p >= 0.5
+        with warnings.catch_warnings():
+            warnings.simplefilter("ignore")
+            ref = dict(acc=S.accuracy_score(y, yh), balanced_acc=S.balanced_accuracy_score(y, yh),
+                       f1=S.f1_score(y, yh, zero_division=1), prec=S.precision_score(y, yh, zero_division=1),
+                       recall=S.recall_score(y, yh, zero_division=1),
+                       roc_auc=0.0 if y.sum() in (0, n) else S.roc_auc_score(y, p),
+                       avg_precision=S.average_precision_score(y, p), kappa=S.cohen_kappa_score(y, yh))
+        for k, v in ref.items():
+            got = getattr(m, k)
+            assert np.isclose(got, v, atol=1e-12) or (np.isnan(got) and np.isnan(v)), (trial, k, got, v)
+    y, p = rng.normal(size=50), rng.normal(size=50)
+    nm = M.compute_numeric_task_metrics(p, y)
+    assert np.isclose(nm.mse, S.mean_squared_error(y, p)) and np.isclose(nm.mae, S.mean_absolute_error(y, p))
+    assert np.isclose(nm.r2, 1.0 - ((y - p) ** 2).sum() / (y ** 2).sum())       # out-of-sample R2 against a zero baseline
+
+
+def test_stratified_sampler_and_eval_draws(tmp_path):
+    """fsmol_task_sampler.py:299-440 / test_utils.py:236-350: split sizes, stratification, determinism in the seed, skipped
+    draws, the numeric-label task filter and the CSV column contract."""
+    import csv
+    from adkf_ift_b200 import eval_utils as E, synthetic
+    from adkf_ift_b200.metrics import BinaryEvalMetrics
+    ds = synthetic.SyntheticFSMolDataset(num_train_tasks=2, num_valid_tasks=1, num_test_tasks=2, molecules_per_task=80)
+    task = next(iter(ds.get_task_reading_iterable(E.DataFold.TEST)))
+    s1 = E.StratifiedTaskSampler(16, 0.0, None).sample(task, seed=3)
+    s2 = E.StratifiedTaskSampler(16, 0.0, None).sample(task, seed=3)
+    s3 = E.StratifiedTaskSampler(16, 0.0, None).sample(task, seed=4)
+    assert len(s1.train_samples) == 16 and len(s1.test_samples) == 64
+    assert [m.smiles for m in s1.train_samples] == [m.smiles for m in s2.train_samples]
+    assert [m.smiles for m in s1.train_samples] != [m.smiles for m in s3.train_samples]
+    assert not {m.smiles for m in s1.train_samples} & {m.smiles for m in s1.test_samples}
+    frac = np.mean([m.bool_label for m in task.samples])
+    assert abs(np.mean([m.bool_label for m in s1.train_samples]) - frac) <= 1.0 / 16 + 1e-9      # stratified
+    assert len(E.StratifiedTaskSampler(16, 0.0, 32).sample(task, seed=0).test_samples) == 32
+    assert len(E.StratifiedTaskSampler(16, 0.0, (8, 256)).sample(task, seed=0).test_samples) == 64
+    with pytest.raises(E.DatasetTooSmallException):
+        E.StratifiedTaskSampler(79, 0.0, None).sample(task, seed=0)
+    draws = list(E.iter_eval_draws(ds, [16, 79, 32], num_samples=2, seed=7))
+    assert len(draws) == 2 and [(d.train_size, d.seed) for d in draws[0][1]] == [(16, 7), (16, 8), (32, 7), (32, 8)]
+    # numeric filter: the synthetic labels lie in (0, 100) -> percentage-like -> filtered; scaled by 50 they are kept
+    assert list(E.iter_eval_draws(ds, [16], 1, filter_numeric_labels=True)) == []
+    ds50 = synthetic.SyntheticFSMolDataset(2, 1, 2, 80, numeric_scale=50.0)
+    assert len(list(E.iter_eval_draws(ds50, [16], 1, filter_numeric_labels=True))) == 2
+
+    def fake_model(sample, tmp, seed):
+        return BinaryEvalMetrics(size=len(sample.test_samples), acc=0.5, balanced_acc=0.5, f1=0.5, prec=0.5, recall=0.5,
+                                 roc_auc=0.5, avg_precision=0.6, kappa=0.0)
+    res = E.eval_model(fake_model, ds, [16, 32], out_dir=str(tmp_path), num_samples=2)
+    assert sorted(res) == sorted(t.name for t in ds.get_task_reading_iterable(E.DataFold.TEST))
+    name = sorted(res)[0]
+    assert [r.num_train for r in res[name]] == [16, 16, 32, 32] and res[name][0].num_test == 64
+    rows = list(csv.DictReader(open(tmp_path / f"{name}_eval_results.csv")))
+    assert list(rows[0].keys())[:6] == ["num_train_requested", "num_train", "fraction_positive_train", "num_test",
+                                        "fraction_positive_test", "seed"]
+    assert abs(float(rows[0]["delta_auprc"]) - (0.6 - res[name][0].fraction_pos_test)) < 1e-12
