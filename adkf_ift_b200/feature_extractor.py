@@ -110,6 +110,23 @@ class BOOMLayer(nn.Module):
         return ops.linear_tc(hid, self.linear2.weight, self.linear2.bias)
 
 
+class RelationalMultiHeadAttentionMP(nn.Module):
+    """Parameter holder with the reference's names (gnn.py:268-310): per edge type a message MLP Linear(2 hidden -> heads x
+    head_dim), a bias-free target-node query projection and a bias-free neighbour-node key projection."""
+
+    def __init__(self, hidden_dim: int, num_heads: int, per_head_dim: int, num_edge_types: int):
+        super().__init__()
+        out = num_heads * per_head_dim
+        self.message_fns = nn.ModuleList(MLP(2 * hidden_dim, out, []) for _ in range(num_edge_types))
+        self.target_node_query_projs = nn.ModuleList(nn.Linear(hidden_dim, out, bias=False) for _ in range(num_edge_types))
+        self.neighbour_node_key_projs = nn.ModuleList(nn.Linear(hidden_dim, out, bias=False) for _ in range(num_edge_types))
+
+    def forward(self, x, gi: ops.GraphIndex):
+        Wqk = torch.cat([p.weight for p in self.target_node_query_projs] + [p.weight for p in self.neighbour_node_key_projs], 0)
+        return ops.mha_message_passing(x, [f._layers[0].weight for f in self.message_fns],
+                                       [f._layers[0].bias for f in self.message_fns], Wqk, gi)
+
+
 class GNNBlock(nn.Module):
     """One residual block (gnn.py:477-515).  `mp_norm_layer` is registered but never applied, exactly like
     the reference, so the state dict keeps its keys."""
@@ -117,11 +134,9 @@ class GNNBlock(nn.Module):
     def __init__(self, config: GNNConfig):
         super().__init__()
         kind = config.type.lower()
-        if kind == "multiheadattention":
-            raise NotImplementedError("gnn type 'MultiHeadAttention' has no sm_100a kernels yet (PNA, MultiAggr and Plain do)")
-        if kind not in ("pna", "multiaggr", "plain"):
+        if kind not in ("pna", "multiaggr", "plain", "multiheadattention"):
             raise ValueError(f"Unknown GNN type {config.type}.")          # gnn.py:447
-        self._mp_mode = {"pna": ops.MP_PNA, "multiaggr": ops.MP_MULTIAGGR, "plain": ops.MP_PLAIN}[kind]
+        self._mp_mode = {"pna": ops.MP_PNA, "multiaggr": ops.MP_MULTIAGGR, "plain": ops.MP_PLAIN, "multiheadattention": -1}[kind]
         if (config.hidden_dim, config.num_heads, config.per_head_dim, config.num_edge_types) != (128, 4, 64, 3):
             raise NotImplementedError("the fused PNA kernel is specialised to hidden 128 / 4 towers / per-head 64 / 3 edge types")
         if config.message_function_depth != 1 or config.dropout_rate != 0.0 or not config.use_rezero_scaling:
@@ -134,9 +149,13 @@ class GNNBlock(nn.Module):
         # gnn.py:421-447: PNA / MultiAggr towers emit 3 x per_head_dim messages aggregated as sum|mean|std|max (x 3 scalers for
         # PNA); Plain towers emit per_head_dim messages aggregated by sum
         msg_dim = config.per_head_dim if kind == "plain" else 3 * config.per_head_dim
-        tower_out = {"pna": 12, "multiaggr": 4, "plain": 1}[kind] * config.per_head_dim
-        self.mp_layers = nn.ModuleList(_TowerMessageFns(tower_in, msg_dim, config.num_edge_types)
-                                       for _ in range(config.num_heads))
+        tower_out = {"pna": 12, "multiaggr": 4, "plain": 1, "multiheadattention": 1}[kind] * config.per_head_dim
+        if kind == "multiheadattention":      # one attention layer over the whole hidden state (gnn.py:409-420)
+            self.mp_layers = nn.ModuleList([RelationalMultiHeadAttentionMP(config.hidden_dim, config.num_heads, config.per_head_dim,
+                                                                           config.num_edge_types)])
+        else:
+            self.mp_layers = nn.ModuleList(_TowerMessageFns(tower_in, msg_dim, config.num_edge_types)
+                                           for _ in range(config.num_heads))
         self.msg_out_projection = nn.Linear(config.num_heads * tower_out, config.hidden_dim)
         self.mp_norm_layer = nn.LayerNorm(config.hidden_dim)
         self.boom_layer = BOOMLayer(config.hidden_dim, config.intermediate_dim)
@@ -148,6 +167,10 @@ class GNNBlock(nn.Module):
         return W, b  # [4,3,192,64], [4,3,192]
 
     def forward(self, h, gi: ops.GraphIndex):
+        if self._mp_mode < 0:
+            agg = self.mp_layers[0](h, gi)                                 # [V, 256]
+            h = h + self.alpha * ops.linear_tc(agg, self.msg_out_projection.weight, self.msg_out_projection.bias)
+            return h + self.alpha * self.boom_layer(self.boom_norm_layer(h))
         W, b = self.stacked_message_weights()
         agg = ops.pna_message_passing(h, W, b, gi) if self._mp_mode == ops.MP_PNA else ops.mp_message_passing(h, W, b, gi, self._mp_mode)   # [V, 3072 | 1024 | 256]
         h = h + self.alpha * ops.linear_tc(agg, self.msg_out_projection.weight, self.msg_out_projection.bias)

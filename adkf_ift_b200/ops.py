@@ -239,6 +239,81 @@ def mp_message_passing(h, W, b, gi: GraphIndex, mode: int):
     return _PNAMessagePassingTC.apply(h, W, b, gi, mode)
 
 
+class _MHAGather(torch.autograd.Function):
+    """XG [E,256] = [x_src | x_tgt] over the type-sorted edges (mha_mp.cu)."""
+
+    @staticmethod
+    def forward(ctx, x, gi: GraphIndex):
+        lib = _cabi.load()
+        ts: TypeSortedEdges = gi.type_sorted
+        E = gi.num_edges
+        XG = torch.empty(max(E, 1), 256, dtype=torch.float32, device=x.device)
+        check(lib.adkf_mha_gather_inputs(dptr(x.contiguous(), torch.float32), dptr(ts.src), dptr(ts.tgt), E, dptr(XG), stream_ptr()),
+              "adkf_mha_gather_inputs")
+        ctx.gi = gi
+        return XG
+
+    @staticmethod
+    def backward(ctx, dXG):
+        lib = _cabi.load()
+        gi = ctx.gi
+        ts: TypeSortedEdges = gi.type_sorted
+        d_x = torch.empty(gi.num_nodes, 128, dtype=torch.float32, device=dXG.device)
+        check(lib.adkf_mha_dx_gather(dptr(dXG.contiguous(), torch.float32), dptr(ts.tptr), dptr(ts.rev), gi.num_nodes, dptr(d_x),
+                                     stream_ptr()), "adkf_mha_dx_gather")
+        return d_x, None
+
+
+class _MHAAttention(torch.autograd.Function):
+    """out [V,256] from message pre-activations pre [E,256] and the node projections QK [V,1536] (mha_mp.cu)."""
+
+    @staticmethod
+    def forward(ctx, pre, QK, gi: GraphIndex):
+        lib = _cabi.load()
+        ts: TypeSortedEdges = gi.type_sorted
+        V, E = gi.num_nodes, gi.num_edges
+        pre, QK = pre.contiguous(), QK.contiguous()
+        out = torch.empty(V, 256, dtype=torch.float32, device=QK.device)
+        probs = torch.empty(max(E, 1), 4, dtype=torch.float32, device=QK.device)
+        check(lib.adkf_mha_attention_fwd(dptr(pre, torch.float32), dptr(QK, torch.float32), dptr(ts.src), dptr(ts.tptr), V, dptr(out),
+                                         dptr(probs), stream_ptr()), "adkf_mha_attention_fwd")
+        ctx.gi = gi
+        ctx.save_for_backward(pre, QK, probs)
+        return out
+
+    @staticmethod
+    def backward(ctx, d_out):
+        lib = _cabi.load()
+        pre, QK, probs = ctx.saved_tensors
+        gi = ctx.gi
+        ts: TypeSortedEdges = gi.type_sorted
+        V, E = gi.num_nodes, gi.num_edges
+        d_pre = torch.empty_like(pre)
+        ds = torch.empty(max(E, 1), 4, dtype=torch.float32, device=QK.device)
+        dQK = torch.empty_like(QK)
+        check(lib.adkf_mha_attention_bwd(dptr(pre), dptr(QK), dptr(ts.src), dptr(ts.rev), dptr(ts.tptr), V, dptr(probs),
+                                         dptr(d_out.contiguous(), torch.float32), dptr(d_pre), dptr(ds), dptr(dQK), stream_ptr()),
+              "adkf_mha_attention_bwd")
+        return d_pre, dQK, None
+
+
+def mha_message_passing(x, msg_weights, msg_biases, Wqk, gi: GraphIndex):
+    """RelationalMultiHeadAttentionMP.forward (gnn.py:316-387): x [V,128]; msg_weights[t] [256,256], msg_biases[t] [256];
+    Wqk [1536,128] = the three target-query then the three neighbour-key projection matrices stacked -> [V,256]."""
+    if getattr(gi, "type_sorted", None) is None:
+        raise RuntimeError("mha_message_passing needs a GraphIndex built by build_graph_index (type-sorted edges)")
+    ts: TypeSortedEdges = gi.type_sorted
+    XG = _MHAGather.apply(x, gi)
+    parts = []
+    for t in range(3):
+        e0, e1 = ts.type_off[t], ts.type_off[t + 1]
+        if e1 > e0:
+            parts.append(linear_tc(XG[e0:e1], msg_weights[t], msg_biases[t]))
+    pre = torch.cat(parts, 0) if parts else XG[:0]
+    QK = linear_tc(x, Wqk)
+    return _MHAAttention.apply(pre, QK, gi)
+
+
 def pna_message_passing(h, W, b, gi: GraphIndex, impl: str = "tcgen05"):
     """h [V,128], W [4,3,192,64], b [4,3,192] -> aggregated messages [V, 3072] (all 4 towers).
     impl="tcgen05": gather + batched tensor-core GEMM + segment kernels (pna_gemm.cu; needs gi.type_sorted);

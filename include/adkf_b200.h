@@ -146,6 +146,23 @@ int adkf_mp_dpre(const float* pre, const int32_t* tptr, int32_t V, int32_t mode,
                  const uint8_t* aux_arg, const float* d_out, float* d_pre, void* stream);
 
 /* ---------------------------------------------------------------------------------------------
+ * `--gnn_type MultiHeadAttention`: RelationalMultiHeadAttentionMP (fs_mol/modules/gnn.py:268-387), hidden 128, 4 heads x 64,
+ * 3 edge types, on the same type-sorted edge arrays (src / tgt / rev [E], tptr [3V+1]) as the tower kernels.
+ *   XG [E,256]  = adkf_mha_gather_inputs(x)        [x_src | x_tgt]  (message MLP input; the MLP itself is adkf_gemm_tf32x3 per type)
+ *   QK [V,1536] = x [Wq_0 Wq_1 Wq_2 Wk_0 Wk_1 Wk_2]^T  (adkf_gemm_tf32x3; target-query / neighbour-key projections of every node)
+ *   out [V,256] = adkf_mha_attention_fwd(pre [E,256], QK): per (target, head) softmax over ALL arriving edges of
+ *                 64^-1/2 <Q_type[tgt], K_type[src]>, weighted sum of relu(pre); probs [E,4] kept for the backward
+ *   adkf_mha_attention_bwd: d_pre [E,256], dQK [V,1536] (ds_ws [E,4] scratch); adkf_mha_dx_gather: d_x from dXG.
+ * ------------------------------------------------------------------------------------------- */
+int adkf_mha_gather_inputs(const float* x, const int32_t* src, const int32_t* tgt, int64_t E, float* XG, void* stream);
+int adkf_mha_dx_gather(const float* dXG, const int32_t* tptr, const int32_t* rev, int32_t V, float* d_x, void* stream);
+int adkf_mha_attention_fwd(const float* pre, const float* QK, const int32_t* src, const int32_t* tptr, int32_t V, float* out,
+                           float* probs, void* stream);
+int adkf_mha_attention_bwd(const float* pre, const float* QK, const int32_t* src, const int32_t* rev, const int32_t* tptr,
+                           int32_t V, const float* probs, const float* d_out, float* d_pre, float* ds_ws, float* dQK,
+                           void* stream);
+
+/* ---------------------------------------------------------------------------------------------
  * Graph readout segment kernels (fs_mol/modules/graph_readout.py:224-259, 286-296).  Nodes of a graph
  * are contiguous: graph_ptr[G+1].
  *   weighted pool : w = softmax over the graph's nodes (mode 0) or sigmoid (mode 1) of scores [V,heads];

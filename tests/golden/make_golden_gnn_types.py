@@ -1,5 +1,5 @@
 """Generates tests/golden/gnn_types.npz: the reference's OWN GraphFeatureExtractor (fs_mol/modules/gnn.py, unmodified,
-through oracle/shims.py) with `--gnn_type MultiAggr` and `Plain` on a seeded synthetic task: features of the support
+through oracle/shims.py) with `--gnn_type MultiAggr`, `Plain` and `MultiHeadAttention` on a seeded synthetic task: features of the support
 graphs and the gradient of a fixed probe loss sum(features * probe) w.r.t. every extractor parameter (per-tensor norms and
 random-probe dot products).  Authoring container only:  python tests/golden/make_golden_gnn_types.py"""
 import os
@@ -26,7 +26,7 @@ def probe_vector(name, shape):
 def main():
     out = {}
     task_id, n_s, n_q, layers = 3, 24, 8, 2
-    for gnn_type in ("MultiAggr", "Plain"):
+    for gnn_type in ("MultiAggr", "Plain", "MultiHeadAttention"):
         torch.manual_seed(0)
         model = rr.build_reference_model(rr.reference_config(num_layers=layers, gnn_type=gnn_type))
         ts = synthetic.make_task_sample(task_id, n_s, n_q)
@@ -44,7 +44,8 @@ def main():
         out[f"{gnn_type}::grad_norms"] = np.array([params[n].grad.double().norm().item() for n in names])
         out[f"{gnn_type}::grad_dots"] = np.array([(params[n].grad.double() * probe_vector(n, params[n].shape)).sum().item()
                                                   for n in names])
-        for n in ("gnn.gnn_blocks.0.alpha", "init_node_proj.weight", "gnn.gnn_blocks.1.mp_layers.2.message_fns.0._layers.0.weight"):
+        tower = "0" if gnn_type == "MultiHeadAttention" else "2"
+        for n in ("gnn.gnn_blocks.0.alpha", "init_node_proj.weight", f"gnn.gnn_blocks.1.mp_layers.{tower}.message_fns.0._layers.0.weight"):
             out[f"{gnn_type}::grad::{n}"] = params[n].grad.numpy()
         print(gnn_type, z.shape, len(names), "tensors; msg_out_projection", tuple(params["gnn.gnn_blocks.0.msg_out_projection.weight"].shape))
     out["meta"] = np.array([task_id, n_s, n_q, layers])

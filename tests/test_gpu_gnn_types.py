@@ -1,5 +1,5 @@
-"""-m gpu parity of the non-default tower GNN types (`--gnn_type MultiAggr`, `Plain`; fs_mol/modules/gnn.py:421-447,
-152-165, 197-240) against fixtures produced by the reference's own GraphFeatureExtractor
+"""-m gpu parity of the non-default GNN types (`--gnn_type MultiAggr`, `Plain`, `MultiHeadAttention`;
+fs_mol/modules/gnn.py:409-447, 152-165, 197-240, 268-387) against fixtures produced by the reference's own GraphFeatureExtractor
 (tests/golden/make_golden_gnn_types.py): features <= 1e-4 relative, per-tensor gradient norms and probe dots of a fixed
 probe loss <= 1e-3 (fp32 against fp32, 87 tensors)."""
 import os
@@ -22,7 +22,7 @@ def rel(a, b):
     return float(np.abs(a - b).max() / max(np.abs(b).max(), 1e-30))
 
 
-@pytest.mark.parametrize("gnn_type", ["MultiAggr", "Plain"])
+@pytest.mark.parametrize("gnn_type", ["MultiAggr", "Plain", "MultiHeadAttention"])
 def test_gnn_type_features_and_gradients(cuda_device, golden_dir, gnn_type):
     from adkf_ift_b200 import dkt, synthetic, task_batch
     from adkf_ift_b200.adaptive_dkt import ADKTModelTrainerConfig
@@ -55,14 +55,13 @@ def test_gnn_type_features_and_gradients(cuda_device, golden_dir, gnn_type):
     e_dot = (np.abs(dots - ref_d) / np.maximum(ref_n, 1e-3 * ref_n.max()) / np.sqrt([params[n].numel() for n in names])).max()
     print(gnn_type, "max rel grad-norm err", e_norm, "max probe-dot err", e_dot)
     assert e_norm < 1e-3 and e_dot < 1e-3
-    for n in ("gnn.gnn_blocks.0.alpha", "init_node_proj.weight", "gnn.gnn_blocks.1.mp_layers.2.message_fns.0._layers.0.weight"):
+    tower = "0" if gnn_type == "MultiHeadAttention" else "2"
+    for n in ("gnn.gnn_blocks.0.alpha", "init_node_proj.weight", f"gnn.gnn_blocks.1.mp_layers.{tower}.message_fns.0._layers.0.weight"):
         got, ref = params[n].grad.cpu().numpy(), g[f"{gnn_type}::grad::{n}"]
         assert rel(got, ref) < 1e-3 or np.abs(got - ref).max() < 1e-5 * ref_n.max(), (n, rel(got, ref))
 
 
-def test_unknown_and_unbuilt_gnn_types(cuda_device):
+def test_unknown_gnn_type(cuda_device):
     from adkf_ift_b200.feature_extractor import GraphFeatureExtractor, cli_default_config
     with pytest.raises(ValueError):
         GraphFeatureExtractor(cli_default_config(2, "NoSuchType"))
-    with pytest.raises(NotImplementedError):
-        GraphFeatureExtractor(cli_default_config(2, "MultiHeadAttention"))
