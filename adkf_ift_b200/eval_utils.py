@@ -34,6 +34,11 @@ class FSMolTask:                    # fs_mol/data/fsmol_task.py:100-117
         neg = [s for s in self.samples if not s.bool_label]
         return pos, neg
 
+    @staticmethod
+    def load_from_file(path) -> "FSMolTask":          # fs_mol/data/fsmol_task.py:108-144
+        from .fsmol_dataset import load_task_from_file
+        return load_task_from_file(str(path))
+
 
 class SamplingException(Exception):
     def __init__(self, task_name: str, num_samples: int, num_train: int, num_valid: int = 0, num_test: Optional[int] = None):

@@ -207,3 +207,54 @@ def test_stratified_sampler_and_eval_draws(tmp_path):
     assert list(rows[0].keys())[:6] == ["num_train_requested", "num_train", "fraction_positive_train", "num_test",
                                         "fraction_positive_test", "seed"]
     assert abs(float(rows[0]["delta_auprc"]) - (0.6 - res[name][0].fraction_pos_test)) < 1e-12
+
+
+def test_fsmol_on_disk_format_round_trip(tmp_path):
+    """`<task>.jsonl.gz` files (fsmol_task.py:108-144) -> FSMolDataset.from_directory (fsmol_dataset.py:66-118) -> the same
+    arrays, dtypes and batcher output as the in-memory tasks; fold ordering, task-list subset selection, repeat."""
+    import json
+    from adkf_ift_b200 import dkt, eval_utils as E, fsmol_dataset as D, synthetic
+    src = synthetic.SyntheticFSMolDataset(num_train_tasks=3, num_valid_tasks=2, num_test_tasks=2, molecules_per_task=20)
+    names = {}
+    for fold, sub in ((E.DataFold.TRAIN, "train"), (E.DataFold.VALIDATION, "valid"), (E.DataFold.TEST, "test")):
+        names[sub] = []
+        for task in src.get_task_reading_iterable(fold):
+            D.write_task_to_file(task, str(tmp_path / sub / f"{task.name}.jsonl.gz"))
+            names[sub].append(task.name)
+    ds = D.FSMolDataset.from_directory(str(tmp_path), num_workers=2, seed=0)
+    assert [ds.get_num_fold_tasks(f) for f in E.DataFold] == [3, 2, 2]
+    assert ds.get_task_names(E.DataFold.TEST) == sorted(names["test"])
+    got = {t.name: t for t in ds.get_task_reading_iterable(E.DataFold.TEST)}
+    for want in src.get_task_reading_iterable(E.DataFold.TEST):
+        t = got[want.name]
+        assert len(t.samples) == len(want.samples)
+        for a, b in zip(t.samples, want.samples):
+            assert (a.smiles, a.bool_label, a.task_name) == (b.smiles, b.bool_label, b.task_name)
+            assert a.numeric_label == b.numeric_label
+            assert a.fingerprint.dtype == np.int32 and np.array_equal(a.fingerprint, b.fingerprint)
+            assert a.descriptors.dtype == np.float32 and np.array_equal(a.descriptors, b.descriptors)
+            assert a.graph.node_features.dtype == np.float32 and np.array_equal(a.graph.node_features, b.graph.node_features)
+            assert all(x.dtype == np.int64 and x.shape[1] == 2 and np.array_equal(x, y)
+                       for x, y in zip(a.graph.adjacency_lists, b.graph.adjacency_lists))
+        # through the sampler and the DKT batcher: identical integer arrays and features
+        s1 = E.StratifiedTaskSampler(8, 0.0, None).sample(t, seed=1)
+        s2 = E.StratifiedTaskSampler(8, 0.0, None).sample(want, seed=1)
+        b1 = dkt.task_sample_to_dkt_task_sample(s1, dkt.get_dkt_batcher(max_num_graphs=64), False).batches[0]
+        b2 = dkt.task_sample_to_dkt_task_sample(s2, dkt.get_dkt_batcher(max_num_graphs=64), False).batches[0]
+        for x, y in zip(b1.support_features.adjacency_lists, b2.support_features.adjacency_lists):
+            assert np.array_equal(x, y)
+        assert np.array_equal(b1.query_features.fingerprints, b2.query_features.fingerprints)
+        assert np.array_equal(b1.support_features.node_features, b2.support_features.node_features)
+    # training fold: every task once per epoch, repeat keeps going
+    it = iter(ds.get_task_reading_iterable(E.DataFold.TRAIN, repeat=True))
+    seen = [next(it).name for _ in range(6)]
+    assert sorted(seen[:3]) == sorted(names["train"]) and sorted(seen[3:]) == sorted(names["train"])
+    # task-list subset (datasets/fsmol-0.1.json style)
+    with open(tmp_path / "tasks.json", "w") as f:
+        json.dump({"train": names["train"][:1], "valid": [], "test": names["test"][1:]}, f)
+    sub = D.FSMolDataset.from_directory(str(tmp_path), task_list_file=str(tmp_path / "tasks.json"))
+    assert sub.get_task_names(E.DataFold.TRAIN) == names["train"][:1] and sub.get_num_fold_tasks(E.DataFold.VALIDATION) == 0
+    assert E.FSMolTask.load_from_file(tmp_path / "test" / f"{names['test'][0]}.jsonl.gz").name == names["test"][0]
+    # an empty adjacency list stays a [0,2] int64 array
+    empty = [m for t in got.values() for m in t.samples for a in m.graph.adjacency_lists if a.shape[0] == 0]
+    assert all(a.shape == (0, 2) for m in empty for a in m.graph.adjacency_lists if a.shape[0] == 0)
