@@ -29,12 +29,14 @@
 // operand combinations (A,B) = (K,K) forward, (K,T) input gradient, (T,T) weight gradient (split-K over the node dimension,
 // deterministic two-pass reduction).
 //
-// CTA = persistent over 128 x 128 output tiles, 16 warps, two smem rings (raw: TMA -> splitter, 2 x 32 KB; split: splitter -> MMA,
-// 2 x 64 KB) + 32 KB of epilogue staging:
+// CTA = persistent over 128 x 128 output tiles, 16 warps, two smem rings (raw: TMA -> splitter, 4 x 32 KB; split B: splitter ->
+// MMA, 2 x 32 KB) + 32 KB of epilogue staging; the split A operand lives in tensor memory (2 stages x 64 columns):
 //   warp 0     TMA producer      cp.async.bulk.tensor.2d -> raw ring
-//   warp 1     MMA issuer        one elected lane: 4 k-steps x 3 tcgen05.mma per k-block, tcgen05.commit frees the split stage
-//   warp 2     TMEM allocator    512 columns: big[2] x 128, small x 128
-//   warps 4-7  splitter          raw tile -> hi/lo K-major tiles (generic proxy -> fence.proxy.async)
+//   warp 1     MMA issuer        one elected lane: 4 k-steps x 3 tcgen05.mma (A from TMEM, B from smem) per k-block,
+//                                tcgen05.commit frees the split stage
+//   warp 2     TMEM allocator    512 columns: big[2] x 128, small x 128, A operand 2 x (32 hi + 32 lo)
+//   warps 4-7  splitter          raw A tile -> hi/lo rows in TMEM (tcgen05.st); raw B tile -> hi/lo K-major smem tiles
+//                                (generic proxy -> fence.proxy.async)
 //   warps 8-15 drain + epilogue  tcgen05.ld of the accumulator rows (warp w owns TMEM lanes 32(w%4).., 64 columns each),
 //              RN accumulation in registers, fused epilogue, stores.
 // Every mbarrier wait is bounded (trap after ~2^28 polls) so that a protocol bug cannot hang the device.
@@ -47,15 +49,17 @@
 namespace adkf {
 
 constexpr int kBM = 128, kBN = 128, kBK = 32;        // tile; 32 floats = 128 B = one swizzle row
-constexpr int kRaw = 2;                              // raw ring depth (TMA destination: A_raw, B_raw)
-constexpr int kSplit = 2;                            // split ring depth (MMA source: A_hi, B_hi, A_lo, B_lo)
+constexpr int kRaw = 4;                              // raw ring depth (TMA destination: A_raw, B_raw)
+constexpr int kSplit = 2;                            // split ring depth (MMA source: B_hi, B_lo in smem; A_hi, A_lo in TMEM)
 constexpr int kTileBytes = kBM * kBK * 4;            // 16 KB
 constexpr int kRawBytes = 2 * kTileBytes;
-constexpr int kSplitBytes = 4 * kTileBytes;
+constexpr int kSplitBytes = 2 * kTileBytes;
 constexpr int kRingBytes = kRaw * kRawBytes + kSplit * kSplitBytes;   // 192 KB
 constexpr int kStageBytes = 8 * 4096;                // epilogue staging: 8 drain warps x (32 rows x 32 columns) fp32
 constexpr int kGemmThreads = 512;
-constexpr int kTmemCols = 512;                       // big[0], big[1], small (128 fp32 columns each); power of two
+constexpr int kTmemCols = 512;                       // big[0], big[1], small (128 fp32 columns each), A operand 2 x 64
+constexpr int kSmallCol = 2 * kBN;                   // first TMEM column of the correction accumulator
+constexpr int kAopCol = 3 * kBN;                     // first TMEM column of the A operand stages (hi 32 + lo 32 columns each)
 constexpr int kGroup = 4;                            // k-blocks accumulated in TMEM between two drains
 constexpr size_t kGemmSmem = (size_t)kRingBytes + kStageBytes + 1024 /*align*/ + 256 /*barriers*/;
 
@@ -103,6 +107,27 @@ __device__ __forceinline__ void umma_tf32(uint32_t tmem_d, uint64_t adesc, uint6
         ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(acc)
         : "memory");
 }
+// A operand in tensor memory (lane = row of the tile, one tf32 per 32-bit column, 8 columns per MMA), B through its
+// shared-memory descriptor
+__device__ __forceinline__ void umma_tf32_ts(uint32_t tmem_d, uint32_t tmem_a, uint64_t bdesc, uint32_t idesc, uint32_t acc) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::tf32 [%0], [%1], %2, %3, p;\n\t}"
+        ::"r"(tmem_d), "r"(tmem_a), "l"(bdesc), "r"(idesc), "r"(acc)
+        : "memory");
+}
+__device__ __forceinline__ void tmem_st32(uint32_t taddr, const uint32_t (&r)[32]) {
+    asm volatile(
+        "tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,%17,%18,%19,%20,"
+        "%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31,%32};"
+        ::"r"(taddr), "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]), "r"(r[8]), "r"(r[9]),
+          "r"(r[10]), "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15]), "r"(r[16]), "r"(r[17]), "r"(r[18]), "r"(r[19]),
+          "r"(r[20]), "r"(r[21]), "r"(r[22]), "r"(r[23]), "r"(r[24]), "r"(r[25]), "r"(r[26]), "r"(r[27]), "r"(r[28]), "r"(r[29]),
+          "r"(r[30]), "r"(r[31])
+        : "memory");
+}
+__device__ __forceinline__ void tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
 __device__ __forceinline__ void umma_commit(uint32_t bar) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
 }
@@ -149,7 +174,7 @@ struct GemmEpilogue {
     // writes D + b*d_off (+ bias + b*bias_off): column blocks / row blocks of the SAME 2-D arrays, one tensor map each.
     int splits;
     int gx, gy, ntiles;   // persistent tile walk: tile -> (bx = tile % gx, by = (tile / gx) % gy, bz = tile / (gx gy))
-    int debug;            // development probe (ADKF_GEMM_DEBUG): 1 = splitter skips the split, 2 = MMA warp skips the MMAs
+    int debug;            // development probe (ADKF_GEMM_DEBUG): 1 = splitter skips the split (128 only A, 256 only B), 2 = no MMAs
     int a_mn, a_k, b_mn, b_k;
     int64_t d_off, bias_off;
     // gram
@@ -226,6 +251,51 @@ __device__ __forceinline__ void split_tile(const unsigned char* __restrict__ raw
             }
         }
     }
+}
+
+// The A operand goes to TENSOR memory instead of shared memory: splitter thread t (warp 4 + t/32, which may touch TMEM lanes
+// 32 (t/32)..) owns row t of the tile, splits its 32 k values and writes hi to 32 TMEM columns and lo to the next 32
+// (tcgen05.st 32x32b: lane = row, register i = column i).  That removes the A_hi / A_lo stores and the three A reads per
+// k-step of the MMAs from the shared-memory pipe, which is what bounded this kernel (ncu r1e: smem pipe 95%+; 224 KB of
+// shared-memory traffic per k-block against 1107 tensor-pipe cycles -> 144 KB).
+//   TR = false: the raw tile is the SWIZZLE_128B box (row t = 128 B, logical chunk j at physical chunk j ^ (t & 7)); the 8
+//               lanes of a quarter warp read 8 different chunks -> conflict-free.
+//   TR = true : the raw tile is [32 k][128 mn]; lane reads of one k are 32 consecutive floats.
+// mu_k (gram centring, else nullptr) points at the task mean for this k-block; kleft = K - k0.
+template <bool TR>
+__device__ __forceinline__ void split_rows_to_tmem(const unsigned char* __restrict__ raw, uint32_t taddr, int t,
+                                                   const float* __restrict__ mu_k, int kleft) {
+    float x[kBK];
+    if (!TR) {
+        const float4* __restrict__ r4 = reinterpret_cast<const float4*>(raw) + t * 8;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            const float4 v = r4[j ^ (t & 7)];
+            x[4 * j] = v.x; x[4 * j + 1] = v.y; x[4 * j + 2] = v.z; x[4 * j + 3] = v.w;
+        }
+    } else {
+        const float* __restrict__ rf = reinterpret_cast<const float*>(raw) + t;
+#pragma unroll
+        for (int k = 0; k < kBK; ++k) x[k] = rf[k * kBM];
+    }
+    if (mu_k != nullptr) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+            if (4 * j + 3 < kleft) {
+                const float4 m = *reinterpret_cast<const float4*>(mu_k + 4 * j);
+                x[4 * j] -= m.x; x[4 * j + 1] -= m.y; x[4 * j + 2] -= m.z; x[4 * j + 3] -= m.w;
+            }
+    }
+    uint32_t hi[kBK], lo[kBK];
+#pragma unroll
+    for (int k = 0; k < kBK; ++k) {
+        const float h = tf32_hi(x[k]);
+        hi[k] = __float_as_uint(h);
+        lo[k] = __float_as_uint(x[k] - h);
+    }
+    tmem_st32(taddr, hi);
+    tmem_st32(taddr + kBK, lo);
+    tmem_st_wait();
 }
 
 // One output tile of the persistent loop: everything a warp role needs, a pure function of the tile index (so every
@@ -320,7 +390,7 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
-    const uint32_t tmem_acc = *tmem_slot;     // columns: big[0] 0..127, big[1] 128..255, small[0] 256..383, small[1] 384..511
+    const uint32_t tmem_acc = *tmem_slot;     // columns: big[0] 0..127, big[1] 128..255, small 256..383, A operand 384..511
 
     if (warp == 0) {
         // ===== TMA producer =====
@@ -352,8 +422,7 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
         for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
             const TileCoord c = tile_coord(ep, tile);
             if (c.skip) continue;
-            const int sb = tl & 1;
-            mbar_wait(tileempty_bar(sb), ((tl >> 1) & 1) ^ 1);             // small[sb] drained two tiles ago
+            mbar_wait(tileempty_bar(0), (tl & 1) ^ 1);                     // small read out by the drain warps of the last tile
             for (int i = 0; i < c.nk; ++i, ++it) {
                 const int s = it % kSplit;
                 const uint32_t ph = (it / kSplit) & 1;
@@ -366,15 +435,16 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
                 tc_fence_after();
                 if (lane == 0) {
                     const uint32_t st = split_base + s * kSplitBytes;
-                    const uint64_t a_hi = smem_desc_k128(st), b_hi = smem_desc_k128(st + kTileBytes);
-                    const uint64_t a_lo = smem_desc_k128(st + 2 * kTileBytes), b_lo = smem_desc_k128(st + 3 * kTileBytes);
-                    const uint32_t acc_big = tmem_acc + (uint32_t)(b * kBN), acc_small = tmem_acc + (uint32_t)((2 + sb) * kBN);
+                    const uint64_t b_hi = smem_desc_k128(st), b_lo = smem_desc_k128(st + kTileBytes);
+                    const uint32_t a_hi = tmem_acc + (uint32_t)(kAopCol + s * 2 * kBK), a_lo = a_hi + kBK;
+                    const uint32_t acc_big = tmem_acc + (uint32_t)(b * kBN), acc_small = tmem_acc + (uint32_t)kSmallCol;
 #pragma unroll
-                    for (int k = 0; k < ((ep.debug & 2) ? 0 : kBK / 8); ++k) {   // UMMA_K = 8 tf32 = 32 B = +2 in the address field
-                        const uint64_t adv = (uint64_t)(2 * k);
-                        umma_tf32(acc_small, a_lo + adv, b_hi + adv, kIdescTf32, (i | k) ? 1u : 0u);
-                        umma_tf32(acc_small, a_hi + adv, b_lo + adv, kIdescTf32, 1u);
-                        umma_tf32(acc_big, a_hi + adv, b_hi + adv, kIdescTf32, (group_first && k == 0) ? 0u : 1u);
+                    for (int k = 0; k < ((ep.debug & 2) ? 0 : kBK / 8); ++k) {   // UMMA_K = 8 tf32: 8 TMEM columns of A, 32 B of B
+                        const uint64_t adv = (uint64_t)(2 * k);                  // (+2 in the descriptor's address field)
+                        const uint32_t ak = (uint32_t)(8 * k);
+                        umma_tf32_ts(acc_small, a_lo + ak, b_hi + adv, kIdescTf32, (i | k) ? 1u : 0u);
+                        umma_tf32_ts(acc_small, a_hi + ak, b_lo + adv, kIdescTf32, 1u);
+                        umma_tf32_ts(acc_big, a_hi + ak, b_hi + adv, kIdescTf32, (group_first && k == 0) ? 0u : 1u);
                     }
                     umma_commit(empty_bar(s));                             // frees the split stage when these MMAs retire
                     if (group_last) umma_commit(accfull_bar(b));
@@ -388,6 +458,7 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
         // ===== splitter (hi/lo, transposing where the operand is not K-major) =====
         const int t = threadIdx.x - 128;                               // 0..127
         const int chunk = (t & 7) ^ ((t >> 3) & 7);                    // logical 16 B chunk of this thread's float4s
+        const uint32_t tmem_a = tmem_acc + ((uint32_t)((warp - 4) * 32) << 16) + (uint32_t)kAopCol;
         uint32_t it = 0;
         for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
             const TileCoord c = tile_coord(ep, tile);
@@ -404,9 +475,13 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
                 const unsigned char* rw = base_ptr + (size_t)r * kRawBytes;
                 unsigned char* st = split_ptr + (size_t)s * kSplitBytes;
                 if (!(ep.debug & 1)) {
-                    split_tile<TA>(rw, st, st + 2 * kTileBytes, t, mu4);
-                    split_tile<TB>(rw + kTileBytes, st + kTileBytes, st + 3 * kTileBytes, t, mu4);
+                    const int k0 = (c.kb0 + i) * kBK;
+                    if (!(ep.debug & 128))
+                        split_rows_to_tmem<TA>(rw, tmem_a + (uint32_t)(s * 2 * kBK), t,
+                                               ep.mode == 1 ? ep.mu + (size_t)c.task * ep.K + k0 : nullptr, ep.K - k0);
+                    if (!(ep.debug & 256)) split_tile<TB>(rw + kTileBytes, st, st + kTileBytes, t, mu4);
                 }
+                tc_fence_before();                                     // the TMEM stores are ordered before the arrive below
                 fence_async_smem();                                    // generic-proxy writes -> visible to the MMA (async proxy)
                 __syncwarp();
                 if (lane == 0) {
@@ -426,7 +501,6 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
         for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
             const TileCoord c = tile_coord(ep, tile);
             if (c.skip) continue;
-            const int sb = tl & 1;
             float acc[64];
 #pragma unroll
             for (int j = 0; j < 64; ++j) acc[j] = 0.f;
@@ -450,13 +524,13 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
 #pragma unroll
             for (int c0 = 0; c0 < ((ep.debug & 32) ? 0 : 64); c0 += 16) {   // the small correction accumulator, once per tile
                 float v[16];
-                tmem_ld16(trow + (uint32_t)((2 + sb) * kBN) + c0, v);
+                tmem_ld16(trow + (uint32_t)kSmallCol + c0, v);
 #pragma unroll
                 for (int j = 0; j < 16; ++j) acc[c0 + j] += v[j];
             }
             tc_fence_before();
             __syncwarp();
-            if (lane == 0) mbar_arrive(tileempty_bar(sb));
+            if (lane == 0) mbar_arrive(tileempty_bar(0));
             gc += (uint32_t)ngroups;
             ++tl;
 

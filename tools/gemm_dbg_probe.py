@@ -23,4 +23,6 @@ t1 = bench(lambda: ops.gemm_tf32x3_batched(XG, False, 0, 64, W2, False, 3 * 192,
 t2 = bench(lambda: ops.gemm_tf32x3(x128, False, w1, False, bb, "leaky_relu"))
 t3 = bench(lambda: ops.gemm_tf32x3(x128, False, wT, True))
 t4 = bench(lambda: ops.gemm_tf32x3(x1408, False, wr, False, br, "relu"))
-print(f"DEBUG={os.environ.get('ADKF_GEMM_DEBUG','0'):>3s} pna_fwd {t1:.3f}  boom1_fwd {t2:.3f}  proj_dX {t3:.3f}  readout_hidden {t4:.3f} ms")
+x3072, wp = torch.randn(V, 3072, device=dev), torch.randn(128, 3072, device=dev)
+t5 = bench(lambda: ops.gemm_tf32x3(x3072, False, wp, False, None, None))
+print(f"DEBUG={os.environ.get('ADKF_GEMM_DEBUG','0'):>3s} pna_fwd {t1:.3f}  boom1_fwd {t2:.3f}  proj_dX {t3:.3f}  readout_hidden {t4:.3f}  proj_fwd {t5:.3f} ms")
