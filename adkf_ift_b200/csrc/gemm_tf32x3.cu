@@ -56,7 +56,7 @@ constexpr int kRawBytes = 2 * kTileBytes;
 constexpr int kSplitBytes = 2 * kTileBytes;
 constexpr int kRingBytes = kRaw * kRawBytes + kSplit * kSplitBytes;   // 192 KB
 constexpr int kStageBytes = 8 * 4096;                // epilogue staging: 8 drain warps x (32 rows x 32 columns) fp32
-constexpr int kGemmThreads = 512;
+constexpr int kGemmThreads = 640;                    // 5 warpgroups: control, A splitter, B splitter, 2 x drain
 constexpr int kTmemCols = 512;                       // big[0], big[1], small (128 fp32 columns each), A operand 2 x 64
 constexpr int kSmallCol = 2 * kBN;                   // first TMEM column of the correction accumulator
 constexpr int kAopCol = 3 * kBN;                     // first TMEM column of the A operand stages (hi 32 + lo 32 columns each)
@@ -128,6 +128,10 @@ __device__ __forceinline__ void tmem_st32(uint32_t taddr, const uint32_t (&r)[32
         : "memory");
 }
 __device__ __forceinline__ void tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
+// Register budget per warpgroup (setmaxnreg): the kernel starts with 96 registers per thread (640 threads); the control
+// and B-splitter warpgroups give registers back, the two drain warpgroups (64 accumulators per thread) take them.
+template <int N> __device__ __forceinline__ void reg_dec() { asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(N)); }
+template <int N> __device__ __forceinline__ void reg_inc() { asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(N)); }
 __device__ __forceinline__ void umma_commit(uint32_t bar) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
 }
@@ -368,10 +372,10 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
     if (threadIdx.x == 0) {
         for (int r = 0; r < kRaw; ++r) {
             mbar_init(rawfull_bar(r), 1);
-            mbar_init(rawempty_bar(r), 4);  // one arrive per splitter warp
+            mbar_init(rawempty_bar(r), 8);  // one arrive per splitter warp (4 A + 4 B)
         }
         for (int s = 0; s < kSplit; ++s) {
-            mbar_init(conv_bar(s), 4);      // one arrive per splitter warp
+            mbar_init(conv_bar(s), 8);      // one arrive per splitter warp
             mbar_init(empty_bar(s), 1);     // tcgen05.commit
         }
         for (int b = 0; b < 2; ++b) {
@@ -392,8 +396,10 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
     tc_fence_after();
     const uint32_t tmem_acc = *tmem_slot;     // columns: big[0] 0..127, big[1] 128..255, small 256..383, A operand 384..511
 
+    // (each setmaxnreg sits at the top of its role's branch so that the code it governs is dominated by it)
     if (warp == 0) {
         // ===== TMA producer =====
+        reg_dec<40>();
         if (lane == 0) {
             uint32_t it = 0;
             for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
@@ -418,6 +424,7 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
         }
     } else if (warp == 1) {
         // ===== MMA issuer =====
+        reg_dec<40>();
         uint32_t it = 0, gc = 0, tl = 0;
         for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
             const TileCoord c = tile_coord(ep, tile);
@@ -454,11 +461,38 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
             gc += (uint32_t)((c.nk + kGroup - 1) / kGroup);
             ++tl;
         }
-    } else if (warp >= 4 && warp < 8) {
-        // ===== splitter (hi/lo, transposing where the operand is not K-major) =====
+    } else if (warp < 4) {
+        reg_dec<40>();                                                 // TMEM allocator / spare warp: the whole warpgroup must execute it
+    } else if (warp < 8) {
+        // ===== A splitter: row t of the raw A tile -> hi / lo in tensor memory (warp w may touch TMEM lanes 32 (w % 4)..) =====
         const int t = threadIdx.x - 128;                               // 0..127
-        const int chunk = (t & 7) ^ ((t >> 3) & 7);                    // logical 16 B chunk of this thread's float4s
         const uint32_t tmem_a = tmem_acc + ((uint32_t)((warp - 4) * 32) << 16) + (uint32_t)kAopCol;
+        uint32_t it = 0;
+        for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+            const TileCoord c = tile_coord(ep, tile);
+            if (c.skip) continue;
+            for (int i = 0; i < c.nk; ++i, ++it) {
+                const int r = it % kRaw, s = it % kSplit;
+                const int k0 = (c.kb0 + i) * kBK;
+                mbar_wait(rawfull_bar(r), (it / kRaw) & 1);
+                mbar_wait(empty_bar(s), ((it / kSplit) & 1) ^ 1);      // the MMAs that read this TMEM stage have retired
+                tc_fence_after();
+                if (!(ep.debug & (1 | 128)))
+                    split_rows_to_tmem<TA>(base_ptr + (size_t)r * kRawBytes, tmem_a + (uint32_t)(s * 2 * kBK), t,
+                                           ep.mode == 1 ? ep.mu + (size_t)c.task * ep.K + k0 : nullptr, ep.K - k0);
+                tc_fence_before();                                     // the TMEM stores are ordered before the arrive below
+                __syncwarp();
+                if (lane == 0) {
+                    mbar_arrive(conv_bar(s));
+                    mbar_arrive(rawempty_bar(r));
+                }
+            }
+        }
+    } else if (warp < 12) {
+        // ===== B splitter: raw B tile -> hi / lo K-major smem tiles (transposing where the operand is not K-major) =====
+        reg_dec<72>();
+        const int t = threadIdx.x - 256;                               // 0..127
+        const int chunk = (t & 7) ^ ((t >> 3) & 7);                    // logical 16 B chunk of this thread's float4s
         uint32_t it = 0;
         for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
             const TileCoord c = tile_coord(ep, tile);
@@ -472,16 +506,9 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
                 }
                 mbar_wait(rawfull_bar(r), (it / kRaw) & 1);
                 mbar_wait(empty_bar(s), ((it / kSplit) & 1) ^ 1);
-                const unsigned char* rw = base_ptr + (size_t)r * kRawBytes;
                 unsigned char* st = split_ptr + (size_t)s * kSplitBytes;
-                if (!(ep.debug & 1)) {
-                    const int k0 = (c.kb0 + i) * kBK;
-                    if (!(ep.debug & 128))
-                        split_rows_to_tmem<TA>(rw, tmem_a + (uint32_t)(s * 2 * kBK), t,
-                                               ep.mode == 1 ? ep.mu + (size_t)c.task * ep.K + k0 : nullptr, ep.K - k0);
-                    if (!(ep.debug & 256)) split_tile<TB>(rw + kTileBytes, st, st + kTileBytes, t, mu4);
-                }
-                tc_fence_before();                                     // the TMEM stores are ordered before the arrive below
+                if (!(ep.debug & (1 | 256)))
+                    split_tile<TB>(base_ptr + (size_t)r * kRawBytes + kTileBytes, st, st + kTileBytes, t, mu4);
                 fence_async_smem();                                    // generic-proxy writes -> visible to the MMA (async proxy)
                 __syncwarp();
                 if (lane == 0) {
@@ -490,10 +517,11 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
                 }
             }
         }
-    } else if (warp >= 8) {
+    } else {
         // ===== drain (RN accumulation of the TMEM partial sums in registers), then epilogue =====
+        reg_inc<136>();
         const int q = warp & 3;                                        // TMEM lane quarter this warp may access
-        const int half = (warp - 8) >> 2;                              // which 64 accumulator columns
+        const int half = (warp - 12) >> 2;                             // which 64 accumulator columns
         const int r_local = q * 32 + lane;
         const uint32_t trow = tmem_acc + ((uint32_t)(q * 32) << 16) + (uint32_t)(half * 64);
         const int colbase = half * 64;
@@ -543,7 +571,7 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
                 float* out = ep.out + c.zslab * ep.split_stride + (int64_t)c.batch * ep.d_off;
                 const float* bias = (ep.bias != nullptr && !(ep.debug & 8)) ? ep.bias + (int64_t)c.batch * ep.bias_off : nullptr;
                 const bool vec_ok = (ep.ldo % 4 == 0) && ((reinterpret_cast<uintptr_t>(out) & 15) == 0);
-                float4* stg = reinterpret_cast<float4*>(stage_ptr + (size_t)(warp - 8) * 4096);
+                float4* stg = reinterpret_cast<float4*>(stage_ptr + (size_t)(warp - 12) * 4096);
                 const int ch = lane & 7, rsub = lane >> 3;
                 const int act = ep.act;
 #pragma unroll

@@ -47,6 +47,13 @@ class GraphIndex:
     type_sorted: Optional["TypeSortedEdges"] = None
 
 
+def _histogram(idx: torch.Tensor, bins: int) -> torch.Tensor:
+    """Counts of idx in [0, bins) without the device->host synchronisation torch.bincount does to size its output (the
+    step must stay asynchronous: a sync here drains the GPU once per step)."""
+    idx = idx.to(torch.int64)
+    return torch.zeros(bins, dtype=torch.int64, device=idx.device).scatter_add_(0, idx, torch.ones_like(idx))
+
+
 def build_graph_index(adjacency_lists: Sequence[torch.Tensor], num_nodes: int,
                       node_to_graph: Optional[torch.Tensor] = None, num_graphs: int = 0) -> GraphIndex:
     """adjacency_lists: 3 x [E_t, 2] int64 CUDA tensors exactly as the reference batcher emits them."""
@@ -70,7 +77,7 @@ def build_graph_index(adjacency_lists: Sequence[torch.Tensor], num_nodes: int,
     graph_ptr = None
     if node_to_graph is not None:
         # nodes of a graph are contiguous (fsmol_batcher.py:200-202): counts -> exclusive scan
-        counts = torch.bincount(node_to_graph, minlength=num_graphs)
+        counts = _histogram(node_to_graph, num_graphs)
         graph_ptr = torch.zeros(num_graphs + 1, **i32)
         graph_ptr[1:] = torch.cumsum(counts, 0).to(torch.int32)
     gi = GraphIndex(num_nodes, etot, rowptr, col_src[:etot], col_type[:etot], col_tgt[:etot], col_eid[:etot],
@@ -145,7 +152,7 @@ def _type_sorted(gi: GraphIndex, edges_per_type: Sequence[int]) -> TypeSortedEdg
     inv = torch.empty_like(perm)
     inv[perm] = torch.arange(E, device=perm.device)
     tptr = torch.zeros(3 * V + 1, dtype=torch.int32, device=perm.device)
-    tptr[1:] = torch.cumsum(torch.bincount(key, minlength=3 * V), 0).to(torch.int32)
+    tptr[1:] = torch.cumsum(_histogram(key, 3 * V), 0).to(torch.int32)
     off = [0]
     for e in edges_per_type:
         off.append(off[-1] + int(e))

@@ -41,6 +41,23 @@ def main():
           f"edges {tb.graph_index.num_edges} graphs {tb.num_graphs}")
     for k, t, c in rows[:40]:
         print(f"{t / 1e3:10.3f} ms {100 * t / tot:6.2f}% x{c:<5d} {k[:110]}")
+    # idle gaps of the device between consecutive kernels (where the host did not keep the stream fed)
+    evs = sorted(((e.time_range.start, e.time_range.end, e.name) for e in prof.events()
+                  if e.device_type == torch.autograd.DeviceType.CUDA and e.time_range.end > e.time_range.start), key=lambda x: x[0])
+    if evs:
+        span = evs[-1][1] - evs[0][0]
+        gaps = []
+        end = evs[0][1]
+        for i in range(1, len(evs)):
+            g = evs[i][0] - end
+            if g > 0:
+                gaps.append((g, evs[i - 1][2][:50], evs[i][2][:50], (evs[i][0] - evs[0][0]) / 1e3))
+            end = max(end, evs[i][1])
+        idle = sum(g[0] for g in gaps)
+        print(f"device span {span / 1e3:.2f} ms, idle between kernels {idle / 1e3:.2f} ms in {len(gaps)} gaps; "
+              f"gaps > 20 us: {sum(g[0] for g in gaps if g[0] > 20) / 1e3:.2f} ms")
+        for g in sorted(gaps, key=lambda x: -x[0])[:12]:
+            print(f"    {g[0]:8.1f} us at {g[3]:7.2f} ms  after {g[1]}  before {g[2]}")
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
     for _ in range(3):
