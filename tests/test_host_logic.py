@@ -103,9 +103,12 @@ def test_unsupported_configurations_fail_loudly():
                             ).normalizing_features
     with pytest.raises(NotImplementedError):
         ADKTModelTrainer(ADKTModelTrainerConfig(use_ard=True))
-    with pytest.raises(NotImplementedError):
+    # every GNN type of the reference is built (MultiHeadAttention included); unknown names raise like gnn.py:447
+    ADKTModelTrainer(ADKTModelTrainerConfig(graph_feature_extractor_config=GraphFeatureExtractorConfig(
+        gnn_config=GNNConfig(type="MultiHeadAttention", per_head_dim=64, intermediate_dim=1024, num_layers=2))))
+    with pytest.raises(ValueError):
         ADKTModelTrainer(ADKTModelTrainerConfig(graph_feature_extractor_config=GraphFeatureExtractorConfig(
-            gnn_config=GNNConfig(type="MultiHeadAttention", per_head_dim=64, intermediate_dim=1024, num_layers=2))))
+            gnn_config=GNNConfig(type="NoSuchMP", num_layers=2))))
 
 
 def test_checkpoint_roundtrip_and_reference_gp_keys(tmp_path):
