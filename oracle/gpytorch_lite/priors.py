@@ -25,6 +25,11 @@ class LogNormalPrior(Prior):
         lx = torch.log(x)
         return -lx - torch.log(scale) - 0.5 * math.log(2 * math.pi) - (lx - loc) ** 2 / (2 * scale ** 2)
 
+    @property
+    def mean(self):
+        """torch.distributions.LogNormal.mean = exp(loc + scale^2 / 2) (read by fs_mol/models/dkt.py:98)."""
+        return torch.exp(self.loc + 0.5 * self.scale ** 2)
+
 
 class NormalPrior(Prior):
     def __init__(self, loc, scale, validate_args=None, transform=None):
