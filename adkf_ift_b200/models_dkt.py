@@ -255,7 +255,11 @@ def gpst_test(train_fp: torch.Tensor, y_train: torch.Tensor, test_fp: torch.Tens
     likelihood = gp_utils.GaussianLikelihood().to(dev)
     model = gp_utils.ExactTanimotoGP(X_train, y_tr, likelihood, use_numeric_labels).to(dev)
     mll = gp_utils.ExactMarginalLogLikelihood(likelihood, model)
+    model.train()
+    likelihood.train()
     gp_utils.fit_gpytorch_scipy(mll)
+    model.eval()
+    likelihood.eval()
     preds: List[np.ndarray] = []
     with torch.no_grad():
         for i in range(0, X_test.shape[0], test_batch_size):
