@@ -366,8 +366,9 @@ class ADKTModelTrainer(ADKTModel):
         """One outer step on this rank's share of the meta-batch (adaptive_dkt_utils.py:352-413): hypergradients of
         the local tasks / global task count, all-reduce, clip, Adam."""
         flat = self._ensure_flat()
-        flat.zero_grad()
+        flat.release_grads()
         total = global_num_tasks if global_num_tasks is not None else tb.num_tasks * distributed.world_size()
         res = run_on_task_batch(self, tb, train=True, grad_scale=1.0 / total)
+        flat.gather_grads()
         self.reduce_and_update()
         return res

@@ -738,16 +738,28 @@ __global__ void splitk_reduce_kernel(const float* __restrict__ ws, int splits, i
 }
 }  // namespace adkf
 
-// split-K plan: only when the output has too few 128 x 128 tiles to fill the 148 SMs; every split gets >= 8 k-blocks
+// split-K plan.  The persistent kernel walks (tile, split) work items 148 at a time, so what matters is how full the LAST
+// wave is: e.g. 66 tiles x 5 splits = 330 items = 2.23 waves runs as 3 waves at 74%.  Cost model in k-block units
+// (one 128x128x32 k-block ~ 0.7 us per CTA): waves x (k-blocks per split + fixed tile cost) + the slab write/read of the
+// reduce pass; every split keeps >= 8 k-blocks.  Deterministic: the plan depends on the shape only.
+static int plan_splits_tiles(int64_t tiles, int nk) {
+    if (nk < 16 || tiles >= 4 * 148) return 1;
+    const int smax = std::min(nk / 8, 64);
+    double best = 1e300;
+    int best_s = 1;
+    for (int s = 1; s <= smax; ++s) {
+        const int per = (nk + s - 1) / s;
+        if ((nk + per - 1) / per != s) continue;                 // s would leave an empty split
+        const int64_t items = tiles * s;
+        const int64_t waves = (items + 147) / 148;
+        double t = (double)waves * (per + 6.0);
+        if (s > 1) t += 4.0 + 0.036 * (double)items;
+        if (t < best * 0.98) { best = t; best_s = s; }           // prefer fewer splits unless >2% better
+    }
+    return best_s;
+}
 static int plan_splits(int64_t M, int32_t N, int32_t K) {
-    const int64_t tiles = ((M + kBM - 1) / kBM) * ((N + kBN - 1) / kBN);
-    const int nk = (K + kBK - 1) / kBK;
-    if (tiles >= 148 || nk < 16) return 1;
-    int splits = (int)((2 * 148 + tiles - 1) / tiles);
-    if (splits > nk / 8) splits = nk / 8;
-    if (splits < 1) splits = 1;
-    const int per = (nk + splits - 1) / splits;
-    return (nk + per - 1) / per;
+    return plan_splits_tiles(((M + kBM - 1) / kBM) * ((N + kBN - 1) / kBN), (K + kBK - 1) / kBK);
 }
 
 extern "C" int64_t adkf_gemm_splitk_ws_floats(int64_t M, int32_t N, int32_t K) {
@@ -770,17 +782,8 @@ static int gemm_launch(const float* A, int transA, int64_t lda, int64_t a_slow, 
     rc = make_map_2d(&mb, B, transB ? b_fast : b_slow, transB ? b_slow : b_fast, ldb, transB ? 1 : 0);
     if (rc) return rc;
     int splits = (batch > 1) ? 1 : plan_splits(M, N, K);
-    if (batch > 1 && splitk_ws != nullptr) {        // batched split-K: same plan for every batch, ws = [batch][splits][M][N]
-        const int64_t tiles = ((M + kBM - 1) / kBM) * ((N + kBN - 1) / kBN) * batch;
-        const int nk0 = (K + kBK - 1) / kBK;
-        if (tiles < 148 && nk0 >= 16) {
-            splits = (int)((2 * 148 + tiles - 1) / tiles);
-            if (splits > nk0 / 8) splits = nk0 / 8;
-            if (splits < 1) splits = 1;
-            const int per = (nk0 + splits - 1) / splits;
-            splits = (nk0 + per - 1) / per;
-        }
-    }
+    if (batch > 1 && splitk_ws != nullptr)          // batched split-K: same plan for every batch, ws = [batch][splits][M][N]
+        splits = plan_splits_tiles(((M + kBM - 1) / kBM) * ((N + kBN - 1) / kBN) * batch, (K + kBK - 1) / kBK);
     if (splits > 1 && (splitk_ws == nullptr || splitk_ws_floats < (int64_t)splits * batch * M * N || bias != nullptr ||
                        act != 0 || ldd != N))
         splits = 1;                                                  // no workspace (or fused epilogue): single pass
@@ -834,14 +837,7 @@ extern "C" int adkf_gemm_tf32x3(const float* A, int32_t transA, int64_t lda, con
 }
 
 extern "C" int64_t adkf_gemm_batched_splitk_ws_floats(int64_t M, int32_t N, int32_t K, int32_t batch) {
-    const int64_t tiles = ((M + kBM - 1) / kBM) * ((N + kBN - 1) / kBN) * batch;
-    const int nk0 = (K + kBK - 1) / kBK;
-    if (tiles >= 148 || nk0 < 16) return 0;
-    int splits = (int)((2 * 148 + tiles - 1) / tiles);
-    if (splits > nk0 / 8) splits = nk0 / 8;
-    if (splits < 1) splits = 1;
-    const int per = (nk0 + splits - 1) / splits;
-    splits = (nk0 + per - 1) / per;
+    const int splits = plan_splits_tiles(((M + kBM - 1) / kBM) * ((N + kBN - 1) / kBN) * batch, (K + kBK - 1) / kBK);
     return splits > 1 ? (int64_t)splits * batch * M * N : 0;
 }
 

@@ -75,6 +75,26 @@ class FlatParams:
             if p.grad is None or p.grad.data_ptr() != self.grad[off:off + n].data_ptr():
                 p.grad = self.grad[off:off + n].view_as(p.data)
 
+    def release_grads(self):
+        """Before a backward pass: zero the flat gradient and detach the per-parameter views, so that autograd hands
+        over each freshly computed gradient instead of launching one `grad += g` kernel per tensor (375 launches)."""
+        self.grad.zero_()
+        for p in self.params:
+            p.grad = None
+
+    def gather_grads(self):
+        """After the backward pass: one multi-tensor copy of the per-parameter gradients into the flat buffer
+        (parameters that took no part keep their zeros, cauchy_hypergradient.py:144-146) and re-attach the views."""
+        views, grads = [], []
+        for p, n, off in zip(self.params, self.sizes, self.offsets):
+            v = self.grad[off:off + n].view_as(p.data)
+            if p.grad is not None:
+                views.append(v)
+                grads.append(p.grad)
+            p.grad = v
+        if views:
+            torch._foreach_copy_(views, grads)
+
     def clip_(self, max_norm: float) -> torch.Tensor:
         """torch.nn.utils.clip_grad_norm_ on the flat buffer: same global 2-norm, one reduction, no host sync."""
         norm = torch.linalg.vector_norm(self.grad, dtype=torch.float64).float()   # fp64 accumulation

@@ -127,6 +127,23 @@ class RelationalMultiHeadAttentionMP(nn.Module):
                                        [f._layers[0].bias for f in self.message_fns], Wqk, gi)
 
 
+class _ReZeroResidual(torch.autograd.Function):
+    """h + alpha * x (gnn.py:497-498, 512-513) as ONE elementwise launch forward and two backward (alpha * g, <g, x>)
+    instead of the five of the unfused expression; every tensor is [V,128] and purely HBM-bound."""
+
+    @staticmethod
+    def forward(ctx, h, x, alpha):
+        ctx.save_for_backward(x, alpha)
+        return torch.addcmul(h, x, alpha)
+
+    @staticmethod
+    def backward(ctx, g):
+        x, alpha = ctx.saved_tensors
+        g = g.contiguous()
+        dalpha = torch.dot(g.view(-1), x.contiguous().view(-1)).reshape(alpha.shape) if ctx.needs_input_grad[2] else None
+        return g, (g * alpha if ctx.needs_input_grad[1] else None), dalpha
+
+
 class GNNBlock(nn.Module):
     """One residual block (gnn.py:477-515).  `mp_norm_layer` is registered but never applied, exactly like
     the reference, so the state dict keeps its keys."""
@@ -169,12 +186,12 @@ class GNNBlock(nn.Module):
     def forward(self, h, gi: ops.GraphIndex):
         if self._mp_mode < 0:
             agg = self.mp_layers[0](h, gi)                                 # [V, 256]
-            h = h + self.alpha * ops.linear_tc(agg, self.msg_out_projection.weight, self.msg_out_projection.bias)
-            return h + self.alpha * self.boom_layer(self.boom_norm_layer(h))
+            h = _ReZeroResidual.apply(h, ops.linear_tc(agg, self.msg_out_projection.weight, self.msg_out_projection.bias), self.alpha)
+            return _ReZeroResidual.apply(h, self.boom_layer(self.boom_norm_layer(h)), self.alpha)
         W, b = self.stacked_message_weights()
         agg = ops.pna_message_passing(h, W, b, gi) if self._mp_mode == ops.MP_PNA else ops.mp_message_passing(h, W, b, gi, self._mp_mode)   # [V, 3072 | 1024 | 256]
-        h = h + self.alpha * ops.linear_tc(agg, self.msg_out_projection.weight, self.msg_out_projection.bias)
-        return h + self.alpha * self.boom_layer(self.boom_norm_layer(h))
+        h = _ReZeroResidual.apply(h, ops.linear_tc(agg, self.msg_out_projection.weight, self.msg_out_projection.bias), self.alpha)
+        return _ReZeroResidual.apply(h, self.boom_layer(self.boom_norm_layer(h)), self.alpha)
 
 
 class GNN(nn.Module):
