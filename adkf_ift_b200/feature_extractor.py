@@ -178,6 +178,10 @@ class GNNBlock(nn.Module):
         self.boom_layer = BOOMLayer(config.hidden_dim, config.intermediate_dim)
         self.boom_norm_layer = nn.LayerNorm(config.hidden_dim)
 
+    def _boom_norm(self, h):
+        ln = self.boom_norm_layer
+        return ops.layernorm128(h, ln.weight, ln.bias, ln.eps)
+
     def stacked_message_weights(self):
         W = torch.stack([torch.stack([fn._layers[0].weight for fn in tw.message_fns]) for tw in self.mp_layers])
         b = torch.stack([torch.stack([fn._layers[0].bias for fn in tw.message_fns]) for tw in self.mp_layers])
@@ -187,11 +191,11 @@ class GNNBlock(nn.Module):
         if self._mp_mode < 0:
             agg = self.mp_layers[0](h, gi)                                 # [V, 256]
             h = _ReZeroResidual.apply(h, ops.linear_tc(agg, self.msg_out_projection.weight, self.msg_out_projection.bias), self.alpha)
-            return _ReZeroResidual.apply(h, self.boom_layer(self.boom_norm_layer(h)), self.alpha)
+            return _ReZeroResidual.apply(h, self.boom_layer(self._boom_norm(h)), self.alpha)
         W, b = self.stacked_message_weights()
         agg = ops.pna_message_passing(h, W, b, gi) if self._mp_mode == ops.MP_PNA else ops.mp_message_passing(h, W, b, gi, self._mp_mode)   # [V, 3072 | 1024 | 256]
         h = _ReZeroResidual.apply(h, ops.linear_tc(agg, self.msg_out_projection.weight, self.msg_out_projection.bias), self.alpha)
-        return _ReZeroResidual.apply(h, self.boom_layer(self.boom_norm_layer(h)), self.alpha)
+        return _ReZeroResidual.apply(h, self.boom_layer(self._boom_norm(h)), self.alpha)
 
 
 class GNN(nn.Module):

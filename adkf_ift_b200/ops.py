@@ -403,6 +403,9 @@ def readout_max(x, graph_ptr, num_graphs):
 # --------------------------------------------------------------------------------------------------
 # sparse ECFP branch of fc[0]
 # --------------------------------------------------------------------------------------------------
+ECFP_DENSE_BWD_MIN_GRAPHS = 512
+
+
 class _EcfpLinear(torch.autograd.Function):
     @staticmethod
     def forward(ctx, base, fp, Wt):
@@ -424,7 +427,12 @@ class _EcfpLinear(torch.autograd.Function):
         (fp,) = ctx.saved_tensors
         d_out = d_out.contiguous()
         d_Wt = None
-        if ctx.needs_input_grad[2]:
+        if ctx.needs_input_grad[2] and fp.shape[0] >= ECFP_DENSE_BWD_MIN_GRAPHS and fp.shape[1] % 4 == 0 \
+                and d_out.shape[1] % 4 == 0 and d_out.data_ptr() % 16 == 0:
+            # many graphs: d_Wt = fp^T @ d_out as ONE (T,T) tensor-core GEMM (small integer counts are exact in tf32);
+            # the per-bit sparse accumulation below is 6x slower at G = 5,120
+            d_Wt = gemm_tf32x3(fp.to(torch.float32), True, d_out, True)
+        elif ctx.needs_input_grad[2]:
             d_Wt = torch.zeros(ctx.wshape, dtype=torch.float32, device=d_out.device)
             rc = lib.adkf_ecfp_linear_bwd(dptr(fp), fp.shape[0], fp.shape[1], dptr(d_out, torch.float32),
                                           ctx.wshape[1], dptr(d_Wt), stream_ptr())
@@ -658,6 +666,45 @@ def act_bwd_colsum(dy: torch.Tensor, y: Optional[torch.Tensor], act: int, want_d
                                  stream_ptr())
     check(rc, "adkf_act_bwd_colsum")
     return dz, db
+
+
+class _LayerNorm128(torch.autograd.Function):
+    """nn.LayerNorm(128) on [V,128] node states (gnn.py:504): warp-per-row kernels, deterministic dgamma / dbeta."""
+
+    @staticmethod
+    def forward(ctx, x, gamma, beta, eps):
+        lib = _cabi.load()
+        if not x.is_cuda or x.dtype != torch.float32 or x.dim() != 2 or x.shape[1] != 128:
+            raise RuntimeError("layernorm128 needs an fp32 CUDA tensor [M,128] (no CPU fallback)")
+        x = x.contiguous()
+        gamma, beta = gamma.contiguous(), beta.contiguous()
+        M = x.shape[0]
+        y = torch.empty_like(x)
+        stats = torch.empty(2, max(M, 1), dtype=torch.float32, device=x.device)
+        rc = lib.adkf_layernorm128_fwd(dptr(x, torch.float32), M, dptr(gamma, torch.float32), dptr(beta, torch.float32),
+                                       float(eps), dptr(y), dptr(stats[0]), dptr(stats[1]), stream_ptr())
+        check(rc, "adkf_layernorm128_fwd")
+        ctx.save_for_backward(x, gamma, stats)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        lib = _cabi.load()
+        x, gamma, stats = ctx.saved_tensors
+        dy = dy.contiguous()
+        M = x.shape[0]
+        dx = torch.empty_like(x)
+        dgb = torch.empty(2, 128, dtype=torch.float32, device=x.device)
+        nws = int(lib.adkf_layernorm128_bwd_ws_floats(M))
+        ws = torch.empty(nws, dtype=torch.float32, device=x.device)
+        rc = lib.adkf_layernorm128_bwd(dptr(dy, torch.float32), dptr(x), dptr(stats[0]), dptr(stats[1]), dptr(gamma), M,
+                                       dptr(dx), dptr(dgb[0]), dptr(dgb[1]), dptr(ws), nws, stream_ptr())
+        check(rc, "adkf_layernorm128_bwd")
+        return dx, dgb[0], dgb[1], None
+
+
+def layernorm128(x: torch.Tensor, gamma: torch.Tensor, beta: torch.Tensor, eps: float = 1e-5) -> torch.Tensor:
+    return _LayerNorm128.apply(x, gamma, beta, eps)
 
 
 class _LinearTC(torch.autograd.Function):

@@ -118,6 +118,18 @@ int adkf_act_bwd_colsum(const float* dY, int64_t ldy, const float* Y, int64_t ld
                         float* dZ, int64_t ldz, float* db, float* ws, int64_t ws_floats, void* stream);
 
 /* ---------------------------------------------------------------------------------------------
+ * nn.LayerNorm(128) of the GNN block (`boom_norm_layer`, fs_mol/modules/gnn.py:462, applied at :504; torch semantics:
+ * biased variance, eps inside the square root) on x [M,128] fp32, 16-byte aligned: one warp per row.
+ *   fwd: y = (x - mean) * rstd * gamma + beta; mean / rstd [M] are kept for the backward pass
+ *   bwd: dx [M,128], dgamma [128], dbeta [128] (deterministic two-pass column sums; ws >= adkf_layernorm128_bwd_ws_floats(M))
+ * ------------------------------------------------------------------------------------------- */
+int adkf_layernorm128_fwd(const float* x, int64_t M, const float* gamma, const float* beta, float eps, float* y,
+                          float* mean, float* rstd, void* stream);
+int64_t adkf_layernorm128_bwd_ws_floats(int64_t M);
+int adkf_layernorm128_bwd(const float* dy, const float* x, const float* mean, const float* rstd, const float* gamma,
+                          int64_t M, float* dx, float* dgamma, float* dbeta, float* ws, int64_t ws_floats, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
  * The same PNA block with its three dense products on the tensor cores (pna_gemm.cu; default path of the extractor):
  *   XG [E,256]   = adkf_pna_gather_inputs(h)            [h_src | h_tgt] per tower, edges sorted by (type, target, message index)
  *   pre [E,768]  = adkf_gemm_tf32x3_batched(XG, W, b)   message MLP pre-activations, 4 towers per launch, one launch per type

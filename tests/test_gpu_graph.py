@@ -199,3 +199,46 @@ def test_ecfp_linear_fwd_bwd(cuda_device):
     out.backward(go.to(cuda_device))
     assert rel(Wc.grad, Wd.grad) < 1e-5
     assert rel(bc.grad, bd.grad) == 0.0
+
+
+def test_ecfp_linear_bwd_dense_path_many_graphs(cuda_device):
+    """G >= 512 graphs: the fingerprint weight gradient runs as one (T,T) tensor-core GEMM; same result as fp64."""
+    from adkf_ift_b200 import ops
+    G = 700
+    assert G >= ops.ECFP_DENSE_BWD_MIN_GRAPHS
+    gen = torch.Generator().manual_seed(11)
+    fp = torch.zeros(G, 2048, dtype=torch.int32)
+    idx = torch.randint(0, 2048, (G, 45), generator=gen)
+    fp.scatter_(1, idx, torch.randint(1, 5, (G, 45), generator=gen, dtype=torch.int32))
+    Wt = torch.randn(2048, 2048, generator=gen) * 0.02
+    base = torch.randn(G, 2048, generator=gen)
+    go = torch.randn(G, 2048, generator=gen)
+    Wc, bc = Wt.to(cuda_device).requires_grad_(True), base.to(cuda_device).requires_grad_(True)
+    out = ops.ecfp_linear(bc, fp.to(cuda_device), Wc)
+    out.backward(go.to(cuda_device))
+    ref_dW = fp.double().t() @ go.double()
+    assert rel(out, base.double() + fp.double() @ Wt.double()) < 1e-5
+    assert rel(Wc.grad, ref_dW) < 1e-5
+
+
+@pytest.mark.parametrize("M", [1, 7, 64, 1000, 70001])
+def test_layernorm128_fwd_bwd(cuda_device, M):
+    """adkf_layernorm128_* vs torch.nn.functional.layer_norm in fp64 (forward 1e-6, gradients 1e-5 relative); bit-identical reruns."""
+    from adkf_ift_b200 import ops
+    gen = torch.Generator().manual_seed(M)
+    x = torch.randn(M, 128, generator=gen) * 3.0 + 0.5
+    gamma, beta = torch.randn(128, generator=gen), torch.randn(128, generator=gen)
+    go = torch.randn(M, 128, generator=gen)
+    xd, gd, bd = (t.double().requires_grad_(True) for t in (x, gamma, beta))
+    ref = torch.nn.functional.layer_norm(xd, (128,), gd, bd, 1e-5)
+    ref.backward(go.double())
+    outs = []
+    for _ in range(2):
+        xc, gc, bc = (t.to(cuda_device).requires_grad_(True) for t in (x, gamma, beta))
+        y = ops.layernorm128(xc, gc, bc, 1e-5)
+        y.backward(go.to(cuda_device))
+        outs.append((y.detach().clone(), xc.grad.clone(), gc.grad.clone(), bc.grad.clone()))
+    y, dx, dg, db = outs[0]
+    assert rel(y, ref) < 1e-6
+    assert rel(dx, xd.grad) < 1e-5 and rel(dg, gd.grad) < 1e-5 and rel(db, bd.grad) < 1e-5
+    assert all(torch.equal(a, b) for a, b in zip(outs[0], outs[1]))

@@ -232,3 +232,47 @@ def test_c3_regression_256_task_meta_test(cuda_device):
     batch = dkt.torchify(hosts[0], torch.device("cpu")).batches[0]
     ref = orc.meta_test_task(P, batch, ocfg)
     assert rel(mean[0], ref["mean"].numpy()) < 2e-3 and rel(var[0], ref["variance"].numpy()) < 2e-3
+
+
+def test_c2_full_size_step_properties(cuda_device):
+    """BASELINE config 2 at full size (16 tasks x (64 support + 256 query), 10 PNA blocks): size-independent properties of
+    the meta-training pass -- bit-identical reruns (no float atomics anywhere on the path; the reference's torch_scatter
+    backward is not reproducible on a GPU), linearity of the accumulated meta-gradient in grad_scale, every task's inner fit
+    converged to a PD optimum, and the flat-buffer hand-over of train_step equal to plain autograd accumulation."""
+    from adkf_ift_b200 import dkt, synthetic, task_batch
+    from adkf_ift_b200.adaptive_dkt import ADKTModelTrainerConfig
+    from adkf_ift_b200.adaptive_dkt_utils import ADKTModelTrainer, run_on_task_batch
+    from adkf_ift_b200.feature_extractor import cli_default_config
+    cfg = ADKTModelTrainerConfig(graph_feature_extractor_config=cli_default_config(10), tasks_per_batch=16, clip_value=1.0,
+                                 learning_rate=1e-4)
+    model = ADKTModelTrainer(cfg)
+    synthetic.deterministic_init_(model, seed=0, alpha=0.5)
+    model.to(cuda_device)
+    hosts = [dkt.task_sample_to_dkt_task_sample(synthetic.make_task_sample(7000 + t, 64, 256),
+                                                dkt.get_dkt_batcher(max_num_graphs=320), False).batches[0] for t in range(16)]
+    tb = task_batch.to_device(task_batch.collate_tasks(hosts, False), cuda_device)
+    assert tb.num_graphs == 16 * 320
+
+    def grads(scale):
+        model.zero_grad(set_to_none=True)
+        res = run_on_task_batch(model, tb, train=True, grad_scale=scale)
+        return res, {n: p.grad.clone() for n, p in model.named_parameters() if p.grad is not None}
+
+    r1, g1 = grads(1.0 / 16)
+    r2, g2 = grads(1.0 / 16)
+    assert int((r1.status & 6).sum().item()) == 0                       # not-PD / not-converged bits clear for all 16 tasks
+    assert torch.isfinite(r1.outer_loss).all()
+    assert torch.equal(r1.phi, r2.phi) and torch.equal(r1.outer_loss, r2.outer_loss)
+    assert all(torch.equal(g1[n], g2[n]) for n in g1), "meta-gradient is not bit-reproducible"
+    _, g3 = grads(2.0 / 16)                                              # scaling by a power of two is exact in fp32
+    assert all(torch.equal(2.0 * g1[n], g3[n]) for n in g1)
+    # train_step: gradients handed over by autograd and gathered into the flat buffer == the plain accumulation above
+    flat = model._ensure_flat()
+    flat.release_grads()
+    run_on_task_batch(model, tb, train=True, grad_scale=1.0 / 16)
+    flat.gather_grads()
+    for n, p in model.named_parameters():
+        if n in g1:
+            assert torch.equal(p.grad, g1[n]), n
+        elif not n.startswith("gp_"):
+            assert p.grad is not None and float(p.grad.abs().max()) == 0.0   # unused parameters keep zeros
