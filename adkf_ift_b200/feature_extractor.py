@@ -193,8 +193,13 @@ class GNNBlock(nn.Module):
             h = _ReZeroResidual.apply(h, ops.linear_tc(agg, self.msg_out_projection.weight, self.msg_out_projection.bias), self.alpha)
             return _ReZeroResidual.apply(h, self.boom_layer(self._boom_norm(h)), self.alpha)
         W, b = self.stacked_message_weights()
-        agg = ops.pna_message_passing(h, W, b, gi) if self._mp_mode == ops.MP_PNA else ops.mp_message_passing(h, W, b, gi, self._mp_mode)   # [V, 3072 | 1024 | 256]
-        h = _ReZeroResidual.apply(h, ops.linear_tc(agg, self.msg_out_projection.weight, self.msg_out_projection.bias), self.alpha)
+        if self._mp_mode == ops.MP_PNA and getattr(gi, "type_sorted", None) is not None:
+            # degree scalers folded out of the aggregate: [V,1024] instead of [V,3072] between aggregation and projection
+            proj = ops.pna_message_passing_projected(h, W, b, self.msg_out_projection.weight, self.msg_out_projection.bias, gi)
+        else:
+            agg = ops.pna_message_passing(h, W, b, gi) if self._mp_mode == ops.MP_PNA else ops.mp_message_passing(h, W, b, gi, self._mp_mode)   # [V, 3072 | 1024 | 256]
+            proj = ops.linear_tc(agg, self.msg_out_projection.weight, self.msg_out_projection.bias)
+        h = _ReZeroResidual.apply(h, proj, self.alpha)
         return _ReZeroResidual.apply(h, self.boom_layer(self._boom_norm(h)), self.alpha)
 
 

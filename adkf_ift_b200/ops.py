@@ -246,6 +246,66 @@ def mp_message_passing(h, W, b, gi: GraphIndex, mode: int):
     return _PNAMessagePassingTC.apply(h, W, b, gi, mode)
 
 
+class _PNACombine(torch.autograd.Function):
+    """out = P[:, :128] + amp * P[:, 128:256] + att * P[:, 256:] + bias (pna_combine.cu)."""
+
+    @staticmethod
+    def forward(ctx, P, bias, amp, att):
+        lib = _cabi.load()
+        P = P.contiguous()
+        V = P.shape[0]
+        out = torch.empty(V, 128, dtype=torch.float32, device=P.device)
+        check(lib.adkf_pna_combine_fwd(dptr(P, torch.float32), dptr(amp), dptr(att),
+                                       dptr(bias.contiguous(), torch.float32) if bias is not None else ctypes.c_void_p(0), V,
+                                       dptr(out), stream_ptr()), "adkf_pna_combine_fwd")
+        ctx.save_for_backward(amp, att)
+        ctx.has_bias = bias is not None
+        return out
+
+    @staticmethod
+    def backward(ctx, g):
+        lib = _cabi.load()
+        amp, att = ctx.saved_tensors
+        g = g.contiguous()
+        V = g.shape[0]
+        dP = torch.empty(V, 384, dtype=torch.float32, device=g.device)
+        want_db = ctx.has_bias and ctx.needs_input_grad[1]
+        db = torch.empty(128, dtype=torch.float32, device=g.device) if want_db else None
+        nws = int(lib.adkf_pna_combine_bwd_ws_floats(V)) if want_db else 0
+        ws = torch.empty(nws, dtype=torch.float32, device=g.device) if want_db else None
+        null = ctypes.c_void_p(0)
+        check(lib.adkf_pna_combine_bwd(dptr(g, torch.float32), dptr(amp), dptr(att), V, dptr(dP), dptr(db) if want_db else null,
+                                       dptr(ws) if want_db else null, nws, stream_ptr()), "adkf_pna_combine_bwd")
+        return dP, db, None, None
+
+
+def pna_degree_scalers(gi: GraphIndex):
+    """(amp [V], att [V]) of gnn.py:242-263, computed once per graph batch and cached on the index."""
+    cached = getattr(gi, "_pna_scalers", None)
+    if cached is None:
+        lib = _cabi.load()
+        ts: TypeSortedEdges = gi.type_sorted
+        V = gi.num_nodes
+        sc = torch.empty(2, max(V, 1), dtype=torch.float32, device=ts.tptr.device)
+        check(lib.adkf_pna_degree_scalers(dptr(ts.tptr), V, dptr(sc[0]), dptr(sc[1]), stream_ptr()), "adkf_pna_degree_scalers")
+        cached = (sc[0], sc[1])
+        gi._pna_scalers = cached
+    return cached
+
+
+def pna_message_passing_projected(h, W, b, W_out, b_out, gi: GraphIndex):
+    """msg_out_projection(PNA aggregate) [V,128] without materialising the [V,3072] scaled aggregate: unscaled aggregation
+    ([V,1024], the MultiAggr kernels) -> ONE GEMM with the three scaler blocks of W_out stacked ([384,1024]) -> combine."""
+    if getattr(gi, "type_sorted", None) is None:
+        raise RuntimeError("pna_message_passing_projected needs a GraphIndex built by build_graph_index (type-sorted edges)")
+    agg = _PNAMessagePassingTC.apply(h, W, b, gi, MP_MULTIAGGR)
+    # W_out [128, 4 towers x (1 | amp | att) x 256] -> [3 x 128, 4 x 256]: row block s holds the columns of scaler s
+    Wcat = W_out.view(128, 4, 3, 256).permute(2, 0, 1, 3).reshape(384, 1024)
+    P = linear_tc(agg, Wcat, None)
+    amp, att = pna_degree_scalers(gi)
+    return _PNACombine.apply(P, b_out, amp, att)
+
+
 class _MHAGather(torch.autograd.Function):
     """XG [E,256] = [x_src | x_tgt] over the type-sorted edges (mha_mp.cu)."""
 

@@ -118,6 +118,19 @@ int adkf_act_bwd_colsum(const float* dY, int64_t ldy, const float* Y, int64_t ld
                         float* dZ, int64_t ldz, float* db, float* ws, int64_t ws_floats, void* stream);
 
 /* ---------------------------------------------------------------------------------------------
+ * PNA degree scalers folded out of the aggregate (gnn.py:242-263 + msg_out_projection, gnn.py:492-495; pna_combine.cu):
+ * out[v] = P[v,0:128] + amp(v) P[v,128:256] + att(v) P[v,256:384] + bias, where P = agg_unscaled [V,1024] @ [W_1;W_amp;W_att]^T.
+ *   adkf_pna_degree_scalers: amp = log(deg+1)/1.1515, att = 1.1515/(log(deg+1)+1e-7) from the type-sorted tptr [3V+1]
+ *   adkf_pna_combine_bwd   : dP [V,384] = [g | amp g | att g]; dbias [128] (may be NULL; ws >= adkf_pna_combine_bwd_ws_floats(V))
+ * ------------------------------------------------------------------------------------------- */
+int adkf_pna_degree_scalers(const int32_t* tptr, int32_t V, float* amp, float* att, void* stream);
+int adkf_pna_combine_fwd(const float* P, const float* amp, const float* att, const float* bias, int64_t V, float* out,
+                         void* stream);
+int64_t adkf_pna_combine_bwd_ws_floats(int64_t V);
+int adkf_pna_combine_bwd(const float* g, const float* amp, const float* att, int64_t V, float* dP, float* dbias, float* ws,
+                         int64_t ws_floats, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
  * nn.LayerNorm(128) of the GNN block (`boom_norm_layer`, fs_mol/modules/gnn.py:462, applied at :504; torch semantics:
  * biased variance, eps inside the square root) on x [M,128] fp32, 16-byte aligned: one warp per row.
  *   fwd: y = (x - mean) * rstd * gamma + beta; mean / rstd [M] are kept for the backward pass

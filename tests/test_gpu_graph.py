@@ -242,3 +242,50 @@ def test_layernorm128_fwd_bwd(cuda_device, M):
     assert rel(y, ref) < 1e-6
     assert rel(dx, xd.grad) < 1e-5 and rel(dg, gd.grad) < 1e-5 and rel(db, bd.grad) < 1e-5
     assert all(torch.equal(a, b) for a, b in zip(outs[0], outs[1]))
+
+
+@pytest.mark.parametrize("n_mol", [3, 24])
+def test_pna_scalers_folded_into_projection(cuda_device, n_mol):
+    """msg_out_projection(PNA aggregate) with the degree scalers folded out of the aggregate ([V,1024] + one [384,1024]
+    GEMM + combine) == the reference formulation ([V,3072] aggregate @ W_out^T): forward and all five gradients, against
+    the fp64 oracle of the unfolded expression; isolated nodes included (amp = 0, att = 1.1515e7 on an all-zero aggregate)."""
+    from adkf_ift_b200 import ops
+    from oracle import adkf_oracle as orc
+    b, _ = make_batch(4, n_mol)
+    V = b.num_nodes + 2                                   # two isolated trailing nodes
+    gen = torch.Generator().manual_seed(3)
+    h = torch.randn(V, 128, generator=gen)
+    W = torch.randn(4, 3, 192, 64, generator=gen) * 0.15
+    bias = torch.randn(4, 3, 192, generator=gen) * 0.1
+    Wo = torch.randn(128, 3072, generator=gen) * 0.02
+    bo = torch.randn(128, generator=gen) * 0.1
+    gout = torch.randn(V, 128, generator=gen)
+    adjs = [torch.from_numpy(a) for a in b.adjacency_lists]
+    hd, Wd, bd, Wod, bod = (x.double().requires_grad_(True) for x in (h, W, bias, Wo, bo))
+    bid = orc.bidirectional_edges(adjs)
+    agg = torch.cat([orc.pna_tower(hd[:, 32 * k:32 * k + 32], bid, [Wd[k, t] for t in range(3)],
+                                   [bd[k, t] for t in range(3)], 64) for k in range(4)], dim=1)
+    ref = agg @ Wod.t() + bod
+    ref.backward(gout.double())
+    gi = ops.build_graph_index([a.to(cuda_device) for a in adjs], V)
+    amp, att = ops.pna_degree_scalers(gi)
+    deg = np.diff(gi.rowptr.cpu().numpy()).astype(np.float32)
+    assert np.allclose(amp.cpu().numpy(), np.log(deg + 1) / 1.1515, rtol=1e-6)
+    assert np.allclose(att.cpu().numpy(), 1.1515 / (np.log(deg + 1) + 1e-7), rtol=1e-6)
+    cs = [x.to(cuda_device).requires_grad_(True) for x in (h, W, bias, Wo, bo)]
+    out = ops.pna_message_passing_projected(*cs, gi)
+    # the unfolded CUDA path on the same inputs gives the fp32 error budget
+    us = [x.to(cuda_device).requires_grad_(True) for x in (h, W, bias, Wo, bo)]
+    unf = ops.linear_tc(ops.pna_message_passing(us[0], us[1], us[2], gi), us[3], us[4])
+    e, eu = rel(out, ref), rel(unf, ref)
+    print("folded fwd rel err", e, "unfolded", eu)
+    assert e < max(2e-5, 4 * eu)
+    assert float(out[-2:].detach().sub(cs[4].detach()).abs().max()) == 0.0      # isolated nodes: exactly the bias
+    out.backward(gout.to(cuda_device))
+    unf.backward(gout.to(cuda_device))
+    for name, c, u, d in zip(("dh", "dW", "db", "dW_out", "db_out"), cs, us, (hd, Wd, bd, Wod, bod)):
+        l2, l2u = rel_l2(c.grad, d.grad), rel_l2(u.grad, d.grad)
+        print("folded bwd", name, "l2-rel", l2, "unfolded", l2u)
+        assert l2 < max(1e-4, 4 * l2u)
+    out2 = ops.pna_message_passing_projected(*[c.detach() for c in cs], gi)
+    assert torch.equal(out2, out.detach())
