@@ -57,6 +57,8 @@ SIGNATURES = {
     "adkf_linear_tf32x3": ([_P, c_int64, c_int32, c_int64, _P, c_int32, c_int64, _P, c_int32, _P, c_int64, _P], ctypes.c_int),
     "adkf_gemm_tf32x3": ([_P, c_int32, c_int64, _P, c_int32, c_int64, c_int64, c_int32, c_int32, _P, c_int32, _P, c_int64,
                           _P, c_int64, _P], ctypes.c_int),
+    "adkf_gemm_tf32x3_masked": ([_P, c_int32, c_int64, _P, c_int32, c_int64, c_int64, c_int32, c_int32, _P, c_int64, c_int32, _P,
+                                 c_int64, _P], ctypes.c_int),
     "adkf_gemm_tf32x3_batched": ([_P, c_int32, c_int64, c_int64, c_int64, c_int32, c_int32, _P, c_int32, c_int64, c_int64, c_int64,
                                   c_int32, c_int32, c_int64, c_int32, c_int32, c_int32, _P, c_int64, c_int32, _P, c_int64,
                                   c_int64, _P, c_int64, _P], ctypes.c_int),

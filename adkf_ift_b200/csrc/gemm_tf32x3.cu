@@ -170,7 +170,11 @@ struct GemmEpilogue {
     int64_t M;
     int N, K;
     const float* bias;
-    int act;              // 0 none, 1 relu, 2 leaky_relu(0.01), 3 subtract the product from what `out` holds
+    int act;              // 0 none, 1 relu, 2 leaky_relu(0.01), 3 subtract the product from what `out` holds,
+                          // 4 / 5: multiply by relu' / leaky_relu'(0.01) of mask[row, col] (the saved activation output of the
+                          // layer below: the input-gradient GEMM of layer l+1 emits dZ_l directly, fs_mol/modules/gnn.py:79-95)
+    const float* mask;
+    int64_t ldm;
     // split-K (mode 0): CTA z handles k-blocks [z * kb_per_split, ...) and writes to out + z * split_stride
     int kb_per_split;
     int64_t split_stride;
@@ -576,6 +580,30 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
                 const int act = ep.act;
 #pragma unroll
                 for (int p = 0; p < 2; ++p) {
+                    // act 4 / 5: the 8 mask vectors this lane needs for the pass are requested BEFORE the staging traffic, so
+                    // their latency hides behind it (a load inside the store loop costs one round trip per store)
+                    float4 mk4[8];
+                    if (act >= 4) {
+                        const int mcol = c.rowB0 + colbase + p * 32 + ch * 4;
+                        const int64_t mrow = (int64_t)c.rowA0 + q * 32 + rsub;
+                        const bool mvec = (ep.ldm % 4 == 0) && ((reinterpret_cast<uintptr_t>(ep.mask) & 15) == 0) && mcol + 4 <= ep.N;
+#pragma unroll
+                        for (int jj = 0; jj < 8; ++jj) {
+                            const int64_t r = mrow + jj * 4;
+                            mk4[jj] = make_float4(1.f, 1.f, 1.f, 1.f);
+                            if (r < ep.M && mcol < ep.N) {
+                                const float* mk = ep.mask + r * ep.ldm + mcol;
+                                if (mvec) {
+                                    mk4[jj] = __ldg(reinterpret_cast<const float4*>(mk));
+                                } else {
+                                    mk4[jj].x = mk[0];
+                                    if (mcol + 1 < ep.N) mk4[jj].y = mk[1];
+                                    if (mcol + 2 < ep.N) mk4[jj].z = mk[2];
+                                    if (mcol + 3 < ep.N) mk4[jj].w = mk[3];
+                                }
+                            }
+                        }
+                    }
 #pragma unroll
                     for (int j = 0; j < 8; ++j)
                         stg[lane * 8 + (j ^ (lane & 7))] =
@@ -609,6 +637,12 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
                             x.z = (x.z > 0.f) ? x.z : 0.01f * x.z; x.w = (x.w > 0.f) ? x.w : 0.01f * x.w;
                         }
                         if (rbase + jj * 4 < ep.M && col < ep.N && !(ep.debug & 4)) {
+                            if (act >= 4) {
+                                const float neg = (act == 4) ? 0.f : 0.01f;
+                                const float4 y = mk4[jj];
+                                x.x *= (y.x > 0.f) ? 1.f : neg; x.y *= (y.y > 0.f) ? 1.f : neg;
+                                x.z *= (y.z > 0.f) ? 1.f : neg; x.w *= (y.w > 0.f) ? 1.f : neg;
+                            }
                             if (full) {
                                 if (act == 3) {                                    // D <- D - A.B^T (trailing update)
                                     const float4 old = *reinterpret_cast<const float4*>(o);
@@ -773,7 +807,8 @@ extern "C" int64_t adkf_gemm_splitk_ws_floats(int64_t M, int32_t N, int32_t K) {
 static int gemm_launch(const float* A, int transA, int64_t lda, int64_t a_slow, int64_t a_fast, const float* B, int transB,
                        int64_t ldb, int64_t b_slow, int64_t b_fast, int64_t M, int32_t N, int32_t K, const float* bias,
                        int32_t act, float* D, int64_t ldd, float* splitk_ws, int64_t splitk_ws_floats, int batch, int a_mn,
-                       int a_k, int b_mn, int b_k, int64_t d_off, int64_t bias_off, cudaStream_t s) {
+                       int a_k, int b_mn, int b_k, int64_t d_off, int64_t bias_off, cudaStream_t s, const float* mask = nullptr,
+                       int64_t ldm = 0) {
     (void)cudaGetLastError();   // a stale error left in this host thread by someone else is not this launch's failure
     CUtensorMap ma, mb;
     // make_map_2d(ptr, rows (mn extent), kdim (k extent), ld, transposed): extents of the WHOLE array
@@ -789,7 +824,7 @@ static int gemm_launch(const float* A, int transA, int64_t lda, int64_t a_slow, 
         splits = 1;                                                  // no workspace (or fused epilogue): single pass
     const int nk = (K + kBK - 1) / kBK;
     GemmEpilogue ep = {};
-    ep.mode = 0; ep.M = M; ep.N = N; ep.K = K; ep.bias = bias; ep.act = act;
+    ep.mode = 0; ep.M = M; ep.N = N; ep.K = K; ep.bias = bias; ep.act = act; ep.mask = mask; ep.ldm = ldm;
     ep.kb_per_split = (nk + splits - 1) / splits;
     static const int dbg = getenv("ADKF_GEMM_DEBUG") ? atoi(getenv("ADKF_GEMM_DEBUG")) : 0;
     ep.debug = dbg;
@@ -834,6 +869,18 @@ extern "C" int adkf_gemm_tf32x3(const float* A, int32_t transA, int64_t lda, con
     if (transA && !transB) return ADKF_ERR_BADARG;                  // (T,K) is not on the path
     return gemm_launch(A, transA, lda, transA ? K : M, transA ? M : K, B, transB, ldb, transB ? K : N, transB ? N : K, M, N, K,
                        bias, act, D, ldd, splitk_ws, splitk_ws_floats, 1, 0, 0, 0, 0, 0, 0, (cudaStream_t)stream);
+}
+
+// D = (A.B^T) * act'(mask): the input-gradient GEMM of a layer fused with the activation derivative of the layer below
+// (mask = that layer's saved activation OUTPUT [M,N], mask_act 1 relu / 2 leaky_relu(0.01)).  No split-K, no bias.
+extern "C" int adkf_gemm_tf32x3_masked(const float* A, int32_t transA, int64_t lda, const float* B, int32_t transB, int64_t ldb,
+                                       int64_t M, int32_t N, int32_t K, const float* mask, int64_t ldm, int32_t mask_act,
+                                       float* D, int64_t ldd, void* stream) {
+    if (M <= 0 || N <= 0) return 0;
+    if (!A || !B || !D || !mask || K <= 0 || (mask_act != 1 && mask_act != 2) || ldm < N) return ADKF_ERR_BADARG;
+    if (transA && !transB) return ADKF_ERR_BADARG;
+    return gemm_launch(A, transA, lda, transA ? K : M, transA ? M : K, B, transB, ldb, transB ? K : N, transB ? N : K, M, N, K,
+                       nullptr, 3 + mask_act, D, ldd, nullptr, 0, 1, 0, 0, 0, 0, 0, 0, (cudaStream_t)stream, mask, ldm);
 }
 
 extern "C" int64_t adkf_gemm_batched_splitk_ws_floats(int64_t M, int32_t N, int32_t K, int32_t batch) {

@@ -83,6 +83,8 @@ class MLP(nn.Module):
 
     def forward(self, x):
         mods = list(self._layers)
+        if len(mods) == 3 and isinstance(mods[1], nn.ReLU):      # one hidden layer: fused two-layer backward when eligible
+            return ops.mlp2_tc(x, mods[0].weight, mods[0].bias, "relu", mods[2].weight, mods[2].bias)
         i = 0
         while i < len(mods):
             fuse_relu = i + 1 < len(mods) and isinstance(mods[i + 1], nn.ReLU)
@@ -106,8 +108,7 @@ class BOOMLayer(nn.Module):
         self.linear2 = nn.Linear(intermediate_dim, inout_dim)
 
     def forward(self, x):
-        hid = ops.linear_tc(x, self.linear1.weight, self.linear1.bias, "leaky_relu")
-        return ops.linear_tc(hid, self.linear2.weight, self.linear2.bias)
+        return ops.mlp2_tc(x, self.linear1.weight, self.linear1.bias, "leaky_relu", self.linear2.weight, self.linear2.bias)
 
 
 class RelationalMultiHeadAttentionMP(nn.Module):

@@ -690,6 +690,25 @@ def gemm_tf32x3(a: torch.Tensor, trans_a: bool, b: torch.Tensor, trans_b: bool, 
     return out
 
 
+def gemm_tf32x3_masked(a: torch.Tensor, b: torch.Tensor, mask: torch.Tensor, mask_act: int) -> torch.Tensor:
+    """(a [M,K] @ b [K,N]) * act'(mask [M,N]) -- the (K,T) input-gradient form with the activation derivative of the layer
+    below applied in the epilogue (mask_act 1 relu, 2 leaky_relu(0.01))."""
+    lib = _cabi.load()
+    M, K = a.shape
+    N = b.shape[1]
+    if b.shape[0] != K or tuple(mask.shape) != (M, N):
+        raise ValueError(f"shape mismatch: a {tuple(a.shape)} b {tuple(b.shape)} mask {tuple(mask.shape)}")
+    for t in (a, b, mask):
+        if not t.is_cuda or t.dtype != torch.float32 or t.stride(1) != 1 or t.stride(0) % 4 or t.data_ptr() % 16:
+            raise RuntimeError("gemm_tf32x3_masked needs 16-byte aligned 2-D fp32 CUDA operands (no CPU fallback)")
+    out = torch.empty(M, N, dtype=torch.float32, device=a.device)
+    rc = lib.adkf_gemm_tf32x3_masked(ctypes.c_void_p(a.data_ptr()), 0, a.stride(0), ctypes.c_void_p(b.data_ptr()), 1, b.stride(0),
+                                     M, N, K, ctypes.c_void_p(mask.data_ptr()), mask.stride(0), int(mask_act), dptr(out), N,
+                                     stream_ptr())
+    check(rc, "adkf_gemm_tf32x3_masked")
+    return out
+
+
 def linear_tf32x3_forward(x: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.Tensor], act=None) -> torch.Tensor:
     """act(x @ weight.T + bias) with fp32-class accuracy on the tensor cores (no autograd; see linear_tc)."""
     return gemm_tf32x3(x.contiguous(), False, weight.contiguous(), False, bias, act)
@@ -789,6 +808,44 @@ class _LinearTC(torch.autograd.Function):
         if ctx.needs_input_grad[1]:
             dw = gemm_tf32x3(dy, True, x, True)                # dW[N,K] = dY^T[N,M] X[M,K]
         return dx, dw, db, None
+
+
+class _MLP2TC(torch.autograd.Function):
+    """Linear -> ReLU | LeakyReLU(0.01) -> Linear (BOOMLayer gnn.py:79-95; hidden-layer MLPs mlp.py:6-22) as one autograd node,
+    so that the backward pass can fuse across the two layers: the input-gradient GEMM of the second layer applies the
+    activation derivative in its epilogue and emits dZ1 directly (the [M,hidden] gradient is written once and never
+    re-read by an elementwise pass); the bias gradients are read-only column sums."""
+
+    @staticmethod
+    def forward(ctx, x, w1, b1, act, w2, b2):
+        hid = gemm_tf32x3(x, False, w1, False, b1, act)
+        y = gemm_tf32x3(hid, False, w2, False, b2, None)
+        ctx.act = ACT_IDS[act]
+        ctx.has_b = (b1 is not None, b2 is not None)
+        ctx.save_for_backward(x, w1, hid, w2)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, w1, hid, w2 = ctx.saved_tensors
+        dy = dy.contiguous()
+        need = ctx.needs_input_grad
+        db2 = act_bwd_colsum(dy, None, 0, True)[1] if (ctx.has_b[1] and need[5]) else None
+        dw2 = gemm_tf32x3(dy, True, hid, True) if need[4] else None          # dW2[N,H] = dY^T hid
+        dz1 = gemm_tf32x3_masked(dy, w2, hid, ctx.act)                        # dZ1[M,H] = (dY W2) * act'(hid)
+        db1 = act_bwd_colsum(dz1, None, 0, True)[1] if (ctx.has_b[0] and need[2]) else None
+        dw1 = gemm_tf32x3(dz1, True, x, True) if need[1] else None
+        dx = gemm_tf32x3(dz1, False, w1, True) if need[0] else None
+        return dx, dw1, db1, None, dw2, db2
+
+
+def mlp2_tc(x, w1, b1, act, w2, b2):
+    """act(x W1^T + b1) W2^T + b2 with the fused backward of _MLP2TC when both layers fit the tensor-core kernel, else two
+    linear_tc calls."""
+    if (x.is_cuda and x.dim() == 2 and ACT_IDS[act] in (1, 2) and _tc_eligible(x, w1) and w2.shape[1] % 4 == 0 and w2.shape[0] % 4 == 0
+            and w2.shape[0] >= 32 and w2.stride(1) == 1 and w2.stride(0) % 4 == 0 and w2.data_ptr() % 16 == 0):
+        return _MLP2TC.apply(x, w1, b1, act, w2, b2)
+    return linear_tc(linear_tc(x, w1, b1, act), w2, b2)
 
 
 def linear_tc(x: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.Tensor] = None, act=None) -> torch.Tensor:

@@ -146,7 +146,8 @@ def dominant_kernel_roofline(model, tb, peaks):
     the readout hidden layer over all V nodes of the 16-task batch (M = V, N = 768, K = 1408, bias + ReLU fused).
     achieved = ALGORITHMIC flops 2 M N K (fp32-equivalent; the kernel issues 3 TF32 MMAs per product, reported beside it)
     over the measured duration; peak = TF32 dense = half of the measured bf16 peak of MEASURED_PEAKS.json.
-    A second entry gives the HBM-bound PNA aggregation kernel (reads pre [E,768], writes the aggregate [V,3072])."""
+    A second entry gives the HBM-bound PNA aggregation kernel of the step (reads the message pre-activations pre [E,768],
+    writes the unscaled aggregate [V,1024] + 2 x 256 aux bytes per node; the degree scalers are folded into the projection)."""
     from adkf_ift_b200 import ops
     gi = tb.graph_index
     V, E = gi.num_nodes, gi.num_edges
@@ -163,7 +164,7 @@ def dominant_kernel_roofline(model, tb, peaks):
     peak = bf16 / 2.0
     roof = {"kernel": "gemm_tf32x3_kernel<false,false> (readout hidden layer, M=V N=768 K=1408, bias+ReLU)", "bound": "tensor",
             "achieved": round(achieved, 1), "peak": round(peak, 1), "unit": "TFLOP/s", "frac": round(achieved / peak, 4),
-            "traffic": 1.142e9, "traffic_source": "ncu --set full, profiles/r1d_gemm_probe_summary.md (dram read+write per launch)",
+            "traffic": 1.142e9, "traffic_source": "ncu --set full, profiles/r1g_ncu_full_summary.md (dram read+write per launch)",
             "peak_source": src, "launch_ms": round(ms, 4), "algorithmic_flops": flops,
             "issued_tf32_tflops": round(3 * achieved, 1), "frac_issued": round(3 * achieved / peak, 4),
             "algorithmic_bytes": 4.0 * (M * K + N * K + M * N), "M": M, "N": N, "K": K}
@@ -177,14 +178,15 @@ def dominant_kernel_roofline(model, tb, peaks):
         lib = _cabi.load()
         ts = gi.type_sorted
         pre = torch.randn(max(E, 1), 768, device=dev)
-        out = torch.empty(V, 3072, device=dev)
+        out = torch.empty(V, 1024, device=dev)
         cnt = torch.empty(V, 4, 64, dtype=torch.uint8, device=dev)
         arg = torch.empty(V, 4, 64, dtype=torch.uint8, device=dev)
-        ms2 = _time_ms(lambda: ops.check(lib.adkf_pna_aggregate_fwd(ops.dptr(pre), ops.dptr(ts.tptr), V, ops.dptr(out), ops.dptr(cnt),
-                                                                    ops.dptr(arg), ops.stream_ptr()), "adkf_pna_aggregate_fwd"))
-    alg2 = 4.0 * 768 * E + 4.0 * 3072 * V + 512.0 * V + 4.0 * (V + 1)
+        ms2 = _time_ms(lambda: ops.check(lib.adkf_mp_aggregate_fwd(ops.dptr(pre), ops.dptr(ts.tptr), V, ops.MP_MULTIAGGR, ops.dptr(out),
+                                                                   ops.dptr(cnt), ops.dptr(arg), ops.stream_ptr()),
+                                         "adkf_mp_aggregate_fwd"))
+    alg2 = 4.0 * 768 * E + 4.0 * 1024 * V + 512.0 * V + 4.0 * (3 * V + 1)
     hbm = peaks.get("hbm_gbs") or 6650.0
-    roof["hbm_kernel"] = {"kernel": "pna_aggregate_fwd_kernel", "bound": "hbm", "achieved": round(alg2 / (ms2 * 1e-3) / 1e9, 1),
+    roof["hbm_kernel"] = {"kernel": "pna_aggregate_fwd_kernel<false> (unscaled aggregate [V,1024])", "bound": "hbm", "achieved": round(alg2 / (ms2 * 1e-3) / 1e9, 1),
                           "peak": hbm, "unit": "GB/s", "frac": round(alg2 / (ms2 * 1e-3) / 1e9 / hbm, 4), "launch_ms": round(ms2, 4),
                           "algorithmic_bytes": alg2, "nodes": V, "directed_edges": E}
     return roof

@@ -270,6 +270,13 @@ int adkf_linear_tf32x3(const float* X, int64_t M, int32_t K, int64_t ldx, const 
 int adkf_gemm_tf32x3(const float* A, int32_t transA, int64_t lda, const float* B, int32_t transB, int64_t ldb,
                      int64_t M, int32_t N, int32_t K, const float* bias, int32_t act, float* D, int64_t ldd,
                      float* splitk_ws, int64_t splitk_ws_floats, void* stream);
+
+/* D[M,N] = (opA(A) . opB(B)^T) * act'(mask[M,N]): the input-gradient GEMM of a dense layer fused with the activation derivative
+ * of the layer below (autograd of Linear -> ReLU / LeakyReLU(0.01) -> Linear: BOOMLayer gnn.py:79-95, MLP mlp.py:6-22).
+ * mask = the saved activation OUTPUT of the layer below (ldm floats per row), mask_act 1 relu / 2 leaky_relu. */
+int adkf_gemm_tf32x3_masked(const float* A, int32_t transA, int64_t lda, const float* B, int32_t transB, int64_t ldb,
+                            int64_t M, int32_t N, int32_t K, const float* mask, int64_t ldm, int32_t mask_act, float* D,
+                            int64_t ldd, void* stream);
 int64_t adkf_gemm_splitk_ws_floats(int64_t M, int32_t N, int32_t K);
 /* Batched form: `batch` products in one launch whose operands are column / row blocks of the same 2-D arrays (one TMA tensor
  * map per operand): batch b uses opA at (row + b*a_mn_stride, k + b*a_k_stride), opB likewise, writes D + b*d_stride and adds

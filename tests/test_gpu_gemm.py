@@ -197,3 +197,37 @@ def test_act_bwd_colsum(cuda_device, M, N, act):
     ref = want.double().sum(0)
     assert float((db.double() - ref).abs().max()) <= 2e-6 * float(want.double().abs().sum(0).max())
     assert torch.equal(db, db2)
+
+
+@pytest.mark.parametrize("act,M,K,H,N", [("leaky_relu", 1000, 128, 1024, 128), ("relu", 333, 1408, 768, 768),
+                                          ("relu", 130, 64, 36, 44)])
+def test_mlp2_tc_fused_backward(cuda_device, act, M, K, H, N):
+    """Linear -> act -> Linear as one autograd node (BOOM layer / hidden-layer MLPs): the input-gradient GEMM of the second
+    layer applies act'(hidden) in its epilogue.  All six gradients against fp64 autograd, and equal (to rounding) to the
+    unfused linear_tc chain; ragged tile edges (M, H, N not multiples of 128) included."""
+    from adkf_ift_b200 import ops
+    g = torch.Generator().manual_seed(9)
+    x = torch.randn(M, K, generator=g)
+    w1, b1 = torch.randn(H, K, generator=g) / K ** 0.5, torch.randn(H, generator=g) * 0.1
+    w2, b2 = torch.randn(N, H, generator=g) / H ** 0.5, torch.randn(N, generator=g) * 0.1
+    go = torch.randn(M, N, generator=g)
+
+    def run(ts, fn):
+        ts = [t.clone().requires_grad_(True) for t in ts]
+        y = fn(*ts)
+        y.backward(go.to(y.device, y.dtype))
+        return [y.detach()] + [t.grad for t in ts]
+
+    def ref_fn(x, w1, b1, w2, b2):
+        h = torch.nn.functional.linear(x, w1, b1)
+        h = torch.relu(h) if act == "relu" else torch.nn.functional.leaky_relu(h, 0.01)
+        return torch.nn.functional.linear(h, w2, b2)
+
+    ref = run([t.double() for t in (x, w1, b1, w2, b2)], ref_fn)
+    dev = [t.to(cuda_device) for t in (x, w1, b1, w2, b2)]
+    got = run(dev, lambda x, w1, b1, w2, b2: ops.mlp2_tc(x, w1, b1, act, w2, b2))
+    unf = run(dev, lambda x, w1, b1, w2, b2: ops.linear_tc(ops.linear_tc(x, w1, b1, act), w2, b2))
+    for name, a, u, r in zip(("y", "dx", "dw1", "db1", "dw2", "db2"), got, unf, ref):
+        e, eu = rel(a, r), rel(u, r)
+        print(f"mlp2_tc {act} {name}: rel err fused {e:.3e} unfused {eu:.3e}")
+        assert e < 5e-6, name
