@@ -82,3 +82,31 @@ def test_flat_params_views_and_clip():
     assert abs(float(torch.linalg.vector_norm(flat.grad, dtype=torch.float64)) - 1.0) < 1e-4
     assert float(p0.grad.flatten()[0]) == float(flat.grad[0])
     assert "fc.0.weight" in model.state_dict()               # names survive the flattening
+
+
+def test_release_and_gather_grads_equal_view_accumulation():
+    """train_step hands the meta-gradient over through FlatParams.release_grads / gather_grads: autograd assigns fresh
+    gradient tensors (no per-parameter `+=` launch) and ONE multi-tensor copy moves them into the flat buffer.  Same flat
+    gradient as accumulating into the views; parameters that took no part keep zeros; views are re-attached."""
+    model = _model()
+    flat = model._ensure_flat()
+    params = model.feature_extractor_params()
+    used = params[: len(params) // 2]                         # the second half stays unused in this "step"
+
+    def loss():
+        return sum((p * p).sum() * (i + 1) for i, p in enumerate(used)) * 1e-3
+
+    flat.zero_grad()
+    loss().backward()
+    ref = flat.grad.clone()
+    assert float(ref.abs().sum()) > 0
+    flat.grad.fill_(7.0)                                      # stale content must not survive
+    flat.release_grads()
+    assert all(p.grad is None for p in params)
+    loss().backward()
+    assert used[0].grad.data_ptr() != flat.grad.data_ptr()    # autograd handed over a fresh tensor
+    flat.gather_grads()
+    assert torch.equal(flat.grad, ref)
+    for p, n, off in zip(flat.params, flat.sizes, flat.offsets):
+        assert p.grad.data_ptr() == flat.grad[off:off + n].data_ptr()
+    assert float(params[-1].grad.abs().max()) == 0.0
