@@ -84,8 +84,7 @@ def run_on_task_batch(model: ADKTModel, tb: DeviceTaskBatch, train: bool = False
         scale = (1.0 / tb.num_tasks) if grad_scale is None else grad_scale
         Z.backward(dZ * scale)
         F_t = aux[:, ops.AUX_FOUTER]
-        n_q = torch.tensor([r - s for r, s in zip(tb.layout.n_rows_host, tb.layout.n_sup_host)],
-                           dtype=torch.float32).to(Z.device, non_blocking=True)
+        n_q = ops.host_to_device([float(r - s) for r, s in zip(tb.layout.n_rows_host, tb.layout.n_sup_host)], torch.float32, Z.device)
         return TaskBatchResult(phi=fit.phi, status=status | fit.status, aux=aux, outer_loss=F_t,
                                loss_per_sample=F_t / n_q)
     model.eval()

@@ -83,7 +83,7 @@ class _SharedPhiNegMLL(torch.autograd.Function):
         if ls_loc is not None:
             aux0[:, ops.AUX_LS_LOC] = ls_loc
         dZ, aux, status = g.hypergradient(gpk.FitResult(phi, aux0, None), mode=2)
-        rows = torch.tensor(layout.n_rows_host, device=Z.device)
+        rows = ops.host_to_device(layout.n_rows_host, torch.int64, Z.device)
         ctx.save_for_backward(dZ, aux, rows)
         ctx.shapes = (raw_noise.shape, raw_outputscale.shape, raw_lengthscale.shape)
         ctx.mark_non_differentiable(status)

@@ -508,6 +508,16 @@ def ecfp_linear(base, fp, Wt):
 # --------------------------------------------------------------------------------------------------
 # batched GP tail
 # --------------------------------------------------------------------------------------------------
+def host_to_device(values, dtype, device) -> torch.Tensor:
+    """Small host list -> device tensor through PINNED memory with an asynchronous copy: `torch.tensor(list, device=cuda)`
+    copies from pageable memory, which blocks the host until the stream reaches the copy -- one hidden synchronisation per
+    call on a step that must stay asynchronous."""
+    t = torch.tensor(values, dtype=dtype)
+    if torch.device(device).type != "cuda":
+        return t.to(device)
+    return t.pin_memory().to(device, non_blocking=True)
+
+
 @dataclass
 class TaskLayout:
     """Row layout of a batch of T tasks inside Z / y: task t owns rows [z_off[t], z_off[t+1]) with the
@@ -532,9 +542,9 @@ class TaskLayout:
             z_off.append(z_off[-1] + r)
             d2_off.append(d2_off[-1] + r * r)
         return TaskLayout(T, [int(x) for x in n_sup], rows,
-                          torch.tensor(z_off, dtype=torch.int32, device=device),
-                          torch.tensor([int(x) for x in n_sup], dtype=torch.int32, device=device),
-                          torch.tensor(d2_off, dtype=torch.int64, device=device),
+                          host_to_device(z_off, torch.int32, device),
+                          host_to_device([int(x) for x in n_sup], torch.int32, device),
+                          host_to_device(d2_off, torch.int64, device),
                           max(rows) if rows else 0, z_off[-1], d2_off[-1])
 
     def ws_floats(self, which: int) -> int:

@@ -118,3 +118,61 @@ def to_device(hb: HostTaskBatch, device, build_index: bool = True) -> DeviceTask
     if build_index:
         db.graph_index = ops.build_graph_index(adjs, hb.num_nodes, n2g, hb.num_graphs)
     return db
+
+
+class DevicePrefetcher:
+    """Double-buffered staging of collated task batches: the H2D copies and the device-side CSR build of batch i+1 run on a
+    side stream while the compute stream works on batch i (the reference copies field by field, synchronously, inside
+    `torchify`, fs_mol/utils/torch_utils.py:7-28).  `next()` makes the compute stream wait for the copy event only.
+
+        pf = DevicePrefetcher(iter_of_host_batches, device)
+        for tb in pf: model.train_step(tb)
+    """
+
+    def __init__(self, host_batches, device, build_index: bool = True):
+        self._it = iter(host_batches)
+        self._device = torch.device(device)
+        self._build_index = build_index
+        self._stream = torch.cuda.Stream(device=self._device)
+        self._ready = None
+        self._issue()
+
+    def _issue(self):
+        try:
+            hb = next(self._it)
+        except StopIteration:
+            self._ready = None
+            return
+        self._stream.wait_stream(torch.cuda.current_stream(self._device))   # buffers freed by the compute stream are safe to reuse
+        with torch.cuda.stream(self._stream):
+            tb = to_device(hb, self._device, build_index=self._build_index)
+            ev = torch.cuda.Event()
+            ev.record(self._stream)
+        self._ready = (tb, ev)
+
+    def __iter__(self):
+        return self
+
+    def __next__(self) -> DeviceTaskBatch:
+        if self._ready is None:
+            raise StopIteration
+        tb, ev = self._ready
+        cur = torch.cuda.current_stream(self._device)
+        cur.wait_event(ev)
+        for t in _tensors_of(tb):
+            t.record_stream(cur)             # allocated on the side stream, consumed on the compute stream
+        self._issue()                        # start staging the next batch behind the work about to be queued
+        return tb
+
+
+def _tensors_of(obj):
+    import dataclasses
+    if torch.is_tensor(obj):
+        if obj.is_cuda:
+            yield obj
+    elif isinstance(obj, (list, tuple)):
+        for o in obj:
+            yield from _tensors_of(o)
+    elif dataclasses.is_dataclass(obj) and not isinstance(obj, type):
+        for f in dataclasses.fields(obj):
+            yield from _tensors_of(getattr(obj, f.name))

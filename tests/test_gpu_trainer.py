@@ -85,3 +85,30 @@ def test_load_model_gnn_weights(cuda_device, tmp_path):
     lrs = [g["lr"] for g in model.optimizer.param_groups]
     assert len(lrs) == 2 and lrs[1] == 0.0 and abs(lrs[0] - 1e-4) < 1e-12          # warm-up: the loaded group starts at 0
     assert sum(p.numel() for p in model.optimizer.param_groups[1]["params"]) == sum(p.numel() for p in model.graph_feature_extractor.parameters())
+
+
+def test_device_prefetcher_matches_direct_staging(cuda_device):
+    """task_batch.DevicePrefetcher (side-stream H2D + CSR build, double buffered) yields the same device batches, in order,
+    as task_batch.to_device, and a model step on them gives bit-identical results."""
+    from adkf_ift_b200 import dkt, synthetic, task_batch
+    from adkf_ift_b200.adaptive_dkt import ADKTModelTrainerConfig
+    from adkf_ift_b200.adaptive_dkt_utils import ADKTModelTrainer, run_on_task_batch
+    from adkf_ift_b200.feature_extractor import cli_default_config
+    model = ADKTModelTrainer(ADKTModelTrainerConfig(graph_feature_extractor_config=cli_default_config(2)))
+    synthetic.deterministic_init_(model, seed=0, alpha=0.5)
+    model.to(cuda_device)
+    hbs = []
+    for j in range(3):
+        hosts = [dkt.task_sample_to_dkt_task_sample(synthetic.make_task_sample(300 + 10 * j + t, 16, 20 + j),
+                                                    dkt.get_dkt_batcher(max_num_graphs=320), False).batches[0] for t in range(2)]
+        hbs.append(task_batch.collate_tasks(hosts, False))
+    got = list(task_batch.DevicePrefetcher(iter(hbs), cuda_device))
+    assert len(got) == 3
+    for hb, tb in zip(hbs, got):
+        ref = task_batch.to_device(hb, cuda_device)
+        assert torch.equal(tb.node_features, ref.node_features) and torch.equal(tb.fingerprints, ref.fingerprints)
+        assert torch.equal(tb.graph_index.rowptr, ref.graph_index.rowptr)
+        assert torch.equal(tb.graph_index.col_src, ref.graph_index.col_src)
+        a = run_on_task_batch(model, tb, train=False)
+        b = run_on_task_batch(model, ref, train=False)
+        assert torch.equal(a.mean, b.mean) and torch.equal(a.phi, b.phi)
