@@ -346,7 +346,13 @@ class ADKTModelTrainer(ADKTModel):
                         optimizer=self.optimizer,
                         lr_lambda=[partial(linear_warmup, warmup_steps=0), partial(linear_warmup, warmup_steps=100)])
             else:
-                self.optimizer = torch.optim.Adam(params, self.config.learning_rate, fused=params[0].is_cuda)
+                # one learning rate for everything: Adam runs on the FLAT buffer as a single tensor (one launch at HBM speed
+                # instead of 11 multi-tensor launches over 375 small tensors: 1.07 -> 0.15 ms); element-wise identical, the
+                # zero padding between tensors stays zero (g = m = v = 0 -> update 0)
+                fp = torch.nn.Parameter(self._flat.flat)
+                fp.grad = self._flat.grad
+                self._flat_param = [fp]                      # kept in a list: not a registered parameter, state_dict unchanged
+                self.optimizer = torch.optim.Adam([fp], self.config.learning_rate, fused=params[0].is_cuda)
         return self._flat
 
     def reduce_and_update(self):
