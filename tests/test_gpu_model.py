@@ -276,3 +276,45 @@ def test_c2_full_size_step_properties(cuda_device):
             assert torch.equal(p.grad, g1[n]), n
         elif not n.startswith("gp_"):
             assert p.grad is not None and float(p.grad.abs().max()) == 0.0   # unused parameters keep zeros
+
+
+@pytest.mark.parametrize("variant", ["gnn+ecfp+pc-descs+fc", "ecfp+fc", "pc-descs+fc"])
+def test_used_features_variants_match_reference(cuda_device, golden_dir, variant):
+    """Every `used_features` variant the reference's ADKTModel can actually construct (the four without "+fc" raise
+    AttributeError: no fc_out_dim, adaptive_dkt.py:48-66 -> recorded in the fixture): GP inputs <=1e-4, posterior at the
+    reference's phi* <=1e-4, own fit <=2e-3 (tests/golden/make_golden_features.py ran the reference's own files)."""
+    from adkf_ift_b200 import dkt, synthetic, task_batch
+    from adkf_ift_b200.adaptive_dkt import ADKTModelTrainerConfig
+    from adkf_ift_b200.adaptive_dkt_utils import ADKTModelTrainer, run_on_task_batch
+    from adkf_ift_b200.feature_extractor import cli_default_config
+    g = np.load(os.path.join(golden_dir, "used_features.npz"))
+    for v in ("gnn+ecfp", "ecfp", "gnn", "pc-descs"):
+        assert int(g[v.replace("+", "_").replace("-", "") + "_ok"]) == 0      # the reference cannot build these
+    key = variant.replace("+", "_").replace("-", "")
+    assert int(g[key + "_ok"]) == 1
+    task_id, n_s, n_q, layers = (int(x) for x in g["meta"])
+    model = ADKTModelTrainer(ADKTModelTrainerConfig(graph_feature_extractor_config=cli_default_config(layers),
+                                                    used_features=variant))
+    synthetic.deterministic_init_(model, seed=0, alpha=0.5)
+    model.to(cuda_device)
+    host = dkt.task_sample_to_dkt_task_sample(synthetic.make_task_sample(task_id, n_s, n_q),
+                                              dkt.get_dkt_batcher(max_num_graphs=320), False)
+    tb = task_batch.to_device(task_batch.collate_tasks([host.batches[0]], False), cuda_device)
+    with torch.no_grad():
+        Z = model.embed(tb).cpu().numpy()
+    e = rel(Z[:n_s], g[key + "_z_support"])
+    print(variant, "z_support rel err", e)
+    assert e < 1e-4
+    phi_ref = torch.from_numpy(g[key + "_phi_star"].astype(np.float32)).view(1, 3)
+    fixed = run_on_task_batch(model, tb, train=False, phi=phi_ref)
+    assert rel(fixed.mean.cpu().numpy()[n_s:], g[key + "_mean"]) < 1e-4
+    assert rel(fixed.variance.cpu().numpy()[n_s:], g[key + "_variance"]) < 1e-4
+    fitted = run_on_task_batch(model, tb, train=False)
+    assert int(fitted.status.item()) & 6 == 0
+    assert rel(fitted.mean.cpu().numpy()[n_s:], g[key + "_mean"]) < 2e-3
+    assert rel(fitted.variance.cpu().numpy()[n_s:], g[key + "_variance"]) < 2e-3
+    # and the whole training pass runs (descriptor block of fc[0] gets a gradient)
+    model.zero_grad(set_to_none=True)
+    run_on_task_batch(model, tb, train=True)
+    assert model.fc[0].weight.grad is not None and torch.isfinite(model.fc[0].weight.grad).all()
+    assert float(model.fc[0].weight.grad.abs().sum()) > 0
