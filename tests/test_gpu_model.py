@@ -318,3 +318,45 @@ def test_used_features_variants_match_reference(cuda_device, golden_dir, variant
     run_on_task_batch(model, tb, train=True)
     assert model.fc[0].weight.grad is not None and torch.isfinite(model.fc[0].weight.grad).all()
     assert float(model.fc[0].weight.grad.abs().sum()) > 0
+
+
+def test_ignore_grad_correction_matches_reference(cuda_device, golden_dir):
+    """ADKTModelTrainerConfig.ignore_grad_correction=True (adaptive_dkt_utils.py:66 -> cauchy_hypergradient.py:66-70): the fused
+    path drops the implicit term (adkf_gp_ift mode 1) and must reproduce the reference's whole-model gradients at its phi*
+    (per-tensor norms and seeded probe dots <=1e-3); with the correction on, the same task gives a DIFFERENT gradient."""
+    from adkf_ift_b200 import dkt, synthetic, task_batch
+    from adkf_ift_b200.adaptive_dkt import ADKTModelTrainerConfig
+    from adkf_ift_b200.adaptive_dkt_utils import ADKTModelTrainer, run_on_task_batch
+    from adkf_ift_b200.feature_extractor import cli_default_config
+    g = np.load(os.path.join(golden_dir, "ignore_grad_correction.npz"))
+    task_id, n_s, n_q, layers = (int(x) for x in g["meta"])
+    host = dkt.task_sample_to_dkt_task_sample(synthetic.make_task_sample(task_id, n_s, n_q),
+                                              dkt.get_dkt_batcher(max_num_graphs=320), False)
+    names = [str(x) for x in g["grad_names"]]
+    phi = torch.from_numpy(g["phi_star"].astype(np.float32)).view(1, 3)
+    got = {}
+    for flag in (True, False):
+        model = ADKTModelTrainer(ADKTModelTrainerConfig(graph_feature_extractor_config=cli_default_config(layers),
+                                                        ignore_grad_correction=flag))
+        synthetic.deterministic_init_(model, seed=0, alpha=0.5)
+        model.to(cuda_device)
+        tb = task_batch.to_device(task_batch.collate_tasks([host.batches[0]], False), cuda_device)
+        model.zero_grad(set_to_none=True)
+        res = run_on_task_batch(model, tb, train=True, grad_scale=1.0, phi=phi)
+        params = dict(model.named_parameters())
+        got[flag] = (float(res.outer_loss.item()),
+                     np.array([params[n].grad.double().norm().item() if params[n].grad is not None else 0.0 for n in names]),
+                     np.array([(params[n].grad.double().cpu() * probe_vector(n, params[n].shape)).sum().item()
+                               if params[n].grad is not None else 0.0 for n in names]),
+                     np.sqrt([params[n].numel() for n in names]))
+    F, norms, dots, rt = got[True]
+    ref_n, ref_d = g["grad_norms"], g["grad_dots"]
+    assert abs(F - float(g["F"])) < 2e-4 * abs(float(g["F"]))
+    big = ref_n > 1e-3 * ref_n.max()
+    e_norm = (np.abs(norms - ref_n)[big] / ref_n[big]).max()
+    e_dot = (np.abs(dots - ref_d) / np.maximum(ref_n, 1e-3 * ref_n.max()) / rt).max()
+    print("ignore_grad_correction: F", F, "grad-norm err", e_norm, "probe-dot err", e_dot)
+    assert e_norm < 1e-3 and e_dot < 1e-3
+    diff = (np.abs(got[False][1] - ref_n)[big] / ref_n[big]).max()
+    print("with the correction the gradient differs by", diff)
+    assert diff > 1e-2
