@@ -236,6 +236,47 @@ def dkt_run_on_task_batch(model: DKTModel, tb, train: bool = False, grad_scale: 
         return mean, var, qm, (mq if model.config.use_numeric_labels else torch.sigmoid(mq))
 
 
+class DKTModelTrainer(DKTModel):
+    """fs_mol/utils/dkt_utils.py:283-431 reduced to the step itself: Adam over ALL parameters (extractor + the shared GP
+    parameters, :296-303), optional clip_grad_norm_ (:383-384).  `train_step` runs the `tasks_per_batch` tasks of a collated
+    DeviceTaskBatch in one pass (dkt_run_on_task_batch) instead of one run_on_batches call per task."""
+
+    def __init__(self, config: DKTModelTrainerConfig):
+        super().__init__(config)
+        self.optimizer = torch.optim.Adam(self.parameters(), config.learning_rate)
+        self.lr_scheduler = None
+
+    def train_step(self, tb):
+        """Returns the mean per-sample loss of the step, as the reference logs it (dkt_utils.py:95-100, 386)."""
+        self.optimizer.zero_grad(set_to_none=True)
+        losses, status = dkt_run_on_task_batch(self, tb, train=True)
+        if self.config.clip_value is not None:
+            torch.nn.utils.clip_grad_norm_(self.parameters(), self.config.clip_value)
+        self.optimizer.step()
+        if self.lr_scheduler is not None:
+            self.lr_scheduler.step()
+        return losses.mean(), status
+
+    def get_model_state(self):
+        return {"model_config": self.config, "model_state_dict": self.state_dict()}
+
+    def save_model(self, path: str, optimizer=None, epoch=None):
+        data = self.get_model_state()
+        if optimizer is not None:
+            data["optimizer_state_dict"] = optimizer.state_dict()
+        if epoch is not None:
+            data["epoch"] = epoch
+        torch.save(data, path)
+
+    @classmethod
+    def build_from_model_file(cls, model_file: str, config_overrides=None, quiet: bool = False, device=None):
+        ck = torch.load(model_file, map_location=device, weights_only=False)
+        model = cls(ck["model_config"])
+        own = model.state_dict()
+        model.load_state_dict({k: v for k, v in ck["model_state_dict"].items() if k in own}, strict=False)
+        return model.to(device) if device is not None else model
+
+
 def gpst_test(train_fp: torch.Tensor, y_train: torch.Tensor, test_fp: torch.Tensor, y_test,
               use_numeric_labels: bool, test_batch_size: int = 700):
     """GP-ST (fs_mol/gpst_test.py:37-116): single-task Tanimoto GP on binary fingerprints.  `train_fp` / `test_fp`
