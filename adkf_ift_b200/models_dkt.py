@@ -313,3 +313,32 @@ def gpst_test(train_fp: torch.Tensor, y_train: torch.Tensor, test_fp: torch.Tens
     else:
         m = metrics.compute_binary_task_metrics(predictions=pred, labels=y_te)
     return m, pred, model._phi()
+
+
+def gpst_run_on_tasks(train_fps: Sequence[torch.Tensor], train_ys: Sequence[torch.Tensor], test_fps: Sequence[torch.Tensor],
+                      use_numeric_labels: bool, fit_max_iter: int = 100, fit_gtol: float = 2e-6):
+    """GP-ST over T tasks in ONE launch per stage (Tanimoto pair statistics, fit, posterior): what `gpst_test` does one task
+    at a time (fs_mol/gpst_test.py:68-104).  train_ys are the CONVERTED training targets (+-1, or standardised log-activities).
+    Returns (list of per-task predictions on the test molecules -- sigmoid(mean) for classification --, phi* [T,3], status [T])."""
+    dev = train_fps[0].device
+    n_s = [int(x.shape[0]) for x in train_fps]
+    n_q = [int(x.shape[0]) for x in test_fps]
+    Z = torch.cat([t for pair in zip(train_fps, test_fps) for t in pair]).float().contiguous()
+    y = torch.cat([t for ys, m in zip(train_ys, n_q) for t in (ys.float().to(dev), torch.zeros(m, device=dev))]).contiguous()
+    layout = ops.TaskLayout.build(n_s, n_q, dev)
+    g = gpk.BatchedExactGP(Z, y, layout, "tanimoto", use_numeric_labels, use_lengthscale_prior=False, qq_block=False,
+                           freeze=0 if use_numeric_labels else ops.FREEZE_NOISE)        # gp_utils.py:143
+    g.noise_loc = float("nan")                                                          # no priors in GP-ST
+    T = len(n_s)
+    noise0 = torch.tensor(gpk.noise_init(use_numeric_labels) - gpk.NOISE_FLOOR)
+    phi0 = torch.zeros(T, 3, dtype=torch.float32)
+    phi0[:, 0] = noise0 + torch.log(-torch.expm1(-noise0))                              # inverse softplus
+    start = gpk.FitResult(phi0.to(dev), torch.zeros(T, ops.AUX, dtype=torch.float32, device=dev), None)
+    res = g.fit(start=start, max_iter=fit_max_iter, gtol=fit_gtol)
+    mean, _, st = g.predict(res.phi)
+    preds, off = [], 0
+    for a, b in zip(n_s, n_q):
+        mq = mean[off + a: off + a + b]
+        preds.append(mq if use_numeric_labels else torch.sigmoid(mq))
+        off += a + b
+    return preds, res.phi, res.status | st
