@@ -897,6 +897,68 @@ __device__ bool build_and_factor_blocked(const GpProblem& pb, const Hyper& h, fl
     return false;
 }
 
+// IFT correction on the support block:  Wm_ss += sign (1/n) [ Gamdot o Ku + Gam o Kudot ], the derivative of df/dD2 along the
+// psi-space direction sh.pd (= t o raw direction).  sign -1: hypergradient (direction v = H^-1 dF/dphi, App. B);
+// sign +1: the mixed second derivative d/deps df/dD2(phi + eps u) for a caller-supplied u (mode 3: double backward of f).
+__device__ void ift_correction(const Carve& cv, int n, int N, const float* __restrict__ D2t, const Hyper& h, int kind,
+                               float* __restrict__ Wt, const float* __restrict__ alpha, GpShared& sh, bool in_smem,
+                               float* smem_f, float* small_ws, float sign) {
+    const float pd0 = sh.pd[0], pd1 = sh.pd[1], pd2 = sh.pd[2];
+    // M2 <- Adot = pd0 I + pd1 K/s + pd2 S   (M2 currently holds S)
+    for (int idx = threadIdx.x; idx < n * n; idx += blockDim.x) {
+        const int i = idx / n, j = idx - i * n;
+        const float k = kernel_only(D2t[(size_t)i * N + j], h.s, h.l, kind);
+        float v = pd1 * k / h.s + pd2 * cv.M2[(size_t)i * cv.ld + j];
+        if (i == j) v += pd0;
+        cv.M2[(size_t)i * cv.ld + j] = v;
+    }
+    __syncthreads();
+    // one warp per row i: X_i = P_i: Adot ; Pdot_i: = -X_i P ; adot_i = -X_i . alpha
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, nw = blockDim.x >> 5;
+    float* adot = cv.vec + n;           // u, w, q no longer needed
+    float* xrow_all = cv.vec + 2 * n;   // needs nw * n floats: placed after vec in the workspace
+    // first pass: adot for every row (needs full X rows) -- compute X row into per-warp buffer
+    float* xbuf = (in_smem ? (smem_f + (size_t)2 * n * cv.ld + 4 * (size_t)n) : (small_ws + (size_t)2 * n * cv.ld + 4 * (size_t)n));
+    (void)xrow_all;
+    for (int i = wid; i < n; i += nw) {
+        float* xr = xbuf + (size_t)wid * n;
+        const float* Pi = cv.M1 + (size_t)i * cv.ld;
+        float ad = 0.f;
+        for (int j = lane; j < n; j += 32) {
+            float acc = 0.f;
+            for (int k = 0; k < n; ++k) acc += Pi[k] * cv.M2[(size_t)k * cv.ld + j];
+            xr[j] = acc;
+            ad += acc * alpha[j];
+        }
+        ad = warp_sum(ad);
+        if (lane == 0) adot[i] = -ad;
+        __syncwarp();
+    }
+    __syncthreads();
+    for (int i = wid; i < n; i += nw) {
+        float* xr = xbuf + (size_t)wid * n;
+        const float* Pi = cv.M1 + (size_t)i * cv.ld;
+        // recompute X row (cheaper than storing an n x n X)
+        for (int j = lane; j < n; j += 32) {
+            float acc = 0.f;
+            for (int k = 0; k < n; ++k) acc += Pi[k] * cv.M2[(size_t)k * cv.ld + j];
+            xr[j] = acc;
+        }
+        __syncwarp();
+        for (int j = lane; j < n; j += 32) {
+            float pdot = 0.f;
+            for (int k = 0; k < n; ++k) pdot += xr[k] * cv.M1[(size_t)k * cv.ld + j];
+            pdot = -pdot;
+            const float gamdot = 0.5f * (pdot - adot[i] * alpha[j] - alpha[i] * adot[j]);
+            const float gam = 0.5f * (Pi[j] - alpha[i] * alpha[j]);
+            const KParts kp = kernel_parts(D2t[(size_t)i * N + j], h.s, h.l, kind);
+            const float kudot = pd1 * kp.Ku / h.s + pd2 * kp.Kul;
+            Wt[(size_t)i * N + j] += sign * (gamdot * kp.Ku + gam * kudot) / n;
+        }
+        __syncwarp();
+    }
+}
+
 // =============================================================================================
 // kernel 3: IFT hypergradient pieces (F, dF/dphi, H, v, Wm)
 // =============================================================================================
@@ -978,6 +1040,23 @@ gp_ift_kernel(const int32_t* __restrict__ z_off, const int32_t* __restrict__ n_s
         return;
     }
 
+    if (ignore_corr == 3) {
+        // mixed second derivative of the inner loss along the raw-space direction u = aux[V..V+2]:
+        // Wm_ss = d/deps df/dD2(phi + eps u), zero elsewhere; aux F / G / H as in mode 2 (double backward of f = -MLL:
+        // H u is formed by the caller from aux H)
+        for (int idx = threadIdx.x; idx < N * N; idx += blockDim.x) Wt[idx] = 0.f;
+        if (threadIdx.x == 0) {
+            for (int i = 0; i < 3; ++i) sh.pd[i] = (pb.free_mask & (1 << i)) ? h.t[i] * auxt[ADKF_AUX_V + i] : 0.f;
+            auxt[ADKF_AUX_F] = sh.f;
+            for (int i = 0; i < 3; ++i) auxt[ADKF_AUX_G + i] = sh.g[i];
+            for (int i = 0; i < 9; ++i) auxt[ADKF_AUX_H + i] = sh.H[i];
+            status[t] = (jit_inner > 0.f) ? ADKF_ST_JITTER : ADKF_ST_OK;
+        }
+        __syncthreads();
+        ift_correction(cv, n, N, D2t, h, kind, Wt, alpha, sh, in_smem, smem_f, small_ws, 1.f);
+        return;
+    }
+
     // ---- joint covariance J = K + sig2 I over support+query: Cholesky, inverse, beta --------------
     // blocked path when three 64 x 64 tiles fit behind the inner problem's shared-memory working set
     const size_t smem_used = in_smem ? ((size_t)2 * n * cv.ld + 4 * (size_t)n + (size_t)(blockDim.x >> 5) * n) : 0;
@@ -1050,62 +1129,7 @@ gp_ift_kernel(const int32_t* __restrict__ z_off, const int32_t* __restrict__ n_s
     if (prof) tk[5] = clock64();
 
     // ---- IFT correction on the support block:  Wm_ss -= (1/n) [ Gamdot o Ku + Gam o Kudot ] ---------
-    if (ignore_corr == 0) {
-        const float pd0 = sh.pd[0], pd1 = sh.pd[1], pd2 = sh.pd[2];
-        // M2 <- Adot = pd0 I + pd1 K/s + pd2 S   (M2 currently holds S)
-        for (int idx = threadIdx.x; idx < n * n; idx += blockDim.x) {
-            const int i = idx / n, j = idx - i * n;
-            const float k = kernel_only(D2t[(size_t)i * N + j], h.s, h.l, kind);
-            float v = pd1 * k / h.s + pd2 * cv.M2[(size_t)i * cv.ld + j];
-            if (i == j) v += pd0;
-            cv.M2[(size_t)i * cv.ld + j] = v;
-        }
-        __syncthreads();
-        // one warp per row i: X_i = P_i: Adot ; Pdot_i: = -X_i P ; adot_i = -X_i . alpha
-        const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, nw = blockDim.x >> 5;
-        float* adot = cv.vec + n;           // u, w, q no longer needed
-        float* xrow_all = cv.vec + 2 * n;   // needs nw * n floats: placed after vec in the workspace
-        // first pass: adot for every row (needs full X rows) -- compute X row into per-warp buffer
-        float* xbuf = (in_smem ? (smem_f + (size_t)2 * n * cv.ld + 4 * (size_t)n) : (small_ws + (size_t)2 * n * cv.ld + 4 * (size_t)n));
-        (void)xrow_all;
-        for (int i = wid; i < n; i += nw) {
-            float* xr = xbuf + (size_t)wid * n;
-            const float* Pi = cv.M1 + (size_t)i * cv.ld;
-            float ad = 0.f;
-            for (int j = lane; j < n; j += 32) {
-                float acc = 0.f;
-                for (int k = 0; k < n; ++k) acc += Pi[k] * cv.M2[(size_t)k * cv.ld + j];
-                xr[j] = acc;
-                ad += acc * alpha[j];
-            }
-            ad = warp_sum(ad);
-            if (lane == 0) adot[i] = -ad;
-            __syncwarp();
-        }
-        __syncthreads();
-        for (int i = wid; i < n; i += nw) {
-            float* xr = xbuf + (size_t)wid * n;
-            const float* Pi = cv.M1 + (size_t)i * cv.ld;
-            // recompute X row (cheaper than storing an n x n X)
-            for (int j = lane; j < n; j += 32) {
-                float acc = 0.f;
-                for (int k = 0; k < n; ++k) acc += Pi[k] * cv.M2[(size_t)k * cv.ld + j];
-                xr[j] = acc;
-            }
-            __syncwarp();
-            for (int j = lane; j < n; j += 32) {
-                float pdot = 0.f;
-                for (int k = 0; k < n; ++k) pdot += xr[k] * cv.M1[(size_t)k * cv.ld + j];
-                pdot = -pdot;
-                const float gamdot = 0.5f * (pdot - adot[i] * alpha[j] - alpha[i] * adot[j]);
-                const float gam = 0.5f * (Pi[j] - alpha[i] * alpha[j]);
-                const KParts kp = kernel_parts(D2t[(size_t)i * N + j], h.s, h.l, kind);
-                const float kudot = pd1 * kp.Ku / h.s + pd2 * kp.Kul;
-                Wt[(size_t)i * N + j] -= (gamdot * kp.Ku + gam * kudot) / n;
-            }
-            __syncwarp();
-        }
-    }
+    if (ignore_corr == 0) ift_correction(cv, n, N, D2t, h, kind, Wt, alpha, sh, in_smem, smem_f, small_ws, -1.f);
     if (prof) {
         tk[6] = clock64();
         printf("joint chol kcycles: load %lld chol_tile %lld inv_tile %lld store+panel %lld trailing %lld\n", g_jprof[0] / 1000,
@@ -1214,7 +1238,7 @@ extern "C" int adkf_gp_ift(int32_t T, const int32_t* z_off, const int32_t* n_sup
                            float* Wm, int32_t* status, float* ws, int64_t ws_floats, void* stream) {
     if (T <= 0) return 0;
     if (!z_off || !n_sup || !d2_off || !D2 || !y || !phi || !aux || !Wm || !status || !ws) return ADKF_ERR_BADARG;
-    if ((mode & 255) < 0 || (mode & 255) > 2) return ADKF_ERR_BADARG;   // bit 8: development probe (phase timings)
+    if ((mode & 255) < 0 || (mode & 255) > 3) return ADKF_ERR_BADARG;   // bit 8: development probe (phase timings)
     cudaStream_t s = (cudaStream_t)stream;
     int e = set_smem_attr((const void*)gp_ift_kernel);
     if (e) return e;

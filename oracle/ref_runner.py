@@ -102,9 +102,10 @@ def reference_meta_test(model, dkt_sample):
     return outs
 
 
-def reference_meta_train_task(model, batch, fit=True):
+def reference_meta_train_task(model, batch, fit=True, phi=None):
     """One task of train_loop (adaptive_dkt_utils.py:361-404) with the reference's own
-    cauchy_hypergradient and functional_call.  Returns F and the per-parameter gradients."""
+    cauchy_hypergradient and functional_call.  Returns F and the per-parameter gradients.
+    `phi` (3 raw values, with fit=False) replaces the inner fit by given GP parameters (fixed-phi goldens)."""
     from botorch.optim.fit import fit_gpytorch_scipy
     from fs_mol.utils._stateless import functional_call
     from fs_mol.utils.cauchy_hypergradient import cauchy_hypergradient
@@ -112,6 +113,10 @@ def reference_meta_train_task(model, batch, fit=True):
     _ = model(batch, train_loss=True)
     if fit:
         fit_gpytorch_scipy(model.mll)
+    elif phi is not None:
+        with torch.no_grad():
+            for p, v in zip(model.gp_params(), phi):
+                p.copy_(torch.as_tensor(v, dtype=p.dtype).reshape(p.shape))
     model.train()
     fe_names = [n for n, _ in model.named_parameters() if not n.startswith("gp_")]
     gp_names = [n for n, _ in model.named_parameters() if n.startswith("gp_")]

@@ -63,13 +63,23 @@ def test_fixed_phi_inner_and_ift(cuda_device, golden_dir, name, kind):
                                 init_mode=0, max_iter=0, phi=phi)
     a = aux.cpu().numpy()[0]
     assert int(st.item()) & ops.ST_NOT_PD == 0
+    # every tolerance below is max(1e-4, 3 x the reference's own fp32 error against its fp64 run) -- the north star's 1e-4
+    # wherever the reference itself achieves it
+    def tol(key):
+        return max(1e-4, 3 * rel(np.atleast_1d(g["fixed_f32_" + key]), np.atleast_1d(g["fixed_f64_" + key])))
     assert abs(a[ops.AUX_F] - g["fixed_f64_f"]) < 1e-4 * abs(g["fixed_f64_f"])
-    assert rel(a[ops.AUX_H:ops.AUX_H + 9].reshape(3, 3), g["fixed_f64_H"]) < 1e-3  # H in fp32: n^3 sums
+    e_H = rel(a[ops.AUX_H:ops.AUX_H + 9].reshape(3, 3), g["fixed_f64_H"])
+    print(name, "inner Hessian rel err", e_H, "tol", tol("H"))
+    assert e_H < tol("H")
     assert abs(a[ops.AUX_LS_LOC] - locs[1]) < 1e-5
     Wm, aux2, st2 = ops.gp_ift(layout, sq.D2, yd, kind, float(locs[0]), 1, phi, aux)
     b = aux2.cpu().numpy()[0]
     assert abs(b[ops.AUX_FOUTER] - g["fixed_f64_F"]) < 1e-4 * abs(g["fixed_f64_F"])
-    assert rel(b[ops.AUX_DF_DPHI:ops.AUX_DF_DPHI + 3], g["fixed_f64_dF_dphi"]) < 1e-3
+    e_dF = rel(b[ops.AUX_DF_DPHI:ops.AUX_DF_DPHI + 3], g["fixed_f64_dF_dphi"])
+    e_v = rel(b[ops.AUX_V:ops.AUX_V + 3], g["fixed_f64_v"])
+    print(name, "dF/dphi rel err", e_dF, "tol", tol("dF_dphi"), " v = H^-1 dF/dphi rel err", e_v, "tol", tol("v"))
+    assert e_dF < tol("dF_dphi")
+    assert e_v < tol("v")
     dZ = ops.gp_sqdist_bwd(Zd, layout, Wm, sq.mu, 1.0).cpu().numpy()
     ref = np.concatenate([g["fixed_f64_dL_dzs"], g["fixed_f64_dL_dzq"]])
     ref32 = np.concatenate([g["fixed_f32_dL_dzs"], g["fixed_f32_dL_dzq"]])

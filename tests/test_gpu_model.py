@@ -72,39 +72,68 @@ def test_meta_test_fixed_phi_and_fitted(cuda_device, golden_dir, name, kernel):
     assert rel(fitted.variance.cpu().numpy()[n:], g["test_variance"]) < 2e-3
 
 
+def _grad_metrics(norms, dots, ref_n, ref_d, numels):
+    """(max relative error of the per-tensor gradient norms over the tensors that carry > 1e-3 of the largest norm,
+    max error of the random-probe dot products relative to |g| sqrt(numel)) against a reference set."""
+    big = ref_n > 1e-3 * ref_n.max()
+    e_norm = np.abs(norms - ref_n)[big] / ref_n[big]
+    e_dot = np.abs(dots - ref_d) / np.maximum(ref_n, 1e-3 * ref_n.max()) / np.sqrt(numels)
+    return float(e_norm.max()), float(e_dot.max())
+
+
 @pytest.mark.parametrize("name,kernel", CASES)
 def test_meta_train_hypergradient_matches_cauchy_hypergradient(cuda_device, golden_dir, name, kernel):
-    """theta-gradients of one training task vs the reference's cauchy_hypergradient on the whole model."""
+    """theta-gradients of one training task vs the reference's cauchy_hypergradient on the whole model.
+
+    FIXED phi (the north star's 1e-4): the truth is the reference's own routine run in FP64 on the same weights / task /
+    phi (tests/golden/theta_grads_f64.npz, make_golden_f64.py); asserted  err(cuda) <= max(1e-4, 3 x err(reference fp32)),
+    the reference's fp32 error being measured against the same truth with the same metric.  FITTED (each side's own inner
+    optimum): 3e-3 against the fp32 fixture (SciPy's stopping error alone moves the reference by 3-4e-4)."""
     from adkf_ift_b200.adaptive_dkt_utils import run_on_task_batch
     g, model, host, tb = build(golden_dir, name, kernel, cuda_device)
+    g64 = np.load(os.path.join(golden_dir, "theta_grads_f64.npz"))
     names = [str(x) for x in g["grad_names"]]
     params = dict(model.named_parameters())
-    for tag, phi, tol in (("fixed", torch.from_numpy(g["train_phi_star"].astype(np.float32)).view(1, 3), 2e-4),
-                          ("fitted", None, 3e-3)):
+    numels = np.array([params[n].numel() for n in names], dtype=np.float64)
+    ref_n, ref_d = g["grad_norms"], g["grad_dots"]
+    n64, d64, F64 = g64[f"{name}::grad_norms"], g64[f"{name}::grad_dots"], float(g64[f"{name}::F"])
+    base_norm, base_dot = _grad_metrics(ref_n, ref_d, n64, d64, numels)          # the reference's own fp32 run vs fp64
+    for tag, phi in (("fixed", torch.from_numpy(g["train_phi_star"].astype(np.float32)).view(1, 3)), ("fitted", None)):
         model.zero_grad(set_to_none=True)
         res = run_on_task_batch(model, tb, train=True, grad_scale=1.0, phi=phi)
         F = float(res.outer_loss.item())
-        assert abs(F - float(g["train_F"])) < tol * abs(float(g["train_F"])), (tag, F, float(g["train_F"]))
         norms = np.array([params[n].grad.double().norm().item() if params[n].grad is not None else 0.0 for n in names])
         dots = np.array([(params[n].grad.double().cpu() * probe_vector(n, params[n].shape)).sum().item()
                          if params[n].grad is not None else 0.0 for n in names])
-        ref_n, ref_d = g["grad_norms"], g["grad_dots"]
-        big = ref_n > 1e-3 * ref_n.max()
-        e_norm = np.abs(norms - ref_n)[big] / ref_n[big]
-        e_dot = np.abs(dots - ref_d) / np.maximum(ref_n, 1e-3 * ref_n.max()) / np.sqrt([params[n].numel() for n in names])
-        print(name, tag, "F", F, "max rel grad-norm err", e_norm.max(), "max probe-dot err / (|g| sqrt(numel))", e_dot.max())
-        assert e_norm.max() < 5 * tol
-        assert e_dot.max() < 5 * tol
-        for n in ("fc.2.bias", "graph_feature_extractor.gnn.gnn_blocks.0.alpha",
-                  "graph_feature_extractor.init_node_proj.weight"):
-            # fc.2.bias shifts every feature row alike -> pairwise distances (hence F and f) do not depend on it:
-            # its true gradient is 0 and both sides hold rounding noise, so the error is measured against the
-            # largest per-tensor gradient norm as well
-            got, want = params[n].grad.cpu().numpy(), g["grad::" + n]
-            e = rel(got, want)
-            e_abs = float(np.abs(got - want).max() / ref_n.max())
-            print("   ", n, e, e_abs)
-            assert e < 5 * tol or e_abs < 1e-5
+        if tag == "fixed":
+            e_norm, e_dot = _grad_metrics(norms, dots, n64, d64, numels)
+            tol_n, tol_d, tol_F = max(1e-4, 3 * base_norm), max(1e-4, 3 * base_dot), 1e-4
+            eF = abs(F - F64) / abs(F64)
+            print(f"hypergradient {name} FIXED phi vs fp64 reference: F {eF:.2e}  grad-norm {e_norm:.2e} (reference fp32: "
+                  f"{base_norm:.2e}, tol {tol_n:.1e})  probe-dot {e_dot:.2e} (reference fp32: {base_dot:.2e}, tol {tol_d:.1e})")
+        else:
+            e_norm, e_dot = _grad_metrics(norms, dots, ref_n, ref_d, numels)
+            tol_n = tol_d = 1.5e-2
+            tol_F = 3e-3
+            eF = abs(F - float(g["train_F"])) / abs(float(g["train_F"]))
+            print(f"hypergradient {name} FITTED vs fp32 reference at its own optimum: F {eF:.2e} grad-norm {e_norm:.2e} "
+                  f"probe-dot {e_dot:.2e}")
+        assert eF < tol_F, (tag, F)
+        assert e_norm < tol_n, (tag, e_norm, tol_n)
+        assert e_dot < tol_d, (tag, e_dot, tol_d)
+        if tag == "fixed":
+            for n in ("fc.2.bias", "graph_feature_extractor.gnn.gnn_blocks.0.alpha",
+                      "graph_feature_extractor.init_node_proj.weight", "fc.0.bias",
+                      "graph_feature_extractor.gnn.gnn_blocks.0.mp_layers.0.message_fns.0._layers.0.weight"):
+                # fc.2.bias shifts every feature row alike -> pairwise distances (hence F and f) do not depend on it:
+                # its true gradient is 0 and every implementation holds rounding noise, so the error is also measured
+                # against the largest per-tensor gradient norm
+                got, want = params[n].grad.cpu().numpy(), g64[f"{name}::grad::{n}"]
+                e = rel(got, want)
+                e_abs = float(np.abs(got - want).max() / n64.max())
+                e_ref = rel(g["grad::" + n], want) if ("grad::" + n) in g else float("nan")
+                print(f"    {n}: max-abs rel {e:.2e} (reference fp32 {e_ref:.2e}), vs largest norm {e_abs:.2e}")
+                assert e < max(1e-4, 3 * (e_ref if e_ref == e_ref else 0.0)) or e_abs < 1e-5
         # unused parameters get zero gradients in the reference (cauchy_hypergradient.py:144-146)
         assert float(ref_n[[i for i, n in enumerate(names) if "mp_norm_layer" in n]].max()) == 0.0
 
