@@ -167,28 +167,70 @@ class MarginalLogLikelihood:
         return self._model.fit_gp(max_iter=max_iter, gtol=gtol)
 
 
+def _bind_task_gp(Z, raws, y, layout, cfg, ls_loc):
+    phi = torch.stack([r.detach().reshape(()) for r in raws]).view(1, 3).float().contiguous()
+    g = gpk.BatchedExactGP(Z, y, layout, cfg.gp_kernel, cfg.use_numeric_labels,
+                           use_lengthscale_prior=ls_loc is not None, qq_block=True)
+    aux0 = torch.zeros(1, ops.AUX, dtype=torch.float32, device=Z.device)
+    if ls_loc is not None:
+        aux0[0, ops.AUX_LS_LOC] = ls_loc
+    return g, gpk.FitResult(phi, aux0, None)
+
+
+class _InnerLossGrad(torch.autograd.Function):
+    """(df/dZ, df/draw_noise, df/draw_outputscale, df/draw_lengthscale) of the inner loss f = -MLL as a DIFFERENTIABLE
+    function of (Z, phi).  Its backward is the second-order information the generic hypergradient routine asks for
+    (cauchy_hypergradient.py:41-64,120-161): for a cotangent u on the phi-gradient it returns H u (w.r.t. phi, from the
+    kernel's analytic 3x3 Hessian) and the mixed term d/deps df/dZ(phi + eps u) (w.r.t. Z, adkf_gp_ift mode 3).  A
+    cotangent on df/dZ would need d2f/dZ2, which nothing on this path uses."""
+
+    @staticmethod
+    def forward(ctx, Z, raw_noise, raw_outputscale, raw_lengthscale, y, layout, cfg, ls_loc):
+        g, fit = _bind_task_gp(Z, (raw_noise, raw_outputscale, raw_lengthscale), y, layout, cfg, ls_loc)
+        dZ, aux, _ = g.hypergradient(fit, mode=2)
+        ctx.gp, ctx.fit = g, gpk.FitResult(fit.phi, aux, None)
+        ctx.shapes = (raw_noise.shape, raw_outputscale.shape, raw_lengthscale.shape)
+        ctx.set_materialize_grads(False)
+        gphi = aux[0, ops.AUX_G:ops.AUX_G + 3]
+        s = ctx.shapes
+        return dZ, gphi[0].reshape(s[0]), gphi[1].reshape(s[1]), gphi[2].reshape(s[2])
+
+    @staticmethod
+    def backward(ctx, cZ, c0, c1, c2):
+        if cZ is not None:
+            raise NotImplementedError("second derivative of the inner GP loss w.r.t. the features (d2f/dZ2) is not on the "
+                                      "ADKF-IFT path: only grad_phi f is differentiated again")
+        aux = ctx.fit.aux
+        u = torch.stack([(torch.zeros((), device=aux.device) if c is None else c.reshape(()).float()) for c in (c0, c1, c2)])
+        H = aux[0, ops.AUX_H:ops.AUX_H + 9].view(3, 3)
+        Hu = H @ u
+        dZ_mixed, _, _ = ctx.gp.inner_mixed_term(ctx.fit, u.view(1, 3))
+        s = ctx.shapes
+        return dZ_mixed, Hu[0].reshape(s[0]), Hu[1].reshape(s[1]), Hu[2].reshape(s[2]), None, None, None, None
+
+
 class _TaskGPLoss(torch.autograd.Function):
     """-MLL (inner) or predictive joint NLL (outer) of one task as a differentiable scalar of (Z, phi):
-    forward and first-order backward both come out of adkf_gp_ift (mode 2 / mode 1)."""
+    forward and first-order backward both come out of adkf_gp_ift (mode 2 / mode 1).  Under create_graph=True the
+    backward of the INNER loss is itself differentiable (_InnerLossGrad) -- the reference's own training-step sequence
+    (functional_call closures + the generic cauchy_hypergradient, adaptive_dkt_utils.py:361-404) runs on this model."""
 
     @staticmethod
     def forward(ctx, Z, raw_noise, raw_outputscale, raw_lengthscale, y, layout, cfg, ls_loc, outer: bool):
-        phi = torch.stack([raw_noise.reshape(()), raw_outputscale.reshape(()), raw_lengthscale.reshape(())]).view(1, 3)
-        g = gpk.BatchedExactGP(Z, y, layout, cfg.gp_kernel, cfg.use_numeric_labels,
-                               use_lengthscale_prior=ls_loc is not None, qq_block=True)
-        aux0 = torch.zeros(1, ops.AUX, dtype=torch.float32, device=Z.device)
-        if ls_loc is not None:
-            aux0[0, ops.AUX_LS_LOC] = ls_loc
-        fit = gpk.FitResult(phi.detach().float().contiguous(), aux0, None)
+        g, fit = _bind_task_gp(Z, (raw_noise, raw_outputscale, raw_lengthscale), y, layout, cfg, ls_loc)
         dZ, aux, _ = g.hypergradient(fit, mode=1 if outer else 2)
-        ctx.save_for_backward(dZ, aux)
+        ctx.save_for_backward(dZ, aux, Z, raw_noise, raw_outputscale, raw_lengthscale)
         ctx.outer = outer
+        ctx.rest = (y, layout, cfg, ls_loc)
         ctx.shapes = (raw_noise.shape, raw_outputscale.shape, raw_lengthscale.shape)
         return aux[0, ops.AUX_FOUTER if outer else ops.AUX_F].clone()
 
     @staticmethod
     def backward(ctx, go):
-        dZ, aux = ctx.saved_tensors
+        dZ, aux, Z, rn, ro, rl = ctx.saved_tensors
+        if torch.is_grad_enabled() and not ctx.outer:           # create_graph=True: keep the gradient differentiable
+            gZ, g0, g1, g2 = _InnerLossGrad.apply(Z, rn, ro, rl, *ctx.rest)
+            return gZ * go, g0 * go, g1 * go, g2 * go, None, None, None, None, None
         k = ops.AUX_DF_DPHI if ctx.outer else ops.AUX_G
         gphi = aux[0, k:k + 3] * go
         s = ctx.shapes

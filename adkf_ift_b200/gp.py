@@ -102,6 +102,20 @@ class BatchedExactGP:
         return dZ, aux, status
 
 
+    def inner_mixed_term(self, fit: FitResult, u: torch.Tensor):
+        """d/deps [df/dZ](phi + eps u) for the inner loss f = -MLL: the product of the mixed second derivative
+        d2f/dZ dphi with a raw-space direction u [T,3] (adkf_gp_ift mode 3).  Returns (dZ_mixed [rows,d], aux with
+        f / grad f / H).  This is what a double backward through the inner loss needs (cauchy_hypergradient.py:120-161
+        differentiates grad_phi f once more w.r.t. theta)."""
+        if not self.qq_block:
+            raise RuntimeError("inner_mixed_term uses the IFT workspace layout: construct with qq_block=True")
+        aux = fit.aux.clone()
+        aux[:, ops.AUX_V:ops.AUX_V + 3] = u.to(aux.dtype).view(-1, 3)
+        Wm, aux, status = ops.gp_ift(self.layout, self.sq.D2, self.y, self.karg, self.noise_loc, self.ls_prior,
+                                     fit.phi, aux, mode=3)
+        return ops.gp_sqdist_bwd(self.Z, self.layout, Wm, self.sq.mu, 1.0, stat=self.stat), aux, status
+
+
 class PredictiveDistribution:
     """Duck-type of the gpytorch MultivariateNormal the reference gets from `gp_likelihood(gp_model(x))`
     (adaptive_dkt.py:203): what run_on_batches and bayes_opt read."""

@@ -72,5 +72,33 @@ def cauchy_hypergradient(f_outer: Callable, f_inner: Callable, params_outer: Tup
     return F.detach()
 
 
+def functional_call(module: torch.nn.Module, parameters_and_buffers, args, kwargs=None):
+    """fs_mol/utils/_stateless.py:79-119: call `module` with some of its parameters / buffers replaced by the given
+    tensors (dotted names as in `named_parameters()`), for the duration of the call only.  The reference swaps the
+    module's class to intercept attribute reads; here the entries of the owning sub-module's `_parameters` / `_buffers`
+    are exchanged and restored, so code that reads `module.weight`, `named_parameters()` or `gp_params()` all sees the
+    substituted tensors (plain tensors are accepted: they need not be nn.Parameter)."""
+    if kwargs is None:
+        kwargs = {}
+    saved = []
+    try:
+        for name, tensor in parameters_and_buffers.items():
+            *path, leaf = name.split(".")
+            owner = module
+            for part in path:
+                owner = getattr(owner, part)
+            store = owner._parameters if leaf in owner._parameters else owner._buffers
+            if leaf not in store:
+                raise KeyError(f"functional_call: {type(module).__name__} has no parameter or buffer named '{name}'")
+            saved.append((store, leaf, store[leaf]))
+            store[leaf] = tensor
+        if isinstance(args, tuple):
+            return module(*args, **kwargs)
+        return module(args, **kwargs)
+    finally:
+        for store, leaf, original in reversed(saved):
+            store[leaf] = original
+
+
 # the JVP variant of the reference computes the same quantity with forward-over-reverse products
 cauchy_hypergradient_jvp = cauchy_hypergradient

@@ -261,3 +261,18 @@ def test_fsmol_on_disk_format_round_trip(tmp_path):
     # an empty adjacency list stays a [0,2] int64 array
     empty = [m for t in got.values() for m in t.samples for a in m.graph.adjacency_lists if a.shape[0] == 0]
     assert all(a.shape == (0, 2) for m in empty for a in m.graph.adjacency_lists if a.shape[0] == 0)
+
+
+def test_functional_call_restores_parameters():
+    """Semantics of functional_call (fs_mol/utils/_stateless.py:79-119): substitution for the call only, restoration
+    afterwards (also after an error), KeyError for unknown names."""
+    from adkf_ift_b200.hypergradient import functional_call
+    m = torch.nn.Sequential(torch.nn.Linear(3, 2), torch.nn.Linear(2, 1))
+    w = torch.randn(2, 3, requires_grad=True)
+    before = m[0].weight
+    y = functional_call(m, {"0.weight": w}, (torch.ones(4, 3),))
+    y.sum().backward()
+    assert w.grad is not None and m[0].weight is before
+    with pytest.raises(KeyError):
+        functional_call(m, {"0.nope": w}, (torch.ones(4, 3),))
+    assert m[0].weight is before
