@@ -113,8 +113,8 @@ def test_meta_train_hypergradient_matches_cauchy_hypergradient(cuda_device, gold
                   f"{base_norm:.2e}, tol {tol_n:.1e})  probe-dot {e_dot:.2e} (reference fp32: {base_dot:.2e}, tol {tol_d:.1e})")
         else:
             e_norm, e_dot = _grad_metrics(norms, dots, ref_n, ref_d, numels)
-            tol_n = tol_d = 1.5e-2
-            tol_F = 3e-3
+            tol_n = tol_d = 3e-3            # measured: <= 5.2e-4 (profiles/r2a_pytest_gpu_s.log)
+            tol_F = 1e-3
             eF = abs(F - float(g["train_F"])) / abs(float(g["train_F"]))
             print(f"hypergradient {name} FITTED vs fp32 reference at its own optimum: F {eF:.2e} grad-norm {e_norm:.2e} "
                   f"probe-dot {e_dot:.2e}")
