@@ -1,0 +1,502 @@
+// gemm_pair.cu -- the fp32-accurate tensor-core GEMM of gemm_tf32x3.cu on CTA PAIRS (tcgen05 cta_group::2), with the two
+// error-compensation products issued in bf16.
+//
+//   D[M,N] = A[M,K] . B[N,K]^T      one cluster of 2 CTAs (one TPC) per 256 x 128 output tile, persistent
+//
+// Why pairs.  ncu on the one-CTA kernel (profiles/r1h_ncu_full_summary.md): tensor pipe 63% active, shared-memory pipe
+// saturated -- 144 KB of smem traffic per 32-wide k-block (TMA fill + splitter read of A and B, hi/lo B tiles written and
+// read three times by the MMAs) against 768 tensor cycles.  112 of those 144 KB belong to the B operand.  With
+// tcgen05.mma.cta_group::2 the two CTAs of a pair share ONE B tile: each CTA loads, splits and stores only 64 of its 128
+// rows and the tensor cores of both SMs read both halves, so the B-side traffic per CTA halves; the A operand (own 128 rows,
+// split into TENSOR memory) is unchanged.
+//
+// Why bf16 corrections.  a.b ~ hi.hi + lo.hi + hi.lo with hi = tf32(v), lo = v - hi.  The two correction products are 2^-11
+// of the result and need ~2^-9 relative accuracy, which bf16 operands deliver: bf16(lo).bf16(hi) + bf16(hi).bf16(lo) runs as
+// ONE kind::f16 MMA chain over the concatenated operands [lo | hi] x [hi | lo] at twice the tf32 rate -- 2 tf32-equivalents
+// per product instead of 3 (the design ceiling moves from 1/3 to 1/2 of the tf32 peak) and the B-side correction tile
+// shrinks from 2 x 8 KB to 8 KB.  Error per product ~2^-20 (tests/test_gpu_gemm.py::test_linear_forward_fp32_class_accuracy).
+// The tf32 correction path is kept as a template switch (ADKF_GEMM_CORR=tf32) for A/B measurements.
+//
+// Per CTA (rank r of the pair), 640 threads, roles as in gemm_tf32x3.cu:
+//   warp 0      TMA producer   own A rows [m0 + 128 r, +128) and own B rows [n0 + 64 r, +64) of each k-block -> local raw ring
+//   warp 1      MMA issuer     rank 0 only: waits for the split stage of BOTH CTAs, issues 4 tf32 + 4 bf16 MMAs (M = 256 over
+//                              the pair), tcgen05.commit multicasts "stage consumed" / "accumulator full" to both CTAs
+//   warp 2      TMEM allocator (cta_group::2, both CTAs)
+//   warps 4-7   A splitter     own raw A tile -> hi (tf32) and [lo | hi] (bf16 pairs) in own TMEM
+//   warps 8-11  B splitter     own raw B half tile -> B_hi (tf32) and B_cat = [hi | lo] (bf16) K-major SWIZZLE_128B tiles in own smem
+//   warps 12-19 drain + epilogue of the own 128 x 128 half of the tile (RN accumulation in registers, see gemm_tf32x3.cu)
+// Cross-CTA signalling: splitter and drain warps of both CTAs arrive on the LEADER's mbarriers (mapa + mbarrier.arrive
+// .release.cluster); everything the leader tells the pair goes through the multicast commit.  Every wait is bounded (trap).
+#include <cuda.h>
+#include <cuda_bf16.h>
+#include <algorithm>
+#include <cstdlib>
+#include "gemm_common.cuh"
+
+namespace adkf {
+namespace pr {
+
+constexpr int kPM = 256;                             // pair tile rows (2 x kBM)
+constexpr int kBH = 64;                              // B rows held by one CTA
+constexpr int kRaw = 6;                              // raw ring depth
+constexpr int kSplit = 2;                            // split stages (B tiles in smem, A operand in TMEM)
+constexpr int kBHalfBytes = kBH * kBK * 4;           // 8 KB
+constexpr int kRawBytes = kTileBytes + kBHalfBytes;  // A 16 KB + B half 8 KB
+constexpr int kSplitBytes = 2 * kBHalfBytes;         // B_hi 8 KB + B_cat (or B_lo) 8 KB
+constexpr int kRingBytes = kRaw * kRawBytes + kSplit * kSplitBytes;   // 144 + 32 KB
+constexpr int kStageBytes = 8 * 4096;
+constexpr int kThreads = 640;
+constexpr int kTmemCols = 512;
+constexpr int kSmallCol = 2 * kBN;
+constexpr int kAopCol = 3 * kBN;                     // A operand: 2 stages x (32 tf32 columns + 32 correction columns)
+constexpr int kGroup = 4;
+constexpr size_t kSmem = (size_t)kRingBytes + kStageBytes + 1024 + 256;
+
+constexpr uint32_t kIdescTf32 = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(kBN >> 3) << 17) | ((uint32_t)(kPM >> 4) << 24);
+constexpr uint32_t kIdescBf16 = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(kBN >> 3) << 17) | ((uint32_t)(kPM >> 4) << 24);
+
+__device__ __forceinline__ uint32_t cluster_rank() {
+    uint32_t r;
+    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+    return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+    asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ uint32_t mapa_rank(uint32_t addr, uint32_t rank) {
+    uint32_t r;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(addr), "r"(rank));
+    return r;
+}
+// arrive on a barrier of (possibly) the other CTA of the pair; the address comes from mapa_rank
+__device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr) {
+    asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+}
+// wait on a LOCAL barrier whose arrivals may come from the other CTA
+__device__ __forceinline__ void mbar_wait_cluster(uint32_t bar, uint32_t parity) {
+    uint32_t done = 0, spins = 0;
+    while (true) {
+        asm volatile(
+            "{\n\t.reg .pred p;\n\t"
+            "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%1], %2;\n\t"
+            "selp.u32 %0, 1, 0, p;\n\t}"
+            : "=r"(done)
+            : "r"(bar), "r"(parity)
+            : "memory");
+        if (done) break;
+        if (++spins > (1u << 24)) __trap();   // a protocol error must not hang the GPU
+    }
+}
+__device__ __forceinline__ void umma2_tf32_ts(uint32_t tmem_d, uint32_t tmem_a, uint64_t bdesc, uint32_t idesc, uint32_t acc) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::2.kind::tf32 [%0], [%1], %2, %3, p;\n\t}"
+        ::"r"(tmem_d), "r"(tmem_a), "l"(bdesc), "r"(idesc), "r"(acc)
+        : "memory");
+}
+__device__ __forceinline__ void umma2_bf16_ts(uint32_t tmem_d, uint32_t tmem_a, uint64_t bdesc, uint32_t idesc, uint32_t acc) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::2.kind::f16 [%0], [%1], %2, %3, p;\n\t}"
+        ::"r"(tmem_d), "r"(tmem_a), "l"(bdesc), "r"(idesc), "r"(acc)
+        : "memory");
+}
+// arrives (count 1) on the barrier at this CTA-relative address in BOTH CTAs once all prior MMAs of the issuing thread retired
+__device__ __forceinline__ void umma2_commit(uint32_t bar) {
+    asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+                 ::"r"(bar), "h"((uint16_t)3)
+                 : "memory");
+}
+__device__ __forceinline__ uint32_t pack_bf16(float lo_k, float hi_k) {   // element k in the low half, k+1 in the high half
+    const __nv_bfloat162 v = __floats2bfloat162_rn(lo_k, hi_k);
+    return *reinterpret_cast<const uint32_t*>(&v);
+}
+
+// ---- A operand: row t of the raw A tile -> tensor memory --------------------------------------------------------------------
+//   columns [0,32)  : hi as tf32
+//   CORR16: columns [32,48) = bf16 pairs of lo, [48,64) = bf16 pairs of hi  (the [lo | hi] operand of the correction MMAs)
+//   else  : columns [32,64) = lo as tf32
+template <bool TR, bool CORR16>
+__device__ __forceinline__ void split_rows_to_tmem(const unsigned char* __restrict__ raw, uint32_t taddr, int t) {
+    float x[kBK];
+    if (!TR) {
+        const float4* __restrict__ r4 = reinterpret_cast<const float4*>(raw) + t * 8;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            const float4 v = r4[j ^ (t & 7)];
+            x[4 * j] = v.x; x[4 * j + 1] = v.y; x[4 * j + 2] = v.z; x[4 * j + 3] = v.w;
+        }
+    } else {
+        const float* __restrict__ rf = reinterpret_cast<const float*>(raw) + t;
+#pragma unroll
+        for (int k = 0; k < kBK; ++k) x[k] = rf[k * kBM];
+    }
+    uint32_t hi[kBK], co[kBK];
+#pragma unroll
+    for (int k = 0; k < kBK; ++k) hi[k] = __float_as_uint(tf32_hi(x[k]));
+    if (CORR16) {
+#pragma unroll
+        for (int c = 0; c < kBK / 2; ++c) {
+            const float h0 = __uint_as_float(hi[2 * c]), h1 = __uint_as_float(hi[2 * c + 1]);
+            co[c] = pack_bf16(x[2 * c] - h0, x[2 * c + 1] - h1);
+            co[kBK / 2 + c] = pack_bf16(h0, h1);
+        }
+    } else {
+#pragma unroll
+        for (int k = 0; k < kBK; ++k) co[k] = __float_as_uint(x[k] - __uint_as_float(hi[k]));
+    }
+    tmem_st32(taddr, hi);
+    tmem_st32(taddr + kBK, co);
+    tmem_st_wait();
+}
+
+// ---- B operand: raw half tile (64 rows x 32 k) -> B_hi (tf32) and the correction tile, K-major SWIZZLE_128B -------------------
+//   row r of a tile = 128 B, logical 16 B chunk j at physical chunk j ^ (r & 7)
+//   CORR16: correction tile row = [bf16 hi k0..31 | bf16 lo k0..31]  (chunks 0-3 hi, 4-7 lo)      else: lo as tf32
+//   TR = false: raw = TMA SWIZZLE_128B box (64 rows x 32 floats); thread t: float4 p = i*128 + t, i < 4 (row p/8, physical chunk p%8)
+//   TR = true : raw = [32 k][64 mn] floats; thread t: row mn = t & 63, k half t >> 6 (16 k values)
+template <bool TR, bool CORR16>
+__device__ __forceinline__ void split_b_half(const unsigned char* __restrict__ raw, unsigned char* __restrict__ hi_t,
+                                             unsigned char* __restrict__ co_t, int t) {
+    float4* __restrict__ hi4 = reinterpret_cast<float4*>(hi_t);
+    uint4* __restrict__ co4 = reinterpret_cast<uint4*>(co_t);
+    if (!TR) {
+        const float4* __restrict__ r4 = reinterpret_cast<const float4*>(raw);
+        float4 v[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) v[i] = r4[i * 128 + t];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            float4 hi, lo;
+            split4(v[i], hi, lo);
+            const int p = i * 128 + t;
+            hi4[p] = hi;
+            if (CORR16) {
+                const int row = p >> 3, j = (p & 7) ^ (row & 7);          // logical chunk of this float4: k = 4j .. 4j+3
+                const bool even = (j & 1) == 0;
+                // the lane holding logical chunk j ^ 1 is lane ^ 1 (same row, physical chunk ^ 1): exchange halves so that each
+                // lane owns one full 16-byte chunk of the correction row (even j: the 8 hi values k = 4j..4j+7; odd j: the 8 lo
+                // values k = 4j-4..4j+3) -- one conflict-free 16-byte store per lane
+                const uint32_t h0 = pack_bf16(hi.x, hi.y), h1 = pack_bf16(hi.z, hi.w);
+                const uint32_t l0 = pack_bf16(lo.x, lo.y), l1 = pack_bf16(lo.z, lo.w);
+                const uint32_t s0 = even ? l0 : h0, s1 = even ? l1 : h1;
+                const uint32_t r0 = __shfl_xor_sync(0xffffffffu, s0, 1), r1 = __shfl_xor_sync(0xffffffffu, s1, 1);
+                const uint4 o = even ? make_uint4(h0, h1, r0, r1) : make_uint4(r0, r1, l0, l1);
+                const int lc = even ? (j >> 1) : (4 + (j >> 1));
+                co4[row * 8 + (lc ^ (row & 7))] = o;
+            } else {
+                reinterpret_cast<float4*>(co_t)[p] = lo;
+            }
+        }
+    } else {
+        const float* __restrict__ rf = reinterpret_cast<const float*>(raw);
+        const int mn = t & 63, kh = t >> 6;
+        float4 v[4];
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            const int c = kh * 4 + q;
+            v[q].x = rf[(4 * c + 0) * kBH + mn];
+            v[q].y = rf[(4 * c + 1) * kBH + mn];
+            v[q].z = rf[(4 * c + 2) * kBH + mn];
+            v[q].w = rf[(4 * c + 3) * kBH + mn];
+        }
+        float4 hi[4], lo[4];
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            split4(v[q], hi[q], lo[q]);
+            const int c = kh * 4 + q;
+            hi4[mn * 8 + (c ^ (mn & 7))] = hi[q];
+            if (!CORR16) reinterpret_cast<float4*>(co_t)[mn * 8 + (c ^ (mn & 7))] = lo[q];
+        }
+        if (CORR16) {
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {                              // 8 k values per 16-byte chunk: float4 groups 2h, 2h+1
+                const int lc = kh * 2 + h;
+                const uint4 oh = make_uint4(pack_bf16(hi[2 * h].x, hi[2 * h].y), pack_bf16(hi[2 * h].z, hi[2 * h].w),
+                                            pack_bf16(hi[2 * h + 1].x, hi[2 * h + 1].y), pack_bf16(hi[2 * h + 1].z, hi[2 * h + 1].w));
+                const uint4 ol = make_uint4(pack_bf16(lo[2 * h].x, lo[2 * h].y), pack_bf16(lo[2 * h].z, lo[2 * h].w),
+                                            pack_bf16(lo[2 * h + 1].x, lo[2 * h + 1].y), pack_bf16(lo[2 * h + 1].z, lo[2 * h + 1].w));
+                co4[mn * 8 + (lc ^ (mn & 7))] = oh;
+                co4[mn * 8 + ((4 + lc) ^ (mn & 7))] = ol;
+            }
+        }
+    }
+}
+
+struct PairTile {
+    int rowA0;             // first output row of THIS CTA's half (also its A rows)
+    int rowB0;             // first output column of the tile
+    int kb0, nk, batch;
+    int64_t zslab;
+};
+
+__device__ __forceinline__ PairTile pair_tile(const GemmEpilogue& ep, int tile, int rank) {
+    PairTile c;
+    const int bx = tile % ep.gx, by = (tile / ep.gx) % ep.gy, bz = tile / (ep.gx * ep.gy);
+    c.rowA0 = by * kPM + rank * kBM;
+    c.rowB0 = bx * kBN;
+    c.zslab = bz;
+    const int split = bz % ep.splits;
+    c.batch = bz / ep.splits;
+    c.kb0 = split * ep.kb_per_split;
+    c.nk = min((ep.K + kBK - 1) / kBK, c.kb0 + ep.kb_per_split) - c.kb0;   // host guarantees >= 1
+    return c;
+}
+
+template <bool TA, bool TB, bool CORR16>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
+gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, GemmEpilogue ep) {
+    extern __shared__ unsigned char smem_raw[];
+    const uint32_t raw = smem_u32(smem_raw);
+    const uint32_t base = (raw + 1023u) & ~1023u;
+    unsigned char* base_ptr = smem_raw + (base - raw);
+    const uint32_t split_base = base + kRaw * kRawBytes;
+    unsigned char* split_ptr = base_ptr + kRaw * kRawBytes;
+    const uint32_t bars = base + kRingBytes + kStageBytes;
+    unsigned char* stage_ptr = base_ptr + kRingBytes;
+    auto rawfull_bar = [&](int r) { return bars + 8u * r; };                                   // local
+    auto rawempty_bar = [&](int r) { return bars + 8u * (kRaw + r); };                         // local
+    auto conv_off = [&](int s) { return 8u * (2 * kRaw + s); };                                // LEADER: split stage filled by both CTAs
+    auto empty_bar = [&](int s) { return bars + 8u * (2 * kRaw + kSplit + s); };               // both (multicast commit)
+    auto accfull_bar = [&](int b) { return bars + 8u * (2 * kRaw + 2 * kSplit + b); };         // both (multicast commit)
+    auto accempty_off = [&](int b) { return 8u * (2 * kRaw + 2 * kSplit + 2 + b); };           // LEADER
+    auto tileempty_off = [&]() { return 8u * (2 * kRaw + 2 * kSplit + 4); };                   // LEADER
+    volatile uint32_t* tmem_slot =
+        reinterpret_cast<volatile uint32_t*>(base_ptr + kRingBytes + kStageBytes + 8 * (2 * kRaw + 2 * kSplit + 6));
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int rank = (int)cluster_rank();
+    const int npairs = (int)(gridDim.x >> 1), pair_id = (int)(blockIdx.x >> 1);
+    const int ntiles = ep.ntiles;
+    const uint32_t leader_bars = mapa_rank(bars, 0);        // shared::cluster address of the leader's barrier block
+
+    if (threadIdx.x == 0) {
+        for (int r = 0; r < kRaw; ++r) {
+            mbar_init(rawfull_bar(r), 1);
+            mbar_init(rawempty_bar(r), 8);                   // 4 A + 4 B splitter warps of this CTA
+        }
+        for (int s = 0; s < kSplit; ++s) {
+            mbar_init(bars + conv_off(s), 16);               // splitter warps of both CTAs
+            mbar_init(empty_bar(s), 1);
+        }
+        for (int b = 0; b < 2; ++b) {
+            mbar_init(accfull_bar(b), 1);
+            mbar_init(bars + accempty_off(b), 16);           // drain warps of both CTAs
+        }
+        mbar_init(bars + tileempty_off(), 16);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 2) {
+        asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32((const void*)tmem_slot)),
+                     "n"(kTmemCols)
+                     : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+    }
+    tc_fence_before();
+    __syncthreads();
+    cluster_sync_all();                                      // the peer's barriers are initialised before anyone arrives remotely
+    tc_fence_after();
+    const uint32_t tmem_acc = *tmem_slot;
+
+    if (warp == 0) {
+        // ===== TMA producer (own A rows, own half of the B rows) =====
+        reg_dec<40>();
+        if (lane == 0) {
+            uint32_t it = 0;
+            for (int tile = pair_id; tile < ntiles; tile += npairs) {
+                const PairTile c = pair_tile(ep, tile, rank);
+                const int a_mn0 = c.rowA0 + c.batch * ep.a_mn, b_mn0 = c.rowB0 + rank * kBH + c.batch * ep.b_mn;
+                const int a_k0 = c.batch * ep.a_k, b_k0 = c.batch * ep.b_k;
+                for (int i = 0; i < c.nk; ++i, ++it) {
+                    const int r = it % kRaw;
+                    const uint32_t ph = (it / kRaw) & 1;
+                    const int k = (c.kb0 + i) * kBK;
+                    mbar_wait(rawempty_bar(r), ph ^ 1);
+                    mbar_expect_tx(rawfull_bar(r), kRawBytes);
+                    const uint32_t dst = base + r * kRawBytes;
+                    if (TA) tma_load_2d(dst, &tmA, rawfull_bar(r), a_mn0, k + a_k0);
+                    else    tma_load_2d(dst, &tmA, rawfull_bar(r), k + a_k0, a_mn0);
+                    if (TB) tma_load_2d(dst + kTileBytes, &tmB, rawfull_bar(r), b_mn0, k + b_k0);
+                    else    tma_load_2d(dst + kTileBytes, &tmB, rawfull_bar(r), k + b_k0, b_mn0);
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ===== MMA issuer: leader CTA only =====
+        reg_dec<40>();
+        if (rank == 0) {
+            uint32_t it = 0, gc = 0, tl = 0;
+            for (int tile = pair_id; tile < ntiles; tile += npairs) {
+                const PairTile c = pair_tile(ep, tile, 0);
+                mbar_wait_cluster(bars + tileempty_off(), (tl & 1) ^ 1);
+                for (int i = 0; i < c.nk; ++i, ++it) {
+                    const int s = it % kSplit;
+                    const uint32_t ph = (it / kSplit) & 1;
+                    const uint32_t g = gc + i / kGroup;
+                    const int b = g & 1;
+                    const bool group_first = (i % kGroup) == 0;
+                    const bool group_last = (i % kGroup) == kGroup - 1 || i == c.nk - 1;
+                    if (group_first) mbar_wait_cluster(bars + accempty_off(b), ((g >> 1) & 1) ^ 1);
+                    mbar_wait_cluster(bars + conv_off(s), ph);
+                    tc_fence_after();
+                    if (lane == 0) {
+                        const uint32_t st = split_base + s * kSplitBytes;
+                        const uint64_t b_hi = smem_desc_k128(st), b_co = smem_desc_k128(st + kBHalfBytes);
+                        const uint32_t a_hi = tmem_acc + (uint32_t)(kAopCol + s * 2 * kBK), a_co = a_hi + kBK;
+                        const uint32_t acc_big = tmem_acc + (uint32_t)(b * kBN), acc_small = tmem_acc + (uint32_t)kSmallCol;
+#pragma unroll
+                        for (int k = 0; k < kBK / 8; ++k) {
+                            const uint64_t adv = (uint64_t)(2 * k);          // 32 bytes of K per MMA (8 tf32 | 16 bf16)
+                            const uint32_t ak = (uint32_t)(8 * k);           // 8 TMEM columns per MMA
+                            umma2_tf32_ts(acc_big, a_hi + ak, b_hi + adv, kIdescTf32, (group_first && k == 0) ? 0u : 1u);
+                            if (CORR16) {
+                                // [lo | hi] (A, bf16) x [hi | lo] (B, bf16): k-steps 0,1 = lo.hi, 2,3 = hi.lo
+                                umma2_bf16_ts(acc_small, a_co + ak, b_co + adv, kIdescBf16, (i | k) ? 1u : 0u);
+                            } else {
+                                umma2_tf32_ts(acc_small, a_co + ak, b_hi + adv, kIdescTf32, (i | k) ? 1u : 0u);   // lo.hi
+                                umma2_tf32_ts(acc_small, a_hi + ak, b_co + adv, kIdescTf32, 1u);                   // hi.lo
+                            }
+                        }
+                        umma2_commit(empty_bar(s));
+                        if (group_last) umma2_commit(accfull_bar(b));
+                    }
+                    __syncwarp();
+                }
+                gc += (uint32_t)((c.nk + kGroup - 1) / kGroup);
+                ++tl;
+            }
+        }
+    } else if (warp < 4) {
+        reg_dec<40>();
+    } else if (warp < 8) {
+        // ===== A splitter =====
+        const int t = threadIdx.x - 128;
+        const uint32_t tmem_a = tmem_acc + ((uint32_t)((warp - 4) * 32) << 16) + (uint32_t)kAopCol;
+        uint32_t it = 0;
+        for (int tile = pair_id; tile < ntiles; tile += npairs) {
+            const PairTile c = pair_tile(ep, tile, rank);
+            for (int i = 0; i < c.nk; ++i, ++it) {
+                const int r = it % kRaw, s = it % kSplit;
+                mbar_wait(rawfull_bar(r), (it / kRaw) & 1);
+                mbar_wait_cluster(empty_bar(s), ((it / kSplit) & 1) ^ 1);
+                tc_fence_after();
+                split_rows_to_tmem<TA, CORR16>(base_ptr + (size_t)r * kRawBytes, tmem_a + (uint32_t)(s * 2 * kBK), t);
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) {
+                    mbar_arrive_cluster(leader_bars + conv_off(s));
+                    mbar_arrive(rawempty_bar(r));
+                }
+            }
+        }
+    } else if (warp < 12) {
+        // ===== B splitter (own 64 rows) =====
+        reg_dec<72>();
+        const int t = threadIdx.x - 256;
+        uint32_t it = 0;
+        for (int tile = pair_id; tile < ntiles; tile += npairs) {
+            const PairTile c = pair_tile(ep, tile, rank);
+            for (int i = 0; i < c.nk; ++i, ++it) {
+                const int r = it % kRaw, s = it % kSplit;
+                mbar_wait(rawfull_bar(r), (it / kRaw) & 1);
+                mbar_wait_cluster(empty_bar(s), ((it / kSplit) & 1) ^ 1);
+                unsigned char* st = split_ptr + (size_t)s * kSplitBytes;
+                split_b_half<TB, CORR16>(base_ptr + (size_t)r * kRawBytes + kTileBytes, st, st + kBHalfBytes, t);
+                fence_async_smem();
+                __syncwarp();
+                if (lane == 0) {
+                    mbar_arrive_cluster(leader_bars + conv_off(s));
+                    mbar_arrive(rawempty_bar(r));
+                }
+            }
+        }
+    } else {
+        // ===== drain + epilogue of the own 128 x 128 half =====
+        reg_inc<136>();
+        const int q = warp & 3;
+        const int half = (warp - 12) >> 2;
+        const uint32_t trow = tmem_acc + ((uint32_t)(q * 32) << 16) + (uint32_t)(half * 64);
+        const int colbase = half * 64;
+        uint32_t gc = 0;
+        for (int tile = pair_id; tile < ntiles; tile += npairs) {
+            const PairTile c = pair_tile(ep, tile, rank);
+            float acc[64];
+#pragma unroll
+            for (int j = 0; j < 64; ++j) acc[j] = 0.f;
+            const int ngroups = (c.nk + kGroup - 1) / kGroup;
+            for (int gl = 0; gl < ngroups; ++gl) {
+                const uint32_t g = gc + gl;
+                const int b = g & 1;
+                mbar_wait_cluster(accfull_bar(b), (g >> 1) & 1);
+                tc_fence_after();
+#pragma unroll
+                for (int c0 = 0; c0 < 64; c0 += 16) {
+                    float v[16];
+                    tmem_ld16(trow + (uint32_t)(b * kBN) + c0, v);
+#pragma unroll
+                    for (int j = 0; j < 16; ++j) acc[c0 + j] += v[j];
+                }
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive_cluster(leader_bars + accempty_off(b));
+            }
+#pragma unroll
+            for (int c0 = 0; c0 < 64; c0 += 16) {
+                float v[16];
+                tmem_ld16(trow + (uint32_t)kSmallCol + c0, v);
+#pragma unroll
+                for (int j = 0; j < 16; ++j) acc[c0 + j] += v[j];
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive_cluster(leader_bars + tileempty_off());
+            gc += (uint32_t)ngroups;
+            gemm_store_tile(ep, c.rowA0, c.rowB0, c.zslab, c.batch, acc, q, lane, colbase,
+                            reinterpret_cast<float4*>(stage_ptr + (size_t)(warp - 12) * 4096));
+        }
+        tc_fence_before();
+    }
+
+    __syncthreads();
+    cluster_sync_all();          // nobody leaves (or frees TMEM) while the peer may still signal this CTA's barriers
+    if (warp == 2) {
+        tc_fence_after();
+        asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_acc), "n"(kTmemCols) : "memory");
+    }
+}
+
+template <bool TA, bool TB, bool C16>
+static int pair_attr() {
+    static bool done = false;
+    if (!done) {
+        cudaError_t e = cudaFuncSetAttribute((const void*)gemm_pair_kernel<TA, TB, C16>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                             (int)kSmem);
+        if (e != cudaSuccess) return (int)e;
+        done = true;
+    }
+    return 0;
+}
+
+template <bool TA, bool TB, bool C16>
+static int pair_launch_t(dim3 grid, cudaStream_t s, const CUtensorMap& ma, const CUtensorMap& mb, const GemmEpilogue& ep) {
+    int rc = pair_attr<TA, TB, C16>();
+    if (rc) return rc;
+    gemm_pair_kernel<TA, TB, C16><<<grid, kThreads, kSmem, s>>>(ma, mb, ep);
+    return 0;
+}
+
+}  // namespace pr
+
+// Launch on CTA pairs.  ep: mode 0 with gx = ceil(N/128), gy = ceil(M/256), ntiles = gx gy splits batch already set.
+int gemm_pair_launch(const CUtensorMap& ma, const CUtensorMap& mb, const GemmEpilogue& ep, int transA, int transB, cudaStream_t s) {
+    static const bool corr16 = !(getenv("ADKF_GEMM_CORR") && getenv("ADKF_GEMM_CORR")[0] == 't');
+    const int pairs = std::max(1, num_sms() / 2);
+    dim3 grid((unsigned)(2 * std::min(ep.ntiles, pairs)));
+    if (!transA && !transB) return corr16 ? pr::pair_launch_t<false, false, true>(grid, s, ma, mb, ep) : pr::pair_launch_t<false, false, false>(grid, s, ma, mb, ep);
+    if (!transA && transB)  return corr16 ? pr::pair_launch_t<false, true, true>(grid, s, ma, mb, ep) : pr::pair_launch_t<false, true, false>(grid, s, ma, mb, ep);
+    return corr16 ? pr::pair_launch_t<true, true, true>(grid, s, ma, mb, ep) : pr::pair_launch_t<true, true, false>(grid, s, ma, mb, ep);
+}
+
+}  // namespace adkf

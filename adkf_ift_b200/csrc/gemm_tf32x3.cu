@@ -43,15 +43,13 @@
 #include <cuda.h>
 #include <algorithm>
 #include <cstdlib>
-#include "common.cuh"
+#include "gemm_common.cuh"
 #include "../../include/adkf_b200.h"
 
 namespace adkf {
 
-constexpr int kBM = 128, kBN = 128, kBK = 32;        // tile; 32 floats = 128 B = one swizzle row
 constexpr int kRaw = 4;                              // raw ring depth (TMA destination: A_raw, B_raw)
 constexpr int kSplit = 2;                            // split ring depth (MMA source: B_hi, B_lo in smem; A_hi, A_lo in TMEM)
-constexpr int kTileBytes = kBM * kBK * 4;            // 16 KB
 constexpr int kRawBytes = 2 * kTileBytes;
 constexpr int kSplitBytes = 2 * kTileBytes;
 constexpr int kRingBytes = kRaw * kRawBytes + kSplit * kSplitBytes;   // 192 KB
@@ -62,148 +60,6 @@ constexpr int kSmallCol = 2 * kBN;                   // first TMEM column of the
 constexpr int kAopCol = 3 * kBN;                     // first TMEM column of the A operand stages (hi 32 + lo 32 columns each)
 constexpr int kGroup = 4;                            // k-blocks accumulated in TMEM between two drains
 constexpr size_t kGemmSmem = (size_t)kRingBytes + kStageBytes + 1024 /*align*/ + 256 /*barriers*/;
-
-// ---- PTX wrappers ---------------------------------------------------------------------------------------
-__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
-
-__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
-    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
-}
-__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
-    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
-    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
-}
-__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
-    uint32_t done = 0, spins = 0;
-    while (true) {
-        asm volatile(
-            "{\n\t.reg .pred p;\n\t"
-            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
-            "selp.u32 %0, 1, 0, p;\n\t}"
-            : "=r"(done)
-            : "r"(bar), "r"(parity)
-            : "memory");
-        if (done) break;
-        if (++spins > (1u << 28)) __trap();   // never hang the GPU on a protocol error
-    }
-}
-__device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map, uint32_t bar, int c0, int c1) {
-    asm volatile(
-        "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
-        ::"r"(dst), "l"(reinterpret_cast<uint64_t>(map)), "r"(bar), "r"(c0), "r"(c1)
-        : "memory");
-}
-__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
-__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
-__device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
-
-__device__ __forceinline__ void umma_tf32(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t acc) {
-    asm volatile(
-        "{\n\t.reg .pred p;\n\t"
-        "setp.ne.b32 p, %4, 0;\n\t"
-        "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}"
-        ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(acc)
-        : "memory");
-}
-// A operand in tensor memory (lane = row of the tile, one tf32 per 32-bit column, 8 columns per MMA), B through its
-// shared-memory descriptor
-__device__ __forceinline__ void umma_tf32_ts(uint32_t tmem_d, uint32_t tmem_a, uint64_t bdesc, uint32_t idesc, uint32_t acc) {
-    asm volatile(
-        "{\n\t.reg .pred p;\n\t"
-        "setp.ne.b32 p, %4, 0;\n\t"
-        "tcgen05.mma.cta_group::1.kind::tf32 [%0], [%1], %2, %3, p;\n\t}"
-        ::"r"(tmem_d), "r"(tmem_a), "l"(bdesc), "r"(idesc), "r"(acc)
-        : "memory");
-}
-__device__ __forceinline__ void tmem_st32(uint32_t taddr, const uint32_t (&r)[32]) {
-    asm volatile(
-        "tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,%17,%18,%19,%20,"
-        "%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31,%32};"
-        ::"r"(taddr), "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]), "r"(r[8]), "r"(r[9]),
-          "r"(r[10]), "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15]), "r"(r[16]), "r"(r[17]), "r"(r[18]), "r"(r[19]),
-          "r"(r[20]), "r"(r[21]), "r"(r[22]), "r"(r[23]), "r"(r[24]), "r"(r[25]), "r"(r[26]), "r"(r[27]), "r"(r[28]), "r"(r[29]),
-          "r"(r[30]), "r"(r[31])
-        : "memory");
-}
-__device__ __forceinline__ void tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
-// Register budget per warpgroup (setmaxnreg): the kernel starts with 96 registers per thread (640 threads); the control
-// and B-splitter warpgroups give registers back, the two drain warpgroups (64 accumulators per thread) take them.
-template <int N> __device__ __forceinline__ void reg_dec() { asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(N)); }
-template <int N> __device__ __forceinline__ void reg_inc() { asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(N)); }
-__device__ __forceinline__ void umma_commit(uint32_t bar) {
-    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
-}
-__device__ __forceinline__ void tmem_ld16(uint32_t taddr, float (&v)[16]) {
-    uint32_t r[16];
-    asm volatile(
-        "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
-        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
-          "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
-        : "r"(taddr)
-        : "memory");
-    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-#pragma unroll
-    for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]);
-}
-
-// K-major, SWIZZLE_128B shared-memory matrix descriptor (cute::UMMA::SmemDescriptor): start address >> 4, leading byte
-// offset 1 (unused for swizzled K-major), stride byte offset 1024 B (one 8-row swizzle atom), version 1, layout 2.
-__device__ __forceinline__ uint64_t smem_desc_k128(uint32_t addr) {
-    return (uint64_t)((addr >> 4) & 0x3FFF) | (1ull << 16) | ((uint64_t)(1024 >> 4) << 32) | (1ull << 46) | (2ull << 61);
-}
-// instruction descriptor: D = f32 (1<<4), A = B = tf32 (2<<7, 2<<10), both K-major, N>>3 at bit 17, M>>4 at bit 24
-constexpr uint32_t kIdescTf32 = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(kBN >> 3) << 17) | ((uint32_t)(kBM >> 4) << 24);
-
-__device__ __forceinline__ uint32_t rna_tf32(float x) {
-    uint32_t u;
-    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(u) : "f"(x));
-    return u;
-}
-
-struct GemmEpilogue {
-    // mode 0: Y = act(acc + bias) (or a split-K partial)       mode 1: per-task squared distances
-    int mode;
-    float* out;
-    int64_t ldo;
-    int64_t M;
-    int N, K;
-    const float* bias;
-    int act;              // 0 none, 1 relu, 2 leaky_relu(0.01), 3 subtract the product from what `out` holds,
-                          // 4 / 5: multiply by relu' / leaky_relu'(0.01) of mask[row, col] (the saved activation output of the
-                          // layer below: the input-gradient GEMM of layer l+1 emits dZ_l directly, fs_mol/modules/gnn.py:79-95)
-    const float* mask;
-    int64_t ldm;
-    // split-K (mode 0): CTA z handles k-blocks [z * kb_per_split, ...) and writes to out + z * split_stride
-    int kb_per_split;
-    int64_t split_stride;
-    // batching (mode 0): blockIdx.z = batch * splits + split.  Batch b reads A at (mn + b*a_mn, k + b*a_k), B likewise,
-    // writes D + b*d_off (+ bias + b*bias_off): column blocks / row blocks of the SAME 2-D arrays, one tensor map each.
-    int splits;
-    int gx, gy, ntiles;   // persistent tile walk: tile -> (bx = tile % gx, by = (tile / gx) % gy, bz = tile / (gx gy))
-    int debug;            // development probe (ADKF_GEMM_DEBUG): 1 = splitter skips the split (128 only A, 256 only B), 2 = no MMAs
-    int a_mn, a_k, b_mn, b_k;
-    int64_t d_off, bias_off;
-    // gram
-    const int32_t* z_off;
-    const int32_t* n_sup;
-    const int64_t* d2_off;
-    const float* mu;      // [T, d]
-    const float* nrm;     // [rows]
-    int qq_block;
-    int stat;             // ADKF_STAT_*
-};
-
-// hi = v rounded to tf32 (round-to-nearest, ties away: what cvt.rna.tf32.f32 does, written as two integer ops so that it
-// stays on the ALU pipe), lo = v - hi (exact in fp32)
-__device__ __forceinline__ float tf32_hi(float v) { return __uint_as_float((__float_as_uint(v) + 0x1000u) & 0xffffe000u); }
-__device__ __forceinline__ void split4(const float4 v, float4& hi, float4& lo) {
-    hi.x = tf32_hi(v.x); lo.x = v.x - hi.x;
-    hi.y = tf32_hi(v.y); lo.y = v.y - hi.y;
-    hi.z = tf32_hi(v.z); lo.z = v.z - hi.z;
-    hi.w = tf32_hi(v.w); lo.w = v.w - hi.w;
-}
 
 // One operand tile, raw -> (hi, lo) in the K-major SWIZZLE_128B layout the MMA descriptors describe (row r = 128 B, its
 // logical 16 B chunk j stored at chunk j ^ (r & 7)).  t = 0..127 (the four splitter warps).
@@ -568,97 +424,8 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
 
             if (ep.debug & 64) continue;
             if (ep.mode == 0) {
-                // Through a warp-private swizzled smem tile (32 rows x 32 columns per pass) so that every global store
-                // instruction writes 4 rows x 128 contiguous bytes (the lane-per-row layout of tcgen05.ld would touch 32
-                // different lines with 16 bytes each).  Bias and activation are applied AFTER the transpose, where a lane
-                // owns 4 fixed columns: one float4 bias load per pass instead of 64 scalar loads per row.
-                float* out = ep.out + c.zslab * ep.split_stride + (int64_t)c.batch * ep.d_off;
-                const float* bias = (ep.bias != nullptr && !(ep.debug & 8)) ? ep.bias + (int64_t)c.batch * ep.bias_off : nullptr;
-                const bool vec_ok = (ep.ldo % 4 == 0) && ((reinterpret_cast<uintptr_t>(out) & 15) == 0);
-                float4* stg = reinterpret_cast<float4*>(stage_ptr + (size_t)(warp - 12) * 4096);
-                const int ch = lane & 7, rsub = lane >> 3;
-                const int act = ep.act;
-#pragma unroll
-                for (int p = 0; p < 2; ++p) {
-                    // act 4 / 5: the 8 mask vectors this lane needs for the pass are requested BEFORE the staging traffic, so
-                    // their latency hides behind it (a load inside the store loop costs one round trip per store)
-                    float4 mk4[8];
-                    if (act >= 4) {
-                        const int mcol = c.rowB0 + colbase + p * 32 + ch * 4;
-                        const int64_t mrow = (int64_t)c.rowA0 + q * 32 + rsub;
-                        const bool mvec = (ep.ldm % 4 == 0) && ((reinterpret_cast<uintptr_t>(ep.mask) & 15) == 0) && mcol + 4 <= ep.N;
-#pragma unroll
-                        for (int jj = 0; jj < 8; ++jj) {
-                            const int64_t r = mrow + jj * 4;
-                            mk4[jj] = make_float4(1.f, 1.f, 1.f, 1.f);
-                            if (r < ep.M && mcol < ep.N) {
-                                const float* mk = ep.mask + r * ep.ldm + mcol;
-                                if (mvec) {
-                                    mk4[jj] = __ldg(reinterpret_cast<const float4*>(mk));
-                                } else {
-                                    mk4[jj].x = mk[0];
-                                    if (mcol + 1 < ep.N) mk4[jj].y = mk[1];
-                                    if (mcol + 2 < ep.N) mk4[jj].z = mk[2];
-                                    if (mcol + 3 < ep.N) mk4[jj].w = mk[3];
-                                }
-                            }
-                        }
-                    }
-#pragma unroll
-                    for (int j = 0; j < 8; ++j)
-                        stg[lane * 8 + (j ^ (lane & 7))] =
-                            make_float4(acc[p * 32 + 4 * j], acc[p * 32 + 4 * j + 1], acc[p * 32 + 4 * j + 2], acc[p * 32 + 4 * j + 3]);
-                    __syncwarp();
-                    const int col = c.rowB0 + colbase + p * 32 + ch * 4;
-                    const bool full = vec_ok && col + 4 <= ep.N;
-                    float4 b4 = make_float4(0.f, 0.f, 0.f, 0.f);
-                    if (bias != nullptr) {
-                        if (col + 4 <= ep.N && ((reinterpret_cast<uintptr_t>(bias + col) & 15) == 0)) {
-                            b4 = *reinterpret_cast<const float4*>(bias + col);
-                        } else {
-                            if (col < ep.N) b4.x = bias[col];
-                            if (col + 1 < ep.N) b4.y = bias[col + 1];
-                            if (col + 2 < ep.N) b4.z = bias[col + 2];
-                            if (col + 3 < ep.N) b4.w = bias[col + 3];
-                        }
-                    }
-                    const int64_t rbase = (int64_t)c.rowA0 + q * 32 + rsub;
-                    float* o = out + rbase * ep.ldo + col;
-                    const int64_t ostep = 4 * ep.ldo;
-#pragma unroll
-                    for (int jj = 0; jj < 8; ++jj, o += ostep) {
-                        const int rr = jj * 4 + rsub;
-                        float4 x = stg[rr * 8 + (ch ^ (rr & 7))];
-                        x.x += b4.x; x.y += b4.y; x.z += b4.z; x.w += b4.w;
-                        if (act == 1) {
-                            x.x = fmaxf(x.x, 0.f); x.y = fmaxf(x.y, 0.f); x.z = fmaxf(x.z, 0.f); x.w = fmaxf(x.w, 0.f);
-                        } else if (act == 2) {
-                            x.x = (x.x > 0.f) ? x.x : 0.01f * x.x; x.y = (x.y > 0.f) ? x.y : 0.01f * x.y;
-                            x.z = (x.z > 0.f) ? x.z : 0.01f * x.z; x.w = (x.w > 0.f) ? x.w : 0.01f * x.w;
-                        }
-                        if (rbase + jj * 4 < ep.M && col < ep.N && !(ep.debug & 4)) {
-                            if (act >= 4) {
-                                const float neg = (act == 4) ? 0.f : 0.01f;
-                                const float4 y = mk4[jj];
-                                x.x *= (y.x > 0.f) ? 1.f : neg; x.y *= (y.y > 0.f) ? 1.f : neg;
-                                x.z *= (y.z > 0.f) ? 1.f : neg; x.w *= (y.w > 0.f) ? 1.f : neg;
-                            }
-                            if (full) {
-                                if (act == 3) {                                    // D <- D - A.B^T (trailing update)
-                                    const float4 old = *reinterpret_cast<const float4*>(o);
-                                    x = make_float4(old.x - x.x, old.y - x.y, old.z - x.z, old.w - x.w);
-                                }
-                                *reinterpret_cast<float4*>(o) = x;
-                            } else {
-                                const float xs[4] = {x.x, x.y, x.z, x.w};
-#pragma unroll
-                                for (int e = 0; e < 4; ++e)
-                                    if (col + e < ep.N) o[e] = (act == 3) ? o[e] - xs[e] : xs[e];
-                            }
-                        }
-                    }
-                    __syncwarp();
-                }
+                gemm_store_tile(ep, c.rowA0, c.rowB0, c.zslab, c.batch, acc, q, lane, colbase,
+                                reinterpret_cast<float4*>(stage_ptr + (size_t)(warp - 12) * 4096));
             } else {
                 const int r0 = ep.z_off[c.task];
                 const int r = c.ti * kBM + r_local;                    // row inside the task
@@ -697,56 +464,6 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
 
 using namespace adkf;
 
-// ---- host: tensor maps through the driver entry point (no link-time dependency on libcuda) --------------------
-typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
-                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
-                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
-
-static EncodeTiledFn encode_fn() {
-    static EncodeTiledFn fn = nullptr;
-    if (fn == nullptr) {
-        void* p = nullptr;
-        cudaDriverEntryPointQueryResult qres;
-        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres) == cudaSuccess &&
-            qres == cudaDriverEntryPointSuccess)
-            fn = reinterpret_cast<EncodeTiledFn>(p);
-    }
-    return fn;
-}
-
-// An operand with `rows` indices on the output side and `kdim` contraction indices.
-//   transposed = 0: stored [rows, kdim] (ld floats per row)  -> box 32 k x 128 rows, SWIZZLE_128B (already K-major)
-//   transposed = 1: stored [kdim, rows]                      -> box 128 rows x 32 k, un-swizzled; the splitter transposes
-static int make_map_2d(CUtensorMap* map, const float* ptr, int64_t rows, int64_t kdim, int64_t ld, int transposed) {
-    EncodeTiledFn fn = encode_fn();
-    if (fn == nullptr) return (int)cudaErrorNotSupported;
-    if ((reinterpret_cast<uintptr_t>(ptr) & 15) || (ld * 4) % 16) return ADKF_ERR_BADARG;
-    const cuuint64_t dims[2] = {(cuuint64_t)(transposed ? rows : kdim), (cuuint64_t)(transposed ? kdim : rows)};
-    const cuuint64_t strides[1] = {(cuuint64_t)ld * 4};
-    const cuuint32_t box[2] = {(cuuint32_t)(transposed ? kBM : kBK), (cuuint32_t)(transposed ? kBK : kBM)};
-    const cuuint32_t estr[2] = {1, 1};
-    CUresult r = CUDA_SUCCESS;
-    for (int attempt = 0; attempt < 2; ++attempt) {
-        r = fn(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(ptr), dims, strides, box, estr,
-               CU_TENSOR_MAP_INTERLEAVE_NONE, transposed ? CU_TENSOR_MAP_SWIZZLE_NONE : CU_TENSOR_MAP_SWIZZLE_128B,
-               CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-        if (r != CUDA_ERROR_INVALID_CONTEXT) break;
-        cudaFree(0);   // a host thread whose first CUDA call is this driver entry point (autograd workers) has no
-                       // current context yet: bind the primary context through the runtime and retry
-    }
-    return r == CUDA_SUCCESS ? 0 : -(1000 + (int)r);   // tensor-map encode failure: -(1000 + CUresult)
-}
-
-static int num_sms() {
-    static int n = 0;
-    if (n == 0) {
-        int dev = 0;
-        if (cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0)
-            n = 148;
-    }
-    return n;
-}
-
 template <bool TA, bool TB>
 static int gemm_attr() {
     static bool done = false;
@@ -776,8 +493,8 @@ __global__ void splitk_reduce_kernel(const float* __restrict__ ws, int splits, i
 // wave is: e.g. 66 tiles x 5 splits = 330 items = 2.23 waves runs as 3 waves at 74%.  Cost model in k-block units
 // (one 128x128x32 k-block ~ 0.7 us per CTA): waves x (k-blocks per split + fixed tile cost) + the slab write/read of the
 // reduce pass; every split keeps >= 8 k-blocks.  Deterministic: the plan depends on the shape only.
-static int plan_splits_tiles(int64_t tiles, int nk) {
-    if (nk < 16 || tiles >= 4 * 148) return 1;
+static int plan_splits_tiles(int64_t tiles, int nk, int workers = 148) {
+    if (nk < 16 || tiles >= 4 * workers) return 1;
     const int smax = std::min(nk / 8, 64);
     double best = 1e300;
     int best_s = 1;
@@ -785,16 +502,30 @@ static int plan_splits_tiles(int64_t tiles, int nk) {
         const int per = (nk + s - 1) / s;
         if ((nk + per - 1) / per != s) continue;                 // s would leave an empty split
         const int64_t items = tiles * s;
-        const int64_t waves = (items + 147) / 148;
+        const int64_t waves = (items + workers - 1) / workers;
         double t = (double)waves * (per + 6.0);
         if (s > 1) t += 4.0 + 0.036 * (double)items;
         if (t < best * 0.98) { best = t; best_s = s; }           // prefer fewer splits unless >2% better
     }
     return best_s;
 }
-static int plan_splits(int64_t M, int32_t N, int32_t K) {
-    return plan_splits_tiles(((M + kBM - 1) / kBM) * ((N + kBN - 1) / kBN), (K + kBK - 1) / kBK);
+// CTA pairs (gemm_pair.cu, 256 x 128 tiles, 74 workers) take every mode-0 product with more than one 128-row tile;
+// ADKF_GEMM_IMPL=1 forces the one-CTA kernel (A/B measurements).
+namespace adkf {
+int gemm_pair_launch(const CUtensorMap& ma, const CUtensorMap& mb, const GemmEpilogue& ep, int transA, int transB, cudaStream_t s);
 }
+static bool use_pair(int64_t M) {
+    static const int impl = getenv("ADKF_GEMM_IMPL") ? atoi(getenv("ADKF_GEMM_IMPL")) : 2;
+    return impl == 2 && M > kBM;
+}
+static int64_t out_tiles(int64_t M, int32_t N) {
+    const int64_t bm = use_pair(M) ? 2 * kBM : kBM;
+    return ((M + bm - 1) / bm) * ((N + kBN - 1) / kBN);
+}
+static int plan_splits_batched(int64_t M, int32_t N, int32_t K, int batch) {
+    return plan_splits_tiles(out_tiles(M, N) * batch, (K + kBK - 1) / kBK, use_pair(M) ? 74 : 148);
+}
+static int plan_splits(int64_t M, int32_t N, int32_t K) { return plan_splits_batched(M, N, K, 1); }
 
 extern "C" int64_t adkf_gemm_splitk_ws_floats(int64_t M, int32_t N, int32_t K) {
     const int s = plan_splits(M, N, K);
@@ -814,11 +545,12 @@ static int gemm_launch(const float* A, int transA, int64_t lda, int64_t a_slow, 
     // make_map_2d(ptr, rows (mn extent), kdim (k extent), ld, transposed): extents of the WHOLE array
     int rc = make_map_2d(&ma, A, transA ? a_fast : a_slow, transA ? a_slow : a_fast, lda, transA ? 1 : 0);
     if (rc) return rc;
-    rc = make_map_2d(&mb, B, transB ? b_fast : b_slow, transB ? b_slow : b_fast, ldb, transB ? 1 : 0);
+    const bool pair = use_pair(M);
+    rc = make_map_2d(&mb, B, transB ? b_fast : b_slow, transB ? b_slow : b_fast, ldb, transB ? 1 : 0, pair ? kBN / 2 : kBN);
     if (rc) return rc;
     int splits = (batch > 1) ? 1 : plan_splits(M, N, K);
     if (batch > 1 && splitk_ws != nullptr)          // batched split-K: same plan for every batch, ws = [batch][splits][M][N]
-        splits = plan_splits_tiles(((M + kBM - 1) / kBM) * ((N + kBN - 1) / kBN) * batch, (K + kBK - 1) / kBK);
+        splits = plan_splits_batched(M, N, K, batch);
     if (splits > 1 && (splitk_ws == nullptr || splitk_ws_floats < (int64_t)splits * batch * M * N || bias != nullptr ||
                        act != 0 || ldd != N))
         splits = 1;                                                  // no workspace (or fused epilogue): single pass
@@ -835,12 +567,14 @@ static int gemm_launch(const float* A, int transA, int64_t lda, int64_t a_slow, 
     } else {
         ep.out = D; ep.ldo = ldd; ep.split_stride = 0; ep.d_off = d_off;
     }
-    ep.gx = (int)((N + kBN - 1) / kBN); ep.gy = (int)((M + kBM - 1) / kBM);
+    ep.gx = (int)((N + kBN - 1) / kBN); ep.gy = (int)((M + (pair ? 2 : 1) * kBM - 1) / ((pair ? 2 : 1) * kBM));
     const int64_t ntiles64 = (int64_t)ep.gx * ep.gy * splits * batch;
     if (ntiles64 > 0x7fffffff) return ADKF_ERR_BADARG;
     ep.ntiles = (int)ntiles64;
     dim3 grid((unsigned)std::min<int64_t>(ntiles64, num_sms()));
-    if (!transA && !transB) {
+    if (pair) {
+        if ((rc = gemm_pair_launch(ma, mb, ep, transA, transB, s))) return rc;
+    } else if (!transA && !transB) {
         if ((rc = gemm_attr<false, false>())) return rc;
         gemm_tf32x3_kernel<false, false><<<grid, kGemmThreads, kGemmSmem, s>>>(ma, mb, ep);
     } else if (!transA && transB) {
@@ -884,7 +618,7 @@ extern "C" int adkf_gemm_tf32x3_masked(const float* A, int32_t transA, int64_t l
 }
 
 extern "C" int64_t adkf_gemm_batched_splitk_ws_floats(int64_t M, int32_t N, int32_t K, int32_t batch) {
-    const int splits = plan_splits_tiles(((M + kBM - 1) / kBM) * ((N + kBN - 1) / kBN) * batch, (K + kBK - 1) / kBK);
+    const int splits = plan_splits_batched(M, N, K, batch);
     return splits > 1 ? (int64_t)splits * batch * M * N : 0;
 }
 
