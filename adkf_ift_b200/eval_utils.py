@@ -30,9 +30,14 @@ class FSMolTask:                    # fs_mol/data/fsmol_task.py:100-117
     samples: List[MoleculeDatapoint]
 
     def get_pos_neg_separated(self) -> Tuple[List[MoleculeDatapoint], List[MoleculeDatapoint]]:
-        pos = [s for s in self.samples if s.bool_label]
-        neg = [s for s in self.samples if not s.bool_label]
-        return pos, neg
+        """fs_mol/data/fsmol_task.py:96-98 unpacks `more_itertools.partition(pred, samples)` as (pos, neg), but partition
+        yields the items with pred == False FIRST: the reference's "pos_samples" are the inactive molecules and its
+        "neg_samples" the active ones.  The sampler below concatenates neg + pos and labels them 0.. / 1.., so the order of
+        the molecules entering StratifiedShuffleSplit -- and therefore every support / query draw -- depends on this.  Kept as
+        is (pinned by tests/golden/eval_harness.npz against the reference's own sampler)."""
+        first = [s for s in self.samples if not s.bool_label]
+        second = [s for s in self.samples if s.bool_label]
+        return first, second
 
     @staticmethod
     def load_from_file(path) -> "FSMolTask":          # fs_mol/data/fsmol_task.py:108-144

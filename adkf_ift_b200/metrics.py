@@ -33,36 +33,41 @@ def _ratio(num: float, den: float, zero_division: float) -> float:
     return float(num / den) if den > 0 else float(zero_division)
 
 
+def _binary_clf_curve(labels: np.ndarray, scores: np.ndarray):
+    """(fps, tps) at every distinct score threshold, descending -- scikit-learn's `_binary_clf_curve`, same operations in
+    the same order (the CSV files of the evaluation harness are compared byte for byte with the reference's, whose metrics
+    are scikit-learn calls: fs_mol/utils/metrics.py:7-18)."""
+    y = np.asarray(labels).astype(bool).astype(np.float64).reshape(-1)
+    s = np.asarray(scores, dtype=np.float64).reshape(-1)
+    order = np.argsort(s, kind="mergesort")[::-1]
+    y, s = y[order], s[order]
+    threshold_idxs = np.r_[np.where(np.diff(s))[0], y.size - 1]
+    tps = np.cumsum(y, dtype=np.float64)[threshold_idxs]
+    fps = 1 + threshold_idxs - tps
+    return fps, tps
+
+
 def roc_auc_score(labels: np.ndarray, scores: np.ndarray) -> float:
-    """Area under the ROC curve = Mann-Whitney U / (n_pos n_neg), ties counted as 1/2 (midranks)."""
-    labels = np.asarray(labels).astype(bool)
-    scores = np.asarray(scores, dtype=np.float64)
-    n_pos, n_neg = int(labels.sum()), int((~labels).sum())
-    order = np.argsort(scores, kind="mergesort")
-    s = scores[order]
-    ranks = np.empty(len(s), dtype=np.float64)
-    i = 0
-    while i < len(s):
-        j = i
-        while j + 1 < len(s) and s[j + 1] == s[i]:
-            j += 1
-        ranks[order[i:j + 1]] = 0.5 * (i + j) + 1.0
-        i = j + 1
-    return float((ranks[labels].sum() - n_pos * (n_pos + 1) / 2.0) / (n_pos * n_neg))
+    """Area under the ROC curve as scikit-learn computes it: roc_curve (collinear points dropped) + trapezoidal rule."""
+    fps, tps = _binary_clf_curve(labels, scores)
+    if len(fps) > 2:
+        keep = np.where(np.r_[True, np.logical_or(np.diff(fps, 2), np.diff(tps, 2)), True])[0]
+        fps, tps = fps[keep], tps[keep]
+    tps, fps = np.r_[0, tps], np.r_[0, fps]
+    fpr, tpr = fps / fps[-1], tps / tps[-1]
+    return float((np.diff(fpr) * (tpr[1:] + tpr[:-1]) / 2.0).sum())
 
 
 def average_precision_score(labels: np.ndarray, scores: np.ndarray) -> float:
-    """sum_k (R_k - R_{k-1}) P_k over the distinct score thresholds, descending (scikit-learn's step-wise definition)."""
-    labels = np.asarray(labels).astype(np.float64)
-    scores = np.asarray(scores, dtype=np.float64)
-    order = np.argsort(-scores, kind="mergesort")
-    y, s = labels[order], scores[order]
-    tp = np.cumsum(y)
-    last = np.r_[np.nonzero(np.diff(s))[0], len(s) - 1]       # last index of every run of equal scores
-    tp_t = tp[last]
-    precision = tp_t / (last + 1.0)
-    recall = tp_t / tp[-1] if tp[-1] > 0 else np.zeros_like(tp_t)
-    return float(np.sum(np.diff(np.r_[0.0, recall]) * precision))
+    """sum_k (R_k - R_{k-1}) P_k over the distinct score thresholds, in scikit-learn's order of operations
+    (precision_recall_curve reversed to increasing thresholds, then -sum(diff(recall) * precision[:-1]))."""
+    fps, tps = _binary_clf_curve(labels, scores)
+    ps = tps + fps
+    precision = np.zeros_like(tps)
+    np.divide(tps, ps, out=precision, where=(ps != 0))
+    recall = np.ones_like(tps) if tps[-1] == 0 else tps / tps[-1]
+    precision, recall = np.hstack((precision[::-1], 1)), np.hstack((recall[::-1], 0))
+    return float(max(0.0, -np.sum(np.diff(recall) * precision[:-1])))
 
 
 def compute_binary_task_metrics(predictions: Sequence[float], labels: Sequence[float]) -> BinaryEvalMetrics:

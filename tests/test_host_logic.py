@@ -276,3 +276,72 @@ def test_functional_call_restores_parameters():
     with pytest.raises(KeyError):
         functional_call(m, {"0.nope": w}, (torch.ones(4, 3),))
     assert m[0].weight is before
+
+
+@pytest.mark.parametrize("numeric", [False, True])
+def test_eval_harness_equals_reference_draws_and_csv_bytes(golden_dir, tmp_path, numeric):
+    """adkf_ift_b200.eval_utils.eval_model / StratifiedTaskSampler / write_csv_summary* / metrics against the
+    reference's OWN harness (fs_mol/utils/test_utils.py:165-350, fs_mol/data/fsmol_task_sampler.py:299-440,
+    fs_mol/utils/metrics.py) run unmodified on the same synthetic tasks with the same stand-in model
+    (tests/golden/make_golden_eval.py): identical support / query molecules per (task, support size, seed), identical CSV bytes."""
+    import dataclasses
+    import zlib
+    from adkf_ift_b200 import eval_utils, metrics
+    g = np.load(os.path.join(golden_dir, "eval_harness.npz"))
+    tag = "numeric" if numeric else "binary"
+    mols, num_samples, seed = (int(x) for x in g["meta"])
+    scale = float(g["numeric_scale"]) if numeric else 1.0
+
+    class Dataset:
+        def get_task_reading_iterable(self, fold, **kw):
+            for tid in g["task_ids"]:
+                ms = synthetic.make_task_molecules(int(tid), mols)
+                ms = [dataclasses.replace(m, numeric_label=m.numeric_label * scale) for m in ms]
+                yield eval_utils.FSMolTask(name=ms[0].task_name, samples=ms)
+
+    def fake_score(smiles):
+        return ((zlib.crc32(smiles.encode()) & 0xFFFFFF) + 0.5) / float(1 << 24)
+
+    seen = {}
+
+    def test_model_fn(task_sample, temp_out_folder, s):
+        key = f"{task_sample.name}|{len(task_sample.train_samples)}|{s}"
+        seen[key + "|support"] = [m.smiles for m in task_sample.train_samples]
+        seen[key + "|query"] = [m.smiles for m in task_sample.test_samples]
+        p = np.array([fake_score(m.smiles) for m in task_sample.test_samples])
+        if numeric:
+            y = np.array([float(m.numeric_label) for m in task_sample.test_samples])
+            return metrics.compute_numeric_task_metrics(predictions=np.log(y) * (0.5 + p), labels=np.log(y))
+        y = np.array([bool(m.bool_label) for m in task_sample.test_samples])
+        return metrics.compute_binary_task_metrics(predictions=p, labels=y)
+
+    res = eval_utils.eval_model(test_model_fn, Dataset(), [int(x) for x in g["sizes"]], out_dir=str(tmp_path),
+                                num_samples=num_samples, test_size_or_ratio=None, fold=eval_utils.DataFold.TEST, seed=seed,
+                                filter_numeric_labels=numeric)
+    assert list(res.keys()) == [str(x) for x in g[f"{tag}::task_names"]]
+    assert [len(v) for v in res.values()] == [int(x) for x in g[f"{tag}::num_results"]]
+    draw_keys = [k for k in g.files if k.startswith(tag + "::") and (k.endswith("|support") or k.endswith("|query"))]
+    assert len(draw_keys) == len(seen) and len(seen) > 0
+    for k in draw_keys:
+        assert seen[k[len(tag) + 2:]] == [str(x) for x in g[k]], k
+    for name in res:
+        with open(os.path.join(str(tmp_path), f"{name}_eval_results.csv"), "rb") as f:
+            assert f.read() == g[f"{tag}::csv|{name}"].tobytes(), name
+
+
+def test_ranking_metrics_bit_identical_to_scikit_learn():
+    """roc_auc / average precision follow scikit-learn's order of operations: EXACT equality (the reference's metrics are
+    scikit-learn calls, fs_mol/utils/metrics.py:38-58, and the result CSVs are compared byte for byte)."""
+    sk = pytest.importorskip("sklearn.metrics")
+    from adkf_ift_b200 import metrics
+    rng = np.random.default_rng(0)
+    for t in range(300):
+        n = int(rng.integers(4, 200))
+        y = rng.random(n) < rng.uniform(0.2, 0.8)
+        if y.all() or (~y).all():
+            continue
+        p = rng.random(n)
+        if t % 3 == 0:
+            p = np.round(p, 1)          # ties
+        assert metrics.roc_auc_score(y, p) == float(sk.roc_auc_score(y, p))
+        assert metrics.average_precision_score(y, p) == float(sk.average_precision_score(y, p))
