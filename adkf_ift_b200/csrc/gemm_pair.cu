@@ -25,8 +25,12 @@
 //   warps 4-7   A splitter     own raw A tile -> hi (tf32) and [lo | hi] (bf16 pairs) in own TMEM
 //   warps 8-11  B splitter     own raw B half tile -> B_hi (tf32) and B_cat = [hi | lo] (bf16) K-major SWIZZLE_128B tiles in own smem
 //   warps 12-19 drain + epilogue of the own 128 x 128 half of the tile (RN accumulation in registers, see gemm_tf32x3.cu)
-// Cross-CTA signalling: splitter and drain warps of both CTAs arrive on the LEADER's mbarriers (mapa + mbarrier.arrive
-// .release.cluster); everything the leader tells the pair goes through the multicast commit.  Every wait is bounded (trap).
+// Cross-CTA signalling: splitter and drain warps of both CTAs arrive on the LEADER's mbarriers (mapa + mbarrier.arrive on the
+// shared::cluster address, default .release.cta semantics as in CUTLASS' ClusterBarrier: cluster-scope release / acquire made
+// every hand-off ~2x slower, profiles/r2_gemm_pair_notes.md); everything the leader tells the pair goes through the multicast
+// commit.  Every wait is bounded (trap).
+// Measured and rejected: corrections accumulated into the hi.hi accumulator to free 128 TMEM columns for 4 operand stages --
+// slower (long-K 1.10 -> 1.14 ms) and 30% more rounding error; the separate correction accumulator stays.
 #include <cuda.h>
 #include <cuda_bf16.h>
 #include <algorithm>
@@ -38,16 +42,17 @@ namespace pr {
 
 constexpr int kPM = 256;                             // pair tile rows (2 x kBM)
 constexpr int kBH = 64;                              // B rows held by one CTA
-constexpr int kRaw = 5;                              // raw ring depth
-constexpr int kSplit = 4;                            // split stages (B tiles in smem, A operand in TMEM)
+constexpr int kRaw = 6;                              // raw ring depth
+constexpr int kSplit = 2;                            // split stages (B tiles in smem, A operand in TMEM)
 constexpr int kBHalfBytes = kBH * kBK * 4;           // 8 KB
 constexpr int kRawBytes = kTileBytes + kBHalfBytes;  // A 16 KB + B half 8 KB
 constexpr int kSplitBytes = 2 * kBHalfBytes;         // B_hi 8 KB + B_cat (or B_lo) 8 KB
-constexpr int kRingBytes = kRaw * kRawBytes + kSplit * kSplitBytes;   // 120 + 64 KB
+constexpr int kRingBytes = kRaw * kRawBytes + kSplit * kSplitBytes;   // 144 + 32 KB
 constexpr int kStageBytes = 8 * 4096;
 constexpr int kThreads = 640;
 constexpr int kTmemCols = 512;
-constexpr int kAopCol = 2 * kBN;                     // A operand: 4 stages x (32 tf32 columns + 32 correction columns)
+constexpr int kSmallCol = 2 * kBN;
+constexpr int kAopCol = 3 * kBN;                     // A operand: 2 stages x (32 tf32 columns + 32 correction columns)
 constexpr int kGroup = 4;
 constexpr size_t kSmem = (size_t)kRingBytes + kStageBytes + 1024 + 256;
 
@@ -117,57 +122,37 @@ __device__ __forceinline__ uint32_t pack_bf16(float lo_k, float hi_k) {   // ele
 //   columns [0,32)  : hi as tf32
 //   CORR16: columns [32,48) = bf16 pairs of lo, [48,64) = bf16 pairs of hi  (the [lo | hi] operand of the correction MMAs)
 //   else  : columns [32,64) = lo as tf32
-__device__ __forceinline__ void tmem_st16(uint32_t taddr, const uint32_t (&r)[16]) {
-    asm volatile("tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16};"
-                 ::"r"(taddr), "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]), "r"(r[8]),
-                   "r"(r[9]), "r"(r[10]), "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15])
-                 : "memory");
-}
-__device__ __forceinline__ void tmem_st8(uint32_t taddr, const uint32_t (&r)[8]) {
-    asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};"
-                 ::"r"(taddr), "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7])
-                 : "memory");
-}
-
-// Processed in two halves of 16 k values (register pressure: the kernel is compiled for 96 registers per thread).
 template <bool TR, bool CORR16>
 __device__ __forceinline__ void split_rows_to_tmem(const unsigned char* __restrict__ raw, uint32_t taddr, int t) {
+    float x[kBK];
+    if (!TR) {
+        const float4* __restrict__ r4 = reinterpret_cast<const float4*>(raw) + t * 8;
 #pragma unroll
-    for (int h = 0; h < 2; ++h) {
-        float x[16];
-        if (!TR) {
-            const float4* __restrict__ r4 = reinterpret_cast<const float4*>(raw) + t * 8;
-#pragma unroll
-            for (int j = 0; j < 4; ++j) {
-                const float4 v = r4[(4 * h + j) ^ (t & 7)];
-                x[4 * j] = v.x; x[4 * j + 1] = v.y; x[4 * j + 2] = v.z; x[4 * j + 3] = v.w;
-            }
-        } else {
-            const float* __restrict__ rf = reinterpret_cast<const float*>(raw) + t;
-#pragma unroll
-            for (int k = 0; k < 16; ++k) x[k] = rf[(16 * h + k) * kBM];
+        for (int j = 0; j < 8; ++j) {
+            const float4 v = r4[j ^ (t & 7)];
+            x[4 * j] = v.x; x[4 * j + 1] = v.y; x[4 * j + 2] = v.z; x[4 * j + 3] = v.w;
         }
-        uint32_t hi[16];
+    } else {
+        const float* __restrict__ rf = reinterpret_cast<const float*>(raw) + t;
 #pragma unroll
-        for (int k = 0; k < 16; ++k) hi[k] = __float_as_uint(tf32_hi(x[k]));
-        tmem_st16(taddr + 16 * h, hi);
-        if (CORR16) {
-            uint32_t lo2[8], hi2[8];
-#pragma unroll
-            for (int c = 0; c < 8; ++c) {
-                const float h0 = __uint_as_float(hi[2 * c]), h1 = __uint_as_float(hi[2 * c + 1]);
-                lo2[c] = pack_bf16(x[2 * c] - h0, x[2 * c + 1] - h1);
-                hi2[c] = pack_bf16(h0, h1);
-            }
-            tmem_st8(taddr + kBK + 8 * h, lo2);
-            tmem_st8(taddr + kBK + kBK / 2 + 8 * h, hi2);
-        } else {
-            uint32_t lo[16];
-#pragma unroll
-            for (int k = 0; k < 16; ++k) lo[k] = __float_as_uint(x[k] - __uint_as_float(hi[k]));
-            tmem_st16(taddr + kBK + 16 * h, lo);
-        }
+        for (int k = 0; k < kBK; ++k) x[k] = rf[k * kBM];
     }
+    uint32_t hi[kBK], co[kBK];
+#pragma unroll
+    for (int k = 0; k < kBK; ++k) hi[k] = __float_as_uint(tf32_hi(x[k]));
+    if (CORR16) {
+#pragma unroll
+        for (int c = 0; c < kBK / 2; ++c) {
+            const float h0 = __uint_as_float(hi[2 * c]), h1 = __uint_as_float(hi[2 * c + 1]);
+            co[c] = pack_bf16(x[2 * c] - h0, x[2 * c + 1] - h1);
+            co[kBK / 2 + c] = pack_bf16(h0, h1);
+        }
+    } else {
+#pragma unroll
+        for (int k = 0; k < kBK; ++k) co[k] = __float_as_uint(x[k] - __uint_as_float(hi[k]));
+    }
+    tmem_st32(taddr, hi);
+    tmem_st32(taddr + kBK, co);
     tmem_st_wait();
 }
 
@@ -281,8 +266,9 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     auto empty_bar = [&](int s) { return bars + 8u * (2 * kRaw + kSplit + s); };               // both (multicast commit)
     auto accfull_bar = [&](int b) { return bars + 8u * (2 * kRaw + 2 * kSplit + b); };         // both (multicast commit)
     auto accempty_off = [&](int b) { return 8u * (2 * kRaw + 2 * kSplit + 2 + b); };           // LEADER
+    auto tileempty_off = [&]() { return 8u * (2 * kRaw + 2 * kSplit + 4); };                   // LEADER
     volatile uint32_t* tmem_slot =
-        reinterpret_cast<volatile uint32_t*>(base_ptr + kRingBytes + kStageBytes + 8 * (2 * kRaw + 2 * kSplit + 4));
+        reinterpret_cast<volatile uint32_t*>(base_ptr + kRingBytes + kStageBytes + 8 * (2 * kRaw + 2 * kSplit + 6));
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int rank = (int)cluster_rank();
@@ -303,6 +289,7 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             mbar_init(accfull_bar(b), 1);
             mbar_init(bars + accempty_off(b), 16);           // drain warps of both CTAs
         }
+        mbar_init(bars + tileempty_off(), 16);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 2) {
@@ -344,9 +331,10 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         // ===== MMA issuer: leader CTA only =====
         reg_dec<40>();
         if (rank == 0) {
-            uint32_t it = 0, gc = 0;
+            uint32_t it = 0, gc = 0, tl = 0;
             for (int tile = pair_id; tile < ntiles; tile += npairs) {
                 const PairTile c = pair_tile(ep, tile, 0);
+                mbar_wait_cluster(bars + tileempty_off(), (tl & 1) ^ 1);
                 for (int i = 0; i < c.nk; ++i, ++it) {
                     const int s = it % kSplit;
                     const uint32_t ph = (it / kSplit) & 1;
@@ -361,10 +349,7 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                         const uint32_t st = split_base + s * kSplitBytes;
                         const uint64_t b_hi = smem_desc_k128(st), b_co = smem_desc_k128(st + kBHalfBytes);
                         const uint32_t a_hi = tmem_acc + (uint32_t)(kAopCol + s * 2 * kBK), a_co = a_hi + kBK;
-                        // ONE accumulator per drain group for hi.hi and the corrections: what the separate correction accumulator
-                        // of gemm_tf32x3.cu costs in tensor memory (128 columns) buys two more operand stages here, and the pair
-                        // kernel is bound by the depth of that pipeline (cross-CTA signalling latency), not by the tensor pipe
-                        const uint32_t acc_big = tmem_acc + (uint32_t)(b * kBN);
+                        const uint32_t acc_big = tmem_acc + (uint32_t)(b * kBN), acc_small = tmem_acc + (uint32_t)kSmallCol;
 #pragma unroll
                         for (int k = 0; k < kBK / 8; ++k) {
                             const uint64_t adv = (uint64_t)(2 * k);          // 32 bytes of K per MMA (8 tf32 | 16 bf16)
@@ -372,10 +357,10 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                             umma2_tf32_ts(acc_big, a_hi + ak, b_hi + adv, kIdescTf32, (group_first && k == 0) ? 0u : 1u);
                             if (CORR16) {
                                 // [lo | hi] (A, bf16) x [hi | lo] (B, bf16): k-steps 0,1 = lo.hi, 2,3 = hi.lo
-                                umma2_bf16_ts(acc_big, a_co + ak, b_co + adv, kIdescBf16, 1u);
+                                umma2_bf16_ts(acc_small, a_co + ak, b_co + adv, kIdescBf16, (i | k) ? 1u : 0u);
                             } else {
-                                umma2_tf32_ts(acc_big, a_co + ak, b_hi + adv, kIdescTf32, 1u);   // lo.hi
-                                umma2_tf32_ts(acc_big, a_hi + ak, b_co + adv, kIdescTf32, 1u);   // hi.lo
+                                umma2_tf32_ts(acc_small, a_co + ak, b_hi + adv, kIdescTf32, (i | k) ? 1u : 0u);   // lo.hi
+                                umma2_tf32_ts(acc_small, a_hi + ak, b_co + adv, kIdescTf32, 1u);                   // hi.lo
                             }
                         }
                         umma2_commit(empty_bar(s));
@@ -384,6 +369,7 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                     __syncwarp();
                 }
                 gc += (uint32_t)((c.nk + kGroup - 1) / kGroup);
+                ++tl;
             }
         }
     } else if (warp < 4) {
@@ -410,7 +396,8 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             }
         }
     } else if (warp < 12) {
-        // ===== B splitter (own 64 rows); stays at the launch budget of 96 registers (5120 + 2 x 12288 + 34816 <= 65536) =====
+        // ===== B splitter (own 64 rows) =====
+        reg_dec<72>();
         const int t = threadIdx.x - 256;
         uint32_t it = 0;
         for (int tile = pair_id; tile < ntiles; tile += npairs) {
@@ -459,6 +446,16 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                 __syncwarp();
                 if (lane == 0) mbar_arrive_cluster(leader_bars + accempty_off(b));
             }
+#pragma unroll
+            for (int c0 = 0; c0 < 64; c0 += 16) {
+                float v[16];
+                tmem_ld16(trow + (uint32_t)kSmallCol + c0, v);
+#pragma unroll
+                for (int j = 0; j < 16; ++j) acc[c0 + j] += v[j];
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive_cluster(leader_bars + tileempty_off());
             gc += (uint32_t)ngroups;
             gemm_store_tile(ep, c.rowA0, c.rowB0, c.zslab, c.batch, acc, q, lane, colbase,
                             reinterpret_cast<float4*>(stage_ptr + (size_t)(warp - 12) * 4096));
