@@ -231,15 +231,66 @@ class ADKTModelTrainer(ADKTModel):
     def save_model(self, path: str, optimizer: Optional[torch.optim.Optimizer] = None, epoch: Optional[int] = None):
         data = self.get_model_state()
         if optimizer is not None:
-            data["optimizer_state_dict"] = optimizer.state_dict()
+            data["optimizer_state_dict"] = self._export_optimizer_state(optimizer)
         if epoch is not None:
             data["epoch"] = epoch
         torch.save(data, path)
 
+    # ---- optimizer state across the flat-buffer optimiser ---------------------------------------------------
+    def _export_optimizer_state(self, optimizer: torch.optim.Optimizer) -> Dict[str, Any]:
+        """`optimizer.state_dict()` in the layout of the reference's `Adam(self.feature_extractor_params())` (one entry per
+        parameter, registration order), also when the step runs on the flat buffer as ONE tensor: the moments are sliced
+        back to the named parameters through the FlatParams offsets, so a checkpoint resumes in a fresh trainer -- or in
+        the reference's own."""
+        flat_param = getattr(self, "_flat_param", None)
+        if self._flat is None or flat_param is None or optimizer is not self.optimizer:
+            return optimizer.state_dict()
+        sd = optimizer.state_dict()
+        st = sd["state"].get(0)
+        group = {k: v for k, v in sd["param_groups"][0].items() if k != "params"}
+        flat = self._flat
+        state = {}
+        if st is not None:
+            for i, (p, n, off) in enumerate(zip(flat.params, flat.sizes, flat.offsets)):
+                state[i] = {"step": st["step"].detach().clone().cpu() if torch.is_tensor(st["step"]) else st["step"],
+                            "exp_avg": st["exp_avg"][off:off + n].view_as(p).clone(),
+                            "exp_avg_sq": st["exp_avg_sq"][off:off + n].view_as(p).clone()}
+        group["params"] = list(range(len(flat.params)))
+        group["fused"] = None
+        return {"state": state, "param_groups": [group]}
+
+    def _import_optimizer_state(self, sd: Dict[str, Any]):
+        """Inverse of _export_optimizer_state: accepts the per-parameter layout (also a reference checkpoint's) and loads it
+        into whichever optimiser is live -- the per-parameter one, or the flat one (moments scattered through the offsets)."""
+        flat_param = getattr(self, "_flat_param", None)
+        if self._flat is None or flat_param is None:
+            self.optimizer.load_state_dict(sd)
+            return
+        flat = self._flat
+        if len(sd["state"]) == 0:
+            return
+        exp_avg = torch.zeros_like(flat.flat)
+        exp_avg_sq = torch.zeros_like(flat.flat)
+        step = None
+        for i, (p, n, off) in enumerate(zip(flat.params, flat.sizes, flat.offsets)):
+            st = sd["state"].get(i)
+            if st is None:
+                continue
+            exp_avg[off:off + n].copy_(st["exp_avg"].reshape(-1))
+            exp_avg_sq[off:off + n].copy_(st["exp_avg_sq"].reshape(-1))
+            step = st["step"]
+        fp = flat_param[0]
+        step_t = torch.as_tensor(float(step), dtype=torch.float32, device=fp.device if self.optimizer.param_groups[0].get("fused") else "cpu")
+        self.optimizer.state[fp] = {"step": step_t, "exp_avg": exp_avg, "exp_avg_sq": exp_avg_sq}
+        for k, v in sd["param_groups"][0].items():
+            if k not in ("params", "fused", "foreach", "capturable", "differentiable"):
+                self.optimizer.param_groups[0][k] = v
+
     def load_model_weights(self, path: str, quiet: bool = False, device: Optional[torch.device] = None):
         """Copies tensors by key.  Reference checkpoints also carry gpytorch's `gp_*` / `mll.*` entries (several
         aliases of the same three tensors plus prior buffers): they are re-initialised per task anyway, so keys
-        this model does not own are skipped."""
+        this model does not own are skipped.  An `optimizer_state_dict` is restored as well (the reference tries to,
+        adaptive_dkt_utils.py:255-258)."""
         ckpt = torch.load(path, map_location=device, weights_only=False)
         own = self.state_dict()
         skipped = []
@@ -252,6 +303,14 @@ class ADKTModelTrainer(ADKTModel):
                 skipped.append(name)
             else:
                 raise KeyError(f"checkpoint tensor {name} {tuple(value.shape)} has no counterpart in the model")
+        opt_sd = ckpt.get("optimizer_state_dict")
+        if opt_sd is not None:
+            try:
+                self._import_optimizer_state(opt_sd)
+            except (ValueError, KeyError, RuntimeError) as e:       # a different parameter set: keep the fresh optimiser
+                if not quiet:
+                    import logging
+                    logging.getLogger(__name__).warning(f"optimizer state of {path} not restored: {e}")
         return skipped
 
     @classmethod
@@ -291,45 +350,81 @@ class ADKTModelTrainer(ADKTModel):
             optimizer=self.optimizer, lr_lambda=[partial(linear_warmup, warmup_steps=0), partial(linear_warmup, warmup_steps=100)])
         self._grouped_optimizer = True
 
-    def train_loop(self, out_dir: str, dataset, device: torch.device, aml_run=None):
-        """adaptive_dkt_utils.py:329-458 on the batched path: every outer step draws `tasks_per_batch` task samples from
-        the (repeating) training iterable, runs fit + IFT hypergradient of all of them in one pass, all-reduces, clips and
-        steps; validates by fine-tuning every `validate_every_num_steps` and keeps `best_validation.pt` / `fully_trained.pt`.
-        With several ranks each rank draws from its own shard of the iterable (`distributed.shard_tasks`)."""
+    def train_loop(self, out_dir: str, dataset, device: torch.device, aml_run=None, num_workers: Optional[int] = None,
+                   emulate_workers: Optional[int] = None):
+        """adaptive_dkt_utils.py:329-458 on the batched path: every outer step takes `tasks_per_batch` task samples from the
+        (repeating) training stream, runs fit + IFT hypergradient of all of them in one pass, all-reduces, clips and steps;
+        validates by fine-tuning every `validate_every_num_steps` and keeps `best_validation.pt` / `fully_trained.pt`.
+
+        The stream is produced as the reference produces it -- by worker processes (host_pipeline.HostBatchPipeline:
+        featurisation + collation off the trainer's core, pinned staging, async H2D one step ahead) -- and the loss of a step
+        is read by the host one step late, so the GPU never waits for Python.  `num_workers=0` runs the same shard
+        generators inline (identical batches, hence identical losses).  With R ranks every rank takes tasks_per_batch / R
+        tasks per step from its own shards of the stream."""
         import logging
+        from .host_pipeline import HostBatchPipeline, StreamSpec
+        from .task_batch import DevicePrefetcher
         log = logging.getLogger(__name__)
+        device = torch.device(device)
+        if device.type == "cuda":
+            torch.cuda.set_device(device)              # the C-ABI launches on the CURRENT device's stream
+        cfg = self.config
+        world, rank = distributed.world_size(), distributed.rank()
+        if cfg.tasks_per_batch % world != 0:
+            raise ValueError(f"tasks_per_batch ({cfg.tasks_per_batch}) must be a multiple of the number of ranks ({world}): "
+                             "every rank takes an equal share of the meta-batch")
         os.makedirs(out_dir, exist_ok=True)
         self.to(device)
-        cfg = self.config
-        self.save_model(os.path.join(out_dir, "best_validation.pt"))
-        it = iter(get_dkt_task_sample_iterable(dataset=dataset, data_fold=DataFold.TRAIN, num_samples=1,
-                                               max_num_graphs=cfg.batch_size, support_size=cfg.support_set_size,
-                                               query_size=cfg.query_set_size, repeat=True,
-                                               filter_numeric_labels=cfg.use_numeric_labels))
-        world, rank = distributed.world_size(), distributed.rank()
+        if rank == 0:
+            self.save_model(os.path.join(out_dir, "best_validation.pt"))
+        if world > 1:
+            torch.distributed.barrier()
+        if num_workers is None:
+            num_workers = max(1, min(4, (os.cpu_count() or 2) // max(world, 1) - 1))
+        spec = StreamSpec(dataset=dataset, data_fold=int(DataFold.TRAIN), support_size=cfg.support_set_size,
+                          query_size=cfg.query_set_size, max_num_graphs=cfg.batch_size,
+                          use_numeric_labels=cfg.use_numeric_labels, tasks_per_step=cfg.tasks_per_batch // world,
+                          num_shards=1, repeat=True)
+        pipe = HostBatchPipeline(spec, num_workers=num_workers, emulate_workers=emulate_workers, rank=rank, world=world)
         best, metric = -np.inf, ("r2" if cfg.use_numeric_labels else "avg_precision")
         losses: List[float] = []
-        for step in range(1, cfg.num_train_steps + 1):
-            drawn = [next(it) for _ in range(cfg.tasks_per_batch)]
-            mine = [drawn[i] for i in distributed.shard_tasks(len(drawn), rank, world)]
-            for smp in mine:
-                assert len(smp.batches) == 1, "a training sample must fit one batch (support + query <= batch_size)"
-            tb = to_device(collate_tasks([smp.batches[0] for smp in mine], cfg.use_numeric_labels), device)
-            res = self.train_step(tb, global_num_tasks=len(drawn))
-            losses.append(float(res.loss_per_sample.mean().item()))
-            if aml_run is not None:
-                aml_run.log("loss", losses[-1])
-            if step % cfg.validate_every_num_steps == 0:
-                valid = validate_by_finetuning_on_tasks(self, dataset, aml_run=aml_run, metric_to_use=metric)
-                log.info(f"Validated at train step [{step}/{cfg.num_train_steps}], valid {metric}: {valid:.3f}, "
-                         f"mean loss {np.mean(losses[-cfg.validate_every_num_steps:]):.5f}")
-                if valid > best:
-                    best = valid
-                    if rank == 0:
-                        self.save_model(os.path.join(out_dir, "best_validation.pt"))
+        readback = _LossReadback(device)
+        try:
+            batches = DevicePrefetcher(pipe, device) if device.type == "cuda" else (to_device(hb, device) for hb in pipe)
+            for step in range(1, cfg.num_train_steps + 1):
+                tb = next(batches)
+                res = self.train_step(tb, global_num_tasks=cfg.tasks_per_batch)
+                for rec in readback.push(res):
+                    self._log_step(rec, losses, aml_run, log)
+                if step % cfg.validate_every_num_steps == 0:
+                    for rec in readback.flush():
+                        self._log_step(rec, losses, aml_run, log)
+                    valid = validate_by_finetuning_on_tasks(self, dataset, aml_run=aml_run, metric_to_use=metric)
+                    log.info(f"Validated at train step [{step}/{cfg.num_train_steps}], valid {metric}: {valid:.3f}, "
+                             f"mean loss {np.mean(losses[-cfg.validate_every_num_steps:]):.5f}")
+                    if valid > best:
+                        best = valid
+                        if rank == 0:
+                            self.save_model(os.path.join(out_dir, "best_validation.pt"), optimizer=self.optimizer, epoch=step)
+            for rec in readback.flush():
+                self._log_step(rec, losses, aml_run, log)
+        finally:
+            pipe.close()
         if rank == 0:
-            self.save_model(os.path.join(out_dir, "fully_trained.pt"))
+            self.save_model(os.path.join(out_dir, "fully_trained.pt"), optimizer=self.optimizer, epoch=cfg.num_train_steps)
         return losses
+
+    @staticmethod
+    def _log_step(rec, losses, aml_run, log):
+        loss, dropped, not_converged = rec
+        losses.append(loss)
+        if aml_run is not None:
+            aml_run.log("loss", loss)
+        if dropped:
+            log.warning(f"step {len(losses)}: {dropped} task(s) dropped from the meta-batch (covariance not positive definite after "
+                        "the jitter ladder, or singular inner Hessian); the mean was renormalised over the remaining tasks")
+        if not_converged:
+            log.info(f"step {len(losses)}: inner fit of {not_converged} task(s) stopped at max_iter")
 
     # ---- one outer step -------------------------------------------------------------------------------
     def _ensure_flat(self) -> FlatParams:
@@ -355,13 +450,17 @@ class ADKTModelTrainer(ADKTModel):
                 self.optimizer = torch.optim.Adam([fp], self.config.learning_rate, fused=params[0].is_cuda)
         return self._flat
 
-    def reduce_and_update(self):
+    def reduce_and_update(self, global_num_tasks: Optional[int] = None):
         """All-reduce (sum) of the flat meta-gradient over the ranks, then clip + Adam -- identical on every rank, so
-        the replicas stay bit-identical (adaptive_dkt_utils.py:406-413)."""
+        the replicas stay bit-identical (adaptive_dkt_utils.py:406-413).  The tail slot of the gradient buffer carries the
+        number of VALID tasks through the same all-reduce; when tasks were dropped the mean is renormalised over the rest."""
         flat = self._ensure_flat()
-        distributed.allreduce_sum_(flat.grad)
-        if self.config.clip_value is not None:
-            flat.clip_(self.config.clip_value)
+        distributed.allreduce_sum_(flat.gbuf)
+        pre_scale = None
+        if global_num_tasks is not None:
+            pre_scale = float(global_num_tasks) / torch.clamp(flat.tail[0], min=1.0)     # == 1.0 exactly when nothing was dropped
+        if self.config.clip_value is not None or pre_scale is not None:
+            flat.clip_(self.config.clip_value, pre_scale)
         self.optimizer.step()
         if self.lr_scheduler is not None:
             self.lr_scheduler.step()
@@ -369,11 +468,58 @@ class ADKTModelTrainer(ADKTModel):
 
     def train_step(self, tb: DeviceTaskBatch, global_num_tasks: Optional[int] = None) -> TaskBatchResult:
         """One outer step on this rank's share of the meta-batch (adaptive_dkt_utils.py:352-413): hypergradients of
-        the local tasks / global task count, all-reduce, clip, Adam."""
+        the local tasks / global task count, all-reduce, clip, Adam.  Tasks whose GP failed (ADKF_ST_NOT_PD /
+        ADKF_ST_HESS_DAMPED: zero gradient, NaN loss) are left out of the mean -- the reference would raise."""
         flat = self._ensure_flat()
         flat.release_grads()
         total = global_num_tasks if global_num_tasks is not None else tb.num_tasks * distributed.world_size()
         res = run_on_task_batch(self, tb, train=True, grad_scale=1.0 / total)
         flat.gather_grads()
-        self.reduce_and_update()
+        flat.tail[0:1].copy_(((res.status & (ops.ST_NOT_PD | ops.ST_HESS_DAMPED)) == 0).sum().to(torch.float32).reshape(1))
+        self.reduce_and_update(total)
         return res
+
+
+class _LossReadback:
+    """Per-step (mean loss per sample over the valid tasks, #dropped tasks, #unconverged fits) read by the host ONE STEP LATE:
+    an async copy into a pinned slot + an event per step, so that the host never drains the GPU inside the loop (a blocking
+    `.item()` per step costs a pipeline refill, ~3 ms at C2)."""
+
+    def __init__(self, device, depth: int = 4):
+        self._cuda = torch.device(device).type == "cuda"
+        self._pin = torch.empty(depth, 3, dtype=torch.float32)
+        if self._cuda:
+            self._pin = self._pin.pin_memory()
+        self._pending: List = []
+        self._i, self._depth = 0, depth
+
+    def push(self, res: TaskBatchResult):
+        bad = (res.status & (ops.ST_NOT_PD | ops.ST_HESS_DAMPED)) != 0
+        nc = (res.status & ops.ST_NOT_CONVERGED) != 0
+        lps = torch.where(bad, torch.zeros_like(res.loss_per_sample), res.loss_per_sample)
+        n_ok = torch.clamp((~bad).sum(), min=1).to(torch.float32)
+        rec = torch.stack([lps.sum() / n_ok, bad.sum().to(torch.float32), nc.sum().to(torch.float32)])
+        slot = self._i % self._depth
+        self._i += 1
+        self._pin[slot].copy_(rec, non_blocking=True)
+        ev = None
+        if self._cuda:
+            ev = torch.cuda.Event()
+            ev.record()
+        self._pending.append((ev, slot))
+        out = []
+        while len(self._pending) > 1:
+            out.append(self._read(self._pending.pop(0)))
+        return out
+
+    def flush(self):
+        out = [self._read(p) for p in self._pending]
+        self._pending = []
+        return out
+
+    def _read(self, item):
+        ev, slot = item
+        if ev is not None:
+            ev.synchronize()
+        v = self._pin[slot]
+        return float(v[0]), int(v[1]), int(v[2])

@@ -493,9 +493,11 @@ static int pair_launch_t(dim3 grid, cudaStream_t s, const CUtensorMap& ma, const
 
 }  // namespace pr
 
+extern int g_gemm_corr16;
+
 // Launch on CTA pairs.  ep: mode 0 with gx = ceil(N/128), gy = ceil(M/256), ntiles = gx gy splits batch already set.
 int gemm_pair_launch(const CUtensorMap& ma, const CUtensorMap& mb, const GemmEpilogue& ep, int transA, int transB, cudaStream_t s) {
-    static const bool corr16 = !(getenv("ADKF_GEMM_CORR") && getenv("ADKF_GEMM_CORR")[0] == 't');
+    const bool corr16 = g_gemm_corr16 != 0;
     const int pairs = std::max(1, num_sms() / 2);
     dim3 grid((unsigned)(2 * std::min(ep.ntiles, pairs)));
     if (!transA && !transB) return corr16 ? pr::pair_launch_t<false, false, true>(grid, s, ma, mb, ep) : pr::pair_launch_t<false, false, false>(grid, s, ma, mb, ep);

@@ -514,9 +514,17 @@ static int plan_splits_tiles(int64_t tiles, int nk, int workers = 148) {
 namespace adkf {
 int gemm_pair_launch(const CUtensorMap& ma, const CUtensorMap& mb, const GemmEpilogue& ep, int transA, int transB, cudaStream_t s);
 }
-static bool use_pair(int64_t M) {
-    static const int impl = getenv("ADKF_GEMM_IMPL") ? atoi(getenv("ADKF_GEMM_IMPL")) : 2;
-    return impl == 2 && M > kBM;
+namespace adkf {
+int g_gemm_impl = getenv("ADKF_GEMM_IMPL") ? atoi(getenv("ADKF_GEMM_IMPL")) : 2;          // 1: one CTA per tile, 2: CTA pairs
+int g_gemm_corr16 = (getenv("ADKF_GEMM_CORR") && getenv("ADKF_GEMM_CORR")[0] == 'b') ? 1 : 0;  // pair kernel: bf16 corrections
+}
+static bool use_pair(int64_t M) { return adkf::g_gemm_impl == 2 && M > kBM; }
+
+extern "C" int adkf_gemm_configure(int32_t impl, int32_t corr16) {
+    const int prev = adkf::g_gemm_impl | (adkf::g_gemm_corr16 << 8);
+    if (impl == 1 || impl == 2) adkf::g_gemm_impl = impl;
+    if (corr16 == 0 || corr16 == 1) adkf::g_gemm_corr16 = corr16;
+    return prev;
 }
 static int64_t out_tiles(int64_t M, int32_t N) {
     const int64_t bm = use_pair(M) ? 2 * kBM : kBM;

@@ -1013,7 +1013,9 @@ gp_ift_kernel(const int32_t* __restrict__ z_off, const int32_t* __restrict__ n_s
     const float jit_inner = sh.jitter;
     float* alpha = cv.vec;
     if (!ok) {
-        if (threadIdx.x == 0) status[t] = ADKF_ST_NOT_PD;
+        // the reference raises here (gpytorch NotPSDError); the batched launch flags the task, gives it a zero gradient and a
+        // NaN loss so that the caller can drop it from the meta-batch mean (adaptive_dkt_utils.train_step)
+        if (threadIdx.x == 0) { status[t] = ADKF_ST_NOT_PD; auxt[ADKF_AUX_FOUTER] = nanf(""); auxt[ADKF_AUX_F] = nanf(""); }
         for (int idx = threadIdx.x; idx < N * N; idx += blockDim.x) Wt[idx] = 0.f;
         return;
     }
@@ -1070,7 +1072,7 @@ gp_ift_kernel(const int32_t* __restrict__ z_off, const int32_t* __restrict__ n_s
         const bool okj = blocked ? build_and_factor_blocked(pj, h, J1, J2, ldN, sh, T0, T1, T2)
                                  : build_and_factor(pj, h, J1, ldN, sh);
         if (!okj) {
-            if (threadIdx.x == 0) status[t] = ADKF_ST_NOT_PD;
+            if (threadIdx.x == 0) { status[t] = ADKF_ST_NOT_PD; auxt[ADKF_AUX_FOUTER] = nanf(""); }
             for (int idx = threadIdx.x; idx < N * N; idx += blockDim.x) Wt[idx] = 0.f;
             return;
         }
@@ -1125,7 +1127,13 @@ gp_ift_kernel(const int32_t* __restrict__ z_off, const int32_t* __restrict__ n_s
         auxt[ADKF_AUX_F] = sh.f;
     }
     __syncthreads();
-    if (sh.flag) st |= ADKF_ST_HESS_DAMPED;
+    if (sh.flag && ignore_corr == 0) {
+        // singular inner Hessian: the reference's torch.linalg.solve raises (cauchy_hypergradient.py:136).  Dropping the IFT
+        // correction silently would hand back a different gradient, so the task is flagged and taken out like a non-PD one.
+        if (threadIdx.x == 0) { status[t] = ADKF_ST_HESS_DAMPED; auxt[ADKF_AUX_FOUTER] = nanf(""); }
+        for (int idx = threadIdx.x; idx < N * N; idx += blockDim.x) Wt[idx] = 0.f;
+        return;
+    }
     if (prof) tk[5] = clock64();
 
     // ---- IFT correction on the support block:  Wm_ss -= (1/n) [ Gamdot o Ku + Gam o Kudot ] ---------

@@ -6,7 +6,7 @@ accumulation rule: grad = sum_t hypergrad_t / tasks_per_batch (:402-403), then c
 Meta-test needs no collective at all: tasks are independent, each rank evaluates its shard.
 """
 import os
-from typing import List, Sequence
+from typing import List, Optional, Sequence
 
 import torch
 import torch.distributed as dist
@@ -63,14 +63,18 @@ class FlatParams:
         self.total = off
         dev = self.params[0].device
         self.flat = torch.zeros(self.total, dtype=torch.float32, device=dev)
-        self.grad = torch.zeros(self.total, dtype=torch.float32, device=dev)
+        # the gradient buffer carries ALIGN extra floats behind the parameters: tail[0] = number of tasks of this rank whose
+        # hypergradient is valid -- it rides along in the ONE all-reduce of the step (no second collective)
+        self.gbuf = torch.zeros(self.total + self.ALIGN, dtype=torch.float32, device=dev)
+        self.grad = self.gbuf[:self.total]
+        self.tail = self.gbuf[self.total:]
         for p, n, off in zip(self.params, self.sizes, self.offsets):
             self.flat[off:off + n].copy_(p.data.reshape(-1))
             p.data = self.flat[off:off + n].view_as(p.data)
             p.grad = self.grad[off:off + n].view_as(p.data)
 
     def zero_grad(self):
-        self.grad.zero_()
+        self.gbuf.zero_()
         for p, n, off in zip(self.params, self.sizes, self.offsets):   # re-attach the views if something replaced .grad
             if p.grad is None or p.grad.data_ptr() != self.grad[off:off + n].data_ptr():
                 p.grad = self.grad[off:off + n].view_as(p.data)
@@ -78,7 +82,7 @@ class FlatParams:
     def release_grads(self):
         """Before a backward pass: zero the flat gradient and detach the per-parameter views, so that autograd hands
         over each freshly computed gradient instead of launching one `grad += g` kernel per tensor (375 launches)."""
-        self.grad.zero_()
+        self.gbuf.zero_()
         for p in self.params:
             p.grad = None
 
@@ -95,8 +99,16 @@ class FlatParams:
         if views:
             torch._foreach_copy_(views, grads)
 
-    def clip_(self, max_norm: float) -> torch.Tensor:
-        """torch.nn.utils.clip_grad_norm_ on the flat buffer: same global 2-norm, one reduction, no host sync."""
+    def clip_(self, max_norm: Optional[float], pre_scale: Optional[torch.Tensor] = None) -> torch.Tensor:
+        """grad <- grad * pre_scale, then torch.nn.utils.clip_grad_norm_(max_norm) -- both factors applied in ONE pass over
+        the flat buffer: same global 2-norm, one reduction, no host sync.  pre_scale (0-dim tensor) renormalises the
+        meta-batch mean when tasks were dropped (1.0 exactly otherwise: bit-identical to no scaling)."""
         norm = torch.linalg.vector_norm(self.grad, dtype=torch.float64).float()   # fp64 accumulation
-        self.grad.mul_(torch.clamp(max_norm / (norm + 1e-6), max=1.0))
+        factor = torch.ones((), dtype=torch.float32, device=self.grad.device)
+        if pre_scale is not None:
+            norm = norm * pre_scale
+            factor = factor * pre_scale
+        if max_norm is not None:
+            factor = factor * torch.clamp(max_norm / (norm + 1e-6), max=1.0)
+        self.grad.mul_(factor)
         return norm

@@ -99,13 +99,18 @@ class FSMolDataset:
         return FSMolDataset(train_data_paths=fold_files("train"), valid_data_paths=sorted(fold_files("valid")),
                             test_data_paths=sorted(fold_files("test")), **kwargs)
 
-    def get_task_reading_iterable(self, data_fold: DataFold, repeat: bool = False) -> Iterable[FSMolTask]:
-        return _TaskIterable(self, DataFold(data_fold), repeat)
+    def get_task_reading_iterable(self, data_fold: DataFold, repeat: bool = False, shard: int = 0,
+                                  num_shards: int = 1) -> Iterable[FSMolTask]:
+        """`shard` / `num_shards`: every num_shards-th task of the (shuffled, repeating) stream starting at `shard`; the other
+        files are not read.  The shuffle comes from the dataset's own generator, whose state travels with the pickled dataset,
+        so the worker processes of host_pipeline agree on the order (fs_mol/data/fsmol_dataset.py:103-142 shards the FILE
+        LIST over its reader workers instead)."""
+        return _TaskIterable(self, DataFold(data_fold), repeat, shard, num_shards)
 
 
 class _TaskIterable:
-    def __init__(self, ds: FSMolDataset, fold: DataFold, repeat: bool):
-        self._ds, self._fold, self._repeat = ds, fold, repeat
+    def __init__(self, ds: FSMolDataset, fold: DataFold, repeat: bool, shard: int = 0, num_shards: int = 1):
+        self._ds, self._fold, self._repeat, self._shard, self._num_shards = ds, fold, repeat, shard, max(1, num_shards)
 
     def __iter__(self) -> Iterator[FSMolTask]:
         ds = self._ds
@@ -113,13 +118,21 @@ class _TaskIterable:
         if not paths:
             return
         workers = max(1, ds._num_workers)
+        rng = np.random.Generator(type(ds._rng.bit_generator)())
+        rng.bit_generator.state = ds._rng.bit_generator.state      # private copy: iterating does not disturb other iterators
+        g = 0
         with ThreadPoolExecutor(max_workers=workers) as pool:
             while True:
                 order = list(paths)
                 if self._fold == DataFold.TRAIN:
-                    ds._rng.shuffle(order)
+                    rng.shuffle(order)
+                mine = []
+                for p in order:
+                    if g % self._num_shards == self._shard:
+                        mine.append(p)
+                    g += 1
                 pending = []
-                for p in order:                               # bounded prefetch: at most `workers` parsed tasks waiting
+                for p in mine:                                # bounded prefetch: at most `workers` parsed tasks waiting
                     pending.append(pool.submit(load_task_from_file, p))
                     if len(pending) > workers:
                         yield pending.pop(0).result()

@@ -211,6 +211,16 @@ class SyntheticFSMolDataset:
                  first_task_id: int = 5000, numeric_scale: float = 1.0):
         self._counts = (num_train_tasks, num_valid_tasks, num_test_tasks)
         self._mols, self._first, self._scale = molecules_per_task, first_task_id, numeric_scale
+        self._cache = {}
+
+    def materialize(self, data_fold) -> "SyntheticFSMolDataset":
+        """Generate and keep every task of a fold in memory (a stand-in for tasks already read from disk): the cache travels
+        with the pickled dataset to host_pipeline's worker processes, which then only sample / featurise / collate."""
+        fold = int(data_fold)
+        start = self._first + sum(self._counts[:fold])
+        for i in range(self._counts[fold]):
+            self._cache[start + i] = self._task(start + i)
+        return self
 
     def get_num_fold_tasks(self, data_fold) -> int:
         return self._counts[int(data_fold)]
@@ -218,16 +228,23 @@ class SyntheticFSMolDataset:
     def _task(self, task_id: int):
         import dataclasses
         from .eval_utils import FSMolTask
+        if task_id in self._cache:
+            return self._cache[task_id]
         mols = make_task_molecules(task_id, self._mols)
         if self._scale != 1.0:
             mols = [dataclasses.replace(m, numeric_label=m.numeric_label * self._scale) for m in mols]
         return FSMolTask(name=mols[0].task_name, samples=mols)
 
-    def get_task_reading_iterable(self, data_fold, repeat: bool = False):
+    def get_task_reading_iterable(self, data_fold, repeat: bool = False, shard: int = 0, num_shards: int = 1):
+        """`shard` / `num_shards`: every num_shards-th task of the (repeating) stream starting at `shard`, without generating
+        the others (host_pipeline workers each take one shard)."""
         fold = int(data_fold)
         start = self._first + sum(self._counts[:fold])
+        g = 0
         while True:
             for i in range(self._counts[fold]):
-                yield self._task(start + i)
-            if not repeat:
+                if g % num_shards == shard:
+                    yield self._task(start + i)
+                g += 1
+            if not repeat or self._counts[fold] == 0:
                 return

@@ -34,10 +34,21 @@ METRIC = "FS-Mol-shaped meta-training tasks/sec (GP fit + IFT hypergradient)"
 UNIT = "tasks/s"
 
 
-def workload_config(n_gpus):
-    return {"workload": "C2: ADKTModel meta-training step, 16 tasks/GPU/step, support 64, query 256, gnn+ecfp+fc, "
+def tasks_per_gpu(n_gpus, scaling="weak"):
+    """weak: 16 tasks per GPU per step (global meta-batch 16 N); strong: BASELINE config 2 as written -- a global meta-batch
+    of 16 tasks split over the GPUs (2 per GPU at N = 8)."""
+    if scaling == "strong":
+        if TASKS_PER_GPU % n_gpus:
+            raise SystemExit(f"--scaling strong needs a number of GPUs that divides {TASKS_PER_GPU}")
+        return TASKS_PER_GPU // n_gpus
+    return TASKS_PER_GPU
+
+
+def workload_config(n_gpus, scaling="weak"):
+    per = tasks_per_gpu(n_gpus, scaling)
+    return {"workload": f"C2: ADKTModel meta-training step, {per} tasks/GPU/step, support 64, query 256, gnn+ecfp+fc, "
                         "matern, IFT hypergradient, clip 1.0, Adam",
-            "tasks_per_step": TASKS_PER_GPU * n_gpus, "support": SUPPORT, "query": QUERY,
+            "tasks_per_step": per * n_gpus, "support": SUPPORT, "query": QUERY,
             "parallelism": f"task-sharded dp{n_gpus}, one NCCL all-reduce of the 101 MB meta-gradient per step",
             "l2": "inputs+weights (~160 MB) and ~20 GB of per-step activations exceed the 126 MB L2; no explicit flush"}
 
@@ -140,7 +151,7 @@ def _time_ms(fn, reps=10, warm=3):
     return e0.elapsed_time(e1) / reps
 
 
-def dominant_kernel_roofline(model, tb, peaks):
+def dominant_kernel_roofline(model, tb, peaks, tf32_peak=None):
     """The dominant kernel of the step is the tcgen05 3xTF32 GEMM (gemm_tf32x3_kernel, ~60% of the device time over its
     three operand forms, profiles/r1c_*): timed here alone, with CUDA events, on its most expensive launch of the step --
     the readout hidden layer over all V nodes of the 16-task batch (M = V, N = 768, K = 1408, bias + ReLU fused).
@@ -158,13 +169,16 @@ def dominant_kernel_roofline(model, tb, peaks):
     flops = 2.0 * M * N * K
     achieved = flops / (ms * 1e-3) / 1e12
     bf16 = peaks.get("bf16_tflops")
-    src = "measured (MEASURED_PEAKS.json bf16_tflops / 2: TF32 runs at half the bf16 rate)"
-    if bf16 is None:
-        bf16, src = 2250.0 * 0.73, "fallback (B200_PROFILING.md nominal bf16 x 0.73) / 2"
-    peak = bf16 / 2.0
-    roof = {"kernel": "gemm_tf32x3_kernel<false,false> (readout hidden layer, M=V N=768 K=1408, bias+ReLU)", "bound": "tensor",
+    if tf32_peak is not None:
+        peak, src = tf32_peak, ("measured in this run: torch.matmul allow_tf32 8192^3, best of 10, CUDA events (the MEASURED_PEAKS.json "
+                                f"recipe; bf16 there: {bf16} TFLOP/s)")
+    elif bf16 is not None:
+        peak, src = bf16 / 2.0, "MEASURED_PEAKS.json bf16_tflops / 2 (TF32 runs at half the bf16 rate)"
+    else:
+        peak, src = 2250.0 * 0.73 / 2.0, "fallback (B200_PROFILING.md nominal bf16 x 0.73) / 2"
+    roof = {"kernel": "gemm_pair_kernel<false,false,false> (cta_group::2; readout hidden layer, M=V N=768 K=1408, bias+ReLU)", "bound": "tensor",
             "achieved": round(achieved, 1), "peak": round(peak, 1), "unit": "TFLOP/s", "frac": round(achieved / peak, 4),
-            "traffic": 1.142e9, "traffic_source": "ncu --set full, profiles/r1g_ncu_full_summary.md (dram read+write per launch)",
+            "traffic": 1.148e9, "traffic_source": "ncu --set full, profiles/r2g_ncu_gemm_pair_summary.md (dram read+write per launch)",
             "peak_source": src, "launch_ms": round(ms, 4), "algorithmic_flops": flops,
             "issued_tf32_tflops": round(3 * achieved, 1), "frac_issued": round(3 * achieved / peak, 4),
             "algorithmic_bytes": 4.0 * (M * K + N * K + M * N), "M": M, "N": N, "K": K}
@@ -224,27 +238,200 @@ def meta_test_throughput(device, cpu_tasks=1):
     out = {"workload": "C3: 256 regression meta-test tasks, support 128, query 192, one batched pass incl. H2D of the tasks",
            "value": 256 / (ms * 1e-3), "unit": UNIT, "ms_per_pass": ms, "h2d_bytes_per_pass": hb.nbytes()}
     if cpu_tasks > 0:
-        from oracle import adkf_oracle as orc
         torch.set_num_threads(os.cpu_count() or 1)
-        P = {n: p.detach().cpu() for n, p in model.named_parameters() if not n.startswith("gp_")}
-        ocfg = orc.OracleConfig(num_layers=10, gp_kernel="matern", use_numeric_labels=True)
-        t = 0.0
-        for i in range(cpu_tasks + 1):
-            batch = dkt.torchify(hosts[i % distinct], torch.device("cpu")).batches[0]
-            t0 = time.perf_counter()
-            orc.meta_test_task(P, batch, ocfg)
-            if i > 0:                      # first call warms the thread pools
-                t += time.perf_counter() - t0
-        out["cpu_baseline"] = {"value": cpu_tasks / t, "unit": UNIT, "cores": torch.get_num_threads(), "kind": "port",
-                               "sample": f"{cpu_tasks} task(s) of the same workload through the CPU oracle, sequential"}
+        try:
+            from oracle import ref_configs
+            run = ref_configs.c3_setup()
+            kind = "reference"
+        except Exception:
+            from oracle import adkf_oracle as orc
+            P = {n: p.detach().cpu() for n, p in model.named_parameters() if not n.startswith("gp_")}
+            ocfg = orc.OracleConfig(num_layers=10, gp_kernel="matern", use_numeric_labels=True)
+
+            def run(task_id):
+                batch = dkt.torchify(hosts[task_id % distinct], torch.device("cpu")).batches[0]
+                t0 = time.perf_counter()
+                orc.meta_test_task(P, batch, ocfg)
+                return time.perf_counter() - t0
+            kind = "port"
+        run(300)                                           # warms the thread pools
+        ts = sorted(run(301 + i) for i in range(cpu_tasks))
+        med = ts[len(ts) // 2]
+        out["cpu_baseline"] = {"value": 1.0 / med, "unit": UNIT, "cores": torch.get_num_threads(), "kind": kind,
+                               "sample": f"median of {cpu_tasks} tasks of the same workload (run_on_batches per task: reinit + "
+                                         "fit_gpytorch_scipy + prediction), sequential"}
     del model
     torch.cuda.empty_cache()
     return out
 
 
+def _cuda_ms(fn, reps, warm=2):
+    for _ in range(warm):
+        fn()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(reps):
+        fn()
+    e1.record()
+    torch.cuda.synchronize()
+    return e0.elapsed_time(e1) / reps
+
+
+def other_configs(device, cpu=True):
+    """BASELINE configs 1, 4 and 5 (reported beside the headline; BASELINE.md section 3 promised tasks/s for all five), each
+    through this package's public surface with host inputs, next to the reference's own files on the host cores."""
+    from adkf_ift_b200 import bo_utils, dkt, ops, synthetic
+    from adkf_ift_b200.adaptive_dkt import ADKTModelTrainerConfig
+    from adkf_ift_b200.adaptive_dkt_utils import ADKTModelTrainer, run_on_batches
+    from adkf_ift_b200.feature_extractor import cli_default_config
+    from adkf_ift_b200.gp_utils import fit_gpytorch_scipy
+    out = {}
+    torch.set_num_threads(os.cpu_count() or 1)
+    ref = None
+    if cpu:
+        try:
+            from oracle import ref_configs as ref
+        except Exception:
+            ref = None
+
+    # ---- C1: classification meta-test, ONE task per call through the reference's call sequence (run_on_batches) -----------
+    model = ADKTModelTrainer(ADKTModelTrainerConfig(graph_feature_extractor_config=cli_default_config(10)))
+    synthetic.deterministic_init_(model, seed=0, alpha=0.5)
+    model.to(device)
+    hosts = [dkt.task_sample_to_dkt_task_sample(synthetic.make_task_sample(700 + i, 16, 32), dkt.get_dkt_batcher(max_num_graphs=320), False)
+             for i in range(8)]
+    k = [0]
+
+    def c1():
+        dev = dkt.torchify(hosts[k[0] % 8], device)
+        k[0] += 1
+        run_on_batches(model, dev.batches, dev.batch_labels, dev.batch_numeric_labels, train=False)   # ends with a D2H of the predictions
+
+    ms = _cuda_ms(c1, 16)
+    out["c1_meta_test_single_task"] = {"workload": "C1: one classification task (support 16, query 32) per run_on_batches call, H2D + D2H included",
+                                       "value": 1e3 / ms, "unit": UNIT, "ms_per_task": ms}
+    if ref is not None:
+        run = ref.c1_setup()
+        run(700)
+        ts = sorted(run(701 + i) for i in range(3))
+        out["c1_meta_test_single_task"]["cpu_baseline"] = {"value": 1.0 / ts[1], "unit": UNIT, "cores": torch.get_num_threads(), "kind": "reference",
+                                                           "sample": "median of 3 tasks through the reference's own run_on_batches"}
+    del model
+    # ---- C4: MoleculeNet ADKF-IFT meta-training step, 9 tasks x (20 support + 32 query), GIN d=300 ------------------------------------
+    from adkf_ift_b200.moleculenet import ADKF_Meta_Trainer, ADKFModel, MolBatch, default_args, merge_mol_batches
+    args = default_args()
+    mmodel = ADKFModel(args)
+    synthetic.deterministic_init_(mmodel, seed=1)
+    mmodel.to(device)
+    trainer = ADKF_Meta_Trainer(args, mmodel)
+    T, n_s, n_q = 9, 20, 32
+
+    def mol(seed, n):
+        d = synthetic.make_mol_graphs(seed, n)
+        return MolBatch(torch.from_numpy(d["x"]), torch.from_numpy(d["edge_index"]), torch.from_numpy(d["edge_attr"]),
+                        torch.from_numpy(d["batch"]), torch.from_numpy(d["y"]), n)
+    parts = []
+    for t in range(T):
+        parts += [mol(100 + 2 * t, n_s), mol(101 + 2 * t, n_q)]
+
+    def c4():
+        mb = merge_mol_batches(parts, device, [n_s] * T, [n_q] * T)          # host graphs -> device, every step
+        res = trainer.train_step(mb)
+        float(res.loss_per_sample.mean().item())
+
+    ms = _cuda_ms(c4, 10)
+    out["c4_moleculenet_train_step"] = {"workload": "C4: ADKF_Meta_Trainer.train_step, 9 Tox21-like tasks x (20 support + 32 query), GIN 5 x 300, "
+                                                    "AdamW, clip 1.0, H2D + loss read included", "value": T * 1e3 / ms, "unit": UNIT, "ms_per_step": ms}
+    if ref is not None:
+        run = ref.c4_setup(n_s, n_q)
+        run(0)
+        ts = sorted(run(1 + i) for i in range(3))
+        out["c4_moleculenet_train_step"]["cpu_baseline"] = {"value": 1.0 / ts[1], "unit": UNIT, "cores": torch.get_num_threads(), "kind": "reference",
+                                                            "sample": "median of 3 tasks: per-task body of the reference's train_step (fit + cauchy_hypergradient), "
+                                                                      "torch_geometric restated (oracle/torch_geometric_lite.py)"}
+    del trainer, mmodel
+    # ---- C5: bayes_opt on a dockstring-shaped pool: fit on 64, joint NLL over the 2248 others (blocked Cholesky), EI over the pool ---
+    x_all, y_all = synthetic.bo_pool(seed=5, pool=2312, dim=2048)
+    X, Y = torch.from_numpy(x_all).to(device), torch.from_numpy(y_all).to(device)
+    rng = np.random.RandomState(0)
+    tr = np.sort(rng.choice(np.arange(2312), size=64, replace=False))
+    te = np.array([i for i in range(2312) if i not in set(tr.tolist())])
+    trd, ted = torch.from_numpy(tr).to(device), torch.from_numpy(te).to(device)
+    y_tr = (Y[trd] - Y[trd].mean()) / Y[trd].std()
+    y_te = (Y[ted] - Y[trd].mean()) / Y[trd].std()
+    state = {}
+
+    def c5_fit_nll():
+        likelihood, gp, mll = bo_utils.create_gp(X[trd], y_tr, "matern", device, 0.01, True)
+        gp.train(); likelihood.train()
+        fit_gpytorch_scipy(mll)
+        gp.eval(); likelihood.eval()
+        state["m"] = (likelihood, gp)
+        float((-likelihood(gp(X[ted])).log_prob(y_te) / len(te)).item())
+
+    def c5_ei():
+        likelihood, gp = state["m"]
+        float(bo_utils.expected_improvement_pool(gp, likelihood, X, float(y_tr.min().item()), tr.tolist()).max().item())
+
+    ms_fit = _cuda_ms(c5_fit_nll, 5)
+    ms_ei = _cuda_ms(c5_ei, 10)
+    # the blocked joint Cholesky alone (m^3/3 flops, trailing updates on the tensor cores)
+    N = 2312
+    layout = ops.TaskLayout.build([64], [N - 64], device)
+    perm = torch.cat([trd, ted])
+    sq = ops.gp_sqdist(X[perm].contiguous(), layout, qq_block=True)
+    yy = torch.cat([y_tr, y_te]).contiguous()
+    phi = state["m"][1]._phi()[0].contiguous()
+    ms_chol = _cuda_ms(lambda: ops.gp_joint_nll_blocked(sq.D2, N, 64, yy, "matern", phi), 10)
+    out["c5_bayes_opt"] = {"workload": "C5: dockstring-shaped pool 2312 x 2048: create_gp + fit on 64 + joint predictive NLL over 2248 molecules; "
+                                       "expected improvement over the whole pool", "fit_plus_joint_nll_ms": ms_fit, "ei_pool_ms": ms_ei,
+                           "value": 1e3 / (ms_fit + ms_ei), "unit": "pool evaluations/s (fit + NLL + EI sweep)",
+                           "joint_nll_blocked": {"ms": ms_chol, "flops": N ** 3 / 3.0, "tflops": N ** 3 / 3.0 / (ms_chol * 1e-3) / 1e12,
+                                                 "bound": "panel factorisations on the FP32 pipe, trailing updates on the tensor pipe"}}
+    if ref is not None:
+        run = ref.c5_setup()
+        run(0, 50)
+        a = [run(1 + i, 300) for i in range(3)]
+        fit_s = sorted(x[0] for x in a)[1]
+        ei_s = sorted(x[1] / x[2] for x in a)[1] * 2312
+        out["c5_bayes_opt"]["cpu_baseline"] = {"value": 1.0 / (fit_s + ei_s), "unit": "pool evaluations/s (fit + NLL + EI sweep)", "cores": torch.get_num_threads(),
+                                               "kind": "reference", "fit_plus_joint_nll_s": fit_s, "ei_pool_s": ei_s,
+                                               "sample": "median of 3: the reference's create_gp + fit + joint log_prob; its one-point-at-a-time EI timed on 300 "
+                                                         "pool molecules and scaled to 2312"}
+    return out
+
+
 # ----------------------------------------------------------------------------------------------------------
-# CPU reference arm (oracle = the reference's algorithm restated on torch CPU + SciPy L-BFGS-B)
+# CPU reference arm
+#   kind "reference": the reference's OWN files (ADKTModelTrainer, run_on_batches, functional_call, cauchy_hypergradient),
+#                     unmodified, from /root/reference or its staged copy oracle/_ref (oracle/build_ref.py), with the
+#                     third-party libraries they import restated by oracle/shims.py where not installed;
+#   kind "port"     : oracle/adkf_oracle.py (the same algorithm restated) when no copy of the reference is available.
 # ----------------------------------------------------------------------------------------------------------
+def reference_setup():
+    """-> (run_task(task_id) -> (seconds, F), kind, description)."""
+    torch.set_num_threads(os.cpu_count() or 1)
+    from adkf_ift_b200 import synthetic
+    try:
+        from oracle import ref_runner as rr
+        report = rr.install()
+    except Exception:                                       # no reference copy on this machine: the restated algorithm
+        return oracle_setup(), "port", "oracle/adkf_oracle.py (reference algorithm restated on torch CPU + SciPy L-BFGS-B)"
+    model = rr.build_reference_model(rr.reference_config(num_layers=10, gp_kernel="matern"))
+
+    def run_task(task_id):
+        s = synthetic.make_task_sample(task_id, SUPPORT, QUERY)
+        _, dev = rr.reference_dkt_sample(s, False, max_num_graphs=SUPPORT + QUERY)
+        t0 = time.perf_counter()
+        out = rr.reference_meta_train_task(model, dev.batches[0])        # adaptive_dkt_utils.py:361-404 for one task
+        return time.perf_counter() - t0, float(out["F"])
+
+    third = ", ".join(f"{k}: {v.split(' ')[0]}" for k, v in sorted(report.items()))
+    return run_task, "reference", ("the reference's own fs_mol files, unmodified (run_on_batches + fit_gpytorch_scipy + functional_call + "
+                                   f"cauchy_hypergradient per task); third-party libraries: {third}")
+
+
 def oracle_setup():
     from adkf_ift_b200 import dkt, synthetic
     from adkf_ift_b200.adaptive_dkt import ADKTModelTrainerConfig
@@ -270,10 +457,12 @@ def oracle_setup():
 
 
 def run_reference(args):
+    """One "step" = a bounded sample of the C2 step: ONE of its 16 tasks through the reference's per-task body (the reference
+    runs the tasks of a meta-batch sequentially, so tasks/s does not depend on how many are timed)."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    run_task = oracle_setup()
+    run_task, kind, desc = reference_setup()
     for i in range(args.warmup):
         run_task(9000 + i)
     t = 0.0
@@ -282,17 +471,42 @@ def run_reference(args):
         t += dt
     value = args.steps / t
     cores = torch.get_num_threads()
-    sample = f"{args.steps} steps x 1 task (support {SUPPORT}, query {QUERY}) of the C2 meta-training step, sequential"
+    sample = (f"{args.steps} steps x 1 task (support {SUPPORT}, query {QUERY}) of the C2 meta-training step, sequential as in "
+              f"train_loop; {desc}")
     print(json.dumps({
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
-        "warmup": args.warmup, "ms_per_step": 1e3 * t / args.steps, "higher_is_better": True, "scaling": "weak",
-        "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": workload_config(args.gpus),
-        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+        "warmup": args.warmup, "ms_per_step": 1e3 * t / args.steps, "higher_is_better": True, "scaling": args.scaling,
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": workload_config(args.gpus, args.scaling),
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": kind, "sample": sample},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0}), flush=True)
 
 
 # ----------------------------------------------------------------------------------------------------------
+def measure_tf32_peak(device):
+    """Dense TF32 tensor-core peak of THIS GPU, the way MEASURED_PEAKS.json measures bf16: torch.matmul (cuBLAS, allow_tf32)
+    on 8192^3, best of 10 with CUDA events (burst)."""
+    old = torch.backends.cuda.matmul.allow_tf32
+    torch.backends.cuda.matmul.allow_tf32 = True
+    try:
+        n = 8192
+        a, b = torch.randn(n, n, device=device), torch.randn(n, n, device=device)
+        for _ in range(3):
+            a @ b
+        torch.cuda.synchronize()
+        best = 1e30
+        for _ in range(10):
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            a @ b
+            e1.record()
+            torch.cuda.synchronize()
+            best = min(best, e0.elapsed_time(e1))
+        return 2.0 * n ** 3 / (best * 1e-3) / 1e12
+    finally:
+        torch.backends.cuda.matmul.allow_tf32 = old
+
+
 def run_b200(args):
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -303,69 +517,70 @@ def run_b200(args):
     device = torch.device("cuda", local)
     if world > 1:
         torch.distributed.init_process_group("nccl", device_id=device)
-    from adkf_ift_b200 import _cabi, task_batch
+    from adkf_ift_b200 import _cabi, ops, synthetic, task_batch
+    from adkf_ift_b200.adaptive_dkt_utils import _LossReadback
+    from adkf_ift_b200.eval_utils import DataFold
+    from adkf_ift_b200.host_pipeline import HostBatchPipeline, StreamSpec
     lib = _cabi.load()
     model = make_model(device)
+    per_gpu = tasks_per_gpu(world, args.scaling)
+    global_tasks = per_gpu * world
+
+    # ---- end-to-end leg set up FIRST (its worker processes are spawned before the timed regions and stay idle-blocked on
+    # their bounded queues while the resident leg runs): the user-facing path from FSMolTask objects in host memory --
+    # stratified support/query draw, DKT batching, multi-task collation in `workers` background processes, pinned staging,
+    # async H2D + CSR build one step ahead, train_step, loss / status read one step late.
+    pool_tasks = 48                                             # 3 step-batches per pass over the pool; every pass re-draws
+    ds = synthetic.SyntheticFSMolDataset(pool_tasks, 0, 0, molecules_per_task=SUPPORT + QUERY,
+                                         first_task_id=20000 + 1000 * rank).materialize(DataFold.TRAIN)
+    workers = args.workers if args.workers is not None else max(2, min(4, (os.cpu_count() or 4) // max(world, 1) - 1))
+    spec = StreamSpec(dataset=ds, data_fold=int(DataFold.TRAIN), support_size=SUPPORT, query_size=QUERY,
+                      max_num_graphs=SUPPORT + QUERY, use_numeric_labels=False, tasks_per_step=per_gpu, num_shards=1, repeat=True)
+    pipe = HostBatchPipeline(spec, num_workers=workers, rank=0, world=1)       # every rank owns its task pool
+
+    # ---- resident leg: 2 pre-collated batches already in HBM (the CSR build stays inside the step) ---------------------
     n_distinct = 2
-    hbs = [task_batch.collate_tasks(host_tasks(1000 * (rank + 1) + 100 * j, TASKS_PER_GPU), False) for j in range(n_distinct)]
+    hbs = [task_batch.collate_tasks(host_tasks(1000 * (rank + 1) + 100 * j, per_gpu), False) for j in range(n_distinct)]
     staged = [task_batch.to_device(hb, device, build_index=False) for hb in hbs]
-    losses = []
+    statuses = []
 
     def step_resident(i):
-        from adkf_ift_b200 import ops
         tb = staged[i % n_distinct]
         tb.graph_index = ops.build_graph_index(tb.adjacency_lists, tb.num_nodes, tb.node_to_graph, tb.num_graphs)
-        res = model.train_step(tb)
-        losses.append(res.loss_per_sample)
+        res = model.train_step(tb, global_num_tasks=global_tasks)
+        statuses.append(res.status)
 
-    def host_stream():
-        i = 0
-        while True:
-            yield hbs[i % n_distinct]
-            i += 1
-
-    prefetch, pending = [], []
-    loss_pin = torch.empty(2, dtype=torch.float32).pin_memory()
+    prefetch = task_batch.DevicePrefetcher(pipe, device)
+    readback = _LossReadback(device)
+    records, h2d_bytes = [], []
 
     def step_e2e(i):
-        # every step copies its inputs from pinned host memory (task_batch.DevicePrefetcher: the copies + CSR build of step
-        # i+1 are queued on a side stream behind step i, so they overlap its compute) and reads its loss back to the host
-        if not prefetch:
-            prefetch.append(task_batch.DevicePrefetcher(host_stream(), device))
-        tb = next(prefetch[0])
-        res = model.train_step(tb)
-        # D2H read of every step's loss, one step late: async copy into a pinned slot + event, and the host reads step i-1's
-        # value after it has queued step i (a blocking .item() per step drains the GPU and costs ~3 ms of launch ramp-up);
-        # the last step of the region reads its own value as well, so all K reads happen inside the timed region
-        slot = i & 1
-        loss_pin[slot:slot + 1].copy_(res.loss_per_sample.mean().reshape(1), non_blocking=True)
-        ev = torch.cuda.Event()
-        ev.record()
-        if pending:
-            pev, pslot = pending.pop()
-            pev.synchronize()
-            losses.append(float(loss_pin[pslot]))
-        pending.append((ev, slot))
+        tb = next(prefetch)
+        res = model.train_step(tb, global_num_tasks=global_tasks)
+        records.extend(readback.push(res))                     # D2H of step i-1's loss + status (12 bytes), one step late
         if i == args.steps - 1:
-            pev, pslot = pending.pop()
-            pev.synchronize()
-            losses.append(float(loss_pin[pslot]))
+            records.extend(readback.flush())                   # ... and the last step's own, inside the timed region
 
     for i in range(args.warmup):
         step_resident(i)
     torch.cuda.synchronize()
+    statuses.clear()
     l0 = lib.adkf_launch_count()
     with ClockSampler(local) as clk:
         ms = timed_region(step_resident, args.steps, world, device)
     launches = lib.adkf_launch_count() - l0
-    status = None
-    for i in range(max(1, min(args.warmup, 2))):
-        step_e2e(i)
+    bad = int(sum(int(((st & (ops.ST_NOT_PD | ops.ST_HESS_DAMPED)) != 0).sum().item()) for st in statuses))
+    assert bad == 0, f"{bad} task(s) of the timed steps failed (status NOT_PD / HESS_DAMPED): the number would be invalid"
+    for i in range(max(3, args.warmup)):
+        step_e2e(-1)
+    records.extend(readback.flush())
     torch.cuda.synchronize()
-    pending.clear()
+    records.clear()
     with ClockSampler(local) as clk2:
         ms_e2e = timed_region(step_e2e, args.steps, world, device)
-    total_tasks = TASKS_PER_GPU * world * args.steps
+    pipe.close()
+    assert len(records) == args.steps and all(r[1] == 0 for r in records), f"e2e: dropped tasks in {records}"
+    total_tasks = global_tasks * args.steps
     value = total_tasks / (ms * 1e-3)
     e2e = total_tasks / (ms_e2e * 1e-3)
     if rank != 0:
@@ -377,32 +592,36 @@ def run_b200(args):
         peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
     except OSError:
         pass
-    staged[0].graph_index = task_batch.ops.build_graph_index(staged[0].adjacency_lists, staged[0].num_nodes,
-                                                             staged[0].node_to_graph, staged[0].num_graphs)
-    roof = dominant_kernel_roofline(model, staged[0], peaks)
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-        "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-        "dtype": "f32", "data": "synthetic", "config": workload_config(world),
-        "e2e": {"value": e2e, "unit": UNIT, "h2d_bytes_per_step": hbs[0].nbytes(), "d2h_bytes_per_step": 4,
-                "ms_per_step": ms_e2e / args.steps,
-                "pipeline": "inputs of step i+1 staged from pinned host memory on a side stream during step i; loss of step i "
-                            "read by the host one step late (pinned slot + event); all K copies and K reads inside the timed region"},
-        "gpu_launches": int(launches), "clocks": clk.summary(), "clocks_e2e": clk2.summary(), "roofline": roof,
-        "last_loss_per_sample": losses[-1],
+        "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": args.scaling, "vs_baseline": None,
+        "dtype": "f32", "data": "synthetic", "config": workload_config(world, args.scaling),
+        "e2e": {"value": e2e, "unit": UNIT, "h2d_bytes_per_step": hbs[0].nbytes(), "d2h_bytes_per_step": 12,
+                "ms_per_step": ms_e2e / args.steps, "host_workers_per_rank": workers, "host_cores": os.cpu_count(),
+                "pipeline": "ADKTModelTrainer's own input path: FSMolTask objects in host memory -> stratified support/query draw "
+                            "+ DKT batching + multi-task collation in background worker processes (every step a NEW draw: no two "
+                            "batches alike) -> pinned ring -> async H2D + CSR build one step ahead -> train_step -> loss and "
+                            "per-task status read by the host one step late; all of it inside the timed region"},
+        "gpu_launches": int(launches), "clocks": clk.summary(), "clocks_e2e": clk2.summary(),
+        "last_loss_per_sample": records[-1][0],
     }
+    if world == 1:
+        staged[0].graph_index = ops.build_graph_index(staged[0].adjacency_lists, staged[0].num_nodes, staged[0].node_to_graph,
+                                                      staged[0].num_graphs)
+        line["roofline"] = dominant_kernel_roofline(model, staged[0], peaks, measure_tf32_peak(device))
     if world == 1 and not args.no_cpu_baseline:
-        run_task = oracle_setup()
+        run_task, kind, desc = reference_setup()
         run_task(9000)  # warm-up (thread pools, allocator)
         n_cpu = args.cpu_tasks
         t = sum(run_task(9100 + i)[0] for i in range(n_cpu))
-        line["cpu_baseline"] = {"value": n_cpu / t, "unit": UNIT, "cores": torch.get_num_threads(), "kind": "port",
-                                "sample": f"{n_cpu} tasks (support {SUPPORT}, query {QUERY}) of the same C2 step through the "
-                                          "CPU oracle (reference algorithm on torch CPU + SciPy L-BFGS-B), sequential"}
+        line["cpu_baseline"] = {"value": n_cpu / t, "unit": UNIT, "cores": torch.get_num_threads(), "kind": kind,
+                                "sample": f"{n_cpu} tasks (support {SUPPORT}, query {QUERY}) of the same C2 step, sequential; {desc}"}
     if world == 1 and not args.no_meta_test:
         del model, staged
         torch.cuda.empty_cache()
-        line["meta_test"] = meta_test_throughput(device, 0 if args.no_cpu_baseline else 1)
+        line["meta_test"] = meta_test_throughput(device, 0 if args.no_cpu_baseline else 3)
+        if not args.no_other_configs:
+            line["other_configs"] = other_configs(device, cpu=not args.no_cpu_baseline)
     print(json.dumps(line), flush=True)
     if world > 1:
         torch.distributed.destroy_process_group()
@@ -417,6 +636,10 @@ def main():
     ap.add_argument("--cpu-tasks", type=int, default=2)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-meta-test", action="store_true", help="skip the C3 meta-test throughput reported beside the headline")
+    ap.add_argument("--no-other-configs", action="store_true", help="skip the C1 / C4 / C5 figures reported beside the headline")
+    ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
+                    help="weak: 16 tasks per GPU per step; strong: a global meta-batch of 16 tasks split over the GPUs")
+    ap.add_argument("--workers", type=int, default=None, help="host featurisation processes per rank of the e2e leg")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

@@ -31,7 +31,10 @@ extern "C" {
 #define ADKF_ST_JITTER        1   /* Cholesky needed diagonal jitter (psd_safe_cholesky fallback) */
 #define ADKF_ST_NOT_PD        2   /* not positive definite after 3 jitter retries                 */
 #define ADKF_ST_NOT_CONVERGED 4   /* inner fit hit max_iter before |grad|_inf <= gtol             */
-#define ADKF_ST_HESS_DAMPED   8   /* inner Hessian was not PD at the optimum (IFT solve damped)    */
+#define ADKF_ST_HESS_DAMPED   8   /* inner Hessian singular in adkf_gp_ift: no hypergradient for the task */
+/* A task flagged NOT_PD or HESS_DAMPED by adkf_gp_ift gets Wm = 0 (zero gradient) and aux[ADKF_AUX_FOUTER] = NaN: the
+ * reference raises in these cases (gpytorch NotPSDError / torch.linalg.solve); the caller drops the task from the meta-batch
+ * mean and renormalises (adaptive_dkt_utils.ADKTModelTrainer.train_step). */
 
 /* GP kernel families (fs_mol/utils/gp_utils.py:22-43, :106-134) */
 #define ADKF_KERNEL_MATERN52 0   /* pair statistic u = centred squared distance, third parameter = lengthscale */
@@ -278,6 +281,13 @@ int adkf_gemm_tf32x3_masked(const float* A, int32_t transA, int64_t lda, const f
                             int64_t M, int32_t N, int32_t K, const float* mask, int64_t ldm, int32_t mask_act, float* D,
                             int64_t ldd, void* stream);
 int64_t adkf_gemm_splitk_ws_floats(int64_t M, int32_t N, int32_t K);
+
+/* Process-wide GEMM variant (development / A-B measurements; initialised from ADKF_GEMM_IMPL / ADKF_GEMM_CORR):
+ *   impl   1 = one CTA per 128 x 128 tile (gemm_tf32x3.cu), 2 = CTA pairs on 256 x 128 tiles (gemm_pair.cu, default); other: keep
+ *   corr16 0 = correction products in tf32 (default, fp32-class accuracy everywhere), 1 = in bf16 (pair kernel only); other: keep
+ * Returns the previous setting as impl | corr16 << 8.  Not thread-safe against concurrent launches.
+ * NOTE: adkf_gemm_splitk_ws_floats depends on impl -- size workspaces after configuring. */
+int adkf_gemm_configure(int32_t impl, int32_t corr16);
 /* Batched form: `batch` products in one launch whose operands are column / row blocks of the same 2-D arrays (one TMA tensor
  * map per operand): batch b uses opA at (row + b*a_mn_stride, k + b*a_k_stride), opB likewise, writes D + b*d_stride and adds
  * bias + b*bias_stride.  a_slow / a_fast (b_slow / b_fast) are the extents of the whole underlying arrays (slow = rows).

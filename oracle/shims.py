@@ -17,8 +17,10 @@ import os
 import sys
 import types
 
-REFERENCE_ROOT = os.environ.get("ADKF_REFERENCE_ROOT", "/root/reference")
 _HERE = os.path.dirname(os.path.abspath(__file__))
+# /root/reference in the authoring container; on the GPU box the unmodified copy staged by oracle/build_ref.py
+REFERENCE_ROOT = os.environ.get("ADKF_REFERENCE_ROOT") or (
+    "/root/reference" if os.path.isdir("/root/reference/fs_mol") else os.path.join(_HERE, "_ref"))
 
 
 def reference_available():

@@ -112,3 +112,75 @@ def test_device_prefetcher_matches_direct_staging(cuda_device):
         a = run_on_task_batch(model, tb, train=False)
         b = run_on_task_batch(model, ref, train=False)
         assert torch.equal(a.mean, b.mean) and torch.equal(a.phi, b.phi)
+
+
+def test_train_loop_pipeline_identical_losses(cuda_device, tmp_path):
+    """train_loop fed by worker processes (featurisation + collation in the background, pinned staging, async
+    H2D, loss read one step late) gives EXACTLY the losses and parameters of the inline path over the same shard generators."""
+    from adkf_ift_b200 import synthetic
+    ds = synthetic.SyntheticFSMolDataset(12, 1, 1, molecules_per_task=64)
+    runs = []
+    for workers in (0, 2):
+        model = small_model(cuda_device, num_train_steps=5, validate_every_num_steps=100)
+        losses = model.train_loop(str(tmp_path / f"w{workers}"), ds, cuda_device, num_workers=workers, emulate_workers=2)
+        runs.append((losses, torch.cat([p.detach().reshape(-1).clone() for p in model.feature_extractor_params()])))
+    assert len(runs[0][0]) == 5 and np.isfinite(runs[0][0]).all()
+    assert runs[0][0] == runs[1][0], (runs[0][0], runs[1][0])
+    assert torch.equal(runs[0][1], runs[1][1])
+
+
+def test_failed_task_is_dropped_and_mean_renormalised(cuda_device):
+    """A task whose covariance is not positive definite (here: NaN labels) is flagged, contributes a zero gradient and a NaN
+    outer loss, and the meta-batch mean is taken over the remaining tasks: the step equals the step on the batch WITHOUT that
+    task (the reference raises in this situation: gpytorch NotPSDError)."""
+    from adkf_ift_b200 import dkt, ops, synthetic, task_batch
+    hosts = [dkt.task_sample_to_dkt_task_sample(synthetic.make_task_sample(500 + t, 16, 24), dkt.get_dkt_batcher(max_num_graphs=96),
+                                                False).batches[0] for t in range(3)]
+    results = []
+    for drop in (False, True):
+        model = small_model(cuda_device)
+        use = hosts if drop else hosts[:2]
+        tb = task_batch.to_device(task_batch.collate_tasks(use, False), cuda_device)
+        if drop:
+            off = sum(h.support_features.num_graphs + h.query_features.num_graphs for h in hosts[:2])
+            tb.labels[off:] = float("nan")                         # third task: NaN labels -> its Cholesky fails
+        res = model.train_step(tb, global_num_tasks=len(use))
+        torch.cuda.synchronize()
+        results.append((res, torch.cat([p.detach().reshape(-1).clone() for p in model.feature_extractor_params()])))
+    res_ok, p_ok = results[0]
+    res_drop, p_drop = results[1]
+    st = res_drop.status.cpu().numpy()
+    assert st[2] & (ops.ST_NOT_PD | ops.ST_HESS_DAMPED) and not (st[:2] & (ops.ST_NOT_PD | ops.ST_HESS_DAMPED)).any()
+    assert torch.isnan(res_drop.outer_loss[2]) and torch.isfinite(res_drop.outer_loss[:2]).all()
+    # same parameters after the step as the 2-task batch (the extractor forward of the extra graphs does not touch the others)
+    rel = float((p_drop - p_ok).abs().max() / p_ok.abs().max())
+    print("dropped-task step vs 2-task step: max parameter difference", rel)
+    assert rel < 1e-6
+
+
+def test_optimizer_state_round_trip(cuda_device, tmp_path):
+    """Adam moments survive save_model / load_model_weights although the live optimiser steps ONE flat tensor: the checkpoint
+    holds per-parameter state (the reference's layout), a fresh trainer continues bit-identically."""
+    from adkf_ift_b200 import dkt, synthetic, task_batch
+    hosts = [dkt.task_sample_to_dkt_task_sample(synthetic.make_task_sample(600 + t, 16, 24), dkt.get_dkt_batcher(max_num_graphs=96),
+                                                False).batches[0] for t in range(2)]
+    hb = task_batch.collate_tasks(hosts, False)
+    a = small_model(cuda_device)
+    for _ in range(2):
+        a.train_step(task_batch.to_device(hb, cuda_device))
+    a.save_model(str(tmp_path / "ckpt.pt"), optimizer=a.optimizer, epoch=2)
+    sd = torch.load(str(tmp_path / "ckpt.pt"), weights_only=False)["optimizer_state_dict"]
+    n_params = len(a.feature_extractor_params())
+    assert len(sd["state"]) == n_params and sd["param_groups"][0]["params"] == list(range(n_params))
+    assert tuple(sd["state"][0]["exp_avg"].shape) == tuple(a.feature_extractor_params()[0].shape)
+    b = small_model(cuda_device)
+    b._ensure_flat()
+    b.load_model_weights(str(tmp_path / "ckpt.pt"), device=cuda_device)
+    a.train_step(task_batch.to_device(hb, cuda_device))
+    b.train_step(task_batch.to_device(hb, cuda_device))
+    pa = torch.cat([p.detach().reshape(-1) for p in a.feature_extractor_params()])
+    pb = torch.cat([p.detach().reshape(-1) for p in b.feature_extractor_params()])
+    assert torch.equal(pa, pb)
+    # and into the reference's own optimiser class (per-parameter Adam)
+    ref_opt = torch.optim.Adam(small_model(cuda_device).feature_extractor_params(), 1e-4)
+    ref_opt.load_state_dict(sd)

@@ -345,3 +345,28 @@ def test_ranking_metrics_bit_identical_to_scikit_learn():
             p = np.round(p, 1)          # ties
         assert metrics.roc_auc_score(y, p) == float(sk.roc_auc_score(y, p))
         assert metrics.average_precision_score(y, p) == float(sk.average_precision_score(y, p))
+
+
+def test_host_pipeline_workers_equal_inline():
+    """host_pipeline.HostBatchPipeline: worker PROCESSES produce exactly the batches, in exactly the order, of the inline
+    round-robin over the same shard generators; ranks see disjoint shards of the task stream (CPU: no pinning)."""
+    from adkf_ift_b200.eval_utils import DataFold
+    from adkf_ift_b200.host_pipeline import HostBatchPipeline, StreamSpec
+    ds = synthetic.SyntheticFSMolDataset(10, 0, 0, molecules_per_task=48)
+    spec = StreamSpec(dataset=ds, data_fold=int(DataFold.TRAIN), support_size=8, query_size=16, max_num_graphs=64,
+                      use_numeric_labels=False, tasks_per_step=2, num_shards=1, repeat=True)
+    inline = HostBatchPipeline(spec, num_workers=0, emulate_workers=2)
+    procs = HostBatchPipeline(spec, num_workers=2)
+    try:
+        for _ in range(5):
+            a, b = next(inline), next(procs)
+            assert a.n_sup == b.n_sup and a.n_query == b.n_query and a.num_nodes == b.num_nodes
+            assert torch.equal(a.node_features, b.node_features) and torch.equal(a.fingerprints, b.fingerprints)
+            assert all(torch.equal(x, y) for x, y in zip(a.adjacency, b.adjacency)) and torch.equal(a.labels, b.labels)
+    finally:
+        procs.close()
+    # two ranks: disjoint task shards
+    r0 = HostBatchPipeline(spec, num_workers=0, emulate_workers=1, rank=0, world=2)
+    r1 = HostBatchPipeline(spec, num_workers=0, emulate_workers=1, rank=1, world=2)
+    f0, f1 = next(r0).fingerprints, next(r1).fingerprints
+    assert f0.shape != f1.shape or not torch.equal(f0, f1)
