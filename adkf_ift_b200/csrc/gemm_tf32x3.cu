@@ -516,14 +516,15 @@ int gemm_pair_launch(const CUtensorMap& ma, const CUtensorMap& mb, const GemmEpi
 }
 namespace adkf {
 int g_gemm_impl = getenv("ADKF_GEMM_IMPL") ? atoi(getenv("ADKF_GEMM_IMPL")) : 2;          // 1: one CTA per tile, 2: CTA pairs
-int g_gemm_corr16 = (getenv("ADKF_GEMM_CORR") && getenv("ADKF_GEMM_CORR")[0] == 'b') ? 1 : 0;  // pair kernel: bf16 corrections
+// pair kernel, correction products: 0 tf32 everywhere, 1 bf16 everywhere, 2 bf16 in the backward forms only (default)
+int g_gemm_corr16 = !getenv("ADKF_GEMM_CORR") ? 2 : (getenv("ADKF_GEMM_CORR")[0] == 'b' ? 1 : (getenv("ADKF_GEMM_CORR")[0] == 't' ? 0 : 2));
 }
 static bool use_pair(int64_t M) { return adkf::g_gemm_impl == 2 && M > kBM; }
 
 extern "C" int adkf_gemm_configure(int32_t impl, int32_t corr16) {
     const int prev = adkf::g_gemm_impl | (adkf::g_gemm_corr16 << 8);
     if (impl == 1 || impl == 2) adkf::g_gemm_impl = impl;
-    if (corr16 == 0 || corr16 == 1) adkf::g_gemm_corr16 = corr16;
+    if (corr16 >= 0 && corr16 <= 2) adkf::g_gemm_corr16 = corr16;
     return prev;
 }
 static int64_t out_tiles(int64_t M, int32_t N) {

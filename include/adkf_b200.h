@@ -284,7 +284,8 @@ int64_t adkf_gemm_splitk_ws_floats(int64_t M, int32_t N, int32_t K);
 
 /* Process-wide GEMM variant (development / A-B measurements; initialised from ADKF_GEMM_IMPL / ADKF_GEMM_CORR):
  *   impl   1 = one CTA per 128 x 128 tile (gemm_tf32x3.cu), 2 = CTA pairs on 256 x 128 tiles (gemm_pair.cu, default); other: keep
- *   corr16 0 = correction products in tf32 (default, fp32-class accuracy everywhere), 1 = in bf16 (pair kernel only); other: keep
+ *   corr16 0 = correction products in tf32, 1 = in bf16, 2 = bf16 for the backward operand forms (K,T) / (T,T) only (default;
+ *          pair kernel only); other: keep
  * Returns the previous setting as impl | corr16 << 8.  Not thread-safe against concurrent launches.
  * NOTE: adkf_gemm_splitk_ws_floats depends on impl -- size workspaces after configuring. */
 int adkf_gemm_configure(int32_t impl, int32_t corr16);
