@@ -131,7 +131,7 @@ def test_train_loop_pipeline_identical_losses(cuda_device, tmp_path):
 
 def test_failed_task_is_dropped_and_mean_renormalised(cuda_device, monkeypatch):
     """A task whose covariance is not positive definite even after the jitter ladder (forced here through its GP parameters:
-    outputscale 1e8, lengthscale 5e8 -> a rank-one K + 1e-4 I in fp32) is flagged, contributes a zero gradient and a NaN
+    outputscale 1e8, lengthscale 1e9 -> a rank-one K + 1e-4 I in fp32) is flagged, contributes a zero gradient and a NaN
     outer loss, and the meta-batch mean is taken over the remaining tasks: the step equals the step on the batch WITHOUT
     that task (the reference raises in this situation: gpytorch NotPSDError)."""
     from adkf_ift_b200 import adaptive_dkt_utils as U
@@ -143,7 +143,7 @@ def test_failed_task_is_dropped_and_mean_renormalised(cuda_device, monkeypatch):
     def sabotaged(g, phi, max_iter, gtol):
         fit = real_fit(g, phi, max_iter, gtol)
         if fit.phi.shape[0] == 3:
-            fit.phi[2] = torch.tensor([-40.0, 18.4, 20.0], device=fit.phi.device)
+            fit.phi[2] = torch.tensor([-40.0, 1e8, 1e9], device=fit.phi.device)   # softplus(x) = x: outputscale 1e8, lengthscale 1e9
         return fit
 
     monkeypatch.setattr(U, "_fit_or_fixed", sabotaged)
