@@ -65,6 +65,8 @@ SIGNATURES = {
     "adkf_gemm_batched_splitk_ws_floats": ([c_int64, c_int32, c_int32, c_int32], c_int64),
     "adkf_gemm_splitk_ws_floats": ([c_int64, c_int32, c_int32], c_int64),
     "adkf_gemm_configure": ([c_int32, c_int32], ctypes.c_int),
+    "adkf_ard_wsqdist": ([_P, c_int32, c_int32, _P, _P, _P, c_int32, _P, c_int32, _P, _P], ctypes.c_int),
+    "adkf_ard_pairquad": ([_P, c_int32, c_int32, _P, _P, _P, _P, c_int32, _P, _P], ctypes.c_int),
     "adkf_gram_sqdist_bwd": ([_P, c_int32, c_int32, _P, _P, c_int32, _P, _P, c_float, _P, _P], ctypes.c_int),
     "adkf_gp_fit": ([c_int32, _P, _P, _P, _P, _P, c_int32, c_float, c_float, c_int32, c_int32, c_int32, c_float,
                      _P, _P, _P, _P, c_int64, _P], ctypes.c_int),

@@ -90,9 +90,10 @@ class GaussianLikelihoodParams(nn.Module):
 
 
 class _BaseKernel(nn.Module):
-    def __init__(self):
+    def __init__(self, ard_num_dims: Optional[int] = None):
         super().__init__()
-        self.raw_lengthscale = nn.Parameter(torch.zeros(1, 1))
+        self.ard_num_dims = ard_num_dims
+        self.raw_lengthscale = nn.Parameter(torch.zeros(1, 1 if ard_num_dims is None else ard_num_dims))
         self.lengthscale_prior_loc: Optional[float] = None
 
     @property
@@ -107,10 +108,10 @@ class _BaseKernel(nn.Module):
 
 
 class _ScaleKernel(nn.Module):
-    def __init__(self):
+    def __init__(self, ard_num_dims: Optional[int] = None):
         super().__init__()
         self.raw_outputscale = nn.Parameter(torch.zeros(()))
-        self.base_kernel = _BaseKernel()
+        self.base_kernel = _BaseKernel(ard_num_dims)
 
     @property
     def outputscale(self):
@@ -130,11 +131,12 @@ class ExactGPLayer(nn.Module):
     def __init__(self, train_x=None, train_y=None, likelihood: Optional[GaussianLikelihoodParams] = None,
                  kernel: str = "matern", ard_num_dims=None, use_numeric_labels: bool = False):
         super().__init__()
-        if ard_num_dims is not None:
-            raise NotImplementedError("--use-ard (2050-dim inner problem) has no sm_100a kernel yet (SURVEY 8(f4))")
         self.kernel = gpk.check_kernel(kernel)
+        if ard_num_dims is not None and self.kernel not in ("matern", "rbf", "RBF"):
+            ard_num_dims = None                          # gp_utils.py:22-43: only the RBF / Matern branches take ard_num_dims
+        self.ard_num_dims = ard_num_dims
         self.use_numeric_labels = use_numeric_labels
-        self.covar_module = _ScaleKernel()
+        self.covar_module = _ScaleKernel(ard_num_dims)
         self.train_inputs: Optional[Tuple[torch.Tensor]] = None
         self.train_targets: Optional[torch.Tensor] = None
         if likelihood is not None:
@@ -242,8 +244,6 @@ class ADKTModel(nn.Module):
     def __init__(self, config: ADKTModelTrainerConfig):
         super().__init__()
         self.config = config
-        if getattr(config, "use_ard", False):
-            raise NotImplementedError("--use-ard has no sm_100a kernel yet (SURVEY 8(f4))")
         if gpk.check_kernel(config.gp_kernel) == "tanimoto":   # ExactGPLayer has no Tanimoto branch (gp_utils.py:22-45)
             raise ValueError("[ERROR] the kernel 'tanimoto' is not supported! (use gp_utils.ExactTanimotoGP)")
         if config.used_features.startswith("gnn"):
@@ -277,12 +277,19 @@ class ADKTModel(nn.Module):
     def _create_tail_gp(self):
         dev = next(self.parameters()).device if any(True for _ in self.parameters()) else None
         self.gp_likelihood = GaussianLikelihoodParams()
-        self.gp_model = ExactGPLayer(likelihood=self.gp_likelihood, kernel=self.config.gp_kernel,
+        ard = getattr(self, "fc_out_dim", None) if getattr(self.config, "use_ard", False) else None   # adaptive_dkt.py:107-110
+        if getattr(self.config, "use_ard", False) and ard is None:
+            raise AttributeError("use_ard needs fc_out_dim, i.e. used_features ending in '+fc' (adaptive_dkt.py:107-108)")
+        self.gp_model = ExactGPLayer(likelihood=self.gp_likelihood, kernel=self.config.gp_kernel, ard_num_dims=ard,
                                      use_numeric_labels=self.config.use_numeric_labels)
         if dev is not None:
             self.gp_likelihood.to(dev)
             self.gp_model.to(dev)
         self.mll = MarginalLogLikelihood(self)
+
+    @property
+    def use_ard(self) -> bool:
+        return self.gp_model.ard_num_dims is not None
 
     def compute_median_lengthscale_init(self, gp_input: torch.Tensor) -> torch.Tensor:
         """sqrt(0.5 * lower-median of the positive pairwise squared distances) (adaptive_dkt.py:128-131), from
@@ -300,6 +307,15 @@ class ADKTModel(nn.Module):
         n = gp_input.shape[0]
         layout = ops.TaskLayout.build([n], [0], gp_input.device)
         y = targets if targets is not None else torch.zeros(n, device=gp_input.device)
+        if self.use_ard:
+            from .gp_ard import BatchedARDExactGP
+            g = BatchedARDExactGP(gp_input.float(), y.float(), layout, self.config.gp_kernel, self.config.use_numeric_labels,
+                                  use_lengthscale_prior)
+            phi0, l0, loc = g.init_phi()
+            self._write_phi(phi0[0])
+            self.gp_model.covar_module.base_kernel.lengthscale_prior_loc = loc[0] if use_lengthscale_prior else None
+            self._bound = dict(gp=g, ard=True, ls_loc=loc, use_prior=use_lengthscale_prior)
+            return
         g = gpk.BatchedExactGP(gp_input.float(), y.float(), layout, self.config.gp_kernel,
                                self.config.use_numeric_labels, use_lengthscale_prior)
         init = g.init()
@@ -312,10 +328,10 @@ class ADKTModel(nn.Module):
         with torch.no_grad():
             self.gp_likelihood.noise_covar.raw_noise.copy_(phi3[0:1])
             self.gp_model.covar_module.raw_outputscale.copy_(phi3[1])
-            self.gp_model.covar_module.base_kernel.raw_lengthscale.copy_(phi3[2].view(1, 1))
+            self.gp_model.covar_module.base_kernel.raw_lengthscale.copy_(phi3[2:].view(1, -1))
 
     def _read_phi(self) -> torch.Tensor:
-        return torch.stack([p.detach().reshape(()) for p in self.gp_params()]).view(1, 3).float().contiguous()
+        return torch.cat([p.detach().reshape(-1) for p in self.gp_params()]).view(1, -1).float().contiguous()
 
     def fit_gp(self, max_iter: int = 50, gtol: float = 2e-6):
         """Replacement for `fit_gpytorch_scipy(model.mll)` (adaptive_dkt_utils.py:91): on-device Newton fit of the
@@ -323,6 +339,11 @@ class ADKTModel(nn.Module):
         if self._bound is None:
             raise RuntimeError("no task bound: call model(batch, train_loss=True) first")
         b = self._bound
+        if b.get("ard"):
+            res = b["gp"].fit(start=self._read_phi())
+            self._write_phi(res.phi[0])
+            b["fit"] = res
+            return res
         start = gpk.FitResult(self._read_phi(), b["fit"].aux, b["fit"].status)
         res = b["gp"].fit(start=start, max_iter=max_iter, gtol=gtol)
         self._write_phi(res.phi[0])
@@ -391,6 +412,9 @@ class ADKTModel(nn.Module):
                 return None
             ls_loc = self.gp_model.covar_module.base_kernel.lengthscale_prior_loc
             phi = self.gp_params()
+            if self.use_ard:
+                raise NotImplementedError("use_ard: the differentiable single-task losses (functional_call surface) exist for the scalar "
+                                          "lengthscale only; meta-training with ARD goes through run_on_task_batch / train_step")
             if train_loss:
                 layout = ops.TaskLayout.build([n], [0], zs.device)
                 return _TaskGPLoss.apply(zs, phi[0], phi[1], phi[2], ys, layout, cfg, ls_loc, False)
@@ -409,6 +433,13 @@ class ADKTModel(nn.Module):
             m = zq.shape[0]
             layout = ops.TaskLayout.build([n], [m], zs.device)
             Z = torch.cat([zs.detach(), zq])
+            if self.use_ard:
+                from .gp_ard import BatchedARDExactGP
+                ga = BatchedARDExactGP(Z, torch.cat([ys, torch.zeros(m, device=ys.device)]), layout, cfg.gp_kernel,
+                                       cfg.use_numeric_labels, cfg.use_lengthscale_prior)
+                mean, var, _ = ga.predict(self._read_phi())
+                self.gp_model.set_train_data(inputs=zs.detach(), targets=ys, strict=False)
+                return gpk.PredictiveDistribution(mean[n:], var[n:], None)
             g = gpk.BatchedExactGP(Z, torch.cat([ys, torch.zeros(m, device=ys.device)]), layout, cfg.gp_kernel,
                                    cfg.use_numeric_labels, cfg.use_lengthscale_prior, qq_block=True)
             phi = self._read_phi()

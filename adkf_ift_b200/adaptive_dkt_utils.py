@@ -74,6 +74,8 @@ def run_on_task_batch(model: ADKTModel, tb: DeviceTaskBatch, train: bool = False
     (default 1/T = the reference's `/ tasks_per_batch`), into `.grad` of the feature-extractor parameters.
     `phi` [T,3] skips the inner fit and evaluates at the given raw GP parameters (fixed-phi parity checks)."""
     cfg = model.config
+    if getattr(cfg, "use_ard", False):
+        return _run_on_task_batch_ard(model, tb, train, grad_scale, phi)
     if train:
         model.train()
         Z = model.embed(tb)
@@ -99,6 +101,38 @@ def run_on_task_batch(model: ADKTModel, tb: DeviceTaskBatch, train: bool = False
         preds = mq if cfg.use_numeric_labels else torch.sigmoid(mq)
     return TaskBatchResult(phi=fit.phi, status=fit.status | st, aux=fit.aux, mean=mean, variance=var, preds=preds,
                            query_mask=qm)
+
+
+def _run_on_task_batch_ard(model: ADKTModel, tb: DeviceTaskBatch, train: bool, grad_scale: Optional[float],
+                           phi: Optional[torch.Tensor]) -> TaskBatchResult:
+    """--use-ard (adaptive_dkt_train.py:107,151): d + 2 inner parameters per task, batched L-BFGS fit and matrix-free (CG)
+    inverse-Hessian-vector product on the device (gp_ard.py) instead of the reference's dense 2050 x 2050 Hessian."""
+    from .gp_ard import ARDFit, BatchedARDExactGP
+    cfg = model.config
+    model.train(train)
+    with torch.set_grad_enabled(train):
+        Z = model.embed(tb)
+    g = BatchedARDExactGP(Z.detach(), tb.labels, tb.layout, cfg.gp_kernel, cfg.use_numeric_labels, cfg.use_lengthscale_prior)
+    if phi is None:
+        fit = g.fit()
+    else:
+        phi0, l0, loc = g.init_phi()
+        p = phi.to(Z.device, torch.float32).view(tb.num_tasks, -1).contiguous()
+        f, grad, st = g.value_and_grad(p, loc)
+        fit = ARDFit(p, f, grad, loc, l0, 0, st)
+    aux = torch.zeros(tb.num_tasks, ops.AUX, dtype=torch.float32, device=Z.device)
+    if train:
+        dZ, info = g.hypergradient(fit, ignore_grad_correction=cfg.ignore_grad_correction)
+        scale = (1.0 / tb.num_tasks) if grad_scale is None else grad_scale
+        Z.backward(dZ * scale)
+        F_t = info["F"]
+        n_q = ops.host_to_device([float(r - s) for r, s in zip(tb.layout.n_rows_host, tb.layout.n_sup_host)], torch.float32, Z.device)
+        return TaskBatchResult(phi=fit.phi, status=fit.status | info["status"], aux=aux, outer_loss=F_t, loss_per_sample=F_t / n_q)
+    mean, var, st = g.predict(fit.phi)
+    qm = _query_mask(tb.layout, Z.device)
+    mq = mean[qm]
+    preds = mq if cfg.use_numeric_labels else torch.sigmoid(mq)
+    return TaskBatchResult(phi=fit.phi, status=fit.status | st, aux=aux, mean=mean, variance=var, preds=preds, query_mask=qm)
 
 
 def run_on_batches_raw(model: ADKTModel, batches: Sequence, batch_labels: Sequence, batch_numeric_labels: Sequence,

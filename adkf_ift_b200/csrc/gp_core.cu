@@ -74,6 +74,17 @@ __device__ __forceinline__ float kernel_only(float u, float s, float l, int kind
     if (kind == ADKF_KERNEL_POLY2) return s * (u + l) * (u + l);
     return s * u;
 }
+// d2K/du2 for the stationary kernels (u = squared distance, l = lengthscale): what the directional derivative of dK/du along a
+// change of the DISTANCES needs (ARD: the lengthscales act on u itself, adkf_gp_ift mode 4)
+__device__ __forceinline__ float kernel_uu(float u, float s, float l, int kind) {
+    const float il2 = 1.f / (l * l);
+    if (kind == ADKF_KERNEL_MATERN52) {
+        const float r = sqrtf(fmaxf(u * il2, 1e-30f));
+        return s * (25.f / 12.f) * il2 * il2 * expf(-kSqrt5 * r);
+    }
+    if (kind == ADKF_KERNEL_RBF) return 0.25f * s * il2 * il2 * expf(-0.5f * u * il2);
+    return 0.f;
+}
 __device__ __forceinline__ bool kind_is_stationary(int kind) { return kind == ADKF_KERNEL_MATERN52 || kind == ADKF_KERNEL_RBF; }
 // parameters the inner problem optimises: bit i <-> raw parameter i.  cossim / Tanimoto have no third parameter; the
 // caller can freeze more through the ADKF_KERNEL_FREEZE_* bits of the `kernel` argument (ExactTanimotoGP keeps the noise
@@ -900,19 +911,25 @@ __device__ bool build_and_factor_blocked(const GpProblem& pb, const Hyper& h, fl
 // IFT correction on the support block:  Wm_ss += sign (1/n) [ Gamdot o Ku + Gam o Kudot ], the derivative of df/dD2 along the
 // psi-space direction sh.pd (= t o raw direction).  sign -1: hypergradient (direction v = H^-1 dF/dphi, App. B);
 // sign +1: the mixed second derivative d/deps df/dD2(phi + eps u) for a caller-supplied u (mode 3: double backward of f).
+//   ddot (mode 4, else false): Wt holds on entry a direction dD2 of the pair statistics themselves (support block); then
+//   Adot += Ku o dD2 and Kudot += Kuu o dD2, and sums[0..1] receive sum_ij gamdot_ij delta_ij and
+//   sum_ij (gamdot_ij K_ij + gam_ij Kdot_ij) -- the pieces of d/deps of the (noise, outputscale) gradient components.
 __device__ void ift_correction(const Carve& cv, int n, int N, const float* __restrict__ D2t, const Hyper& h, int kind,
                                float* __restrict__ Wt, const float* __restrict__ alpha, GpShared& sh, bool in_smem,
-                               float* smem_f, float* small_ws, float sign) {
+                               float* smem_f, float* small_ws, float sign, bool ddot = false) {
     const float pd0 = sh.pd[0], pd1 = sh.pd[1], pd2 = sh.pd[2];
-    // M2 <- Adot = pd0 I + pd1 K/s + pd2 S   (M2 currently holds S)
+    // M2 <- Adot = pd0 I + pd1 K/s + pd2 S (+ Ku o dD2)   (M2 currently holds S)
     for (int idx = threadIdx.x; idx < n * n; idx += blockDim.x) {
         const int i = idx / n, j = idx - i * n;
-        const float k = kernel_only(D2t[(size_t)i * N + j], h.s, h.l, kind);
+        const float u = D2t[(size_t)i * N + j];
+        const float k = kernel_only(u, h.s, h.l, kind);
         float v = pd1 * k / h.s + pd2 * cv.M2[(size_t)i * cv.ld + j];
+        if (ddot) v += kernel_parts(u, h.s, h.l, kind).Ku * Wt[(size_t)i * N + j];
         if (i == j) v += pd0;
         cv.M2[(size_t)i * cv.ld + j] = v;
     }
     __syncthreads();
+    float dsum[2] = {0.f, 0.f};
     // one warp per row i: X_i = P_i: Adot ; Pdot_i: = -X_i P ; adot_i = -X_i . alpha
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, nw = blockDim.x >> 5;
     float* adot = cv.vec + n;           // u, w, q no longer needed
@@ -951,11 +968,25 @@ __device__ void ift_correction(const Carve& cv, int n, int N, const float* __res
             pdot = -pdot;
             const float gamdot = 0.5f * (pdot - adot[i] * alpha[j] - alpha[i] * adot[j]);
             const float gam = 0.5f * (Pi[j] - alpha[i] * alpha[j]);
-            const KParts kp = kernel_parts(D2t[(size_t)i * N + j], h.s, h.l, kind);
-            const float kudot = pd1 * kp.Ku / h.s + pd2 * kp.Kul;
-            Wt[(size_t)i * N + j] += sign * (gamdot * kp.Ku + gam * kudot) / n;
+            const float u = D2t[(size_t)i * N + j];
+            const KParts kp = kernel_parts(u, h.s, h.l, kind);
+            float kudot = pd1 * kp.Ku / h.s + pd2 * kp.Kul;
+            if (ddot) {
+                const float dd = Wt[(size_t)i * N + j];
+                kudot += kernel_uu(u, h.s, h.l, kind) * dd;
+                const float kdot = pd1 * kp.K / h.s + pd2 * kp.Kl + kp.Ku * dd;
+                if (i == j) dsum[0] += gamdot;
+                dsum[1] += gamdot * kp.K + gam * kdot;
+                Wt[(size_t)i * N + j] = (gamdot * kp.Ku + gam * kudot) / n;
+            } else {
+                Wt[(size_t)i * N + j] += sign * (gamdot * kp.Ku + gam * kudot) / n;
+            }
         }
         __syncwarp();
+    }
+    if (ddot) {
+        __syncthreads();
+        block_sum_multi<2>(dsum, sh.red, sh.sums);
     }
 }
 
@@ -1056,6 +1087,35 @@ gp_ift_kernel(const int32_t* __restrict__ z_off, const int32_t* __restrict__ n_s
         }
         __syncthreads();
         ift_correction(cv, n, N, D2t, h, kind, Wt, alpha, sh, in_smem, smem_f, small_ws, 1.f);
+        return;
+    }
+    if (ignore_corr == 4) {
+        // ARD building block: directional derivative of the inner gradient along (u_noise, u_outputscale) = aux[V..V+1] AND a
+        // direction dD2 of the pair statistics (support block of Wm on entry).  Out: Wm_ss = d/deps df/dD2, aux[DF_DPHI..+1] =
+        // d/deps of the raw (noise, outputscale) gradient components.  The caller contracts Wm_ss with the per-dimension pair
+        // differences for the lengthscale components (adkf_ard_pairquad): no (d+2)^2 Hessian is ever formed.
+        if (threadIdx.x == 0) {
+            sh.pd[0] = (pb.free_mask & 1) ? h.t[0] * auxt[ADKF_AUX_V + 0] : 0.f;
+            sh.pd[1] = (pb.free_mask & 2) ? h.t[1] * auxt[ADKF_AUX_V + 1] : 0.f;
+            sh.pd[2] = 0.f;
+        }
+        __syncthreads();
+        ift_correction(cv, n, N, D2t, h, kind, Wt, alpha, sh, in_smem, smem_f, small_ws, 1.f, true);
+        if (threadIdx.x == 0) {
+            // g_raw = t o g_psi:  d g_raw = t dg_psi + c u g_psi.   n g_psi_noise = tr(Gamma) - dlogp/dsig2,
+            // n g_psi_s = sum(Gamma o K) / s
+            float lp = 0.f, d1 = 0.f, d2 = 0.f;
+            if (!isnan(pb.noise_loc)) lognormal_terms(h.sig2, pb.noise_loc, lp, d1, d2);
+            const float u0 = auxt[ADKF_AUX_V + 0], u1 = auxt[ADKF_AUX_V + 1];
+            const float gpsi0 = sh.g_psi[0], gpsi1 = sh.g_psi[1];
+            const float dg0 = ((float)sh.sums[0] - d2 * sh.pd[0]) / n;
+            const float dg1 = ((float)sh.sums[1] / h.s - (gpsi1 * n) * sh.pd[1] / h.s) / n;
+            auxt[ADKF_AUX_DF_DPHI + 0] = (pb.free_mask & 1) ? h.t[0] * dg0 + h.c[0] * u0 * gpsi0 : 0.f;
+            auxt[ADKF_AUX_DF_DPHI + 1] = (pb.free_mask & 2) ? h.t[1] * dg1 + h.c[1] * u1 * gpsi1 : 0.f;
+            auxt[ADKF_AUX_F] = sh.f;
+            for (int i = 0; i < 3; ++i) auxt[ADKF_AUX_G + i] = sh.g[i];
+            status[t] = (jit_inner > 0.f) ? ADKF_ST_JITTER : ADKF_ST_OK;
+        }
         return;
     }
 
@@ -1246,7 +1306,7 @@ extern "C" int adkf_gp_ift(int32_t T, const int32_t* z_off, const int32_t* n_sup
                            float* Wm, int32_t* status, float* ws, int64_t ws_floats, void* stream) {
     if (T <= 0) return 0;
     if (!z_off || !n_sup || !d2_off || !D2 || !y || !phi || !aux || !Wm || !status || !ws) return ADKF_ERR_BADARG;
-    if ((mode & 255) < 0 || (mode & 255) > 3) return ADKF_ERR_BADARG;   // bit 8: development probe (phase timings)
+    if ((mode & 255) < 0 || (mode & 255) > 4) return ADKF_ERR_BADARG;   // bit 8: development probe (phase timings)
     cudaStream_t s = (cudaStream_t)stream;
     int e = set_smem_attr((const void*)gp_ift_kernel);
     if (e) return e;

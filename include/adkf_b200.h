@@ -282,6 +282,19 @@ int adkf_gemm_tf32x3_masked(const float* A, int32_t transA, int64_t lda, const f
                             int64_t ldd, void* stream);
 int64_t adkf_gemm_splitk_ws_floats(int64_t M, int32_t N, int32_t K);
 
+/* ---- --use-ard: one lengthscale per feature (ExactGPLayer(..., ard_num_dims=d), fs_mol/utils/gp_utils.py:14,27,30) -------------
+ * The kernel acts on u_ab = sum_k w_k (z_ak - z_bk)^2, w_k = 1 / l_k^2; the n x n work runs in adkf_gp_fit / _predict / _ift on u
+ * with the scalar lengthscale fixed to 1.  Task layout as in the batched GP tail (z_off, n_sup, d2_off; leading dimension N_t).
+ *   adkf_ard_wsqdist : D2[t][a][b] = sum_k c[t][k] (z_ak - z_bk)^2 (c of either sign); support_only != 0: rows/cols < n_sup[t] only
+ *   adkf_ard_pairquad: q[t][k] = sum_ab G[t][a][b] (z_ak - z_bk)^2 over the same index range
+ * adkf_gp_ift mode 4 (aux[ADKF_AUX_V..+1] = direction of the raw noise / outputscale, support block of Wm = direction dD2 on
+ * entry) returns Wm_ss = d/deps df/dD2 and aux[ADKF_AUX_DF_DPHI..+1] = d/deps of the raw (noise, outputscale) gradient: with
+ * the two contractions above that is one Hessian-vector product of the (d+2)-dimensional inner problem, no Hessian formed. */
+int adkf_ard_wsqdist(const float* Z, int32_t d, int32_t T, const int32_t* z_off, const int32_t* n_sup, const int64_t* d2_off,
+                     int32_t max_n, const float* c, int32_t support_only, float* D2, void* stream);
+int adkf_ard_pairquad(const float* Z, int32_t d, int32_t T, const int32_t* z_off, const int32_t* n_sup, const int64_t* d2_off,
+                      const float* G, int32_t support_only, float* q, void* stream);
+
 /* Process-wide GEMM variant (development / A-B measurements; initialised from ADKF_GEMM_IMPL / ADKF_GEMM_CORR):
  *   impl   1 = one CTA per 128 x 128 tile (gemm_tf32x3.cu), 2 = CTA pairs on 256 x 128 tiles (gemm_pair.cu, default); other: keep
  *   corr16 0 = correction products in tf32, 1 = in bf16, 2 = bf16 for the backward operand forms (K,T) / (T,T) only (default;

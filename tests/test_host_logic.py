@@ -101,8 +101,12 @@ def test_unsupported_configurations_fail_loudly():
             ADKTModelTrainer(ADKTModelTrainerConfig(gp_kernel=bad))
     assert ADKTModelTrainer(ADKTModelTrainerConfig(gp_kernel="cossim", graph_feature_extractor_config=cli_default_config(1))
                             ).normalizing_features
-    with pytest.raises(NotImplementedError):
-        ADKTModelTrainer(ADKTModelTrainerConfig(use_ard=True))
+    # --use-ard: one raw lengthscale per GP input dimension (adaptive_dkt.py:107-110, gp_utils.py:27,30)
+    ard = ADKTModelTrainer(ADKTModelTrainerConfig(use_ard=True, graph_feature_extractor_config=cli_default_config(1)))
+    assert [tuple(p.shape) for p in ard.gp_params()] == [(1,), (), (1, 2048)] and ard.use_ard
+    with pytest.raises(AttributeError):               # like the reference: fc_out_dim only exists with '+fc'
+        ADKTModelTrainer(ADKTModelTrainerConfig(use_ard=True, used_features="gnn+ecfp",
+                                                graph_feature_extractor_config=cli_default_config(1)))
     # every GNN type of the reference is built (MultiHeadAttention included); unknown names raise like gnn.py:447
     ADKTModelTrainer(ADKTModelTrainerConfig(graph_feature_extractor_config=GraphFeatureExtractorConfig(
         gnn_config=GNNConfig(type="MultiHeadAttention", per_head_dim=64, intermediate_dim=1024, num_layers=2))))
