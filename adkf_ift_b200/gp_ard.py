@@ -174,11 +174,13 @@ class BatchedARDExactGP:
         q = self.be.pairquad(W, True)
         n = self.be.n.to(self.dtype)[:, None]
         g_ell = q * (-2.0 / ell ** 3)
-        f = f3.to(self.dtype)
+        # the objective is carried in fp64: with d = 2048 the summed lengthscale prior is ~200 of f while a line-search step
+        # changes f by ~1e-5 -- below fp32 resolution at that magnitude (the kernels' data term is O(1) and stays fp32)
+        f = f3.double()
         if self.use_ls_prior:
-            lp, d1, _ = _lognormal(ell, ls_loc[:, None])
-            f = f - lp.sum(1) / n[:, 0]
-            g_ell = g_ell - d1 / n
+            lp, d1, _ = _lognormal(ell.double(), ls_loc.double()[:, None])
+            f = f - lp.sum(1) / n[:, 0].double()
+            g_ell = g_ell - d1.to(self.dtype) / n
         t = torch.sigmoid(phi[:, 2:])
         grad = torch.cat([g2.to(self.dtype), t * g_ell], 1)
         if keep:
@@ -233,6 +235,7 @@ class BatchedARDExactGP:
             p = torch.where(bad[:, None], -g, p)
             gp_ = torch.where(bad, -(g * g).sum(1), gp_)
             step = torch.ones(self.T, dtype=self.dtype, device=phi.device)
+            gp_ = gp_.double()
             if not S:
                 step = step / g.abs().sum(1).clamp_min(1.0)
             accepted = done.clone()
@@ -240,7 +243,7 @@ class BatchedARDExactGP:
             for _ in range(20):                                                # Armijo backtracking, per task
                 trial = phi + step[:, None] * p
                 ft, gt, _ = self.value_and_grad(trial, ls_loc)
-                ok = (~accepted) & torch.isfinite(ft) & (ft <= f + 1e-4 * step * gp_)
+                ok = (~accepted) & torch.isfinite(ft) & (ft <= f + 1e-4 * step.double() * gp_)
                 f_new = torch.where(ok, ft, f_new)
                 g_new = torch.where(ok[:, None], gt, g_new)
                 phi_new = torch.where(ok[:, None], trial, phi_new)
@@ -257,7 +260,7 @@ class BatchedARDExactGP:
                 RHO.append(torch.where(good, 1.0 / sy.clamp_min(1e-30), torch.zeros_like(sy)))
                 if len(S) > history:
                     S.pop(0); Y.pop(0); RHO.pop(0)
-            stalled = ~accepted | ((f - f_new).abs() <= 1e-9 * f.abs().clamp_min(1.0))
+            stalled = ~accepted | ((f - f_new).abs() <= 1e-12 * f.abs().clamp_min(1.0))
             phi, f, g = phi_new, f_new, g_new
             done = done | (g.abs().max(1).values <= gtol) | stalled
             if bool(done.all()):

@@ -154,18 +154,20 @@ def test_failed_task_is_dropped_and_mean_renormalised(cuda_device, monkeypatch):
         tb = task_batch.to_device(task_batch.collate_tasks(use, False), cuda_device)
         res = model.train_step(tb, global_num_tasks=len(use))
         torch.cuda.synchronize()
-        results.append((res, torch.cat([p.detach().reshape(-1).clone() for p in model.feature_extractor_params()])))
+        # the (renormalised, clipped) meta-gradient the optimiser saw -- parameters after ONE Adam step are lr * sign-like and
+        # would amplify rounding differences of near-zero gradient elements
+        results.append((res, model._flat.grad.detach().clone()))
     res_ok, p_ok = results[0]
     res_drop, p_drop = results[1]
     st = res_drop.status.cpu().numpy()
     print("status of the three tasks", st)
     assert st[2] & (ops.ST_NOT_PD | ops.ST_HESS_DAMPED) and not (st[:2] & (ops.ST_NOT_PD | ops.ST_HESS_DAMPED)).any()
     assert torch.isnan(res_drop.outer_loss[2]) and torch.isfinite(res_drop.outer_loss[:2]).all()
-    # same parameters after the step as the 2-task batch (the extractor forward of the extra graphs does not touch the others)
+    # same meta-gradient as the 2-task batch (the extractor forward of the extra graphs does not touch the others)
     assert torch.isfinite(p_drop).all()
-    rel = float((p_drop - p_ok).abs().max() / p_ok.abs().max())
-    print("dropped-task step vs 2-task step: max parameter difference", rel)
-    assert rel < 1e-6
+    rel = float((p_drop - p_ok).norm() / p_ok.norm())
+    print("dropped-task step vs 2-task step: relative l2 difference of the meta-gradient", rel)
+    assert rel < 1e-5
 
 
 def test_optimizer_state_round_trip(cuda_device, tmp_path):
