@@ -75,6 +75,7 @@ SIGNATURES = {
                      _P], ctypes.c_int),
     "adkf_chol_blocked_ws_floats": ([c_int32], c_int64),
     "adkf_gp_joint_nll_blocked": ([_P, c_int32, c_int32, _P, c_int32, _P, c_float, _P, c_int64, _P, _P, _P], ctypes.c_int),
+    "adkf_gp_joint_nll_blocked_ladder": ([_P, c_int32, c_int32, _P, c_int32, _P, _P, c_int64, _P, _P, _P], ctypes.c_int),
     "adkf_ei_pool": ([_P, _P, c_int32, c_float, c_float, _P, _P, _P], ctypes.c_int),
     "adkf_csr_from_edge_index": ([_P, c_int64, c_int32, c_int32, _P, _P, _P, _P, _P], ctypes.c_int),
     "adkf_embed_sum2": ([_P, c_int64, c_int32, _P, _P, _P, _P], ctypes.c_int),

@@ -37,7 +37,8 @@ __device__ __forceinline__ float kernel_value(float u, float s, float l, int kin
 
 // J[i][j] = K(u_ij) + (i == j)(sig2 + jitter); identity on the padding
 __global__ void build_cov_kernel(const float* __restrict__ U, int N, int Np, int kind, const float* __restrict__ phi,
-                                 float jitter, float* __restrict__ J) {
+                                 float jitter, float* __restrict__ J, const int32_t* __restrict__ gate) {
+    if (gate != nullptr && *gate == 0) return;
     const float sig2 = softplusf(phi[0]) + 1e-4f, s = softplusf(phi[1]), l = softplusf(phi[2]);
     const size_t total = (size_t)Np * Np;
     for (size_t idx = blockIdx.x * (size_t)blockDim.x + threadIdx.x; idx < total; idx += (size_t)gridDim.x * blockDim.x) {
@@ -55,7 +56,9 @@ __global__ void build_cov_kernel(const float* __restrict__ U, int N, int Np, int
 
 // diagonal block: Cholesky in shared memory, L11 written back (upper triangle zeroed), X = L11^-1 to Xout [128,128]
 __global__ void __launch_bounds__(512, 1)
-potrf128_kernel(float* __restrict__ A, int ld, float* __restrict__ Xout, int32_t* __restrict__ status) {
+potrf128_kernel(float* __restrict__ A, int ld, float* __restrict__ Xout, int32_t* __restrict__ status,
+                const int32_t* __restrict__ gate) {
+    if (gate != nullptr && *gate == 0) return;
     extern __shared__ float sm[];
     float* L = sm;                    // [128][129]
     float* X = sm + kNB * kNBld;      // [128][129]
@@ -111,7 +114,8 @@ potrf128_kernel(float* __restrict__ A, int ld, float* __restrict__ Xout, int32_t
 //   out[0] = NLL of all N rows, out[1] = NLL of the first n_sup rows, out[2] = out[0] - out[1], out[3] = log det J.
 __global__ void __launch_bounds__(512, 1)
 blocked_solve_nll_kernel(const float* __restrict__ Lm, int ld, const float* __restrict__ Xblk, const float* __restrict__ y,
-                         int N, int Np, int n_sup, float* __restrict__ w, float* __restrict__ out) {
+                         int N, int Np, int n_sup, float* __restrict__ w, float* __restrict__ out, const int32_t* __restrict__ gate) {
+    if (gate != nullptr && *gate == 0) return;
     __shared__ float r[kNB];
     __shared__ double red[4][16];
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
@@ -185,14 +189,22 @@ extern "C" int64_t adkf_chol_blocked_ws_floats(int32_t N) {
     return Np * Np + (Np / kNB) * kNB * kNB + Np + 8;     // J | X blocks | w | out
 }
 
-extern "C" int adkf_gp_joint_nll_blocked(const float* U, int32_t N, int32_t n_sup, const float* y, int32_t kernel,
-                                         const float* phi, float jitter, float* ws, int64_t ws_floats, float* out4,
-                                         int32_t* status, void* stream) {
-    if (N <= 0) return 0;
-    if (!U || !y || !phi || !ws || !out4 || !status || n_sup < 0 || n_sup > N) return ADKF_ERR_BADARG;
-    if ((kernel & 0xff) < 0 || (kernel & 0xff) > ADKF_KERNEL_TANIMOTO) return ADKF_ERR_BADARG;
-    if (ws_floats < adkf_chol_blocked_ws_floats(N)) return ADKF_ERR_BADARG;
-    cudaStream_t s = (cudaStream_t)stream;
+namespace adkf {
+int gemm_tf32x3_gated(const float* A, int32_t transA, int64_t lda, const float* B, int32_t transB, int64_t ldb, int64_t M, int32_t N,
+                      int32_t K, int32_t act, float* D, int64_t ldd, const int32_t* gate, cudaStream_t stream);
+
+// Between two attempts of the jitter ladder: the next attempt runs (gate = 1) only if the previous one flagged NOT_PD, and
+// then the flag is replaced by ADKF_ST_JITTER (psd_safe_cholesky: success with jitter is a warning, not an error).
+__global__ void ladder_gate_kernel(int32_t* __restrict__ status, int32_t* __restrict__ gate) {
+    const bool failed = (*status & ADKF_ST_NOT_PD) != 0;
+    *gate = failed ? 1 : 0;
+    if (failed) *status = ADKF_ST_JITTER;
+}
+}  // namespace adkf
+
+// one attempt; gate == nullptr: unconditional
+static int joint_nll_attempt(const float* U, int32_t N, int32_t n_sup, const float* y, int32_t kernel, const float* phi, float jitter,
+                             float* ws, float* out4, int32_t* status, const int32_t* gate, cudaStream_t s) {
     const int Np = (N + kNB - 1) / kNB * kNB, nblk = Np / kNB;
     float* J = ws;
     float* X = J + (size_t)Np * Np;
@@ -204,29 +216,64 @@ extern "C" int adkf_gp_joint_nll_blocked(const float* U, int32_t N, int32_t n_su
         if (e != cudaSuccess) return (int)e;
         attr_done = true;
     }
-    cudaMemsetAsync(status, 0, sizeof(int32_t), s);
-    build_cov_kernel<<<148 * 8, 256, 0, s>>>(U, N, Np, kernel & 0xff, phi, jitter, J);
+    build_cov_kernel<<<148 * 8, 256, 0, s>>>(U, N, Np, kernel & 0xff, phi, jitter, J, gate);
     int launches = 2;
     for (int k = 0; k < nblk; ++k) {
         float* Akk = J + (size_t)k * kNB * Np + (size_t)k * kNB;
         float* Xk = X + (size_t)k * kNB * kNB;
-        potrf128_kernel<<<1, 512, smem, s>>>(Akk, Np, Xk, status);
+        potrf128_kernel<<<1, 512, smem, s>>>(Akk, Np, Xk, status, gate);
         ++launches;
         const int64_t M = (int64_t)Np - (int64_t)(k + 1) * kNB;
         if (M > 0) {
             float* A21 = Akk + (size_t)kNB * Np;
-            int rc = adkf_gemm_tf32x3(A21, 0, Np, Xk, 0, kNB, M, kNB, kNB, nullptr, 0, A21, Np, nullptr, 0, stream);
+            int rc = gemm_tf32x3_gated(A21, 0, Np, Xk, 0, kNB, M, kNB, kNB, 0, A21, Np, gate, s);
             if (rc) return rc;
             float* A22 = A21 + kNB;
-            rc = adkf_gemm_tf32x3(A21, 0, Np, A21, 0, Np, M, (int32_t)M, kNB, nullptr, ADKF_EPI_SUB_FROM_D, A22, Np, nullptr, 0,
-                                  stream);
+            rc = gemm_tf32x3_gated(A21, 0, Np, A21, 0, Np, M, (int32_t)M, kNB, ADKF_EPI_SUB_FROM_D, A22, Np, gate, s);
             if (rc) return rc;
         }
     }
-    blocked_solve_nll_kernel<<<1, 512, 0, s>>>(J, Np, X, y, N, Np, n_sup, w, out4);
+    blocked_solve_nll_kernel<<<1, 512, 0, s>>>(J, Np, X, y, N, Np, n_sup, w, out4, gate);
     adkf_count_launches(launches);
     ADKF_LAUNCH_CHECK();
     return 0;
+}
+
+extern "C" int adkf_gp_joint_nll_blocked(const float* U, int32_t N, int32_t n_sup, const float* y, int32_t kernel,
+                                         const float* phi, float jitter, float* ws, int64_t ws_floats, float* out4,
+                                         int32_t* status, void* stream) {
+    if (N <= 0) return 0;
+    if (!U || !y || !phi || !ws || !out4 || !status || n_sup < 0 || n_sup > N) return ADKF_ERR_BADARG;
+    if ((kernel & 0xff) < 0 || (kernel & 0xff) > ADKF_KERNEL_TANIMOTO) return ADKF_ERR_BADARG;
+    if (ws_floats < adkf_chol_blocked_ws_floats(N)) return ADKF_ERR_BADARG;
+    cudaStream_t s = (cudaStream_t)stream;
+    cudaMemsetAsync(status, 0, sizeof(int32_t), s);
+    return joint_nll_attempt(U, N, n_sup, y, kernel, phi, jitter, ws, out4, status, nullptr, s);
+}
+
+// gpytorch's psd_safe_cholesky ladder (plain attempt, then diagonal jitter 1e-6, 1e-5, 1e-4) entirely on the device: the three
+// jittered attempts are enqueued behind the first one and every kernel of an attempt returns at once unless the attempt before
+// it flagged ADKF_ST_NOT_PD -- no host synchronisation inside the op.  status: 0, ADKF_ST_JITTER, or
+// ADKF_ST_NOT_PD if even 1e-4 did not help.
+extern "C" int adkf_gp_joint_nll_blocked_ladder(const float* U, int32_t N, int32_t n_sup, const float* y, int32_t kernel,
+                                                const float* phi, float* ws, int64_t ws_floats, float* out4, int32_t* status,
+                                                void* stream) {
+    if (N <= 0) return 0;
+    if (!U || !y || !phi || !ws || !out4 || !status || n_sup < 0 || n_sup > N) return ADKF_ERR_BADARG;
+    if ((kernel & 0xff) < 0 || (kernel & 0xff) > ADKF_KERNEL_TANIMOTO) return ADKF_ERR_BADARG;
+    if (ws_floats < adkf_chol_blocked_ws_floats(N)) return ADKF_ERR_BADARG;
+    cudaStream_t s = (cudaStream_t)stream;
+    const int64_t Np = ((int64_t)N + kNB - 1) / kNB * kNB;
+    int32_t* gates = reinterpret_cast<int32_t*>(ws + Np * Np + (Np / kNB) * kNB * kNB + Np);      // the 8 spare words of the workspace
+    cudaMemsetAsync(status, 0, sizeof(int32_t), s);
+    int rc = joint_nll_attempt(U, N, n_sup, y, kernel, phi, 0.f, ws, out4, status, nullptr, s);
+    const float jit[3] = {1e-6f, 1e-5f, 1e-4f};
+    for (int a = 0; a < 3 && rc == 0; ++a) {
+        ladder_gate_kernel<<<1, 1, 0, s>>>(status, gates + a);
+        adkf_count_launches(1);
+        rc = joint_nll_attempt(U, N, n_sup, y, kernel, phi, jit[a], ws, out4, status, gates + a, s);
+    }
+    return rc;
 }
 
 extern "C" int adkf_ei_pool(const float* mean, const float* var, int32_t m, float noise, float best_f,

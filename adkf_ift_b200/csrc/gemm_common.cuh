@@ -130,6 +130,8 @@ struct GemmEpilogue {
     // writes D + b*d_off (+ bias + b*bias_off): column blocks / row blocks of the SAME 2-D arrays, one tensor map each.
     int splits;
     int gx, gy, ntiles;   // persistent tile walk: tile -> (bx = tile % gx, by = (tile / gx) % gy, bz = tile / (gx gy))
+    const int32_t* gate;  // optional device word: the launch is a no-op when *gate == 0 (device-side jitter ladder of the blocked
+                          // Cholesky: later attempts run only if the previous one failed, without a host round trip)
     int debug;            // development probe (ADKF_GEMM_DEBUG): 1 = splitter skips the split (128 only A, 256 only B), 2 = no MMAs
     int a_mn, a_k, b_mn, b_k;
     int64_t d_off, bias_off;

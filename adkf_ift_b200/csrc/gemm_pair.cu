@@ -252,6 +252,7 @@ __device__ __forceinline__ PairTile pair_tile(const GemmEpilogue& ep, int tile, 
 template <bool TA, bool TB, bool CORR16>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
 gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, GemmEpilogue ep) {
+    if (ep.gate != nullptr && *ep.gate == 0) return;     // gated launch (uniform over the grid: nothing has been set up yet)
     extern __shared__ unsigned char smem_raw[];
     const uint32_t raw = smem_u32(smem_raw);
     const uint32_t base = (raw + 1023u) & ~1023u;

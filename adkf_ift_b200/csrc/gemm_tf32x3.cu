@@ -207,6 +207,7 @@ __device__ __forceinline__ TileCoord tile_coord(const GemmEpilogue& ep, int tile
 template <bool TA, bool TB>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, GemmEpilogue ep) {
+    if (ep.gate != nullptr && *ep.gate == 0) return;     // gated launch (uniform over the grid: nothing has been set up yet)
     extern __shared__ unsigned char smem_raw[];
     const uint32_t raw = smem_u32(smem_raw);
     const uint32_t base = (raw + 1023u) & ~1023u;                  // SWIZZLE_128B tiles need 1024 B alignment
@@ -548,7 +549,7 @@ static int gemm_launch(const float* A, int transA, int64_t lda, int64_t a_slow, 
                        int64_t ldb, int64_t b_slow, int64_t b_fast, int64_t M, int32_t N, int32_t K, const float* bias,
                        int32_t act, float* D, int64_t ldd, float* splitk_ws, int64_t splitk_ws_floats, int batch, int a_mn,
                        int a_k, int b_mn, int b_k, int64_t d_off, int64_t bias_off, cudaStream_t s, const float* mask = nullptr,
-                       int64_t ldm = 0) {
+                       int64_t ldm = 0, const int32_t* gate = nullptr) {
     (void)cudaGetLastError();   // a stale error left in this host thread by someone else is not this launch's failure
     CUtensorMap ma, mb;
     // make_map_2d(ptr, rows (mn extent), kdim (k extent), ld, transposed): extents of the WHOLE array
@@ -565,7 +566,7 @@ static int gemm_launch(const float* A, int transA, int64_t lda, int64_t a_slow, 
         splits = 1;                                                  // no workspace (or fused epilogue): single pass
     const int nk = (K + kBK - 1) / kBK;
     GemmEpilogue ep = {};
-    ep.mode = 0; ep.M = M; ep.N = N; ep.K = K; ep.bias = bias; ep.act = act; ep.mask = mask; ep.ldm = ldm;
+    ep.mode = 0; ep.M = M; ep.N = N; ep.K = K; ep.bias = bias; ep.act = act; ep.mask = mask; ep.ldm = ldm; ep.gate = gate;
     ep.kb_per_split = (nk + splits - 1) / splits;
     static const int dbg = getenv("ADKF_GEMM_DEBUG") ? atoi(getenv("ADKF_GEMM_DEBUG")) : 0;
     ep.debug = dbg;
@@ -613,6 +614,16 @@ extern "C" int adkf_gemm_tf32x3(const float* A, int32_t transA, int64_t lda, con
     return gemm_launch(A, transA, lda, transA ? K : M, transA ? M : K, B, transB, ldb, transB ? K : N, transB ? N : K, M, N, K,
                        bias, act, D, ldd, splitk_ws, splitk_ws_floats, 1, 0, 0, 0, 0, 0, 0, (cudaStream_t)stream);
 }
+
+// adkf_gemm_tf32x3 without split-K whose launch is skipped on the device when *gate == 0 (chol_blocked.cu)
+namespace adkf {
+int gemm_tf32x3_gated(const float* A, int32_t transA, int64_t lda, const float* B, int32_t transB, int64_t ldb, int64_t M, int32_t N,
+                      int32_t K, int32_t act, float* D, int64_t ldd, const int32_t* gate, cudaStream_t stream) {
+    if (M <= 0 || N <= 0) return 0;
+    return gemm_launch(A, transA, lda, transA ? K : M, transA ? M : K, B, transB, ldb, transB ? K : N, transB ? N : K, M, N, K,
+                       nullptr, act, D, ldd, nullptr, 0, 1, 0, 0, 0, 0, 0, 0, stream, nullptr, 0, gate);
+}
+}  // namespace adkf
 
 // D = (A.B^T) * act'(mask): the input-gradient GEMM of a layer fused with the activation derivative of the layer below
 // (mask = that layer's saved activation OUTPUT [M,N], mask_act 1 relu / 2 leaky_relu(0.01)).  No split-K, no bias.

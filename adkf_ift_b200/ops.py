@@ -879,7 +879,8 @@ def linear_tc(x: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.Tensor
 def gp_joint_nll_blocked(U: torch.Tensor, N: int, n_sup: int, y: torch.Tensor, kernel, phi: torch.Tensor):
     """(out4, status): out4 = [NLL(all N rows), NLL(support rows), F = -log p(y_q | y_s), log det J] for ONE task whose
     pair statistics U [N*N] came from gp_sqdist(..., qq_block=True).  Follows psd_safe_cholesky's jitter ladder
-    (0, 1e-6, 1e-5, 1e-4): the status word is read back between attempts (evaluation path, not the training loop)."""
+    (0, 1e-6, 1e-5, 1e-4) ON THE DEVICE (adkf_gp_joint_nll_blocked_ladder): no host synchronisation inside the op; status is
+    0, ST_JITTER or ST_NOT_PD."""
     lib = _cabi.load()
     dev = U.device
     nws = int(lib.adkf_chol_blocked_ws_floats(N))
@@ -887,15 +888,10 @@ def gp_joint_nll_blocked(U: torch.Tensor, N: int, n_sup: int, y: torch.Tensor, k
     out = torch.zeros(4, dtype=torch.float32, device=dev)
     status = torch.zeros(1, dtype=torch.int32, device=dev)
     phi = phi.contiguous().view(-1)[:3]
-    for jitter in (0.0, 1e-6, 1e-5, 1e-4):
-        rc = lib.adkf_gp_joint_nll_blocked(dptr(U, torch.float32), int(N), int(n_sup), dptr(y.contiguous(), torch.float32),
-                                           kernel_arg(kernel) & 0xff, dptr(phi, torch.float32), float(jitter), dptr(ws), nws,
-                                           dptr(out), dptr(status), stream_ptr())
-        check(rc, "adkf_gp_joint_nll_blocked")
-        if int(status.item()) & ST_NOT_PD == 0:
-            if jitter > 0.0:
-                status |= ST_JITTER
-            break
+    rc = lib.adkf_gp_joint_nll_blocked_ladder(dptr(U, torch.float32), int(N), int(n_sup), dptr(y.contiguous(), torch.float32),
+                                              kernel_arg(kernel) & 0xff, dptr(phi, torch.float32), dptr(ws), nws, dptr(out),
+                                              dptr(status), stream_ptr())
+    check(rc, "adkf_gp_joint_nll_blocked_ladder")
     return out, status
 
 

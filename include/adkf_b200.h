@@ -365,6 +365,11 @@ int adkf_gp_ift(int32_t T, const int32_t* z_off, const int32_t* n_sup, const int
 int64_t adkf_chol_blocked_ws_floats(int32_t N);
 int adkf_gp_joint_nll_blocked(const float* U, int32_t N, int32_t n_sup, const float* y, int32_t kernel, const float* phi,
                               float jitter, float* ws, int64_t ws_floats, float* out4, int32_t* status, void* stream);
+/* The same with gpytorch's psd_safe_cholesky jitter ladder (0, 1e-6, 1e-5, 1e-4) run ON THE DEVICE: the jittered attempts are
+ * enqueued behind the first and skip themselves unless the previous attempt flagged ADKF_ST_NOT_PD; no host synchronisation.
+ * status[0]: 0, ADKF_ST_JITTER (a jittered attempt succeeded) or ADKF_ST_NOT_PD. */
+int adkf_gp_joint_nll_blocked_ladder(const float* U, int32_t N, int32_t n_sup, const float* y, int32_t kernel, const float* phi,
+                                     float* ws, int64_t ws_floats, float* out4, int32_t* status, void* stream);
 
 /* Analytic expected improvement for MINIMISATION over a candidate pool, on the latent posterior (variance minus noise):
  * botorch ExpectedImprovement(model, best_f, maximize=False) evaluated per molecule in bayes_opt/bo_utils.py:368-378.

@@ -132,3 +132,42 @@ def test_run_gp_ei_bo_loop_improves(cuda_device):
     best = bo_utils.min_so_far(rec)
     print("BO record", rec, "best-so-far", best[-1])
     assert best[-1] < rec[0] and best[-1] < 300
+
+
+@pytest.mark.parametrize("outputscale_raw,duplicates", [(0.4, False), (30.0, True), (3000.0, True)])
+def test_joint_nll_device_jitter_ladder_equals_host_ladder(cuda_device, outputscale_raw, duplicates):
+    """adkf_gp_joint_nll_blocked_ladder (psd_safe_cholesky's 0 / 1e-6 / 1e-5 / 1e-4 ladder run on the device through gated
+    launches, no host synchronisation) == the same ladder driven from the host with the single-attempt entry point: same
+    status word, bit-identical outputs -- for a well-conditioned covariance, one that needs jitter and one that stays non-PD."""
+    import ctypes
+    from adkf_ift_b200 import _cabi, ops
+    lib = _cabi.load()
+    rng = np.random.default_rng(3)
+    N, n, d = 600, 48, 24
+    Z = rng.normal(size=(N, d)).astype(np.float32)
+    if duplicates:
+        Z[200:400] = Z[:200]                                  # exact duplicates: K is singular up to the noise
+    y = rng.normal(size=N).astype(np.float32)
+    phi = np.array([-30.0, outputscale_raw, 1.5], np.float32)   # noise at its 1e-4 floor
+    layout = ops.TaskLayout.build([n], [N - n], cuda_device)
+    Zd, yd = torch.from_numpy(Z).to(cuda_device), torch.from_numpy(y).to(cuda_device)
+    sq = ops.gp_sqdist(Zd, layout, qq_block=True)
+    phid = torch.from_numpy(phi).to(cuda_device)
+    out, status = ops.gp_joint_nll_blocked(sq.D2, N, n, yd, "matern", phid)
+    # host-driven reference ladder
+    nws = int(lib.adkf_chol_blocked_ws_floats(N))
+    ws = torch.empty(nws, dtype=torch.float32, device=cuda_device)
+    want = torch.zeros(4, dtype=torch.float32, device=cuda_device)
+    st = torch.zeros(1, dtype=torch.int32, device=cuda_device)
+    want_status = ops.ST_NOT_PD
+    for jitter in (0.0, 1e-6, 1e-5, 1e-4):
+        rc = lib.adkf_gp_joint_nll_blocked(ops.dptr(sq.D2), N, n, ops.dptr(yd), ops.kernel_arg("matern") & 0xff, ops.dptr(phid),
+                                           ctypes.c_float(jitter), ops.dptr(ws), nws, ops.dptr(want), ops.dptr(st), ops.stream_ptr())
+        assert rc == 0
+        if int(st.item()) & ops.ST_NOT_PD == 0:
+            want_status = ops.ST_JITTER if jitter > 0 else 0
+            break
+    print(f"outputscale raw {outputscale_raw}, duplicates {duplicates}: ladder status {int(status.item())}, host ladder {want_status}")
+    assert int(status.item()) == want_status
+    if want_status != ops.ST_NOT_PD:
+        assert torch.equal(out, want)
