@@ -78,13 +78,18 @@ def run_on_task_batch(model: ADKTModel, tb: DeviceTaskBatch, train: bool = False
         return _run_on_task_batch_ard(model, tb, train, grad_scale, phi)
     if train:
         model.train()
-        Z = model.embed(tb)
-        g = gpk.BatchedExactGP(Z, tb.labels, tb.layout, cfg.gp_kernel, cfg.use_numeric_labels,
-                               cfg.use_lengthscale_prior, qq_block=True)
-        fit = _fit_or_fixed(g, phi, fit_max_iter, fit_gtol)
-        dZ, aux, status = g.hypergradient(fit, mode=1 if cfg.ignore_grad_correction else 0)
+        with ops.nvtx_range("adkf/embed"):
+            Z = model.embed(tb)
+        with ops.nvtx_range("adkf/gram"):
+            g = gpk.BatchedExactGP(Z, tb.labels, tb.layout, cfg.gp_kernel, cfg.use_numeric_labels,
+                                   cfg.use_lengthscale_prior, qq_block=True)
+        with ops.nvtx_range("adkf/fit"):
+            fit = _fit_or_fixed(g, phi, fit_max_iter, fit_gtol)
+        with ops.nvtx_range("adkf/ift"):
+            dZ, aux, status = g.hypergradient(fit, mode=1 if cfg.ignore_grad_correction else 0)
         scale = (1.0 / tb.num_tasks) if grad_scale is None else grad_scale
-        Z.backward(dZ * scale)
+        with ops.nvtx_range("adkf/backward"):
+            Z.backward(dZ * scale)
         F_t = aux[:, ops.AUX_FOUTER]
         n_q = ops.host_to_device([float(r - s) for r, s in zip(tb.layout.n_rows_host, tb.layout.n_sup_host)], torch.float32, Z.device)
         return TaskBatchResult(phi=fit.phi, status=status | fit.status, aux=aux, outer_loss=F_t,
@@ -489,13 +494,15 @@ class ADKTModelTrainer(ADKTModel):
         the replicas stay bit-identical (adaptive_dkt_utils.py:406-413).  The tail slot of the gradient buffer carries the
         number of VALID tasks through the same all-reduce; when tasks were dropped the mean is renormalised over the rest."""
         flat = self._ensure_flat()
-        distributed.allreduce_sum_(flat.gbuf)
+        with ops.nvtx_range("adkf/all-reduce"):
+            distributed.allreduce_sum_(flat.gbuf)
         pre_scale = None
         if global_num_tasks is not None:
             pre_scale = float(global_num_tasks) / torch.clamp(flat.tail[0], min=1.0)     # == 1.0 exactly when nothing was dropped
-        if self.config.clip_value is not None or pre_scale is not None:
-            flat.clip_(self.config.clip_value, pre_scale)
-        self.optimizer.step()
+        with ops.nvtx_range("adkf/clip+adam"):
+            if self.config.clip_value is not None or pre_scale is not None:
+                flat.clip_(self.config.clip_value, pre_scale)
+            self.optimizer.step()
         if self.lr_scheduler is not None:
             self.lr_scheduler.step()
         self._step += 1

@@ -17,6 +17,25 @@ KERNEL_STATS = {"matern": 0, "rbf": 0, "RBF": 0, "linear": 1, "poli1": 1, "poli2
 FREEZE_NOISE, FREEZE_OUTPUTSCALE, FREEZE_THIRD = 0x100, 0x200, 0x400
 
 
+class nvtx_range:
+    """NVTX range around one phase of the step (embed / gram / fit / ift / backward / all-reduce / clip+adam), so that an
+    nsys / ncu timeline reads like the call stack of SURVEY section 3; ADKF_NVTX=0 turns the markers off."""
+    enabled = os.environ.get("ADKF_NVTX", "1") != "0"
+
+    def __init__(self, name: str):
+        self.name = name
+
+    def __enter__(self):
+        if self.enabled and torch.cuda.is_available():
+            torch.cuda.nvtx.range_push(self.name)
+        return self
+
+    def __exit__(self, *exc):
+        if self.enabled and torch.cuda.is_available():
+            torch.cuda.nvtx.range_pop()
+        return False
+
+
 def kernel_arg(kernel, freeze: int = 0) -> int:
     """`kernel` argument of adkf_gp_fit / adkf_gp_ift: family id | ADKF_KERNEL_FREEZE_* bits."""
     return (KERNEL_IDS[kernel] if isinstance(kernel, str) else int(kernel)) | int(freeze)
