@@ -200,6 +200,9 @@ __global__ void ladder_gate_kernel(int32_t* __restrict__ status, int32_t* __rest
     *gate = failed ? 1 : 0;
     if (failed) *status = ADKF_ST_JITTER;
 }
+__global__ void ladder_finish_kernel(int32_t* __restrict__ status) {
+    if (*status & ADKF_ST_NOT_PD) *status = ADKF_ST_NOT_PD;        // not positive definite even with the largest jitter
+}
 }  // namespace adkf
 
 // one attempt; gate == nullptr: unconditional
@@ -273,6 +276,8 @@ extern "C" int adkf_gp_joint_nll_blocked_ladder(const float* U, int32_t N, int32
         adkf_count_launches(1);
         rc = joint_nll_attempt(U, N, n_sup, y, kernel, phi, jit[a], ws, out4, status, gates + a, s);
     }
+    ladder_finish_kernel<<<1, 1, 0, s>>>(status);
+    adkf_count_launches(1);
     return rc;
 }
 
