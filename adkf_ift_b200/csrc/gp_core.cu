@@ -555,6 +555,7 @@ gp_fit_kernel(const int32_t* __restrict__ z_off, const int32_t* __restrict__ n_s
     pb.free_mask = free_mask_of(kind);
     pb.noise_loc = noise_prior_loc;
     bool in_smem;
+    if (ws_off[gridDim.x] < 0) { if (threadIdx.x == 0) status[t] = ADKF_ST_BADWS; return; }
     Carve cv = carve_workspace(pb.n, smem_f, ws + ws_off[t], in_smem);
     float* auxt = aux + (size_t)t * ADKF_AUX;
     int st = ADKF_ST_OK;
@@ -673,6 +674,7 @@ gp_predict_kernel(const int32_t* __restrict__ z_off, const int32_t* __restrict__
     pb.free_mask = 7;
     const int n = pb.n, m = N - n;
     bool in_smem;
+    if (ws_off[gridDim.x] < 0) { if (threadIdx.x == 0) status[t] = ADKF_ST_BADWS; return; }
     Carve cv = carve_workspace(n, smem_f, ws + ws_off[t], in_smem);
     float ph[3] = {phi[t * 3], phi[t * 3 + 1], phi[t * 3 + 2]};
     const Hyper h = make_hyper(ph);
@@ -1028,6 +1030,7 @@ gp_ift_kernel(const int32_t* __restrict__ z_off, const int32_t* __restrict__ n_s
     int st = ADKF_ST_OK;
     // workspace: [J1 N x ldN][J2 N x ldN][beta N][small n-matrices if they do not fit in smem]
     const int ldN = N | 1;
+    if (ws_off[gridDim.x] < 0) { if (threadIdx.x == 0) status[t] = ADKF_ST_BADWS; return; }
     float* wst = ws + ws_off[t];
     float* J1 = wst;
     float* J2 = wst + (size_t)N * ldN;
@@ -1240,7 +1243,7 @@ extern "C" int64_t adkf_gp_ws_floats(int32_t T, const int32_t* z_off, const int3
 }
 
 // The per-task workspace offsets are computed on the device from z_off / n_sup (no host sync, no H2D).
-__global__ void gp_ws_offsets_kernel(int T, const int32_t* z_off, const int32_t* n_sup, int which, int64_t* off) {
+__global__ void gp_ws_offsets_kernel(int T, const int32_t* z_off, const int32_t* n_sup, int which, int64_t* off, int64_t ws_floats) {
     if (blockIdx.x == 0 && threadIdx.x == 0) {
         int64_t acc = 2 * (int64_t)(T + 1);
         for (int t = 0; t < T; ++t) {
@@ -1251,7 +1254,9 @@ __global__ void gp_ws_offsets_kernel(int T, const int32_t* z_off, const int32_t*
             if (which == 2) need += (int64_t)2 * N * (N | 1) + N;
             acc += (need + 3) & ~(int64_t)3;
         }
-        off[T] = acc;
+        // the caller's workspace is checked ON THE DEVICE (z_off / n_sup are device arrays): an undersized or stale buffer flags
+        // every task with ADKF_ST_BADWS instead of writing out of bounds
+        off[T] = (acc <= ws_floats) ? acc : -1;
     }
 }
 
@@ -1274,7 +1279,8 @@ extern "C" int adkf_gp_fit(int32_t T, const int32_t* z_off, const int32_t* n_sup
     int e = set_smem_attr((const void*)gp_fit_kernel);
     if (e) return e;
     int64_t* off = reinterpret_cast<int64_t*>(ws);
-    gp_ws_offsets_kernel<<<1, 1, 0, s>>>(T, z_off, n_sup, 0, off);
+    if (ws_floats < 2 * ((int64_t)T + 1)) return ADKF_ERR_BADARG;
+    gp_ws_offsets_kernel<<<1, 1, 0, s>>>(T, z_off, n_sup, 0, off, ws_floats);
     gp_fit_kernel<<<T, kGpThreads, gp_smem_bytes(), s>>>(z_off, n_sup, d2_off, D2, y, kernel, noise_init,
                                                         noise_prior_loc, ls_prior, init_mode, max_iter, gtol,
                                                         phi_io, aux, status, ws, off);
@@ -1292,7 +1298,8 @@ extern "C" int adkf_gp_predict(int32_t T, const int32_t* z_off, const int32_t* n
     int e = set_smem_attr((const void*)gp_predict_kernel);
     if (e) return e;
     int64_t* off = reinterpret_cast<int64_t*>(ws);
-    gp_ws_offsets_kernel<<<1, 1, 0, s>>>(T, z_off, n_sup, 1, off);
+    if (ws_floats < 2 * ((int64_t)T + 1)) return ADKF_ERR_BADARG;
+    gp_ws_offsets_kernel<<<1, 1, 0, s>>>(T, z_off, n_sup, 1, off, ws_floats);
     gp_predict_kernel<<<T, kGpThreads, gp_smem_bytes(), s>>>(z_off, n_sup, d2_off, D2, y, kernel, phi, mean, var,
                                                             status, ws, off);
     adkf_count_launches(2);
@@ -1311,7 +1318,8 @@ extern "C" int adkf_gp_ift(int32_t T, const int32_t* z_off, const int32_t* n_sup
     int e = set_smem_attr((const void*)gp_ift_kernel);
     if (e) return e;
     int64_t* off = reinterpret_cast<int64_t*>(ws);
-    gp_ws_offsets_kernel<<<1, 1, 0, s>>>(T, z_off, n_sup, 2, off);
+    if (ws_floats < 2 * ((int64_t)T + 1)) return ADKF_ERR_BADARG;
+    gp_ws_offsets_kernel<<<1, 1, 0, s>>>(T, z_off, n_sup, 2, off, ws_floats);
     gp_ift_kernel<<<T, kGpThreads, gp_smem_bytes(), s>>>(z_off, n_sup, d2_off, D2, y, kernel, noise_prior_loc,
                                                         ls_prior, mode, phi, aux, Wm, status,
                                                         ws, off);

@@ -42,7 +42,7 @@ def kernel_arg(kernel, freeze: int = 0) -> int:
 AUX = 32
 AUX_F, AUX_G, AUX_H, AUX_L0, AUX_LS_LOC, AUX_ITERS, AUX_FOUTER, AUX_DF_DPHI, AUX_V, AUX_JITTER, AUX_NFEV = (
     0, 1, 4, 13, 14, 15, 16, 17, 20, 23, 24)
-ST_JITTER, ST_NOT_PD, ST_NOT_CONVERGED, ST_HESS_DAMPED = 1, 2, 4, 8
+ST_JITTER, ST_NOT_PD, ST_NOT_CONVERGED, ST_HESS_DAMPED, ST_BADWS = 1, 2, 4, 8, 16
 MP_PARTIALS = 64
 
 

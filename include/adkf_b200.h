@@ -31,6 +31,7 @@ extern "C" {
 #define ADKF_ST_JITTER        1   /* Cholesky needed diagonal jitter (psd_safe_cholesky fallback) */
 #define ADKF_ST_NOT_PD        2   /* not positive definite after 3 jitter retries                 */
 #define ADKF_ST_NOT_CONVERGED 4   /* inner fit hit max_iter before |grad|_inf <= gtol             */
+#define ADKF_ST_BADWS        16   /* workspace smaller than adkf_gp_ws_floats() for this batch: nothing was computed   */
 #define ADKF_ST_HESS_DAMPED   8   /* inner Hessian singular in adkf_gp_ift: no hypergradient for the task */
 /* A task flagged NOT_PD or HESS_DAMPED by adkf_gp_ift gets Wm = 0 (zero gradient) and aux[ADKF_AUX_FOUTER] = NaN: the
  * reference raises in these cases (gpytorch NotPSDError / torch.linalg.solve); the caller drops the task from the meta-batch

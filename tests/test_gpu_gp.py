@@ -279,3 +279,36 @@ def test_dot_family_hypergradient_vs_autograd_oracle(cuda_device, kern):
     e = rel(dZ, want)
     print(kern, "dL/dZ rel err", e, "cond(H)", float(torch.linalg.cond(ref["H"])))
     assert e < tol
+
+
+def test_undersized_workspace_is_flagged_not_overrun(cuda_device):
+    """adkf_gp_fit / _predict / _ift lay out per-task workspace slices from device-side sizes; a caller-owned buffer
+    that is too small (e.g. reused after the batch grew) must be refused ON THE DEVICE: every task gets ADKF_ST_BADWS and
+    nothing is written (compute-sanitizer is not available on this pool, so the bound is checked explicitly)."""
+    from adkf_ift_b200 import _cabi, ops
+    lib = _cabi.load()
+    rng = np.random.default_rng(0)
+    n, m, d = 40, 30, 16
+    Z = torch.from_numpy(rng.normal(size=(n + m, d)).astype(np.float32)).to(cuda_device)
+    y = torch.from_numpy(rng.normal(size=n + m).astype(np.float32)).to(cuda_device)
+    layout = ops.TaskLayout.build([n], [m], cuda_device)
+    sq = ops.gp_sqdist(Z, layout, qq_block=True)
+    need = layout.ws_floats(2)
+    phi = torch.zeros(1, 3, device=cuda_device)
+    aux = torch.zeros(1, ops.AUX, device=cuda_device)
+    Wm = torch.full_like(sq.D2, 7.0)
+    status = torch.zeros(1, dtype=torch.int32, device=cuda_device)
+    small = need // 2
+    guard = torch.full((small + 4096,), -3.0, device=cuda_device)          # the tail past `small` must stay untouched
+    rc = lib.adkf_gp_ift(1, ops.dptr(layout.z_off), ops.dptr(layout.n_sup), ops.dptr(layout.d2_off), ops.dptr(sq.D2), ops.dptr(y),
+                         ops.kernel_arg("matern"), float(math.log(0.1) + 0.0625), 1, 0, ops.dptr(phi), ops.dptr(aux), ops.dptr(Wm),
+                         ops.dptr(status), ops.dptr(guard), small, ops.stream_ptr())
+    assert rc == 0
+    assert int(status.item()) == ops.ST_BADWS
+    assert bool((guard[small:] == -3.0).all()) and bool((Wm == 7.0).all())
+    # with the right size the same call succeeds
+    ws = torch.empty(need, device=cuda_device)
+    rc = lib.adkf_gp_ift(1, ops.dptr(layout.z_off), ops.dptr(layout.n_sup), ops.dptr(layout.d2_off), ops.dptr(sq.D2), ops.dptr(y),
+                         ops.kernel_arg("matern"), float(math.log(0.1) + 0.0625), 1, 0, ops.dptr(phi), ops.dptr(aux), ops.dptr(Wm),
+                         ops.dptr(status), ops.dptr(ws), need, ops.stream_ptr())
+    assert rc == 0 and int(status.item()) & ops.ST_BADWS == 0
