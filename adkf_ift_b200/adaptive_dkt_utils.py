@@ -489,13 +489,14 @@ class ADKTModelTrainer(ADKTModel):
                 self.optimizer = torch.optim.Adam([fp], self.config.learning_rate, fused=params[0].is_cuda)
         return self._flat
 
-    def reduce_and_update(self, global_num_tasks: Optional[int] = None):
+    def reduce_and_update(self, global_num_tasks: Optional[int] = None, already_reduced: bool = False):
         """All-reduce (sum) of the flat meta-gradient over the ranks, then clip + Adam -- identical on every rank, so
         the replicas stay bit-identical (adaptive_dkt_utils.py:406-413).  The tail slot of the gradient buffer carries the
         number of VALID tasks through the same all-reduce; when tasks were dropped the mean is renormalised over the rest."""
         flat = self._ensure_flat()
-        with ops.nvtx_range("adkf/all-reduce"):
-            distributed.allreduce_sum_(flat.gbuf)
+        if not already_reduced:
+            with ops.nvtx_range("adkf/all-reduce"):
+                distributed.allreduce_sum_(flat.gbuf)
         pre_scale = None
         if global_num_tasks is not None:
             pre_scale = float(global_num_tasks) / torch.clamp(flat.tail[0], min=1.0)     # == 1.0 exactly when nothing was dropped
@@ -514,10 +515,21 @@ class ADKTModelTrainer(ADKTModel):
         flat = self._ensure_flat()
         flat.release_grads()
         total = global_num_tasks if global_num_tasks is not None else tb.num_tasks * distributed.world_size()
+        overlap = distributed.world_size() > 1 and getattr(self, "overlap_allreduce", True)
+        if overlap:
+            if getattr(self, "_reducer", None) is None or self._reducer.flat is not flat:
+                self._reducer = distributed.BucketedReducer(flat)
+            self._reducer.prepare()             # buckets are all-reduced behind the backward pass, last layers first
         res = run_on_task_batch(self, tb, train=True, grad_scale=1.0 / total)
-        flat.gather_grads()
-        flat.tail[0:1].copy_(((res.status & (ops.ST_NOT_PD | ops.ST_HESS_DAMPED)) == 0).sum().to(torch.float32).reshape(1))
-        self.reduce_and_update(total)
+        valid = ((res.status & (ops.ST_NOT_PD | ops.ST_HESS_DAMPED)) == 0).sum().to(torch.float32).reshape(1)
+        if overlap:
+            flat.tail[0:1].copy_(valid)
+            with ops.nvtx_range("adkf/all-reduce (tail of the bucketed reduction)"):
+                self._reducer.finish()
+        else:
+            flat.gather_grads()
+            flat.tail[0:1].copy_(valid)
+        self.reduce_and_update(total, already_reduced=overlap)
         return res
 
 

@@ -42,19 +42,21 @@ namespace pr {
 
 constexpr int kPM = 256;                             // pair tile rows (2 x kBM)
 constexpr int kBH = 64;                              // B rows held by one CTA
-constexpr int kRaw = 6;                              // raw ring depth
-constexpr int kSplit = 2;                            // split stages (B tiles in smem, A operand in TMEM)
+// NS = number of split stages (B tiles in smem, A operand in TMEM).  NS = 2: hi.hi and the corrections in separate TMEM
+// accumulators (big[2] + small + 2 operand stages = 512 columns).  NS = 4: the corrections go to the hi.hi accumulator of their
+// drain group (big[2] + 4 operand stages): twice the pipeline depth for the cross-CTA hand-offs, one more rounding per product.
+constexpr int raw_depth(int NS) { return NS == 4 ? 5 : 6; }
 constexpr int kBHalfBytes = kBH * kBK * 4;           // 8 KB
 constexpr int kRawBytes = kTileBytes + kBHalfBytes;  // A 16 KB + B half 8 KB
 constexpr int kSplitBytes = 2 * kBHalfBytes;         // B_hi 8 KB + B_cat (or B_lo) 8 KB
-constexpr int kRingBytes = kRaw * kRawBytes + kSplit * kSplitBytes;   // 144 + 32 KB
+constexpr int ring_bytes(int NS) { return raw_depth(NS) * kRawBytes + NS * kSplitBytes; }   // 144 + 32 KB | 120 + 64 KB
 constexpr int kStageBytes = 8 * 4096;
 constexpr int kThreads = 640;
 constexpr int kTmemCols = 512;
-constexpr int kSmallCol = 2 * kBN;
-constexpr int kAopCol = 3 * kBN;                     // A operand: 2 stages x (32 tf32 columns + 32 correction columns)
+constexpr int kSmallCol = 2 * kBN;                   // NS = 2 only
+constexpr int aop_col(int NS) { return NS == 4 ? 2 * kBN : 3 * kBN; }   // A operand stages: 32 tf32 columns + 32 correction columns each
 constexpr int kGroup = 4;
-constexpr size_t kSmem = (size_t)kRingBytes + kStageBytes + 1024 + 256;
+constexpr size_t smem_bytes(int NS) { return (size_t)ring_bytes(NS) + kStageBytes + 1024 + 256; }
 
 constexpr uint32_t kIdescTf32 = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(kBN >> 3) << 17) | ((uint32_t)(kPM >> 4) << 24);
 constexpr uint32_t kIdescBf16 = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(kBN >> 3) << 17) | ((uint32_t)(kPM >> 4) << 24);
@@ -249,10 +251,12 @@ __device__ __forceinline__ PairTile pair_tile(const GemmEpilogue& ep, int tile, 
     return c;
 }
 
-template <bool TA, bool TB, bool CORR16>
+template <bool TA, bool TB, bool CORR16, int NS>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
 gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, GemmEpilogue ep) {
     if (ep.gate != nullptr && *ep.gate == 0) return;     // gated launch (uniform over the grid: nothing has been set up yet)
+    constexpr int kRaw = raw_depth(NS), kSplit = NS, kRingBytes = ring_bytes(NS), kAopCol = aop_col(NS);
+    constexpr bool kMerged = NS == 4;
     extern __shared__ unsigned char smem_raw[];
     const uint32_t raw = smem_u32(smem_raw);
     const uint32_t base = (raw + 1023u) & ~1023u;
@@ -290,7 +294,7 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             mbar_init(accfull_bar(b), 1);
             mbar_init(bars + accempty_off(b), 16);           // drain warps of both CTAs
         }
-        mbar_init(bars + tileempty_off(), 16);
+        if (!kMerged) mbar_init(bars + tileempty_off(), 16);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 2) {
@@ -335,7 +339,7 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             uint32_t it = 0, gc = 0, tl = 0;
             for (int tile = pair_id; tile < ntiles; tile += npairs) {
                 const PairTile c = pair_tile(ep, tile, 0);
-                mbar_wait_cluster(bars + tileempty_off(), (tl & 1) ^ 1);
+                if (!kMerged) mbar_wait_cluster(bars + tileempty_off(), (tl & 1) ^ 1);
                 for (int i = 0; i < c.nk; ++i, ++it) {
                     const int s = it % kSplit;
                     const uint32_t ph = (it / kSplit) & 1;
@@ -350,17 +354,18 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                         const uint32_t st = split_base + s * kSplitBytes;
                         const uint64_t b_hi = smem_desc_k128(st), b_co = smem_desc_k128(st + kBHalfBytes);
                         const uint32_t a_hi = tmem_acc + (uint32_t)(kAopCol + s * 2 * kBK), a_co = a_hi + kBK;
-                        const uint32_t acc_big = tmem_acc + (uint32_t)(b * kBN), acc_small = tmem_acc + (uint32_t)kSmallCol;
+                        const uint32_t acc_big = tmem_acc + (uint32_t)(b * kBN);
+                        const uint32_t acc_small = kMerged ? acc_big : tmem_acc + (uint32_t)kSmallCol;
 #pragma unroll
-                        for (int k = 0; k < kBK / 8; ++k) {
+                        for (int k = 0; k < ((ep.debug & 2) ? 0 : kBK / 8); ++k) {   // ADKF_GEMM_DEBUG bit 1: no MMAs (development probe)
                             const uint64_t adv = (uint64_t)(2 * k);          // 32 bytes of K per MMA (8 tf32 | 16 bf16)
                             const uint32_t ak = (uint32_t)(8 * k);           // 8 TMEM columns per MMA
                             umma2_tf32_ts(acc_big, a_hi + ak, b_hi + adv, kIdescTf32, (group_first && k == 0) ? 0u : 1u);
                             if (CORR16) {
                                 // [lo | hi] (A, bf16) x [hi | lo] (B, bf16): k-steps 0,1 = lo.hi, 2,3 = hi.lo
-                                umma2_bf16_ts(acc_small, a_co + ak, b_co + adv, kIdescBf16, (i | k) ? 1u : 0u);
+                                umma2_bf16_ts(acc_small, a_co + ak, b_co + adv, kIdescBf16, (kMerged || (i | k)) ? 1u : 0u);
                             } else {
-                                umma2_tf32_ts(acc_small, a_co + ak, b_hi + adv, kIdescTf32, (i | k) ? 1u : 0u);   // lo.hi
+                                umma2_tf32_ts(acc_small, a_co + ak, b_hi + adv, kIdescTf32, (kMerged || (i | k)) ? 1u : 0u);   // lo.hi
                                 umma2_tf32_ts(acc_small, a_hi + ak, b_co + adv, kIdescTf32, 1u);                   // hi.lo
                             }
                         }
@@ -437,7 +442,7 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                 mbar_wait_cluster(accfull_bar(b), (g >> 1) & 1);
                 tc_fence_after();
 #pragma unroll
-                for (int c0 = 0; c0 < 64; c0 += 16) {
+                for (int c0 = 0; c0 < ((ep.debug & 32) ? 0 : 64); c0 += 16) {     // bit 5: no TMEM drains
                     float v[16];
                     tmem_ld16(trow + (uint32_t)(b * kBN) + c0, v);
 #pragma unroll
@@ -447,17 +452,20 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                 __syncwarp();
                 if (lane == 0) mbar_arrive_cluster(leader_bars + accempty_off(b));
             }
+            if (!kMerged) {
 #pragma unroll
-            for (int c0 = 0; c0 < 64; c0 += 16) {
-                float v[16];
-                tmem_ld16(trow + (uint32_t)kSmallCol + c0, v);
+                for (int c0 = 0; c0 < ((ep.debug & 32) ? 0 : 64); c0 += 16) {
+                    float v[16];
+                    tmem_ld16(trow + (uint32_t)kSmallCol + c0, v);
 #pragma unroll
-                for (int j = 0; j < 16; ++j) acc[c0 + j] += v[j];
+                    for (int j = 0; j < 16; ++j) acc[c0 + j] += v[j];
+                }
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive_cluster(leader_bars + tileempty_off());
             }
-            tc_fence_before();
-            __syncwarp();
-            if (lane == 0) mbar_arrive_cluster(leader_bars + tileempty_off());
             gc += (uint32_t)ngroups;
+            if (ep.debug & 64) continue;                                       // bit 6: no epilogue
             gemm_store_tile(ep, c.rowA0, c.rowB0, c.zslab, c.batch, acc, q, lane, colbase,
                             reinterpret_cast<float4*>(stage_ptr + (size_t)(warp - 12) * 4096));
         }
@@ -472,24 +480,23 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     }
 }
 
-template <bool TA, bool TB, bool C16>
-static int pair_attr() {
+template <bool TA, bool TB, bool C16, int NS>
+static int pair_launch_t(dim3 grid, cudaStream_t s, const CUtensorMap& ma, const CUtensorMap& mb, const GemmEpilogue& ep) {
     static bool done = false;
     if (!done) {
-        cudaError_t e = cudaFuncSetAttribute((const void*)gemm_pair_kernel<TA, TB, C16>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                             (int)kSmem);
+        cudaError_t e = cudaFuncSetAttribute((const void*)gemm_pair_kernel<TA, TB, C16, NS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                             (int)smem_bytes(NS));
         if (e != cudaSuccess) return (int)e;
         done = true;
     }
+    gemm_pair_kernel<TA, TB, C16, NS><<<grid, kThreads, smem_bytes(NS), s>>>(ma, mb, ep);
     return 0;
 }
 
-template <bool TA, bool TB, bool C16>
-static int pair_launch_t(dim3 grid, cudaStream_t s, const CUtensorMap& ma, const CUtensorMap& mb, const GemmEpilogue& ep) {
-    int rc = pair_attr<TA, TB, C16>();
-    if (rc) return rc;
-    gemm_pair_kernel<TA, TB, C16><<<grid, kThreads, kSmem, s>>>(ma, mb, ep);
-    return 0;
+template <bool TA, bool TB>
+static int pair_launch_f(bool c16, bool merged, dim3 grid, cudaStream_t s, const CUtensorMap& ma, const CUtensorMap& mb, const GemmEpilogue& ep) {
+    if (merged) return c16 ? pair_launch_t<TA, TB, true, 4>(grid, s, ma, mb, ep) : pair_launch_t<TA, TB, false, 4>(grid, s, ma, mb, ep);
+    return c16 ? pair_launch_t<TA, TB, true, 2>(grid, s, ma, mb, ep) : pair_launch_t<TA, TB, false, 2>(grid, s, ma, mb, ep);
 }
 
 }  // namespace pr
@@ -504,11 +511,12 @@ int gemm_pair_launch(const CUtensorMap& ma, const CUtensorMap& mb, const GemmEpi
     // of the network moves every gradient below it by ~5e-4 (profiles/r2i_corr16_bisect.txt); the backward pass is LINEAR in
     // the upstream gradient, there the same error stays at 1e-6.
     const bool corr16 = g_gemm_corr16 == 1 || (g_gemm_corr16 == 2 && (transA || transB));
+    static const int merged = getenv("ADKF_GEMM_MERGE") ? atoi(getenv("ADKF_GEMM_MERGE")) : 0;   // development switch (A/B runs)
     const int pairs = std::max(1, num_sms() / 2);
     dim3 grid((unsigned)(2 * std::min(ep.ntiles, pairs)));
-    if (!transA && !transB) return corr16 ? pr::pair_launch_t<false, false, true>(grid, s, ma, mb, ep) : pr::pair_launch_t<false, false, false>(grid, s, ma, mb, ep);
-    if (!transA && transB)  return corr16 ? pr::pair_launch_t<false, true, true>(grid, s, ma, mb, ep) : pr::pair_launch_t<false, true, false>(grid, s, ma, mb, ep);
-    return corr16 ? pr::pair_launch_t<true, true, true>(grid, s, ma, mb, ep) : pr::pair_launch_t<true, true, false>(grid, s, ma, mb, ep);
+    if (!transA && !transB) return pr::pair_launch_f<false, false>(corr16, merged != 0, grid, s, ma, mb, ep);
+    if (!transA && transB) return pr::pair_launch_f<false, true>(corr16, merged != 0, grid, s, ma, mb, ep);
+    return pr::pair_launch_f<true, true>(corr16, merged != 0, grid, s, ma, mb, ep);
 }
 
 }  // namespace adkf

@@ -112,3 +112,84 @@ class FlatParams:
             factor = factor * torch.clamp(max_norm / (norm + 1e-6), max=1.0)
         self.grad.mul_(factor)
         return norm
+
+
+class BucketedReducer:
+    """The all-reduce of the flat meta-gradient, cut into buckets and started WHILE the backward pass is still running.
+
+    Parameters are registered bottom-up (init projection, GNN blocks 0..L-1, readout, fc) and the backward pass produces their
+    gradients top-down, so buckets are contiguous slices of the flat buffer taken from its END: as soon as every parameter of
+    a bucket has its gradient (post-accumulate-grad hooks), the gradients are copied into the bucket's slice and
+    `all_reduce(slice, async_op=True)` is issued -- NCCL runs it on its own stream behind the work queued so far, the
+    remaining backward kernels keep the compute stream busy.  `finish()` reduces whatever is left (parameters that took no
+    part never fire a hook: their slices hold zeros, cauchy_hypergradient.py:144-146) together with the tail slot, and waits.
+    Element-wise the result equals ONE all-reduce of the whole buffer: replicas stay bit-identical."""
+
+    def __init__(self, flat: FlatParams, bucket_floats: int = 6_000_000):
+        self.flat = flat
+        self.buckets = []                      # (lo, hi, [param indices]) from the end of the buffer
+        idx, hi = [], flat.total
+        for i in range(len(flat.params) - 1, -1, -1):
+            idx.append(i)
+            lo = flat.offsets[i]
+            if hi - lo >= bucket_floats or i == 0:
+                self.buckets.append((lo, hi, list(idx)))
+                idx, hi = [], lo
+        self._bucket_of = {}
+        for b, (_, _, members) in enumerate(self.buckets):
+            for i in members:
+                self._bucket_of[i] = b
+        self._pending, self._works, self._done = [], [], []
+        self._armed = False
+        self._handles = [p.register_post_accumulate_grad_hook(self._make_hook(i)) for i, p in enumerate(flat.params)]
+
+    def _make_hook(self, i):
+        def hook(param):
+            if not self._armed:
+                return
+            b = self._bucket_of[i]
+            self._pending[b] -= 1
+            if self._pending[b] == 0:
+                self._launch(b)
+        return hook
+
+    def _copy_bucket(self, b):
+        flat = self.flat
+        views, grads = [], []
+        for i in self.buckets[b][2]:
+            p, n, off = flat.params[i], flat.sizes[i], flat.offsets[i]
+            v = flat.grad[off:off + n].view_as(p.data)
+            if p.grad is not None and p.grad.data_ptr() != v.data_ptr():
+                views.append(v)
+                grads.append(p.grad)
+            p.grad = v
+        if views:
+            torch._foreach_copy_(views, grads)
+
+    def _launch(self, b):
+        self._copy_bucket(b)
+        lo, hi, _ = self.buckets[b]
+        self._works.append(dist.all_reduce(self.flat.gbuf[lo:hi], op=dist.ReduceOp.SUM, async_op=True))
+        self._done[b] = True
+
+    def prepare(self):
+        """Before the backward pass (after FlatParams.release_grads)."""
+        self._pending = [len(m) for _, _, m in self.buckets]
+        self._done = [False] * len(self.buckets)
+        self._works = []
+        self._armed = True
+
+    def finish(self):
+        """After the backward pass and after the caller wrote the tail slot: reduce the rest, wait for everything."""
+        self._armed = False
+        rest = [b for b, d in enumerate(self._done) if not d]
+        for b in rest:
+            self._copy_bucket(b)
+        flat = self.flat
+        for b in rest:                                      # the unreduced buckets need not be adjacent: one call each
+            blo, bhi, _ = self.buckets[b]
+            self._works.append(dist.all_reduce(flat.gbuf[blo:bhi], op=dist.ReduceOp.SUM, async_op=True))
+        self._works.append(dist.all_reduce(flat.tail, op=dist.ReduceOp.SUM, async_op=True))
+        for w in self._works:
+            w.wait()
+        self._works = []

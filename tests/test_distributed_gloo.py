@@ -110,3 +110,48 @@ def test_release_and_gather_grads_equal_view_accumulation():
     for p, n, off in zip(flat.params, flat.sizes, flat.offsets):
         assert p.grad.data_ptr() == flat.grad[off:off + n].data_ptr()
     assert float(params[-1].grad.abs().max()) == 0.0
+
+
+def _bucket_worker(rank, world, port, out):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+    torch.set_num_threads(2)
+    distributed.init_from_env(device="cpu")
+    model = _model()
+    flat = model._ensure_flat()
+    params = model.feature_extractor_params()
+    used = [p for i, p in enumerate(params) if i % 7 != 3]          # some parameters take no part (their hooks never fire)
+
+    def loss():
+        return sum((p * p).sum() * (i + 1 + rank) for i, p in enumerate(used)) * 1e-3
+
+    # (a) one all-reduce of the whole buffer
+    flat.release_grads()
+    loss().backward()
+    flat.gather_grads()
+    flat.tail[0] = 3.0 + rank
+    distributed.allreduce_sum_(flat.gbuf)
+    ref = flat.gbuf.clone()
+    # (b) bucketed, launched from the gradient hooks during the backward pass
+    red = distributed.BucketedReducer(flat, bucket_floats=200_000)
+    assert len(red.buckets) > 3 and red.buckets[0][1] == flat.total and red.buckets[-1][0] == 0
+    flat.release_grads()
+    red.prepare()
+    loss().backward()
+    flat.tail[0] = 3.0 + rank
+    red.finish()
+    out[rank] = (torch.equal(flat.gbuf, ref), float(flat.tail[0]), len(red.buckets),
+                 all(p.grad.data_ptr() == flat.grad[o:o + n].data_ptr() for p, n, o in zip(flat.params, flat.sizes, flat.offsets)))
+    torch.distributed.destroy_process_group()
+
+
+def test_bucketed_overlapped_allreduce_equals_single_allreduce():
+    """distributed.BucketedReducer (buckets all-reduced from the gradient hooks while the backward pass runs, last layers
+    first) gives bit-for-bit the buffer of ONE all-reduce, carries the valid-task count in the tail slot and re-attaches the
+    gradient views -- world size 2, gloo."""
+    port = _free_port()
+    mgr = mp.Manager()
+    out = mgr.dict()
+    mp.spawn(_bucket_worker, args=(2, port, out), nprocs=2, join=True)
+    for r in (0, 1):
+        same, tail, nb, views = out[r]
+        assert same and tail == 7.0 and views, (r, out[r])
