@@ -533,7 +533,9 @@ def run_b200(args):
     pool_tasks = 48                                             # 3 step-batches per pass over the pool; every pass re-draws
     ds = synthetic.SyntheticFSMolDataset(pool_tasks, 0, 0, molecules_per_task=SUPPORT + QUERY,
                                          first_task_id=20000 + 1000 * rank).materialize(DataFold.TRAIN)
-    workers = args.workers if args.workers is not None else max(2, min(4, (os.cpu_count() or 4) // max(world, 1) - 1))
+    # featurising one task costs ~8 ms of one core: 16 tasks per step need 3-4 workers to stay ahead of a ~90 ms step, 2 tasks
+    # per step (strong scaling at N = 8) need one -- more would only compete with the launch threads for the cores
+    workers = args.workers if args.workers is not None else max(1, min(4, (os.cpu_count() or 4) // max(world, 1) - 1, (per_gpu + 3) // 4))
     spec = StreamSpec(dataset=ds, data_fold=int(DataFold.TRAIN), support_size=SUPPORT, query_size=QUERY,
                       max_num_graphs=SUPPORT + QUERY, use_numeric_labels=False, tasks_per_step=per_gpu, num_shards=1, repeat=True)
     pipe = HostBatchPipeline(spec, num_workers=workers, rank=0, world=1)       # every rank owns its task pool
