@@ -283,6 +283,6 @@ class GraphFeatureExtractor(nn.Module):
         if gi is None:
             gi = ops.build_graph_index(list(batch.adjacency_lists), int(batch.node_features.shape[0]),
                                        batch.node_to_graph, int(batch.num_graphs))
-        h0 = self.init_node_proj(batch.node_features)
+        h0 = ops.linear_tc(batch.node_features, self.init_node_proj.weight, self.init_node_proj.bias)
         states = self.gnn(h0, gi)
         return self.readout(torch.cat(states, dim=-1), gi)

@@ -745,7 +745,10 @@ def linear_tf32x3_forward(x: torch.Tensor, weight: torch.Tensor, bias: Optional[
 
 def _tc_eligible(x, weight) -> bool:
     K, N = weight.shape[1], weight.shape[0]
-    return (x.is_cuda and K % 4 == 0 and N % 4 == 0 and K >= 32 and N >= 32 and x.stride(-1) == 1 and weight.stride(1) == 1
+    # every layer whose K and N are multiples of 4 (16-byte rows for the tensor maps) goes to the tensor-core GEMM, the 12-wide
+    # attention-score layer and the 32-wide input projection included: a 128-wide tile wastes MMA columns there but still beats
+    # the cuBLAS SIMT kernels they used to fall back to (3 launches, 1.5 ms per step) and keeps the path on our own kernels
+    return (x.is_cuda and K % 4 == 0 and N % 4 == 0 and K >= 4 and N >= 4 and x.stride(-1) == 1 and weight.stride(1) == 1
             and x.stride(0) % 4 == 0 and weight.stride(0) % 4 == 0 and x.data_ptr() % 16 == 0 and weight.data_ptr() % 16 == 0)
 
 
@@ -872,14 +875,14 @@ def mlp2_tc(x, w1, b1, act, w2, b2):
     """act(x W1^T + b1) W2^T + b2 with the fused backward of _MLP2TC when both layers fit the tensor-core kernel, else two
     linear_tc calls."""
     if (x.is_cuda and x.dim() == 2 and ACT_IDS[act] in (1, 2) and _tc_eligible(x, w1) and w2.shape[1] % 4 == 0 and w2.shape[0] % 4 == 0
-            and w2.shape[0] >= 32 and w2.stride(1) == 1 and w2.stride(0) % 4 == 0 and w2.data_ptr() % 16 == 0):
+            and w2.shape[0] >= 4 and w2.stride(1) == 1 and w2.stride(0) % 4 == 0 and w2.data_ptr() % 16 == 0):
         return _MLP2TC.apply(x, w1, b1, act, w2, b2)
     return linear_tc(linear_tc(x, w1, b1, act), w2, b2)
 
 
 def linear_tc(x: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.Tensor] = None, act=None) -> torch.Tensor:
     """Drop-in for F.linear(+activation) on [rows, K] inputs.  Shapes the tensor-core kernel does not take (K or N not a
-    multiple of 4, tiny layers such as the 12 attention scores or the 32-wide input projection) stay on cuBLAS."""
+    multiple of 4: only the 42 phys-chem descriptors of the non-default `pc-descs` feature set) stay on cuBLAS."""
     if not x.is_cuda:
         raise RuntimeError("adkf_ift_b200 kernels need CUDA tensors (no CPU fallback)")
     if x.dim() == 2 and _tc_eligible(x, weight):

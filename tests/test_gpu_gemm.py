@@ -112,6 +112,28 @@ def test_weight_gradient_form_tt_splitk(cuda_device, M, N, K):
     assert torch.equal(out, out2), "split-K reduction must be deterministic"
 
 
+@pytest.mark.parametrize("M,K,N", [(1187, 768, 12), (3000, 32, 128), (257, 12, 768), (100, 8, 4)])
+def test_linear_tc_tiny_layers(cuda_device, M, K, N):
+    """The 12-wide attention-score layer (graph_readout.py:224-259), the 32 -> 128 input projection
+    (graph_feature_extractor.py:76-98) and other narrow shapes on the tensor-core GEMM: forward, dX (K = N_layer), dW, db
+    against fp64 autograd -- these used to fall back to cuBLAS SIMT."""
+    from adkf_ift_b200 import ops
+    g = torch.Generator().manual_seed(M + N)
+    x, w, b, go = torch.randn(M, K, generator=g), torch.randn(N, K, generator=g) / K ** 0.5, torch.randn(N, generator=g), torch.randn(M, N, generator=g)
+    assert ops._tc_eligible(x.to(cuda_device), w.to(cuda_device))
+    outs = []
+    for dev, dt, fn in (("cpu", torch.float64, lambda a, ww, bb: torch.relu(torch.nn.functional.linear(a, ww, bb))),
+                        (cuda_device, torch.float32, lambda a, ww, bb: ops.linear_tc(a, ww, bb, "relu"))):
+        xx, ww, bb = (t.to(dev, dt).clone().requires_grad_(True) for t in (x, w, b))
+        y = fn(xx, ww, bb)
+        y.backward(go.to(dev, dt))
+        outs.append((y.detach(), xx.grad, ww.grad, bb.grad))
+    for name, a, r in zip(("y", "dx", "dw", "db"), outs[1], outs[0]):
+        e = rel(a, r)
+        print(f"tiny layer M={M} K={K} N={N} {name}: rel err {e:.3e}")
+        assert e < 5e-6, name
+
+
 @pytest.mark.parametrize("act", [None, "relu", "leaky_relu"])
 def test_linear_tc_autograd(cuda_device, act):
     """linear_tc (forward + both gradient GEMMs + bias gradient) against fp64 autograd, also on a strided weight view
