@@ -126,7 +126,7 @@ class _PinnedRing:
         self._slots[self._i] = slot
         self._i = (self._i + 1) % len(self._slots)
         return HostTaskBatch(num_tasks=hb.num_tasks, n_sup=hb.n_sup, n_query=hb.n_query, num_graphs=hb.num_graphs,
-                             num_nodes=hb.num_nodes, adjacency=adj, bool_labels=hb.bool_labels, **out)
+                             num_nodes=hb.num_nodes, adjacency=adj, bool_labels=hb.bool_labels, max_degree=hb.max_degree, **out)
 
 
 class HostBatchPipeline:

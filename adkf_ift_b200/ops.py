@@ -64,6 +64,14 @@ class GraphIndex:
     graph_ptr: Optional[torch.Tensor] = None  # [G+1] int32
     num_graphs: int = 0
     type_sorted: Optional["TypeSortedEdges"] = None
+    max_degree: Optional[int] = None          # largest in-degree (host value: from the batcher, else one device read at build time)
+    tile_node0: Optional[torch.Tensor] = None  # fused message passing: first node owned by each 112-row tile of the CSR
+
+    @property
+    def fused_ok(self) -> bool:
+        """The fused message-passing kernel needs every node's edges inside one 128-row tile: in-degree <= 16."""
+        return (self.tile_node0 is not None and self.max_degree is not None
+                and self.max_degree <= int(_cabi.load().adkf_pna_fused_max_degree()))
 
 
 def _histogram(idx: torch.Tensor, bins: int) -> torch.Tensor:
@@ -74,8 +82,10 @@ def _histogram(idx: torch.Tensor, bins: int) -> torch.Tensor:
 
 
 def build_graph_index(adjacency_lists: Sequence[torch.Tensor], num_nodes: int,
-                      node_to_graph: Optional[torch.Tensor] = None, num_graphs: int = 0) -> GraphIndex:
-    """adjacency_lists: 3 x [E_t, 2] int64 CUDA tensors exactly as the reference batcher emits them."""
+                      node_to_graph: Optional[torch.Tensor] = None, num_graphs: int = 0,
+                      max_degree: Optional[int] = None) -> GraphIndex:
+    """adjacency_lists: 3 x [E_t, 2] int64 CUDA tensors exactly as the reference batcher emits them.  max_degree: the largest
+    in-degree when the host already knows it (the collation computes it); None reads it back from the device once."""
     lib = _cabi.load()
     assert len(adjacency_lists) == 3, "FS-Mol has 3 edge types"
     dev = adjacency_lists[0].device
@@ -103,6 +113,14 @@ def build_graph_index(adjacency_lists: Sequence[torch.Tensor], num_nodes: int,
                     rev_pos[:etot], degree[:num_nodes], graph_ptr, num_graphs)
     if etot > 0:
         gi.type_sorted = _type_sorted(gi, [2 * e for e in es])
+    if num_nodes > 0:
+        # tiles of the fused message-passing kernel: tile j = CSR rows [112 j, 112 j + 128) owns the nodes whose first row is in
+        # [112 j, 112 j + 112)
+        ntiles = int(lib.adkf_pna_fused_num_tiles(etot))
+        stride = (128 - int(lib.adkf_pna_fused_max_degree()))
+        bounds = torch.arange(ntiles + 1, dtype=torch.int32, device=dev) * stride
+        gi.tile_node0 = torch.searchsorted(rowptr[:num_nodes], bounds, right=False).to(torch.int32)
+        gi.max_degree = int(max_degree) if max_degree is not None else (int(degree[:num_nodes].max().item()) if etot > 0 else 0)
     return gi
 
 
@@ -160,6 +178,7 @@ class TypeSortedEdges:
     rev: torch.Tensor        # [E] int32 sorted position of the reversed copy of edge r
     tptr: torch.Tensor       # [3V+1] int32
     type_off: List[int]      # host: first sorted position of every type (+ E at the end)
+    csr2ts: Optional[torch.Tensor] = None   # [E] int32 sorted position of CSR row p
 
 
 def _type_sorted(gi: GraphIndex, edges_per_type: Sequence[int]) -> TypeSortedEdges:
@@ -177,7 +196,8 @@ def _type_sorted(gi: GraphIndex, edges_per_type: Sequence[int]) -> TypeSortedEdg
         off.append(off[-1] + int(e))
     assert off[-1] == E
     return TypeSortedEdges(gi.col_src[perm].contiguous(), gi.col_tgt[perm].contiguous(),
-                           inv[gi.rev_pos.to(torch.int64)[perm]].to(torch.int32).contiguous(), tptr, off)
+                           inv[gi.rev_pos.to(torch.int64)[perm]].to(torch.int32).contiguous(), tptr, off,
+                           inv.to(torch.int32).contiguous())
 
 
 MP_PNA, MP_MULTIAGGR, MP_PLAIN = 0, 1, 2          # ADKF_MP_* of include/adkf_b200.h
@@ -258,10 +278,87 @@ class _PNAMessagePassingTC(torch.autograd.Function):
         return d_h, d_W, d_b, None, None
 
 
+def _fused_args(h, W, b, gi: GraphIndex):
+    return (dptr(h, torch.float32), dptr(W, torch.float32), dptr(b, torch.float32), dptr(gi.rowptr), dptr(gi.col_src),
+            dptr(gi.col_tgt), dptr(gi.col_type), dptr(gi.tile_node0))
+
+
+class _PNAMessagePassingFused(torch.autograd.Function):
+    """MultiAggr-layout message passing (unscaled sum | mean | pseudo-std | max, [V,1024]) with ONE kernel in the forward pass
+    (pna_fused.cu: gather -> tcgen05 message MLP -> segment aggregation; neither the gathered inputs nor the pre-activations
+    reach HBM) and a recomputing d-pre kernel in the backward pass; the weight / input gradient GEMMs and the d_h gather are
+    those of _PNAMessagePassingTC.  Forward output bit-identical to _PNAMessagePassingTC(mode=MP_MULTIAGGR)."""
+
+    @staticmethod
+    def forward(ctx, h, W, b, gi: GraphIndex):
+        lib = _cabi.load()
+        h, W, b = h.contiguous(), W.contiguous(), b.contiguous()
+        if W.shape[2] != 192:
+            raise ValueError(f"fused message passing needs 192-wide messages, got {W.shape[2]}")
+        V, E = gi.num_nodes, gi.num_edges
+        out = torch.empty(V, 1024, dtype=torch.float32, device=h.device)
+        aux_cnt = torch.empty(V, 4, 64, dtype=torch.uint8, device=h.device)
+        aux_arg = torch.empty(V, 4, 64, dtype=torch.uint8, device=h.device)
+        check(lib.adkf_pna_fused_fwd(*_fused_args(h, W, b, gi), V, E, dptr(out), dptr(aux_cnt), dptr(aux_arg), stream_ptr()),
+              "adkf_pna_fused_fwd")
+        ctx.gi = gi
+        ctx.save_for_backward(h, W, b, out, aux_cnt, aux_arg)
+        return out
+
+    @staticmethod
+    def backward(ctx, d_out):
+        lib = _cabi.load()
+        h, W, b, out, aux_cnt, aux_arg = ctx.saved_tensors
+        gi = ctx.gi
+        ts: TypeSortedEdges = gi.type_sorted
+        V, E = gi.num_nodes, gi.num_edges
+        msg = 192
+        f32 = dict(dtype=torch.float32, device=W.device)
+        d_W = torch.zeros_like(W)
+        d_b = torch.zeros(4, 3, msg, **f32)
+        d_h = torch.zeros(V, 128, **f32) if E == 0 else torch.empty(V, 128, **f32)
+        if E == 0:
+            return d_h, d_W, d_b, None
+        d_out = d_out.contiguous()
+        d_pre = torch.empty(E, 4 * msg, **f32)
+        check(lib.adkf_pna_fused_dpre(*_fused_args(h, W, b, gi), dptr(ts.csr2ts), V, E, dptr(out), dptr(aux_cnt), dptr(aux_arg),
+                                      dptr(d_out, torch.float32), dptr(d_pre), stream_ptr()), "adkf_pna_fused_dpre")
+        XG = torch.empty(E, 256, **f32)                       # inputs of the weight-gradient GEMM, re-gathered (L2-resident h)
+        check(lib.adkf_pna_gather_inputs(dptr(h), dptr(ts.src), dptr(ts.tgt), E, dptr(XG), stream_ptr()), "adkf_pna_gather_inputs")
+        dXG = torch.empty(E, 256, **f32)
+        W2 = W.view(12 * msg, 64)
+        for t in range(3):
+            e0, e1 = ts.type_off[t], ts.type_off[t + 1]
+            if e1 <= e0:
+                continue
+            n = e1 - e0
+            gemm_tf32x3_batched(d_pre[e0:e1], False, 0, msg, W2[t * msg:], True, 0, 3 * msg, n, 64, msg, 4, dXG[e0:e1], 256, 64)
+            gemm_tf32x3_batched(d_pre[e0:e1], True, msg, 0, XG[e0:e1], True, 64, 0, msg, 64, n, 4,
+                                d_W.view(-1)[t * msg * 64:], 64, 3 * msg * 64, allow_splitk=True)
+            d_b[:, t] = act_bwd_colsum(d_pre[e0:e1], None, 0, True)[1].view(4, msg)
+        check(lib.adkf_pna_dh_gather(dptr(dXG), dptr(ts.tptr), dptr(ts.rev), V, dptr(d_h), stream_ptr()), "adkf_pna_dh_gather")
+        return d_h, d_W, d_b, None
+
+
+# ADKF_PNA_FUSED=0 keeps the gather -> batched GEMM -> aggregate chain (A/B runs, and the reference for the bit-equality test)
+_FUSED_DEFAULT = os.environ.get("ADKF_PNA_FUSED", "1") != "0"
+
+
+def multiaggr_message_passing(h, W, b, gi: GraphIndex, fused: Optional[bool] = None):
+    """Unscaled [V,1024] aggregate of the 4 towers: the fused kernel when the graph allows it (in-degree <= 16), else the
+    three-kernel chain."""
+    use = _FUSED_DEFAULT if fused is None else fused
+    if use and gi.fused_ok and gi.num_edges > 0:
+        return _PNAMessagePassingFused.apply(h, W, b, gi)
+    return _PNAMessagePassingTC.apply(h, W, b, gi, MP_MULTIAGGR)
+
+
 def mp_message_passing(h, W, b, gi: GraphIndex, mode: int):
     """h [V,128], W [4,3,msg,64], b [4,3,msg] -> aggregated messages of all 4 towers for GNN types PNA / MultiAggr / Plain."""
     if getattr(gi, "type_sorted", None) is None:
         raise RuntimeError("mp_message_passing needs a GraphIndex built by build_graph_index (type-sorted edges)")
+    if mode == MP_MULTIAGGR:
+        return multiaggr_message_passing(h, W, b, gi)
     return _PNAMessagePassingTC.apply(h, W, b, gi, mode)
 
 
@@ -317,7 +414,7 @@ def pna_message_passing_projected(h, W, b, W_out, b_out, gi: GraphIndex):
     ([V,1024], the MultiAggr kernels) -> ONE GEMM with the three scaler blocks of W_out stacked ([384,1024]) -> combine."""
     if getattr(gi, "type_sorted", None) is None:
         raise RuntimeError("pna_message_passing_projected needs a GraphIndex built by build_graph_index (type-sorted edges)")
-    agg = _PNAMessagePassingTC.apply(h, W, b, gi, MP_MULTIAGGR)
+    agg = multiaggr_message_passing(h, W, b, gi)
     # W_out [128, 4 towers x (1 | amp | att) x 256] -> [3 x 128, 4 x 256]: row block s holds the columns of scaler s
     Wcat = W_out.view(128, 4, 3, 256).permute(2, 0, 1, 3).reshape(384, 1024)
     P = linear_tc(agg, Wcat, None)
@@ -706,7 +803,10 @@ def gemm_tf32x3(a: torch.Tensor, trans_a: bool, b: torch.Tensor, trans_b: bool, 
     if out is None:
         out = torch.empty(M, N, dtype=torch.float32, device=a.device)
     ws, nws = None, 0
-    if bias is None and ACT_IDS[act] == 0:
+    # split-K only for the backward operand forms: a forward (K,K) product must give every output row the same bits whatever the
+    # number of rows in the launch (the split plan depends on the shape), so that a task's features -- and with them every
+    # ReLU / arg-max decision of its gradient -- do not depend on which other tasks share the batch
+    if bias is None and ACT_IDS[act] == 0 and (trans_a or trans_b):
         nws = int(lib.adkf_gemm_splitk_ws_floats(M, N, K))
         if nws:
             ws = torch.empty(nws, dtype=torch.float32, device=a.device)

@@ -37,6 +37,8 @@ class HostTaskBatch:
     descriptors: torch.Tensor        # [G, 42] f32
     labels: torch.Tensor             # [G] f32: +-1 (classification) or standardised numeric
     bool_labels: torch.Tensor        # [G] bool (metrics)
+    max_degree: int = -1             # largest in-degree over the bidirectional edge set (host-computed; -1 = unknown): lets the
+                                     # extractor pick the fused message-passing kernel without a device round trip
 
     def nbytes(self) -> int:
         ts = [self.node_features, *self.adjacency, self.node_to_graph, self.fingerprints, self.descriptors,
@@ -92,7 +94,10 @@ def collate_tasks(batches: Sequence[DKTBatch], use_numeric_labels: bool, pin: bo
         labels = ((np.concatenate([np.asarray(p[1]) for p in parts]).astype(np.float32) - 0.5) * 2.0).astype(np.float32)
     bool_labels = np.concatenate([np.asarray(x, dtype=bool) for b in batches
                                   for x in (b.support_labels, b.query_labels)])
+    ends = np.concatenate([a.reshape(-1) for a in adjacency]) if adjacency else np.zeros(0, dtype=np.int64)
+    max_degree = int(np.bincount(ends).max()) if ends.size else 0      # every bond is a message in both directions
     return HostTaskBatch(
+        max_degree=max_degree,
         num_tasks=len(batches),
         n_sup=[int(b.support_features.num_graphs) for b in batches],
         n_query=[int(b.query_features.num_graphs) for b in batches],
@@ -116,7 +121,8 @@ def to_device(hb: HostTaskBatch, device, build_index: bool = True) -> DeviceTask
                          fingerprints=cp(hb.fingerprints), descriptors=cp(hb.descriptors), labels=cp(hb.labels),
                          layout=ops.TaskLayout.build(hb.n_sup, hb.n_query, device))
     if build_index:
-        db.graph_index = ops.build_graph_index(adjs, hb.num_nodes, n2g, hb.num_graphs)
+        db.graph_index = ops.build_graph_index(adjs, hb.num_nodes, n2g, hb.num_graphs,
+                                               max_degree=hb.max_degree if hb.max_degree >= 0 else None)
     return db
 
 

@@ -161,6 +161,27 @@ int adkf_pna_aggregate_fwd(const float* pre, const int32_t* tptr, int32_t V, flo
 int adkf_pna_dpre(const float* pre, const int32_t* tptr, int32_t V, const float* fwd_out, const uint8_t* aux_cnt,
                   const uint8_t* aux_arg, const float* d_out, float* d_pre, void* stream);
 int adkf_pna_dh_gather(const float* dXG, const int32_t* tptr, const int32_t* rev, int32_t V, float* d_h, void* stream);
+/* ---------------------------------------------------------------------------------------------
+ * The tower-style message passing of a PNA / MultiAggr block as ONE kernel per direction (pna_fused.cu; default when the
+ * largest in-degree is <= adkf_pna_fused_max_degree()): gather [h_src | h_tgt] -> message MLP on tcgen05 (3xTF32) -> bias + ReLU ->
+ * sum | mean | pseudo-std | max per target node.  Replaces RelationalMP.forward + RelationalMultiAggrMP._aggregate_messages
+ * (fs_mol/modules/gnn.py:129-150, 197-240) without writing the gathered inputs [E,256] or the pre-activations [E,768] to HBM.
+ *   fwd : h [V,128], W [4][3][192][64], b [4][3][192] -> out [V,1024] (unscaled aggregate, ADKF_MP_MULTIAGGR layout),
+ *         aux_cnt / aux_arg [V,4,64]; bit-identical to gather + adkf_gemm_tf32x3_batched + adkf_mp_aggregate_fwd
+ *   dpre: recomputes the pre-activations and emits d pre [E,768] in (type, target)-sorted row order (csr2ts [E] maps a CSR
+ *         row to its sorted position), ready for the weight / input gradient GEMMs
+ * CSR arrays as built by adkf_graph_csr_build; tile_node0 [adkf_pna_fused_num_tiles(E) + 1]: first node v with
+ * rowptr[v] >= 112 j (last entry V).
+ * ------------------------------------------------------------------------------------------- */
+int32_t adkf_pna_fused_num_tiles(int64_t E);
+int32_t adkf_pna_fused_max_degree(void);
+int adkf_pna_fused_fwd(const float* h, const float* W, const float* b, const int32_t* rowptr, const int32_t* col_src,
+                       const int32_t* col_tgt, const uint8_t* col_type, const int32_t* tile_node0, int32_t V, int64_t E,
+                       float* out, uint8_t* aux_cnt, uint8_t* aux_arg, void* stream);
+int adkf_pna_fused_dpre(const float* h, const float* W, const float* b, const int32_t* rowptr, const int32_t* col_src,
+                        const int32_t* col_tgt, const uint8_t* col_type, const int32_t* tile_node0, const int32_t* csr2ts,
+                        int32_t V, int64_t E, const float* fwd_out, const uint8_t* aux_cnt, const uint8_t* aux_arg,
+                        const float* d_out, float* d_pre, void* stream);
 /* The other two tower-style message-passing types of GNNBlock (fs_mol/modules/gnn.py:421-447), same edge layout:
  *   ADKF_MP_MULTIAGGR  RelationalMultiAggrMP without PNA scalers: pre [E,768] -> out [V,1024]  (gnn.py:197-240)
  *   ADKF_MP_PLAIN      RelationalMP: relu + scatter_sum of 64-wide messages, pre [E,256] -> out [V,256]  (gnn.py:152-165;

@@ -123,6 +123,52 @@ def test_pna_fwd_bwd(cuda_device, n_mol, impl):
     assert torch.equal(out2, out.detach())
 
 
+@pytest.mark.parametrize("n_mol", [3, 40, 300])
+def test_pna_fused_equals_three_kernel_chain(cuda_device, n_mol):
+    """pna_fused.cu (gather -> tcgen05 message MLP -> segment aggregation in ONE kernel; recomputing d-pre kernel in the backward
+    pass) against the gather -> batched GEMM -> aggregate chain it replaces: forward output and aux bytes BIT-identical, backward
+    within fp32 rounding of the d-pre arithmetic (the chain rule is the same code, FMA contraction may differ)."""
+    from adkf_ift_b200 import ops
+    b, _ = make_batch(5, n_mol)
+    V = b.num_nodes
+    gen = torch.Generator().manual_seed(7)
+    h = torch.randn(V, 128, generator=gen)
+    W = torch.randn(4, 3, 192, 64, generator=gen) * 0.15
+    bias = torch.randn(4, 3, 192, generator=gen) * 0.1
+    gout = torch.randn(V, 1024, generator=gen)
+    gi = ops.build_graph_index([torch.from_numpy(a).to(cuda_device) for a in b.adjacency_lists], V)
+    assert gi.fused_ok and gi.max_degree <= 16
+    res = {}
+    for fused in (False, True):
+        hc, Wc, bc = (x.to(cuda_device).requires_grad_(True) for x in (h, W, bias))
+        out = ops.multiaggr_message_passing(hc, Wc, bc, gi, fused=fused)
+        out.backward(gout.to(cuda_device))
+        res[fused] = (out.detach(), hc.grad, Wc.grad, bc.grad)
+    assert torch.equal(res[True][0], res[False][0]), rel(res[True][0], res[False][0])
+    for name, gf, gu in zip(("dh", "dW", "db"), res[True][1:], res[False][1:]):
+        e = rel(gf, gu)
+        print("fused vs chain", name, e)
+        assert e < 2e-6, (name, e)
+    # host-known degree (the collation's value) takes the same path without the device read
+    gi2 = ops.build_graph_index([torch.from_numpy(a).to(cuda_device) for a in b.adjacency_lists], V, max_degree=gi.max_degree)
+    out2 = ops.multiaggr_message_passing(h.to(cuda_device), W.to(cuda_device), bias.to(cuda_device), gi2, fused=True)
+    assert torch.equal(out2, res[True][0])
+
+
+def test_pna_fused_falls_back_on_high_degree(cuda_device):
+    """A hub with in-degree 40 does not fit a 128-row tile with 112-row stride: the dispatcher keeps the three-kernel chain."""
+    from adkf_ift_b200 import ops
+    V = 44
+    a0 = np.stack([np.arange(1, 41), np.zeros(40, np.int64)], axis=1).astype(np.int64)
+    adjs = [torch.from_numpy(a0), torch.from_numpy(np.array([[41, 42]], np.int64)), torch.zeros(0, 2, dtype=torch.int64)]
+    gi = ops.build_graph_index([a.to(cuda_device) for a in adjs], V)
+    assert gi.max_degree == 40 and not gi.fused_ok
+    gen = torch.Generator().manual_seed(3)
+    h, W, bias = torch.randn(V, 128, generator=gen), torch.randn(4, 3, 192, 64, generator=gen) * 0.15, torch.randn(4, 3, 192, generator=gen)
+    out = ops.multiaggr_message_passing(h.to(cuda_device), W.to(cuda_device), bias.to(cuda_device), gi)
+    assert out.shape == (V, 1024) and bool(torch.isfinite(out).all())
+
+
 @pytest.mark.parametrize("impl", ["tcgen05", "simt"])
 def test_pna_isolated_and_high_degree_nodes(cuda_device, impl):
     """Edge cases: a node without edges (all aggregates 0) and a hub with in-degree 40 (> the 32-message buffer)."""
