@@ -29,6 +29,7 @@ SIGNATURES = {
     "adkf_pna_dh_gather": ([_P, _P, _P, c_int32, _P, _P], ctypes.c_int),
     "adkf_pna_fused_num_tiles": ([c_int64], c_int32),
     "adkf_pna_fused_max_degree": ([], c_int32),
+    "adkf_pna_fused_set_debug": ([_P], None),
     "adkf_pna_fused_fwd": ([_P, _P, _P, _P, _P, _P, _P, _P, c_int32, c_int64, _P, _P, _P, _P], ctypes.c_int),
     "adkf_pna_fused_dpre": ([_P, _P, _P, _P, _P, _P, _P, _P, _P, c_int32, c_int64, _P, _P, _P, _P, _P, _P], ctypes.c_int),
     "adkf_mha_gather_inputs": ([_P, _P, _P, c_int64, _P, _P], ctypes.c_int),

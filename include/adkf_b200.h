@@ -175,6 +175,8 @@ int adkf_pna_dh_gather(const float* dXG, const int32_t* tptr, const int32_t* rev
  * ------------------------------------------------------------------------------------------- */
 int32_t adkf_pna_fused_num_tiles(int64_t E);
 int32_t adkf_pna_fused_max_degree(void);
+/* development probe: per-CTA cycle counters [148][16] of the next fused launches (waits / work per warp role); NULL = off */
+void adkf_pna_fused_set_debug(void* buf);
 int adkf_pna_fused_fwd(const float* h, const float* W, const float* b, const int32_t* rowptr, const int32_t* col_src,
                        const int32_t* col_tgt, const uint8_t* col_type, const int32_t* tile_node0, int32_t V, int64_t E,
                        float* out, uint8_t* aux_cnt, uint8_t* aux_arg, void* stream);
