@@ -340,15 +340,21 @@ class _PNAMessagePassingFused(torch.autograd.Function):
         return d_h, d_W, d_b, None
 
 
-# ADKF_PNA_FUSED=0 keeps the gather -> batched GEMM -> aggregate chain (A/B runs, and the reference for the bit-equality test)
-_FUSED_DEFAULT = os.environ.get("ADKF_PNA_FUSED", "1") != "0"
+# Which path runs (measured on the C2 graph batch, tools/pna_fused_probe.py, profiles/r2p_pna_fused_probe.txt): the fused forward
+# is 0.93 ms against 0.99 ms for the chain, but a backward pass that has to RECOMPUTE the pre-activations costs 2.09 ms against
+# 1.46 ms for the chain that saved them (the recompute repeats the gather + MMA work of the forward; the d-pre arithmetic per node is
+# latency-bound).  So by default the fused kernel serves the passes that need no gradient (meta-test, evaluation, prediction) and
+# meta-training keeps the chain.  ADKF_PNA_FUSED=0: never fused; =2: fused in training as well (A/B runs).
+_FUSED_MODE = int(os.environ.get("ADKF_PNA_FUSED", "1"))
 
 
 def multiaggr_message_passing(h, W, b, gi: GraphIndex, fused: Optional[bool] = None):
-    """Unscaled [V,1024] aggregate of the 4 towers: the fused kernel when the graph allows it (in-degree <= 16), else the
-    three-kernel chain."""
-    use = _FUSED_DEFAULT if fused is None else fused
-    if use and gi.fused_ok and gi.num_edges > 0:
+    """Unscaled [V,1024] aggregate of the 4 towers: the fused kernel when the graph allows it (in-degree <= 16) and no gradient is
+    wanted (see above; `fused` overrides the choice), else the three-kernel chain."""
+    if fused is None:
+        needs_grad = torch.is_grad_enabled() and (h.requires_grad or W.requires_grad or b.requires_grad)
+        fused = _FUSED_MODE == 2 or (_FUSED_MODE == 1 and not needs_grad)
+    if fused and gi.fused_ok and gi.num_edges > 0:
         return _PNAMessagePassingFused.apply(h, W, b, gi)
     return _PNAMessagePassingTC.apply(h, W, b, gi, MP_MULTIAGGR)
 
