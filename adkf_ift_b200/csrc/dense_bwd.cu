@@ -113,3 +113,49 @@ extern "C" int adkf_act_bwd_colsum(const float* dY, int64_t ldy, const float* Y,
     }
     return 0;
 }
+
+// ---- adkf_act_bwd_colsum_noalloc: the same two kernels with the column-sum partials in a file-scope device array --------------
+// For callers that cannot allocate (CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc): no workspace
+// argument, no cudaMalloc / cudaFree / allocating library call anywhere on this path.  Every GPU that loads the library holds the
+// array (kNoAllocMaxFloats * 4 bytes = 4.6 MiB) until exit.  All calls share it: two calls that OVERLAP on the GPU (different
+// streams without an ordering between them) race on it; calls on one stream are ordered and safe.  Nothing in it has to start at
+// zero: act_bwd_colsum_kernel writes every partial[b][c], b < nblk, c < N before colsum_finish_kernel reads exactly those.
+namespace adkf {
+constexpr int64_t kNoAllocMaxFloats = 1184ll * 1024;       // db_blocks(M) <= 148 * 8 = 1184 row blocks x N <= 1024 columns at full height
+static __device__ __align__(256) float g_colsum_scratch[kNoAllocMaxFloats];
+}  // namespace adkf
+
+// device address of g_colsum_scratch on the CURRENT device (in host code the symbol's name is only a host-side stand-in, not a
+// device pointer): looked up once per device with that device current, return code checked
+static int noalloc_scratch(float** out) {
+    constexpr int kMaxDev = 64;
+    static float* ptrs[kMaxDev] = {};
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return (int)e;
+    if (dev < 0 || dev >= kMaxDev) return ADKF_ERR_BADARG;
+    if (ptrs[dev] == nullptr) {
+        float* p = nullptr;
+        e = cudaGetSymbolAddress((void**)&p, adkf::g_colsum_scratch);
+        if (e != cudaSuccess) return (int)e;
+        if (p == nullptr) return (int)cudaErrorInvalidSymbol;
+        ptrs[dev] = p;
+    }
+    *out = ptrs[dev];
+    return 0;
+}
+
+extern "C" int64_t adkf_act_bwd_colsum_noalloc_max_floats(void) { return adkf::kNoAllocMaxFloats; }
+
+extern "C" int adkf_act_bwd_colsum_noalloc(const float* dY, int64_t ldy, const float* Y, int64_t ldyy, int64_t M, int32_t N,
+                                           int32_t act, float* dZ, int64_t ldz, float* db, void* stream) {
+    if (M <= 0 || N <= 0) return 0;
+    // the partials of this problem must fit the static array: ADKF_ERR_TOOLARGE, nothing is launched
+    if (db != nullptr && adkf_act_bwd_colsum_ws_floats(M, N) > adkf::kNoAllocMaxFloats) return ADKF_ERR_TOOLARGE;
+    float* ws = nullptr;
+    if (db != nullptr) {
+        const int rc = noalloc_scratch(&ws);
+        if (rc) return rc;
+    }
+    return adkf_act_bwd_colsum(dY, ldy, Y, ldyy, M, N, act, dZ, ldz, db, ws, ws ? adkf::kNoAllocMaxFloats : 0, stream);
+}

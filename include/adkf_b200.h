@@ -120,6 +120,17 @@ int adkf_mp_pna_bwd(const float* h, const float* W, const float* b, const int32_
 int64_t adkf_act_bwd_colsum_ws_floats(int64_t M, int32_t N);
 int adkf_act_bwd_colsum(const float* dY, int64_t ldy, const float* Y, int64_t ldyy, int64_t M, int32_t N, int32_t act,
                         float* dZ, int64_t ldz, float* db, float* ws, int64_t ws_floats, void* stream);
+/* adkf_act_bwd_colsum for callers that cannot allocate (CUDA graph capture, serving loops, harnesses that forbid cudaMalloc).
+ * NO COUNTERPART IN THE REFERENCE.  Same kernels and the same result bit for bit;
+ * the column-sum partials live in a file-scope `static __device__` array of adkf_act_bwd_colsum_noalloc_max_floats() floats
+ * (1184 x 1024 = 4.6 MiB, held by every GPU that loads the library until exit) instead of a caller workspace; the path calls no
+ * cudaMalloc / cudaFree / allocating routine.  Returns ADKF_ERR_TOOLARGE (nothing launched) when
+ * adkf_act_bwd_colsum_ws_floats(M, N) exceeds that maximum.  All calls share the array: calls that overlap on the GPU (streams
+ * without an ordering between them) race; calls on one stream are safe.  Nothing needs clearing between calls (every partial
+ * that is read was written by the same call). */
+int64_t adkf_act_bwd_colsum_noalloc_max_floats(void);
+int adkf_act_bwd_colsum_noalloc(const float* dY, int64_t ldy, const float* Y, int64_t ldyy, int64_t M, int32_t N, int32_t act,
+                                float* dZ, int64_t ldz, float* db, void* stream);
 
 /* ---------------------------------------------------------------------------------------------
  * PNA degree scalers folded out of the aggregate (gnn.py:242-263 + msg_out_projection, gnn.py:492-495; pna_combine.cu):
