@@ -60,6 +60,7 @@ constexpr size_t smem_bytes(int NS) { return (size_t)ring_bytes(NS) + kStageByte
 
 constexpr uint32_t kIdescTf32 = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(kBN >> 3) << 17) | ((uint32_t)(kPM >> 4) << 24);
 constexpr uint32_t kIdescBf16 = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(kBN >> 3) << 17) | ((uint32_t)(kPM >> 4) << 24);
+constexpr uint32_t kIdescF16 = (1u << 4) | (0u << 7) | (0u << 10) | ((uint32_t)(kBN >> 3) << 17) | ((uint32_t)(kPM >> 4) << 24);
 
 __device__ __forceinline__ uint32_t cluster_rank() {
     uint32_t r;
@@ -119,12 +120,30 @@ __device__ __forceinline__ uint32_t pack_bf16(float lo_k, float hi_k) {   // ele
     const __nv_bfloat162 v = __floats2bfloat162_rn(lo_k, hi_k);
     return *reinterpret_cast<const uint32_t*>(&v);
 }
+// fp16 pair, saturating (|v| > 65504 -> +-65504 instead of inf): one F2FP.SATFINITE.F16.F32.PACK_AB
+__device__ __forceinline__ uint32_t pack_f16(float lo_k, float hi_k) {
+    uint32_t d;
+    asm("cvt.rn.satfinite.f16x2.f32 %0, %1, %2;" : "=r"(d) : "f"(hi_k), "f"(lo_k));
+    return d;
+}
+// Correction operands.  CORR = 0: tf32 (two tf32 correction MMAs per k-step).  CORR = 1: bf16 (one kind::f16 chain over [lo | hi] x
+// [hi | lo]; full exponent range, 8-bit mantissas: 2^-20 per product).  CORR = 2: fp16 with the lo parts SCALED by 2^11 (exact) and the
+// correction accumulator scaled back by 2^-11 when it is drained: tf32's hi has 10 explicit mantissa bits, exactly what fp16 holds,
+// and lo * 2^11 has the magnitude of the value itself, so for 6.1e-5 <= |v| <= 65504 the operands are as exact as the tf32 correction
+// operands (2^-22 per product) at the kind::f16 rate; outside that range the correction degrades gracefully (subnormal / saturated
+// fp16) towards plain TF32 for those elements.  Used for the FORWARD products (activations and weights); the backward keeps bf16
+// because gradients can be arbitrarily small (ReZero alpha ~ 1e-7).
+constexpr float kLoScale = 2048.f, kLoUnscale = 1.f / 2048.f;
+template <int CORR> __device__ __forceinline__ uint32_t pack_corr_lo(float a, float b) {
+    return CORR == 2 ? pack_f16(a * kLoScale, b * kLoScale) : pack_bf16(a, b);
+}
+template <int CORR> __device__ __forceinline__ uint32_t pack_corr_hi(float a, float b) { return CORR == 2 ? pack_f16(a, b) : pack_bf16(a, b); }
 
 // ---- A operand: row t of the raw A tile -> tensor memory --------------------------------------------------------------------
 //   columns [0,32)  : hi as tf32
 //   CORR16: columns [32,48) = bf16 pairs of lo, [48,64) = bf16 pairs of hi  (the [lo | hi] operand of the correction MMAs)
 //   else  : columns [32,64) = lo as tf32
-template <bool TR, bool CORR16>
+template <bool TR, int CORR16>
 __device__ __forceinline__ void split_rows_to_tmem(const unsigned char* __restrict__ raw, uint32_t taddr, int t) {
     float x[kBK];
     if (!TR) {
@@ -146,8 +165,8 @@ __device__ __forceinline__ void split_rows_to_tmem(const unsigned char* __restri
 #pragma unroll
         for (int c = 0; c < kBK / 2; ++c) {
             const float h0 = __uint_as_float(hi[2 * c]), h1 = __uint_as_float(hi[2 * c + 1]);
-            co[c] = pack_bf16(x[2 * c] - h0, x[2 * c + 1] - h1);
-            co[kBK / 2 + c] = pack_bf16(h0, h1);
+            co[c] = pack_corr_lo<CORR16>(x[2 * c] - h0, x[2 * c + 1] - h1);
+            co[kBK / 2 + c] = pack_corr_hi<CORR16>(h0, h1);
         }
     } else {
 #pragma unroll
@@ -163,7 +182,7 @@ __device__ __forceinline__ void split_rows_to_tmem(const unsigned char* __restri
 //   CORR16: correction tile row = [bf16 hi k0..31 | bf16 lo k0..31]  (chunks 0-3 hi, 4-7 lo)      else: lo as tf32
 //   TR = false: raw = TMA SWIZZLE_128B box (64 rows x 32 floats); thread t: float4 p = i*128 + t, i < 4 (row p/8, physical chunk p%8)
 //   TR = true : raw = [32 k][64 mn] floats; thread t: row mn = t & 63, k half t >> 6 (16 k values)
-template <bool TR, bool CORR16>
+template <bool TR, int CORR16>
 __device__ __forceinline__ void split_b_half(const unsigned char* __restrict__ raw, unsigned char* __restrict__ hi_t,
                                              unsigned char* __restrict__ co_t, int t) {
     float4* __restrict__ hi4 = reinterpret_cast<float4*>(hi_t);
@@ -185,8 +204,8 @@ __device__ __forceinline__ void split_b_half(const unsigned char* __restrict__ r
                 // the lane holding logical chunk j ^ 1 is lane ^ 1 (same row, physical chunk ^ 1): exchange halves so that each
                 // lane owns one full 16-byte chunk of the correction row (even j: the 8 hi values k = 4j..4j+7; odd j: the 8 lo
                 // values k = 4j-4..4j+3) -- one conflict-free 16-byte store per lane
-                const uint32_t h0 = pack_bf16(hi.x, hi.y), h1 = pack_bf16(hi.z, hi.w);
-                const uint32_t l0 = pack_bf16(lo.x, lo.y), l1 = pack_bf16(lo.z, lo.w);
+                const uint32_t h0 = pack_corr_hi<CORR16>(hi.x, hi.y), h1 = pack_corr_hi<CORR16>(hi.z, hi.w);
+                const uint32_t l0 = pack_corr_lo<CORR16>(lo.x, lo.y), l1 = pack_corr_lo<CORR16>(lo.z, lo.w);
                 const uint32_t s0 = even ? l0 : h0, s1 = even ? l1 : h1;
                 const uint32_t r0 = __shfl_xor_sync(0xffffffffu, s0, 1), r1 = __shfl_xor_sync(0xffffffffu, s1, 1);
                 const uint4 o = even ? make_uint4(h0, h1, r0, r1) : make_uint4(r0, r1, l0, l1);
@@ -220,10 +239,10 @@ __device__ __forceinline__ void split_b_half(const unsigned char* __restrict__ r
 #pragma unroll
             for (int h = 0; h < 2; ++h) {                              // 8 k values per 16-byte chunk: float4 groups 2h, 2h+1
                 const int lc = kh * 2 + h;
-                const uint4 oh = make_uint4(pack_bf16(hi[2 * h].x, hi[2 * h].y), pack_bf16(hi[2 * h].z, hi[2 * h].w),
-                                            pack_bf16(hi[2 * h + 1].x, hi[2 * h + 1].y), pack_bf16(hi[2 * h + 1].z, hi[2 * h + 1].w));
-                const uint4 ol = make_uint4(pack_bf16(lo[2 * h].x, lo[2 * h].y), pack_bf16(lo[2 * h].z, lo[2 * h].w),
-                                            pack_bf16(lo[2 * h + 1].x, lo[2 * h + 1].y), pack_bf16(lo[2 * h + 1].z, lo[2 * h + 1].w));
+                const uint4 oh = make_uint4(pack_corr_hi<CORR16>(hi[2 * h].x, hi[2 * h].y), pack_corr_hi<CORR16>(hi[2 * h].z, hi[2 * h].w),
+                                            pack_corr_hi<CORR16>(hi[2 * h + 1].x, hi[2 * h + 1].y), pack_corr_hi<CORR16>(hi[2 * h + 1].z, hi[2 * h + 1].w));
+                const uint4 ol = make_uint4(pack_corr_lo<CORR16>(lo[2 * h].x, lo[2 * h].y), pack_corr_lo<CORR16>(lo[2 * h].z, lo[2 * h].w),
+                                            pack_corr_lo<CORR16>(lo[2 * h + 1].x, lo[2 * h + 1].y), pack_corr_lo<CORR16>(lo[2 * h + 1].z, lo[2 * h + 1].w));
                 co4[mn * 8 + (lc ^ (mn & 7))] = oh;
                 co4[mn * 8 + ((4 + lc) ^ (mn & 7))] = ol;
             }
@@ -251,7 +270,7 @@ __device__ __forceinline__ PairTile pair_tile(const GemmEpilogue& ep, int tile, 
     return c;
 }
 
-template <bool TA, bool TB, bool CORR16, int NS>
+template <bool TA, bool TB, int CORR16, int NS>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
 gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, GemmEpilogue ep) {
     if (ep.gate != nullptr && *ep.gate == 0) return;     // gated launch (uniform over the grid: nothing has been set up yet)
@@ -363,7 +382,7 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                             umma2_tf32_ts(acc_big, a_hi + ak, b_hi + adv, kIdescTf32, (group_first && k == 0) ? 0u : 1u);
                             if (CORR16) {
                                 // [lo | hi] (A, bf16) x [hi | lo] (B, bf16): k-steps 0,1 = lo.hi, 2,3 = hi.lo
-                                umma2_bf16_ts(acc_small, a_co + ak, b_co + adv, kIdescBf16, (kMerged || (i | k)) ? 1u : 0u);
+                                umma2_bf16_ts(acc_small, a_co + ak, b_co + adv, CORR16 == 2 ? kIdescF16 : kIdescBf16, (kMerged || (i | k)) ? 1u : 0u);
                             } else {
                                 umma2_tf32_ts(acc_small, a_co + ak, b_hi + adv, kIdescTf32, (kMerged || (i | k)) ? 1u : 0u);   // lo.hi
                                 umma2_tf32_ts(acc_small, a_hi + ak, b_co + adv, kIdescTf32, 1u);                   // hi.lo
@@ -458,7 +477,7 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                     float v[16];
                     tmem_ld16(trow + (uint32_t)kSmallCol + c0, v);
 #pragma unroll
-                    for (int j = 0; j < 16; ++j) acc[c0 + j] += v[j];
+                    for (int j = 0; j < 16; ++j) acc[c0 + j] += (CORR16 == 2) ? v[j] * kLoUnscale : v[j];   // (power of two: exact)
                 }
                 tc_fence_before();
                 __syncwarp();
@@ -480,7 +499,7 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     }
 }
 
-template <bool TA, bool TB, bool C16, int NS>
+template <bool TA, bool TB, int C16, int NS>
 static int pair_launch_t(dim3 grid, cudaStream_t s, const CUtensorMap& ma, const CUtensorMap& mb, const GemmEpilogue& ep) {
     static bool done = false;
     if (!done) {
@@ -494,9 +513,11 @@ static int pair_launch_t(dim3 grid, cudaStream_t s, const CUtensorMap& ma, const
 }
 
 template <bool TA, bool TB>
-static int pair_launch_f(bool c16, bool merged, dim3 grid, cudaStream_t s, const CUtensorMap& ma, const CUtensorMap& mb, const GemmEpilogue& ep) {
-    if (merged) return c16 ? pair_launch_t<TA, TB, true, 4>(grid, s, ma, mb, ep) : pair_launch_t<TA, TB, false, 4>(grid, s, ma, mb, ep);
-    return c16 ? pair_launch_t<TA, TB, true, 2>(grid, s, ma, mb, ep) : pair_launch_t<TA, TB, false, 2>(grid, s, ma, mb, ep);
+static int pair_launch_f(int c16, bool merged, dim3 grid, cudaStream_t s, const CUtensorMap& ma, const CUtensorMap& mb, const GemmEpilogue& ep) {
+    if (merged && c16 != 2)     // (the merged accumulator cannot carry the 2^11 scale of the fp16 corrections)
+        return c16 ? pair_launch_t<TA, TB, 1, 4>(grid, s, ma, mb, ep) : pair_launch_t<TA, TB, 0, 4>(grid, s, ma, mb, ep);
+    if (c16 == 2) return pair_launch_t<TA, TB, 2, 2>(grid, s, ma, mb, ep);
+    return c16 ? pair_launch_t<TA, TB, 1, 2>(grid, s, ma, mb, ep) : pair_launch_t<TA, TB, 0, 2>(grid, s, ma, mb, ep);
 }
 
 }  // namespace pr
@@ -510,7 +531,13 @@ int gemm_pair_launch(const CUtensorMap& ma, const CUtensorMap& mb, const GemmEpi
     // rounding error (1e-6 instead of 3e-7) flips more ReLU / arg-max decisions of the extractor, and a single flip near the top
     // of the network moves every gradient below it by ~5e-4 (profiles/r2i_corr16_bisect.txt); the backward pass is LINEAR in
     // the upstream gradient, there the same error stays at 1e-6.
-    const bool corr16 = g_gemm_corr16 == 1 || (g_gemm_corr16 == 2 && (transA || transB));
+    // 3 (default): fp16 scaled corrections forward, bf16 backward.  4: fp16 everywhere (A/B runs).
+    const bool bwd_form = transA || transB;
+    int corr16 = 0;
+    if (g_gemm_corr16 == 1) corr16 = 1;
+    else if (g_gemm_corr16 == 2) corr16 = bwd_form ? 1 : 0;
+    else if (g_gemm_corr16 == 3) corr16 = bwd_form ? 1 : 2;
+    else if (g_gemm_corr16 == 4) corr16 = 2;
     static const int merged = getenv("ADKF_GEMM_MERGE") ? atoi(getenv("ADKF_GEMM_MERGE")) : 0;   // development switch (A/B runs)
     const int pairs = std::max(1, num_sms() / 2);
     dim3 grid((unsigned)(2 * std::min(ep.ntiles, pairs)));

@@ -43,6 +43,7 @@
 #include <cuda.h>
 #include <algorithm>
 #include <cstdlib>
+#include <string>
 #include "gemm_common.cuh"
 #include "../../include/adkf_b200.h"
 
@@ -517,15 +518,26 @@ int gemm_pair_launch(const CUtensorMap& ma, const CUtensorMap& mb, const GemmEpi
 }
 namespace adkf {
 int g_gemm_impl = getenv("ADKF_GEMM_IMPL") ? atoi(getenv("ADKF_GEMM_IMPL")) : 2;          // 1: one CTA per tile, 2: CTA pairs
-// pair kernel, correction products: 0 tf32 everywhere, 1 bf16 everywhere, 2 bf16 in the backward forms only (default)
-int g_gemm_corr16 = !getenv("ADKF_GEMM_CORR") ? 2 : (getenv("ADKF_GEMM_CORR")[0] == 'b' ? 1 : (getenv("ADKF_GEMM_CORR")[0] == 't' ? 0 : 2));
+// pair kernel, correction products (ADKF_GEMM_CORR = tf32 | bf16 | mixed | fp16 | fp16all): 0 tf32 everywhere, 1 bf16 everywhere,
+// 2 tf32 forward / bf16 backward (round-2 default until the fp16 scheme), 3 (default) scaled fp16 forward / bf16 backward, 4 fp16 everywhere
+static int corr_from_env() {
+    const char* e = getenv("ADKF_GEMM_CORR");
+    if (!e) return 3;
+    const std::string v(e);
+    if (v == "tf32" || v == "t") return 0;
+    if (v == "bf16" || v == "b") return 1;
+    if (v == "mixed" || v == "m") return 2;
+    if (v == "fp16all") return 4;
+    return 3;
+}
+int g_gemm_corr16 = corr_from_env();
 }
 static bool use_pair(int64_t M) { return adkf::g_gemm_impl == 2 && M > kBM; }
 
 extern "C" int adkf_gemm_configure(int32_t impl, int32_t corr16) {
     const int prev = adkf::g_gemm_impl | (adkf::g_gemm_corr16 << 8);
     if (impl == 1 || impl == 2) adkf::g_gemm_impl = impl;
-    if (corr16 >= 0 && corr16 <= 2) adkf::g_gemm_corr16 = corr16;
+    if (corr16 >= 0 && corr16 <= 4) adkf::g_gemm_corr16 = corr16;
     return prev;
 }
 static int64_t out_tiles(int64_t M, int32_t N) {

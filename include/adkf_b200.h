@@ -332,8 +332,10 @@ int adkf_ard_pairquad(const float* Z, int32_t d, int32_t T, const int32_t* z_off
 
 /* Process-wide GEMM variant (development / A-B measurements; initialised from ADKF_GEMM_IMPL / ADKF_GEMM_CORR):
  *   impl   1 = one CTA per 128 x 128 tile (gemm_tf32x3.cu), 2 = CTA pairs on 256 x 128 tiles (gemm_pair.cu, default); other: keep
- *   corr16 0 = correction products in tf32, 1 = in bf16, 2 = bf16 for the backward operand forms (K,T) / (T,T) only (default;
- *          pair kernel only); other: keep
+ *   corr16 correction products of the pair kernel: 0 = tf32, 1 = bf16, 2 = tf32 forward / bf16 for the backward operand forms
+ *          (K,T) / (T,T), 3 = scaled fp16 forward / bf16 backward (default), 4 = scaled fp16 everywhere; other: keep.
+ *          Scaled fp16: lo parts x 2^11 as fp16, accumulator x 2^-11 -- as exact as tf32 corrections for operand magnitudes in
+ *          [6.1e-5, 65504]; elements outside that range lose their correction (TF32-class accuracy for them).
  * Returns the previous setting as impl | corr16 << 8.  Not thread-safe against concurrent launches.
  * NOTE: adkf_gemm_splitk_ws_floats depends on impl -- size workspaces after configuring. */
 int adkf_gemm_configure(int32_t impl, int32_t corr16);

@@ -138,21 +138,41 @@ def test_pna_fused_equals_three_kernel_chain(cuda_device, n_mol):
     gout = torch.randn(V, 1024, generator=gen)
     gi = ops.build_graph_index([torch.from_numpy(a).to(cuda_device) for a in b.adjacency_lists], V)
     assert gi.fused_ok and gi.max_degree <= 16
+    from adkf_ift_b200 import _cabi
+    lib = _cabi.load()
+    # the fused kernel issues tf32 correction products; the chain's forward GEMM is configured to do the same for the bit-for-bit
+    # comparison (its default, scaled-fp16 corrections, has the same accuracy but other bits: compared at 2e-6 below)
+    prev = lib.adkf_gemm_configure(2, 2)
+    try:
+        _fused_vs_chain(ops, cuda_device, gi, h, W, bias, gout, exact=True)
+    finally:
+        lib.adkf_gemm_configure(prev & 0xff, prev >> 8)
+    _fused_vs_chain(ops, cuda_device, gi, h, W, bias, gout, exact=False)
+    # host-known degree (the collation's value) takes the same path without the device read
+    gi2 = ops.build_graph_index([torch.from_numpy(a).to(cuda_device) for a in b.adjacency_lists], V, max_degree=gi.max_degree)
+    out1 = ops.multiaggr_message_passing(h.to(cuda_device), W.to(cuda_device), bias.to(cuda_device), gi, fused=True)
+    out2 = ops.multiaggr_message_passing(h.to(cuda_device), W.to(cuda_device), bias.to(cuda_device), gi2, fused=True)
+    assert torch.equal(out2, out1)
+
+
+def _fused_vs_chain(ops, cuda_device, gi, h, W, bias, gout, exact):
     res = {}
     for fused in (False, True):
         hc, Wc, bc = (x.to(cuda_device).requires_grad_(True) for x in (h, W, bias))
         out = ops.multiaggr_message_passing(hc, Wc, bc, gi, fused=fused)
         out.backward(gout.to(cuda_device))
         res[fused] = (out.detach(), hc.grad, Wc.grad, bc.grad)
-    assert torch.equal(res[True][0], res[False][0]), rel(res[True][0], res[False][0])
+    if exact:
+        assert torch.equal(res[True][0], res[False][0]), rel(res[True][0], res[False][0])
+    else:
+        # other forward bits: outputs agree to rounding; the gradients are not compared here because ONE flipped ReLU / arg-max
+        # decision of a near-tie in this random data moves a gradient entry by ~1e-2 -- they are compared above
+        assert rel(res[True][0], res[False][0]) < 5e-5     # (the pseudo-std sqrt(sum relu(m^2 - mean^2) + 1e-7) amplifies rounding where m^2 ~ mean^2)
+        return
     for name, gf, gu in zip(("dh", "dW", "db"), res[True][1:], res[False][1:]):
         e = rel(gf, gu)
         print("fused vs chain", name, e)
         assert e < 2e-6, (name, e)
-    # host-known degree (the collation's value) takes the same path without the device read
-    gi2 = ops.build_graph_index([torch.from_numpy(a).to(cuda_device) for a in b.adjacency_lists], V, max_degree=gi.max_degree)
-    out2 = ops.multiaggr_message_passing(h.to(cuda_device), W.to(cuda_device), bias.to(cuda_device), gi2, fused=True)
-    assert torch.equal(out2, res[True][0])
 
 
 def test_pna_fused_falls_back_on_high_degree(cuda_device):
@@ -333,5 +353,9 @@ def test_pna_scalers_folded_into_projection(cuda_device, n_mol):
         l2, l2u = rel_l2(c.grad, d.grad), rel_l2(u.grad, d.grad)
         print("folded bwd", name, "l2-rel", l2, "unfolded", l2u)
         assert l2 < max(1e-4, 4 * l2u)
-    out2 = ops.pna_message_passing_projected(*[c.detach() for c in cs], gi)
-    assert torch.equal(out2, out.detach())
+    # run-to-run bit stability of the training path (no float atomics) ...
+    out2 = ops.pna_message_passing_projected(*[c.detach().requires_grad_(True) for c in cs], gi)
+    assert torch.equal(out2.detach(), out.detach())
+    # ... and the no-gradient pass (fused message-passing kernel where the graph allows it) agrees with it to rounding
+    out3 = ops.pna_message_passing_projected(*[c.detach() for c in cs], gi)
+    assert rel(out3, out) < 5e-5
