@@ -132,6 +132,7 @@ struct GemmEpilogue {
     int gx, gy, ntiles;   // persistent tile walk: tile -> (bx = tile % gx, by = (tile / gx) % gy, bz = tile / (gx gy))
     const int32_t* gate;  // optional device word: the launch is a no-op when *gate == 0 (device-side jitter ladder of the blocked
                           // Cholesky: later attempts run only if the previous one failed, without a host round trip)
+    int tma_store;        // pair kernel: the output tile leaves through TMA bulk stores (see pair_store_tile_tma); else gemm_store_tile
     int debug;            // development probe (ADKF_GEMM_DEBUG): 1 = splitter skips the split (128 only A, 256 only B), 2 = no MMAs
     int a_mn, a_k, b_mn, b_k;
     int64_t d_off, bias_off;
@@ -305,4 +306,24 @@ static inline int num_sms() {
             n = 148;
     }
     return n;
+}
+
+// Output map of the TMA-store epilogue: D [rows, cols] fp32 with row stride ld, box 32 columns (128 B) x 32 rows, SWIZZLE_128B (the
+// layout of the warp-private staging tile).  Rows / columns past the extents are clipped by the hardware.
+static inline int make_out_map_2d(CUtensorMap* map, float* ptr, int64_t rows, int64_t cols, int64_t ld) {
+    EncodeTiledFn fn = encode_fn();
+    if (fn == nullptr) return (int)cudaErrorNotSupported;
+    if ((reinterpret_cast<uintptr_t>(ptr) & 15) || (ld * 4) % 16) return ADKF_ERR_BADARG;
+    const cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+    const cuuint64_t strides[1] = {(cuuint64_t)ld * 4};
+    const cuuint32_t box[2] = {32, 32};
+    const cuuint32_t estr[2] = {1, 1};
+    CUresult r = CUDA_SUCCESS;
+    for (int attempt = 0; attempt < 2; ++attempt) {
+        r = fn(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, ptr, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+               CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        if (r != CUDA_ERROR_INVALID_CONTEXT) break;
+        cudaFree(0);
+    }
+    return r == CUDA_SUCCESS ? 0 : -(1000 + (int)r);
 }

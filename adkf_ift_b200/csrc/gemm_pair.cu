@@ -45,18 +45,23 @@ constexpr int kBH = 64;                              // B rows held by one CTA
 // NS = number of split stages (B tiles in smem, A operand in TMEM).  NS = 2: hi.hi and the corrections in separate TMEM
 // accumulators (big[2] + small + 2 operand stages = 512 columns).  NS = 4: the corrections go to the hi.hi accumulator of their
 // drain group (big[2] + 4 operand stages): twice the pipeline depth for the cross-CTA hand-offs, one more rounding per product.
-constexpr int raw_depth(int NS) { return NS == 4 ? 5 : 6; }
+// Staging tiles per drain warp / raw ring depth by operand form: the (K,T) instantiation (input gradients -- the only form with
+// masked outputs) has two staging tiles per warp (TMA-fetched mask boxes, both passes in flight) and a 5-deep raw ring; the other
+// forms keep one staging tile and the 6-deep ring (A/B on one box, profiles/r2s_gemm_trace_*.txt: depth 5 costs the long-K forward
+// launches 4%, the masked TMA epilogue saves 1.9 ms per step).
+constexpr int stage_bufs(bool TA, bool TB) { return (!TA && TB) ? 2 : 1; }
+constexpr int raw_depth(int NS, int bufs) { return (NS == 4 || bufs == 2) ? 5 : 6; }
 constexpr int kBHalfBytes = kBH * kBK * 4;           // 8 KB
 constexpr int kRawBytes = kTileBytes + kBHalfBytes;  // A 16 KB + B half 8 KB
 constexpr int kSplitBytes = 2 * kBHalfBytes;         // B_hi 8 KB + B_cat (or B_lo) 8 KB
-constexpr int ring_bytes(int NS) { return raw_depth(NS) * kRawBytes + NS * kSplitBytes; }   // 144 + 32 KB | 120 + 64 KB
-constexpr int kStageBytes = 8 * 4096;
+constexpr int ring_bytes(int NS, int bufs) { return raw_depth(NS, bufs) * kRawBytes + NS * kSplitBytes; }   // 144 + 32 KB | 120 + 64 KB
+constexpr int stage_bytes(int bufs) { return 8 * bufs * 4096; }   // per drain warp `bufs` 32 x 32 fp32 staging tiles
 constexpr int kThreads = 640;
 constexpr int kTmemCols = 512;
 constexpr int kSmallCol = 2 * kBN;                   // NS = 2 only
 constexpr int aop_col(int NS) { return NS == 4 ? 2 * kBN : 3 * kBN; }   // A operand stages: 32 tf32 columns + 32 correction columns each
 constexpr int kGroup = 4;
-constexpr size_t smem_bytes(int NS) { return (size_t)ring_bytes(NS) + kStageBytes + 1024 + 256; }
+constexpr size_t smem_bytes(int NS, int bufs) { return (size_t)ring_bytes(NS, bufs) + stage_bytes(bufs) + 1024 + 512; }
 
 constexpr uint32_t kIdescTf32 = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(kBN >> 3) << 17) | ((uint32_t)(kPM >> 4) << 24);
 constexpr uint32_t kIdescBf16 = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(kBN >> 3) << 17) | ((uint32_t)(kPM >> 4) << 24);
@@ -250,6 +255,108 @@ __device__ __forceinline__ void split_b_half(const unsigned char* __restrict__ r
     }
 }
 
+// ---- TMA-store epilogue ------------------------------------------------------------------------------------------------------
+// The short-K launches of the step (message MLP K = 64, BOOM expand / input gradients K = 128) are EPILOGUE-bound: per-role cycle
+// counters (tools/gemm_pair_profile.py, profiles/r2r_gemm_pair_roles.txt) show the drain warps spending 80% of the kernel inside
+// gemm_store_tile (7.7k cycles per 128 x 128 tile: smem transpose, 16 LDS + 16 predicated STG per lane, address arithmetic) while
+// the MMA warp waits for the accumulators.  Here a warp writes its 32 x 32 sub-tile ONCE into its staging tile in the SWIZZLE_128B
+// layout (lane = row, the layout tcgen05.ld delivers; bias and activation applied on the way) and one lane hands it to the TMA
+// unit: cp.async.bulk.tensor store, rows / columns past the array clipped by the hardware.  No LDS, no STG, no per-element
+// predicates.  Used for mode-0 outputs with act 0 | 1 | 2 | 4 | 5, no split-K, N % 32 == 0 (host: gemm_launch).
+__device__ __forceinline__ void tma_store_2d(const CUtensorMap* map, uint32_t src, int c0, int c1) {
+    asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];"
+                 ::"l"(reinterpret_cast<uint64_t>(map)), "r"(src), "r"(c0), "r"(c1)
+                 : "memory");
+}
+__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait_read0() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait0() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+
+// Start of a tile for a drain warp (before it waits for the accumulator): the bulk stores of its previous tile have read both
+// staging tiles; for act 4 / 5 the 32 x 32 boxes of the activation-derivative mask (the saved output of the layer below) are
+// fetched by TMA into the staging tiles, where pair_store_tile_tma overwrites them in place with the result -- lane-per-row reads
+// of a row-major mask straight from global memory touch 32 lines per request (measured slower than the old epilogue).
+// Returns 1 when mask loads were issued (the caller keeps the phase of `mbar`).
+__device__ __forceinline__ int pair_tile_begin_tma(const GemmEpilogue& ep, const CUtensorMap* tmM, const int rowA0, const int rowB0,
+                                                   const int q, const int lane, const int colbase, const uint32_t stg_addr,
+                                                   const uint32_t mbar) {
+    const int row0 = rowA0 + q * 32;
+    const int col0 = rowB0 + colbase;
+    const int npass = (row0 < ep.M) ? min(2, max(0, (ep.N - col0 + 31) / 32)) : 0;
+    if (lane == 0) {
+        bulk_wait_read0();
+        if (ep.act >= 4 && npass > 0) {
+            mbar_expect_tx(mbar, (uint32_t)npass * 4096u);
+            for (int p = 0; p < npass; ++p) tma_load_2d(stg_addr + (uint32_t)p * 4096u, tmM, mbar, col0 + p * 32, row0);
+        }
+    }
+    __syncwarp();
+    return (ep.act >= 4 && npass > 0) ? 1 : 0;
+}
+
+// acc[j] = row rowA0 + q*32 + lane, column rowB0 + colbase + j of the batch's product; stg = this warp's two 4 KB staging tiles
+template <int BUFS>
+__device__ __forceinline__ void pair_store_tile_tma(const GemmEpilogue& ep, const CUtensorMap* tmO, const int rowA0, const int rowB0,
+                                                    const int batch, const float (&acc)[64], const int q, const int lane,
+                                                    const int colbase, float4* __restrict__ stg, const uint32_t stg_addr,
+                                                    const uint32_t mbar, const uint32_t mask_phase) {
+    const int row0 = rowA0 + q * 32;
+    if (row0 >= ep.M) return;                                   // (uniform over the warp)
+    const float* bias = (ep.bias != nullptr) ? ep.bias + (int64_t)batch * ep.bias_off : nullptr;
+    const int coff = (int)((int64_t)batch * ep.d_off);          // column-batched outputs only (host-checked)
+    const int act = ep.act;
+    if (act >= 4 && rowB0 + colbase < ep.N) mbar_wait(mbar, mask_phase);    // the mask boxes of this tile have landed
+#pragma unroll
+    for (int p = 0; p < 2; ++p) {
+        const int col = rowB0 + colbase + p * 32;
+        if (col >= ep.N) break;                                 // N % 32 == 0: a 32-column pass is all valid or all outside
+        float4* __restrict__ sp = stg + (BUFS == 2 ? p : 0) * 256;
+        if (BUFS == 1 && p == 1) { if (lane == 0) bulk_wait_read0(); __syncwarp(); }   // one staging tile: pass 0's store has read it
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            float4 x = make_float4(acc[p * 32 + 4 * j], acc[p * 32 + 4 * j + 1], acc[p * 32 + 4 * j + 2], acc[p * 32 + 4 * j + 3]);
+            if (bias != nullptr) {
+                const float4 b4 = __ldg(reinterpret_cast<const float4*>(bias + col) + j);     // (same address in every lane)
+                x.x += b4.x; x.y += b4.y; x.z += b4.z; x.w += b4.w;
+            }
+            if (act == 1) {
+                x.x = fmaxf(x.x, 0.f); x.y = fmaxf(x.y, 0.f); x.z = fmaxf(x.z, 0.f); x.w = fmaxf(x.w, 0.f);
+            } else if (act == 2) {
+                x.x = (x.x > 0.f) ? x.x : 0.01f * x.x; x.y = (x.y > 0.f) ? x.y : 0.01f * x.y;
+                x.z = (x.z > 0.f) ? x.z : 0.01f * x.z; x.w = (x.w > 0.f) ? x.w : 0.01f * x.w;
+            } else if (act >= 4) {                              // activation derivative of the layer below (its saved output)
+                const float neg = (act == 4) ? 0.f : 0.01f;
+                const float4 y = sp[lane * 8 + (j ^ (lane & 7))];
+                x.x *= (y.x > 0.f) ? 1.f : neg; x.y *= (y.y > 0.f) ? 1.f : neg;
+                x.z *= (y.z > 0.f) ? 1.f : neg; x.w *= (y.w > 0.f) ? 1.f : neg;
+            }
+            sp[lane * 8 + (j ^ (lane & 7))] = x;
+        }
+        fence_async_smem();                                     // generic-proxy writes -> visible to the TMA unit
+        __syncwarp();
+        if (lane == 0) {
+            tma_store_2d(tmO, stg_addr + (uint32_t)(BUFS == 2 ? p : 0) * 4096u, col + coff, row0);
+            bulk_commit();
+        }
+    }
+}
+
+// Development build (-DADKF_PAIR_PROFILE, ADKF_NVCC_EXTRA of build.py): per-CTA cycle counters of every warp role, read back with
+// adkf_gemm_pair_profile_read.  [cta][32]: 0-3 TMA (wait raw slot, total) | 4-7 MMA (wait acc, wait split stage, wait corr acc,
+// total) | 8-11 A splitter (wait raw, wait stage, work, total) | 12-15 B splitter (same) | 16-20 drain warp 12 (wait acc, drain,
+// epilogue, total, tiles)
+#ifdef ADKF_PAIR_PROFILE
+__device__ unsigned long long g_pair_prof[160 * 32];
+#define PROF_DECL(n) long long prof_[n] = {}; const long long prof_t0_ = clock64(); long long prof_c_ = prof_t0_
+#define PROF_LAP(i) do { const long long now_ = clock64(); prof_[i] += now_ - prof_c_; prof_c_ = now_; } while (0)
+#define PROF_OUT(base, n) do { if (lane == 0) { for (int q_ = 0; q_ < n; ++q_) g_pair_prof[blockIdx.x * 32 + base + q_] = (unsigned long long)prof_[q_]; \
+                                               g_pair_prof[blockIdx.x * 32 + base + n] = (unsigned long long)(clock64() - prof_t0_); } } while (0)
+#else
+#define PROF_DECL(n)
+#define PROF_LAP(i)
+#define PROF_OUT(base, n)
+#endif
+
 struct PairTile {
     int rowA0;             // first output row of THIS CTA's half (also its A rows)
     int rowB0;             // first output column of the tile
@@ -272,9 +379,11 @@ __device__ __forceinline__ PairTile pair_tile(const GemmEpilogue& ep, int tile, 
 
 template <bool TA, bool TB, int CORR16, int NS>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
-gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, GemmEpilogue ep) {
+gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                 const __grid_constant__ CUtensorMap tmO, const __grid_constant__ CUtensorMap tmM, GemmEpilogue ep) {
     if (ep.gate != nullptr && *ep.gate == 0) return;     // gated launch (uniform over the grid: nothing has been set up yet)
-    constexpr int kRaw = raw_depth(NS), kSplit = NS, kRingBytes = ring_bytes(NS), kAopCol = aop_col(NS);
+    constexpr int kBufs = stage_bufs(TA, TB), kStageBytes = stage_bytes(kBufs);
+    constexpr int kRaw = raw_depth(NS, kBufs), kSplit = NS, kRingBytes = ring_bytes(NS, kBufs), kAopCol = aop_col(NS);
     constexpr bool kMerged = NS == 4;
     extern __shared__ unsigned char smem_raw[];
     const uint32_t raw = smem_u32(smem_raw);
@@ -291,8 +400,9 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     auto accfull_bar = [&](int b) { return bars + 8u * (2 * kRaw + 2 * kSplit + b); };         // both (multicast commit)
     auto accempty_off = [&](int b) { return 8u * (2 * kRaw + 2 * kSplit + 2 + b); };           // LEADER
     auto tileempty_off = [&]() { return 8u * (2 * kRaw + 2 * kSplit + 4); };                   // LEADER
+    auto maskfull_bar = [&](int w) { return bars + 8u * (2 * kRaw + 2 * kSplit + 6 + w); };    // local, one per drain warp (TMA mask boxes)
     volatile uint32_t* tmem_slot =
-        reinterpret_cast<volatile uint32_t*>(base_ptr + kRingBytes + kStageBytes + 8 * (2 * kRaw + 2 * kSplit + 6));
+        reinterpret_cast<volatile uint32_t*>(base_ptr + kRingBytes + kStageBytes + 8 * (2 * kRaw + 2 * kSplit + 6 + 8));
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int rank = (int)cluster_rank();
@@ -314,6 +424,7 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             mbar_init(bars + accempty_off(b), 16);           // drain warps of both CTAs
         }
         if (!kMerged) mbar_init(bars + tileempty_off(), 16);
+        for (int w = 0; w < 8; ++w) mbar_init(maskfull_bar(w), 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 2) {
@@ -332,6 +443,7 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         // ===== TMA producer (own A rows, own half of the B rows) =====
         reg_dec<40>();
         if (lane == 0) {
+            PROF_DECL(2);
             uint32_t it = 0;
             for (int tile = pair_id; tile < ntiles; tile += npairs) {
                 const PairTile c = pair_tile(ep, tile, rank);
@@ -341,7 +453,9 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                     const int r = it % kRaw;
                     const uint32_t ph = (it / kRaw) & 1;
                     const int k = (c.kb0 + i) * kBK;
+                    PROF_LAP(1);
                     mbar_wait(rawempty_bar(r), ph ^ 1);
+                    PROF_LAP(0);
                     mbar_expect_tx(rawfull_bar(r), kRawBytes);
                     const uint32_t dst = base + r * kRawBytes;
                     if (TA) tma_load_2d(dst, &tmA, rawfull_bar(r), a_mn0, k + a_k0);
@@ -350,15 +464,19 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                     else    tma_load_2d(dst + kTileBytes, &tmB, rawfull_bar(r), k + b_k0, b_mn0);
                 }
             }
+            PROF_OUT(0, 2);
         }
     } else if (warp == 1) {
         // ===== MMA issuer: leader CTA only =====
         reg_dec<40>();
         if (rank == 0) {
             uint32_t it = 0, gc = 0, tl = 0;
+            PROF_DECL(4);
             for (int tile = pair_id; tile < ntiles; tile += npairs) {
                 const PairTile c = pair_tile(ep, tile, 0);
+                PROF_LAP(3);
                 if (!kMerged) mbar_wait_cluster(bars + tileempty_off(), (tl & 1) ^ 1);
+                PROF_LAP(2);
                 for (int i = 0; i < c.nk; ++i, ++it) {
                     const int s = it % kSplit;
                     const uint32_t ph = (it / kSplit) & 1;
@@ -366,8 +484,11 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                     const int b = g & 1;
                     const bool group_first = (i % kGroup) == 0;
                     const bool group_last = (i % kGroup) == kGroup - 1 || i == c.nk - 1;
+                    PROF_LAP(3);
                     if (group_first) mbar_wait_cluster(bars + accempty_off(b), ((g >> 1) & 1) ^ 1);
+                    PROF_LAP(0);
                     mbar_wait_cluster(bars + conv_off(s), ph);
+                    PROF_LAP(1);
                     tc_fence_after();
                     if (lane == 0) {
                         const uint32_t st = split_base + s * kSplitBytes;
@@ -396,6 +517,7 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                 gc += (uint32_t)((c.nk + kGroup - 1) / kGroup);
                 ++tl;
             }
+            PROF_OUT(3, 4);
         }
     } else if (warp < 4) {
         reg_dec<40>();
@@ -404,12 +526,16 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         const int t = threadIdx.x - 128;
         const uint32_t tmem_a = tmem_acc + ((uint32_t)((warp - 4) * 32) << 16) + (uint32_t)kAopCol;
         uint32_t it = 0;
+        PROF_DECL(3);
         for (int tile = pair_id; tile < ntiles; tile += npairs) {
             const PairTile c = pair_tile(ep, tile, rank);
             for (int i = 0; i < c.nk; ++i, ++it) {
                 const int r = it % kRaw, s = it % kSplit;
+                PROF_LAP(2);
                 mbar_wait(rawfull_bar(r), (it / kRaw) & 1);
+                PROF_LAP(0);
                 mbar_wait_cluster(empty_bar(s), ((it / kSplit) & 1) ^ 1);
+                PROF_LAP(1);
                 tc_fence_after();
                 split_rows_to_tmem<TA, CORR16>(base_ptr + (size_t)r * kRawBytes, tmem_a + (uint32_t)(s * 2 * kBK), t);
                 tc_fence_before();
@@ -420,17 +546,22 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                 }
             }
         }
+        if (warp == 4) PROF_OUT(8, 3);
     } else if (warp < 12) {
         // ===== B splitter (own 64 rows) =====
         reg_dec<72>();
         const int t = threadIdx.x - 256;
         uint32_t it = 0;
+        PROF_DECL(3);
         for (int tile = pair_id; tile < ntiles; tile += npairs) {
             const PairTile c = pair_tile(ep, tile, rank);
             for (int i = 0; i < c.nk; ++i, ++it) {
                 const int r = it % kRaw, s = it % kSplit;
+                PROF_LAP(2);
                 mbar_wait(rawfull_bar(r), (it / kRaw) & 1);
+                PROF_LAP(0);
                 mbar_wait_cluster(empty_bar(s), ((it / kSplit) & 1) ^ 1);
+                PROF_LAP(1);
                 unsigned char* st = split_ptr + (size_t)s * kSplitBytes;
                 split_b_half<TB, CORR16>(base_ptr + (size_t)r * kRawBytes + kTileBytes, st, st + kBHalfBytes, t);
                 fence_async_smem();
@@ -441,6 +572,7 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                 }
             }
         }
+        if (warp == 8) PROF_OUT(12, 3);
     } else {
         // ===== drain + epilogue of the own 128 x 128 half =====
         reg_inc<136>();
@@ -449,8 +581,16 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         const uint32_t trow = tmem_acc + ((uint32_t)(q * 32) << 16) + (uint32_t)(half * 64);
         const int colbase = half * 64;
         uint32_t gc = 0;
+        PROF_DECL(3);
+        const uint32_t stg_addr = base + (uint32_t)kRingBytes + (uint32_t)(warp - 12) * (uint32_t)(kBufs * 4096);
+        uint32_t mask_loads = 0;                                 // tiles of this warp for which mask boxes were fetched (barrier phase)
         for (int tile = pair_id; tile < ntiles; tile += npairs) {
             const PairTile c = pair_tile(ep, tile, rank);
+            uint32_t mask_phase = 0;
+            if (ep.tma_store) {
+                mask_phase = mask_loads & 1;
+                mask_loads += (uint32_t)pair_tile_begin_tma(ep, &tmM, c.rowA0, c.rowB0, q, lane, colbase, stg_addr, maskfull_bar(warp - 12));
+            }
             float acc[64];
 #pragma unroll
             for (int j = 0; j < 64; ++j) acc[j] = 0.f;
@@ -458,7 +598,9 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             for (int gl = 0; gl < ngroups; ++gl) {
                 const uint32_t g = gc + gl;
                 const int b = g & 1;
+                PROF_LAP(1);
                 mbar_wait_cluster(accfull_bar(b), (g >> 1) & 1);
+                PROF_LAP(0);
                 tc_fence_after();
 #pragma unroll
                 for (int c0 = 0; c0 < ((ep.debug & 32) ? 0 : 64); c0 += 16) {     // bit 5: no TMEM drains
@@ -484,11 +626,20 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                 if (lane == 0) mbar_arrive_cluster(leader_bars + tileempty_off());
             }
             gc += (uint32_t)ngroups;
+            PROF_LAP(1);
             if (ep.debug & 64) continue;                                       // bit 6: no epilogue
-            gemm_store_tile(ep, c.rowA0, c.rowB0, c.zslab, c.batch, acc, q, lane, colbase,
-                            reinterpret_cast<float4*>(stage_ptr + (size_t)(warp - 12) * 4096));
+            if (ep.tma_store)
+                pair_store_tile_tma<kBufs>(ep, &tmO, c.rowA0, c.rowB0, c.batch, acc, q, lane, colbase,
+                                    reinterpret_cast<float4*>(stage_ptr + (size_t)(warp - 12) * (kBufs * 4096)), stg_addr, maskfull_bar(warp - 12),
+                                    mask_phase);
+            else
+                gemm_store_tile(ep, c.rowA0, c.rowB0, c.zslab, c.batch, acc, q, lane, colbase,
+                                reinterpret_cast<float4*>(stage_ptr + (size_t)(warp - 12) * (kBufs * 4096)));
+            PROF_LAP(2);
         }
+        if (ep.tma_store && lane == 0) bulk_wait0();            // the bulk stores of this warp are complete before the CTA exits
         tc_fence_before();
+        if (warp == 12) PROF_OUT(16, 3);
     }
 
     __syncthreads();
@@ -500,24 +651,25 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
 }
 
 template <bool TA, bool TB, int C16, int NS>
-static int pair_launch_t(dim3 grid, cudaStream_t s, const CUtensorMap& ma, const CUtensorMap& mb, const GemmEpilogue& ep) {
+static int pair_launch_t(dim3 grid, cudaStream_t s, const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& mo, const CUtensorMap& mm, const GemmEpilogue& ep) {
     static bool done = false;
     if (!done) {
         cudaError_t e = cudaFuncSetAttribute((const void*)gemm_pair_kernel<TA, TB, C16, NS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                             (int)smem_bytes(NS));
+                                             (int)smem_bytes(NS, stage_bufs(TA, TB)));
         if (e != cudaSuccess) return (int)e;
         done = true;
     }
-    gemm_pair_kernel<TA, TB, C16, NS><<<grid, kThreads, smem_bytes(NS), s>>>(ma, mb, ep);
+    gemm_pair_kernel<TA, TB, C16, NS><<<grid, kThreads, smem_bytes(NS, stage_bufs(TA, TB)), s>>>(ma, mb, mo, mm, ep);
     return 0;
 }
 
 template <bool TA, bool TB>
-static int pair_launch_f(int c16, bool merged, dim3 grid, cudaStream_t s, const CUtensorMap& ma, const CUtensorMap& mb, const GemmEpilogue& ep) {
+static int pair_launch_f(int c16, bool merged, dim3 grid, cudaStream_t s, const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& mo,
+                         const CUtensorMap& mm, const GemmEpilogue& ep) {
     if (merged && c16 != 2)     // (the merged accumulator cannot carry the 2^11 scale of the fp16 corrections)
-        return c16 ? pair_launch_t<TA, TB, 1, 4>(grid, s, ma, mb, ep) : pair_launch_t<TA, TB, 0, 4>(grid, s, ma, mb, ep);
-    if (c16 == 2) return pair_launch_t<TA, TB, 2, 2>(grid, s, ma, mb, ep);
-    return c16 ? pair_launch_t<TA, TB, 1, 2>(grid, s, ma, mb, ep) : pair_launch_t<TA, TB, 0, 2>(grid, s, ma, mb, ep);
+        return c16 ? pair_launch_t<TA, TB, 1, 4>(grid, s, ma, mb, mo, mm, ep) : pair_launch_t<TA, TB, 0, 4>(grid, s, ma, mb, mo, mm, ep);
+    if (c16 == 2) return pair_launch_t<TA, TB, 2, 2>(grid, s, ma, mb, mo, mm, ep);
+    return c16 ? pair_launch_t<TA, TB, 1, 2>(grid, s, ma, mb, mo, mm, ep) : pair_launch_t<TA, TB, 0, 2>(grid, s, ma, mb, mo, mm, ep);
 }
 
 }  // namespace pr
@@ -525,7 +677,8 @@ static int pair_launch_f(int c16, bool merged, dim3 grid, cudaStream_t s, const 
 extern int g_gemm_corr16;
 
 // Launch on CTA pairs.  ep: mode 0 with gx = ceil(N/128), gy = ceil(M/256), ntiles = gx gy splits batch already set.
-int gemm_pair_launch(const CUtensorMap& ma, const CUtensorMap& mb, const GemmEpilogue& ep, int transA, int transB, cudaStream_t s) {
+int gemm_pair_launch(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& mo, const CUtensorMap& mm, const GemmEpilogue& ep,
+                     int transA, int transB, cudaStream_t s) {
     // 0: tf32 corrections everywhere; 1: bf16 everywhere; 2 (default): bf16 for the BACKWARD forms only -- (K,T) input gradients
     // (plain and masked) and (T,T) weight gradients.  The forward (K,K) products keep tf32 corrections: a 4x larger forward
     // rounding error (1e-6 instead of 3e-7) flips more ReLU / arg-max decisions of the extractor, and a single flip near the top
@@ -541,9 +694,21 @@ int gemm_pair_launch(const CUtensorMap& ma, const CUtensorMap& mb, const GemmEpi
     static const int merged = getenv("ADKF_GEMM_MERGE") ? atoi(getenv("ADKF_GEMM_MERGE")) : 0;   // development switch (A/B runs)
     const int pairs = std::max(1, num_sms() / 2);
     dim3 grid((unsigned)(2 * std::min(ep.ntiles, pairs)));
-    if (!transA && !transB) return pr::pair_launch_f<false, false>(corr16, merged != 0, grid, s, ma, mb, ep);
-    if (!transA && transB) return pr::pair_launch_f<false, true>(corr16, merged != 0, grid, s, ma, mb, ep);
-    return pr::pair_launch_f<true, true>(corr16, merged != 0, grid, s, ma, mb, ep);
+    if (!transA && !transB) return pr::pair_launch_f<false, false>(corr16, merged != 0, grid, s, ma, mb, mo, mm, ep);
+    if (!transA && transB) return pr::pair_launch_f<false, true>(corr16, merged != 0, grid, s, ma, mb, mo, mm, ep);
+    return pr::pair_launch_f<true, true>(corr16, merged != 0, grid, s, ma, mb, mo, mm, ep);
 }
 
 }  // namespace adkf
+
+#ifdef ADKF_PAIR_PROFILE
+extern "C" int adkf_gemm_pair_profile_read(unsigned long long* host_buf /*[160*32]*/, int clear) {
+    cudaError_t e = cudaDeviceSynchronize();
+    if (e == cudaSuccess) e = cudaMemcpyFromSymbol(host_buf, adkf::pr::g_pair_prof, sizeof(unsigned long long) * 160 * 32);
+    if (e == cudaSuccess && clear) {
+        static unsigned long long zeros[160 * 32] = {};
+        e = cudaMemcpyToSymbol(adkf::pr::g_pair_prof, zeros, sizeof(zeros));
+    }
+    return (int)e;
+}
+#endif

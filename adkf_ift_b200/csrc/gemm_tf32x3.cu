@@ -514,7 +514,8 @@ static int plan_splits_tiles(int64_t tiles, int nk, int workers = 148) {
 // CTA pairs (gemm_pair.cu, 256 x 128 tiles, 74 workers) take every mode-0 product with more than one 128-row tile;
 // ADKF_GEMM_IMPL=1 forces the one-CTA kernel (A/B measurements).
 namespace adkf {
-int gemm_pair_launch(const CUtensorMap& ma, const CUtensorMap& mb, const GemmEpilogue& ep, int transA, int transB, cudaStream_t s);
+int gemm_pair_launch(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& mo, const CUtensorMap& mm, const GemmEpilogue& ep,
+                     int transA, int transB, cudaStream_t s);
 }
 namespace adkf {
 int g_gemm_impl = getenv("ADKF_GEMM_IMPL") ? atoi(getenv("ADKF_GEMM_IMPL")) : 2;          // 1: one CTA per tile, 2: CTA pairs
@@ -595,7 +596,19 @@ static int gemm_launch(const float* A, int transA, int64_t lda, int64_t a_slow, 
     ep.ntiles = (int)ntiles64;
     dim3 grid((unsigned)std::min<int64_t>(ntiles64, num_sms()));
     if (pair) {
-        if ((rc = gemm_pair_launch(ma, mb, ep, transA, transB, s))) return rc;
+        // TMA-store epilogue (gemm_pair.cu): plain / bias / activation outputs without split-K whose 32-column passes are all-in or
+        // all-out (N % 32 == 0), column-batched at most; everything else (D -= .., split-K slabs, odd widths) keeps gemm_store_tile
+        static const int tma_env = getenv("ADKF_GEMM_TMA_STORE") ? atoi(getenv("ADKF_GEMM_TMA_STORE")) : 1;
+        CUtensorMap mo = ma, mm = ma;
+        const bool bias_ok = bias == nullptr || ((reinterpret_cast<uintptr_t>(bias) & 15) == 0 && bias_off % 4 == 0);
+        const bool mask_ok = act < 4 || (!transA && transB && mask != nullptr && ldm % 4 == 0 && (reinterpret_cast<uintptr_t>(mask) & 15) == 0);
+        if (tma_env && act >= 0 && act != 3 && act <= 5 && splits == 1 && N % 32 == 0 && bias_ok && mask_ok &&
+            (int64_t)(batch - 1) * d_off + N <= ldd && M < 0x7fffffff) {
+            if (make_out_map_2d(&mo, D, M, ldd, ldd) == 0 &&
+                (act < 4 || make_out_map_2d(&mm, const_cast<float*>(mask), M, N, ldm) == 0))
+                ep.tma_store = 1;
+        }
+        if ((rc = gemm_pair_launch(ma, mb, mo, mm, ep, transA, transB, s))) return rc;
     } else if (!transA && !transB) {
         if ((rc = gemm_attr<false, false>())) return rc;
         gemm_tf32x3_kernel<false, false><<<grid, kGemmThreads, kGemmSmem, s>>>(ma, mb, ep);
