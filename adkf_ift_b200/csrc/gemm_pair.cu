@@ -121,6 +121,37 @@ __device__ __forceinline__ void umma2_commit(uint32_t bar) {
                  ::"r"(bar), "h"((uint16_t)3)
                  : "memory");
 }
+// The same three instructions issued by ONE elected lane of a CONVERGED warp (elect.sync inside the statement).  Under
+// `if (lane == 0)` ptxas cannot prove the issuing thread unique and wraps every tcgen05.mma in an ELECT + vote + branch loop with
+// its operands moved to uniform registers one by one: the per-role counters (tools/gemm_pair_profile.py) showed the MMA warp ~900
+// cycles per k-block inside the issue section for 8 MMAs whose tensor-pipe time is 512 cycles -- the issue, not the pipe, paced
+// the long-K launches (tensor pipe 48% active in ncu).
+__device__ __forceinline__ void umma2_tf32_ts_e(uint32_t tmem_d, uint32_t tmem_a, uint64_t bdesc, uint32_t idesc, uint32_t acc) {
+    asm volatile(
+        "{\n\t.reg .pred p, q;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "elect.sync _|q, 0xffffffff;\n\t"
+        "@q tcgen05.mma.cta_group::2.kind::tf32 [%0], [%1], %2, %3, p;\n\t}"
+        ::"r"(tmem_d), "r"(tmem_a), "l"(bdesc), "r"(idesc), "r"(acc)
+        : "memory");
+}
+__device__ __forceinline__ void umma2_bf16_ts_e(uint32_t tmem_d, uint32_t tmem_a, uint64_t bdesc, uint32_t idesc, uint32_t acc) {
+    asm volatile(
+        "{\n\t.reg .pred p, q;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "elect.sync _|q, 0xffffffff;\n\t"
+        "@q tcgen05.mma.cta_group::2.kind::f16 [%0], [%1], %2, %3, p;\n\t}"
+        ::"r"(tmem_d), "r"(tmem_a), "l"(bdesc), "r"(idesc), "r"(acc)
+        : "memory");
+}
+__device__ __forceinline__ void umma2_commit_e(uint32_t bar) {
+    asm volatile(
+        "{\n\t.reg .pred q;\n\t"
+        "elect.sync _|q, 0xffffffff;\n\t"
+        "@q tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;\n\t}"
+        ::"r"(bar), "h"((uint16_t)3)
+        : "memory");
+}
 __device__ __forceinline__ uint32_t pack_bf16(float lo_k, float hi_k) {   // element k in the low half, k+1 in the high half
     const __nv_bfloat162 v = __floats2bfloat162_rn(lo_k, hi_k);
     return *reinterpret_cast<const uint32_t*>(&v);
@@ -490,7 +521,7 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                     mbar_wait_cluster(bars + conv_off(s), ph);
                     PROF_LAP(1);
                     tc_fence_after();
-                    if (lane == 0) {
+                    {                                            // every lane runs this; one elected lane issues (see umma2_*_e)
                         const uint32_t st = split_base + s * kSplitBytes;
                         const uint64_t b_hi = smem_desc_k128(st), b_co = smem_desc_k128(st + kBHalfBytes);
                         const uint32_t a_hi = tmem_acc + (uint32_t)(kAopCol + s * 2 * kBK), a_co = a_hi + kBK;
@@ -500,17 +531,17 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                         for (int k = 0; k < ((ep.debug & 2) ? 0 : kBK / 8); ++k) {   // ADKF_GEMM_DEBUG bit 1: no MMAs (development probe)
                             const uint64_t adv = (uint64_t)(2 * k);          // 32 bytes of K per MMA (8 tf32 | 16 bf16)
                             const uint32_t ak = (uint32_t)(8 * k);           // 8 TMEM columns per MMA
-                            umma2_tf32_ts(acc_big, a_hi + ak, b_hi + adv, kIdescTf32, (group_first && k == 0) ? 0u : 1u);
+                            umma2_tf32_ts_e(acc_big, a_hi + ak, b_hi + adv, kIdescTf32, (group_first && k == 0) ? 0u : 1u);
                             if (CORR16) {
                                 // [lo | hi] (A, bf16) x [hi | lo] (B, bf16): k-steps 0,1 = lo.hi, 2,3 = hi.lo
-                                umma2_bf16_ts(acc_small, a_co + ak, b_co + adv, CORR16 == 2 ? kIdescF16 : kIdescBf16, (kMerged || (i | k)) ? 1u : 0u);
+                                umma2_bf16_ts_e(acc_small, a_co + ak, b_co + adv, CORR16 == 2 ? kIdescF16 : kIdescBf16, (kMerged || (i | k)) ? 1u : 0u);
                             } else {
-                                umma2_tf32_ts(acc_small, a_co + ak, b_hi + adv, kIdescTf32, (kMerged || (i | k)) ? 1u : 0u);   // lo.hi
-                                umma2_tf32_ts(acc_small, a_hi + ak, b_co + adv, kIdescTf32, 1u);                   // hi.lo
+                                umma2_tf32_ts_e(acc_small, a_co + ak, b_hi + adv, kIdescTf32, (kMerged || (i | k)) ? 1u : 0u);   // lo.hi
+                                umma2_tf32_ts_e(acc_small, a_hi + ak, b_co + adv, kIdescTf32, 1u);                   // hi.lo
                             }
                         }
-                        umma2_commit(empty_bar(s));
-                        if (group_last) umma2_commit(accfull_bar(b));
+                        umma2_commit_e(empty_bar(s));
+                        if (group_last) umma2_commit_e(accfull_bar(b));
                     }
                     __syncwarp();
                 }

@@ -302,7 +302,7 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
                 if (group_first) mbar_wait(accempty_bar(b), ((g >> 1) & 1) ^ 1);   // drained two groups ago
                 mbar_wait(conv_bar(s), ph);
                 tc_fence_after();
-                if (lane == 0) {
+                {                                                // every lane runs this; one elected lane issues (umma_*_e)
                     const uint32_t st = split_base + s * kSplitBytes;
                     const uint64_t b_hi = smem_desc_k128(st), b_lo = smem_desc_k128(st + kTileBytes);
                     const uint32_t a_hi = tmem_acc + (uint32_t)(kAopCol + s * 2 * kBK), a_lo = a_hi + kBK;
@@ -311,12 +311,12 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
                     for (int k = 0; k < ((ep.debug & 2) ? 0 : kBK / 8); ++k) {   // UMMA_K = 8 tf32: 8 TMEM columns of A, 32 B of B
                         const uint64_t adv = (uint64_t)(2 * k);                  // (+2 in the descriptor's address field)
                         const uint32_t ak = (uint32_t)(8 * k);
-                        umma_tf32_ts(acc_small, a_lo + ak, b_hi + adv, kIdescTf32, (i | k) ? 1u : 0u);
-                        umma_tf32_ts(acc_small, a_hi + ak, b_lo + adv, kIdescTf32, 1u);
-                        umma_tf32_ts(acc_big, a_hi + ak, b_hi + adv, kIdescTf32, (group_first && k == 0) ? 0u : 1u);
+                        umma_tf32_ts_e(acc_small, a_lo + ak, b_hi + adv, kIdescTf32, (i | k) ? 1u : 0u);
+                        umma_tf32_ts_e(acc_small, a_hi + ak, b_lo + adv, kIdescTf32, 1u);
+                        umma_tf32_ts_e(acc_big, a_hi + ak, b_hi + adv, kIdescTf32, (group_first && k == 0) ? 0u : 1u);
                     }
-                    umma_commit(empty_bar(s));                             // frees the split stage when these MMAs retire
-                    if (group_last) umma_commit(accfull_bar(b));
+                    umma_commit_e(empty_bar(s));                             // frees the split stage when these MMAs retire
+                    if (group_last) umma_commit_e(accfull_bar(b));
                 }
                 __syncwarp();
             }
