@@ -64,6 +64,9 @@ SIGNATURES = {
     "adkf_linear_tf32x3": ([_P, c_int64, c_int32, c_int64, _P, c_int32, c_int64, _P, c_int32, _P, c_int64, _P], ctypes.c_int),
     "adkf_gemm_tf32x3": ([_P, c_int32, c_int64, _P, c_int32, c_int64, c_int64, c_int32, c_int32, _P, c_int32, _P, c_int64,
                           _P, c_int64, _P], ctypes.c_int),
+    "adkf_gemm_presplit": ([_P, c_int64, c_int32, c_int64, c_int32, _P, _P, _P], ctypes.c_int),
+    "adkf_gemm_tf32x3_pre": ([_P, c_int64, _P, _P, c_int32, c_int64, c_int32, c_int32, _P, c_int32, _P, c_int64, c_int32, _P, c_int64, _P],
+                             ctypes.c_int),
     "adkf_gemm_tf32x3_masked": ([_P, c_int32, c_int64, _P, c_int32, c_int64, c_int64, c_int32, c_int32, _P, c_int64, c_int32, _P,
                                  c_int64, _P], ctypes.c_int),
     "adkf_gemm_tf32x3_batched": ([_P, c_int32, c_int64, c_int64, c_int64, c_int32, c_int32, _P, c_int32, c_int64, c_int64, c_int64,

@@ -213,6 +213,68 @@ __device__ __forceinline__ void split_rows_to_tmem(const unsigned char* __restri
     tmem_st_wait();
 }
 
+// N consecutive TMEM columns of this thread's lane from N registers (N a multiple of 4, <= 32): tcgen05.st x16 / x8 / x4 pieces
+template <int N>
+__device__ __forceinline__ void tmem_st_cols(uint32_t taddr, const uint32_t* r) {
+    if constexpr (N >= 16) {
+        asm volatile(
+            "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16};"
+            ::"r"(taddr), "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]), "r"(r[8]), "r"(r[9]),
+              "r"(r[10]), "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15])
+            : "memory");
+        tmem_st_cols<N - 16>(taddr + 16, r + 16);
+    } else if constexpr (N >= 8) {
+        asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};"
+                     ::"r"(taddr), "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7])
+                     : "memory");
+        tmem_st_cols<N - 8>(taddr + 8, r + 8);
+    } else if constexpr (N >= 4) {
+        asm volatile("tcgen05.st.sync.aligned.32x32b.x4.b32 [%0], {%1,%2,%3,%4};" ::"r"(taddr), "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3])
+                     : "memory");
+        tmem_st_cols<N - 4>(taddr + 4, r + 4);
+    }
+}
+
+// The k range [K0, K0 + NK) of row t of the raw A tile -> its columns of the operand stage (layout of split_rows_to_tmem).  Used by
+// the pre-split-B variant, where the B-splitter warps have no B tile to split and take half of the A rows' k columns (same TMEM
+// lane quarters as the A-splitter warps).  NK and K0 are multiples of 8; no tcgen05.wait here (the caller waits once).
+template <bool TR, int CORR16, int K0, int NK>
+__device__ __forceinline__ void split_rows_part_to_tmem(const unsigned char* __restrict__ raw, uint32_t taddr, int t) {
+    float x[NK];
+    if (!TR) {
+        const float4* __restrict__ r4 = reinterpret_cast<const float4*>(raw) + t * 8;
+#pragma unroll
+        for (int j = 0; j < NK / 4; ++j) {
+            const float4 v = r4[(K0 / 4 + j) ^ (t & 7)];
+            x[4 * j] = v.x; x[4 * j + 1] = v.y; x[4 * j + 2] = v.z; x[4 * j + 3] = v.w;
+        }
+    } else {
+        const float* __restrict__ rf = reinterpret_cast<const float*>(raw) + t;
+#pragma unroll
+        for (int k = 0; k < NK; ++k) x[k] = rf[(K0 + k) * kBM];
+    }
+    uint32_t hi[NK];
+#pragma unroll
+    for (int k = 0; k < NK; ++k) hi[k] = __float_as_uint(tf32_hi(x[k]));
+    tmem_st_cols<NK>(taddr + K0, hi);
+    if (CORR16) {
+        uint32_t cl[NK / 2], ch[NK / 2];
+#pragma unroll
+        for (int c = 0; c < NK / 2; ++c) {
+            const float h0 = __uint_as_float(hi[2 * c]), h1 = __uint_as_float(hi[2 * c + 1]);
+            cl[c] = pack_corr_lo<CORR16>(x[2 * c] - h0, x[2 * c + 1] - h1);
+            ch[c] = pack_corr_hi<CORR16>(h0, h1);
+        }
+        tmem_st_cols<NK / 2>(taddr + kBK + K0 / 2, cl);
+        tmem_st_cols<NK / 2>(taddr + kBK + kBK / 2 + K0 / 2, ch);
+    } else {
+        uint32_t lo[NK];
+#pragma unroll
+        for (int k = 0; k < NK; ++k) lo[k] = __float_as_uint(x[k] - __uint_as_float(hi[k]));
+        tmem_st_cols<NK>(taddr + kBK + K0, lo);
+    }
+}
+
 // ---- B operand: raw half tile (64 rows x 32 k) -> B_hi (tf32) and the correction tile, K-major SWIZZLE_128B -------------------
 //   row r of a tile = 128 B, logical 16 B chunk j at physical chunk j ^ (r & 7)
 //   CORR16: correction tile row = [bf16 hi k0..31 | bf16 lo k0..31]  (chunks 0-3 hi, 4-7 lo)      else: lo as tf32
@@ -408,20 +470,37 @@ __device__ __forceinline__ PairTile pair_tile(const GemmEpilogue& ep, int tile, 
     return c;
 }
 
-template <bool TA, bool TB, int CORR16, int NS>
+// PRE: the B operand arrives PRE-SPLIT (adkf_gemm_presplit: the weight's tf32 `hi` image through tmB, its [hi | lo] 16-bit image
+// through tmC, both K-major): warp 3 TMA-loads the two 8 KB half tiles straight into a 4-deep ring of B stages, the B-splitter
+// warps split k 16..31 of the A rows instead (the A-splitter warps k 0..15) and relay "B stage landed" to the leader.  Forward and
+// input-gradient products only (B = a weight matrix, re-split by every one of the ~1000 M-tiles otherwise); TA = TB = false.
+template <bool TA, bool TB, int NS, bool PRE> struct PairCfg {
+    static constexpr int kBufs = PRE ? 2 : stage_bufs(TA, TB);
+    static constexpr int kRawSlot = PRE ? kTileBytes : kRawBytes;          // PRE: the raw ring holds A tiles only
+    static constexpr int kRaw = PRE ? 5 : raw_depth(NS, kBufs);
+    static constexpr int kBSt = PRE ? 4 : NS;                             // B stages in shared memory (non-PRE: one per A stage)
+    static constexpr int kRingBytes = kRaw * kRawSlot + kBSt * kSplitBytes;
+    static constexpr int kStageBytes = stage_bytes(kBufs);
+    static constexpr size_t kSmem = (size_t)kRingBytes + kStageBytes + 1024 + 512;
+};
+
+template <bool TA, bool TB, int CORR16, int NS, bool PRE>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
 gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-                 const __grid_constant__ CUtensorMap tmO, const __grid_constant__ CUtensorMap tmM, GemmEpilogue ep) {
+                 const __grid_constant__ CUtensorMap tmC, const __grid_constant__ CUtensorMap tmO,
+                 const __grid_constant__ CUtensorMap tmM, GemmEpilogue ep) {
     if (ep.gate != nullptr && *ep.gate == 0) return;     // gated launch (uniform over the grid: nothing has been set up yet)
-    constexpr int kBufs = stage_bufs(TA, TB), kStageBytes = stage_bytes(kBufs);
-    constexpr int kRaw = raw_depth(NS, kBufs), kSplit = NS, kRingBytes = ring_bytes(NS, kBufs), kAopCol = aop_col(NS);
+    using Cfg = PairCfg<TA, TB, NS, PRE>;
+    constexpr int kBufs = Cfg::kBufs, kStageBytes = Cfg::kStageBytes, kRawSlot = Cfg::kRawSlot, kBSt = Cfg::kBSt;
+    constexpr int kRaw = Cfg::kRaw, kSplit = NS, kRingBytes = Cfg::kRingBytes, kAopCol = aop_col(NS);
     constexpr bool kMerged = NS == 4;
+    static_assert(!PRE || (!TA && !TB && NS == 2 && CORR16 != 0), "pre-split B: forward operand forms, 16-bit corrections");
     extern __shared__ unsigned char smem_raw[];
     const uint32_t raw = smem_u32(smem_raw);
     const uint32_t base = (raw + 1023u) & ~1023u;
     unsigned char* base_ptr = smem_raw + (base - raw);
-    const uint32_t split_base = base + kRaw * kRawBytes;
-    unsigned char* split_ptr = base_ptr + kRaw * kRawBytes;
+    const uint32_t split_base = base + kRaw * kRawSlot;
+    unsigned char* split_ptr = base_ptr + kRaw * kRawSlot;
     const uint32_t bars = base + kRingBytes + kStageBytes;
     unsigned char* stage_ptr = base_ptr + kRingBytes;
     auto rawfull_bar = [&](int r) { return bars + 8u * r; };                                   // local
@@ -432,8 +511,10 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     auto accempty_off = [&](int b) { return 8u * (2 * kRaw + 2 * kSplit + 2 + b); };           // LEADER
     auto tileempty_off = [&]() { return 8u * (2 * kRaw + 2 * kSplit + 4); };                   // LEADER
     auto maskfull_bar = [&](int w) { return bars + 8u * (2 * kRaw + 2 * kSplit + 6 + w); };    // local, one per drain warp (TMA mask boxes)
+    auto bfull_bar = [&](int sb) { return bars + 8u * (2 * kRaw + 2 * kSplit + 14 + sb); };    // PRE: local, TMA bytes of B stage sb
+    auto bempty_bar = [&](int sb) { return bars + 8u * (2 * kRaw + 2 * kSplit + 18 + sb); };   // PRE: both (multicast commit)
     volatile uint32_t* tmem_slot =
-        reinterpret_cast<volatile uint32_t*>(base_ptr + kRingBytes + kStageBytes + 8 * (2 * kRaw + 2 * kSplit + 6 + 8));
+        reinterpret_cast<volatile uint32_t*>(base_ptr + kRingBytes + kStageBytes + 8 * (2 * kRaw + 2 * kSplit + 22));
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int rank = (int)cluster_rank();
@@ -456,6 +537,7 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         }
         if (!kMerged) mbar_init(bars + tileempty_off(), 16);
         for (int w = 0; w < 8; ++w) mbar_init(maskfull_bar(w), 1);
+        for (int sb = 0; sb < 4; ++sb) { mbar_init(bfull_bar(sb), 1); mbar_init(bempty_bar(sb), 1); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 2) {
@@ -487,12 +569,14 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                     PROF_LAP(1);
                     mbar_wait(rawempty_bar(r), ph ^ 1);
                     PROF_LAP(0);
-                    mbar_expect_tx(rawfull_bar(r), kRawBytes);
-                    const uint32_t dst = base + r * kRawBytes;
+                    mbar_expect_tx(rawfull_bar(r), kRawSlot);
+                    const uint32_t dst = base + r * kRawSlot;
                     if (TA) tma_load_2d(dst, &tmA, rawfull_bar(r), a_mn0, k + a_k0);
                     else    tma_load_2d(dst, &tmA, rawfull_bar(r), k + a_k0, a_mn0);
-                    if (TB) tma_load_2d(dst + kTileBytes, &tmB, rawfull_bar(r), b_mn0, k + b_k0);
-                    else    tma_load_2d(dst + kTileBytes, &tmB, rawfull_bar(r), k + b_k0, b_mn0);
+                    if (!PRE) {
+                        if (TB) tma_load_2d(dst + kTileBytes, &tmB, rawfull_bar(r), b_mn0, k + b_k0);
+                        else    tma_load_2d(dst + kTileBytes, &tmB, rawfull_bar(r), k + b_k0, b_mn0);
+                    }
                 }
             }
             PROF_OUT(0, 2);
@@ -522,7 +606,8 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                     PROF_LAP(1);
                     tc_fence_after();
                     {                                            // every lane runs this; one elected lane issues (see umma2_*_e)
-                        const uint32_t st = split_base + s * kSplitBytes;
+                        const int sb = PRE ? (int)(it % kBSt) : s;
+                        const uint32_t st = split_base + sb * kSplitBytes;
                         const uint64_t b_hi = smem_desc_k128(st), b_co = smem_desc_k128(st + kBHalfBytes);
                         const uint32_t a_hi = tmem_acc + (uint32_t)(kAopCol + s * 2 * kBK), a_co = a_hi + kBK;
                         const uint32_t acc_big = tmem_acc + (uint32_t)(b * kBN);
@@ -541,6 +626,7 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                             }
                         }
                         umma2_commit_e(empty_bar(s));
+                        if (PRE) umma2_commit_e(bempty_bar(sb));
                         if (group_last) umma2_commit_e(accfull_bar(b));
                     }
                     __syncwarp();
@@ -552,6 +638,23 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         }
     } else if (warp < 4) {
         reg_dec<40>();
+        if (PRE && warp == 3 && lane == 0) {
+            // ===== B producer (pre-split images): own half of the B rows of each k-block -> B stage ring =====
+            uint32_t it = 0;
+            for (int tile = pair_id; tile < ntiles; tile += npairs) {
+                const PairTile c = pair_tile(ep, tile, rank);
+                const int b_mn0 = c.rowB0 + rank * kBH + c.batch * ep.b_mn, b_k0 = c.batch * ep.b_k;
+                for (int i = 0; i < c.nk; ++i, ++it) {
+                    const int sb = (int)(it % kBSt);
+                    const int k = (c.kb0 + i) * kBK;
+                    mbar_wait_cluster(bempty_bar(sb), ((it / kBSt) & 1) ^ 1);
+                    mbar_expect_tx(bfull_bar(sb), kSplitBytes);
+                    const uint32_t dst = split_base + sb * kSplitBytes;
+                    tma_load_2d(dst, &tmB, bfull_bar(sb), k + b_k0, b_mn0);
+                    tma_load_2d(dst + kBHalfBytes, &tmC, bfull_bar(sb), k + b_k0, b_mn0);
+                }
+            }
+        }
     } else if (warp < 8) {
         // ===== A splitter =====
         const int t = threadIdx.x - 128;
@@ -568,7 +671,12 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                 mbar_wait_cluster(empty_bar(s), ((it / kSplit) & 1) ^ 1);
                 PROF_LAP(1);
                 tc_fence_after();
-                split_rows_to_tmem<TA, CORR16>(base_ptr + (size_t)r * kRawBytes, tmem_a + (uint32_t)(s * 2 * kBK), t);
+                if (PRE) {
+                    split_rows_part_to_tmem<TA, CORR16, 0, kBK / 2>(base_ptr + (size_t)r * kRawSlot, tmem_a + (uint32_t)(s * 2 * kBK), t);
+                    tmem_st_wait();
+                } else {
+                    split_rows_to_tmem<TA, CORR16>(base_ptr + (size_t)r * kRawSlot, tmem_a + (uint32_t)(s * 2 * kBK), t);
+                }
                 tc_fence_before();
                 __syncwarp();
                 if (lane == 0) {
@@ -582,6 +690,7 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         // ===== B splitter (own 64 rows) =====
         reg_dec<72>();
         const int t = threadIdx.x - 256;
+        const uint32_t tmem_a = tmem_acc + ((uint32_t)((warp - 8) * 32) << 16) + (uint32_t)kAopCol;   // PRE: same lane quarter as A-splitter warp - 4
         uint32_t it = 0;
         PROF_DECL(3);
         for (int tile = pair_id; tile < ntiles; tile += npairs) {
@@ -593,9 +702,18 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                 PROF_LAP(0);
                 mbar_wait_cluster(empty_bar(s), ((it / kSplit) & 1) ^ 1);
                 PROF_LAP(1);
-                unsigned char* st = split_ptr + (size_t)s * kSplitBytes;
-                split_b_half<TB, CORR16>(base_ptr + (size_t)r * kRawBytes + kTileBytes, st, st + kBHalfBytes, t);
-                fence_async_smem();
+                if (PRE) {
+                    // the B tiles come from the B producer: split the other half of the A rows, then wait for this k-block's B stage
+                    tc_fence_after();
+                    split_rows_part_to_tmem<TA, CORR16, kBK / 2, kBK / 2>(base_ptr + (size_t)r * kRawSlot, tmem_a + (uint32_t)(s * 2 * kBK), t);
+                    tmem_st_wait();
+                    tc_fence_before();
+                    mbar_wait(bfull_bar((int)(it % kBSt)), (it / kBSt) & 1);
+                } else {
+                    unsigned char* st = split_ptr + (size_t)s * kSplitBytes;
+                    split_b_half<TB, CORR16>(base_ptr + (size_t)r * kRawSlot + kTileBytes, st, st + kBHalfBytes, t);
+                    fence_async_smem();
+                }
                 __syncwarp();
                 if (lane == 0) {
                     mbar_arrive_cluster(leader_bars + conv_off(s));
@@ -681,16 +799,18 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     }
 }
 
-template <bool TA, bool TB, int C16, int NS>
-static int pair_launch_t(dim3 grid, cudaStream_t s, const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& mo, const CUtensorMap& mm, const GemmEpilogue& ep) {
+template <bool TA, bool TB, int C16, int NS, bool PRE = false>
+static int pair_launch_t(dim3 grid, cudaStream_t s, const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& mc, const CUtensorMap& mo,
+                         const CUtensorMap& mm, const GemmEpilogue& ep) {
+    constexpr size_t kSmem = PairCfg<TA, TB, NS, PRE>::kSmem;
     static bool done = false;
     if (!done) {
-        cudaError_t e = cudaFuncSetAttribute((const void*)gemm_pair_kernel<TA, TB, C16, NS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                             (int)smem_bytes(NS, stage_bufs(TA, TB)));
+        cudaError_t e = cudaFuncSetAttribute((const void*)gemm_pair_kernel<TA, TB, C16, NS, PRE>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                             (int)kSmem);
         if (e != cudaSuccess) return (int)e;
         done = true;
     }
-    gemm_pair_kernel<TA, TB, C16, NS><<<grid, kThreads, smem_bytes(NS, stage_bufs(TA, TB)), s>>>(ma, mb, mo, mm, ep);
+    gemm_pair_kernel<TA, TB, C16, NS, PRE><<<grid, kThreads, kSmem, s>>>(ma, mb, mc, mo, mm, ep);
     return 0;
 }
 
@@ -698,9 +818,27 @@ template <bool TA, bool TB>
 static int pair_launch_f(int c16, bool merged, dim3 grid, cudaStream_t s, const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& mo,
                          const CUtensorMap& mm, const GemmEpilogue& ep) {
     if (merged && c16 != 2)     // (the merged accumulator cannot carry the 2^11 scale of the fp16 corrections)
-        return c16 ? pair_launch_t<TA, TB, 1, 4>(grid, s, ma, mb, mo, mm, ep) : pair_launch_t<TA, TB, 0, 4>(grid, s, ma, mb, mo, mm, ep);
-    if (c16 == 2) return pair_launch_t<TA, TB, 2, 2>(grid, s, ma, mb, mo, mm, ep);
-    return c16 ? pair_launch_t<TA, TB, 1, 2>(grid, s, ma, mb, mo, mm, ep) : pair_launch_t<TA, TB, 0, 2>(grid, s, ma, mb, mo, mm, ep);
+        return c16 ? pair_launch_t<TA, TB, 1, 4>(grid, s, ma, mb, mb, mo, mm, ep) : pair_launch_t<TA, TB, 0, 4>(grid, s, ma, mb, mb, mo, mm, ep);
+    if (c16 == 2) return pair_launch_t<TA, TB, 2, 2>(grid, s, ma, mb, mb, mo, mm, ep);
+    return c16 ? pair_launch_t<TA, TB, 1, 2>(grid, s, ma, mb, mb, mo, mm, ep) : pair_launch_t<TA, TB, 0, 2>(grid, s, ma, mb, mb, mo, mm, ep);
+}
+
+// adkf_gemm_presplit: W [rows, K] (row stride ld) -> hi [rows, K] (tf32-rounded values) and co [rows, K] 32-bit words, per 32-wide
+// k-block: words 0..15 = 16-bit pairs of hi, words 16..31 = 16-bit pairs of lo (corr 1: bf16; corr 2: fp16 with lo x 2^11) -- the row
+// layout split_b_half writes, so that a SWIZZLE_128B TMA box of either image IS the tile the MMA descriptors describe.
+template <int CORR>
+__global__ void presplit_kernel(const float* __restrict__ W, int64_t rows, int K, int64_t ld, float* __restrict__ hi, uint32_t* __restrict__ co) {
+    const int64_t total = rows * (int64_t)(K / 2);
+    for (int64_t p = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; p < total; p += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t n = p / (K / 2);
+        const int kp = (int)(p - n * (K / 2));               // pair index inside the row: k = 2 kp, 2 kp + 1
+        const int kb = kp >> 4, c = kp & 15;
+        const float2 x = *reinterpret_cast<const float2*>(W + n * ld + 2 * kp);
+        const float h0 = tf32_hi(x.x), h1 = tf32_hi(x.y);
+        *reinterpret_cast<float2*>(hi + n * (int64_t)K + 2 * kp) = make_float2(h0, h1);
+        co[n * (int64_t)K + kb * 32 + c] = pack_corr_hi<CORR>(h0, h1);
+        co[n * (int64_t)K + kb * 32 + 16 + c] = pack_corr_lo<CORR>(x.x - h0, x.y - h1);
+    }
 }
 
 }  // namespace pr
@@ -708,6 +846,23 @@ static int pair_launch_f(int c16, bool merged, dim3 grid, cudaStream_t s, const 
 extern int g_gemm_corr16;
 
 // Launch on CTA pairs.  ep: mode 0 with gx = ceil(N/128), gy = ceil(M/256), ntiles = gx gy splits batch already set.
+int gemm_pair_presplit(const float* W, int64_t rows, int K, int64_t ld, int corr, float* hi, float* co, cudaStream_t s) {
+    const int64_t total = rows * (int64_t)(K / 2);
+    const unsigned grid = (unsigned)std::min<int64_t>((total + 255) / 256, 148 * 16);
+    if (corr == 2) pr::presplit_kernel<2><<<grid, 256, 0, s>>>(W, rows, K, ld, hi, reinterpret_cast<uint32_t*>(co));
+    else pr::presplit_kernel<1><<<grid, 256, 0, s>>>(W, rows, K, ld, hi, reinterpret_cast<uint32_t*>(co));
+    return 0;
+}
+
+// pre-split B: mb = hi image, mc = [hi | lo] image (corr 1 bf16 | 2 scaled fp16, the flavour the images were built with)
+int gemm_pair_launch_pre(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& mc, const CUtensorMap& mo, const CUtensorMap& mm,
+                         const GemmEpilogue& ep, int corr, cudaStream_t s) {
+    const int pairs = std::max(1, num_sms() / 2);
+    dim3 grid((unsigned)(2 * std::min(ep.ntiles, pairs)));
+    if (corr == 2) return pr::pair_launch_t<false, false, 2, 2, true>(grid, s, ma, mb, mc, mo, mm, ep);
+    return pr::pair_launch_t<false, false, 1, 2, true>(grid, s, ma, mb, mc, mo, mm, ep);
+}
+
 int gemm_pair_launch(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& mo, const CUtensorMap& mm, const GemmEpilogue& ep,
                      int transA, int transB, cudaStream_t s) {
     // 0: tf32 corrections everywhere; 1: bf16 everywhere; 2 (default): bf16 for the BACKWARD forms only -- (K,T) input gradients

@@ -514,6 +514,9 @@ static int plan_splits_tiles(int64_t tiles, int nk, int workers = 148) {
 // CTA pairs (gemm_pair.cu, 256 x 128 tiles, 74 workers) take every mode-0 product with more than one 128-row tile;
 // ADKF_GEMM_IMPL=1 forces the one-CTA kernel (A/B measurements).
 namespace adkf {
+int gemm_pair_presplit(const float* W, int64_t rows, int K, int64_t ld, int corr, float* hi, float* co, cudaStream_t s);
+int gemm_pair_launch_pre(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& mc, const CUtensorMap& mo, const CUtensorMap& mm,
+                         const GemmEpilogue& ep, int corr, cudaStream_t s);
 int gemm_pair_launch(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& mo, const CUtensorMap& mm, const GemmEpilogue& ep,
                      int transA, int transB, cudaStream_t s);
 }
@@ -660,6 +663,52 @@ extern "C" int adkf_gemm_tf32x3_masked(const float* A, int32_t transA, int64_t l
     if (transA && !transB) return ADKF_ERR_BADARG;
     return gemm_launch(A, transA, lda, transA ? K : M, transA ? M : K, B, transB, ldb, transB ? K : N, transB ? N : K, M, N, K,
                        nullptr, 3 + mask_act, D, ldd, nullptr, 0, 1, 0, 0, 0, 0, 0, 0, (cudaStream_t)stream, mask, ldm);
+}
+
+// ---- pre-split weight images (gemm_pair.cu, PRE variant) ----------------------------------------------------------------------
+extern "C" int adkf_gemm_presplit(const float* W, int64_t rows, int32_t K, int64_t ldw, int32_t corr, float* hi, float* co, void* stream) {
+    if (rows <= 0 || K <= 0) return 0;
+    if (!W || !hi || !co || K % 32 || ldw % 2 || (reinterpret_cast<uintptr_t>(W) & 7) || (reinterpret_cast<uintptr_t>(hi) & 15) ||
+        (reinterpret_cast<uintptr_t>(co) & 15) || (corr != 1 && corr != 2))
+        return ADKF_ERR_BADARG;
+    (void)cudaGetLastError();
+    const int rc = adkf::gemm_pair_presplit(W, rows, K, ldw, corr, hi, co, (cudaStream_t)stream);
+    adkf_count_launches(1);
+    ADKF_LAUNCH_CHECK();
+    return rc;
+}
+
+extern "C" int adkf_gemm_tf32x3_pre(const float* A, int64_t lda, const float* B_hi, const float* B_co, int32_t corr, int64_t M, int32_t N,
+                                    int32_t K, const float* bias, int32_t act, const float* mask, int64_t ldm, int32_t mask_act, float* D,
+                                    int64_t ldd, void* stream) {
+    if (M <= 0 || N <= 0) return 0;
+    if (!A || !B_hi || !B_co || !D || K <= 0 || K % 32 || M <= kBM || act < 0 || act > 2 || (corr != 1 && corr != 2)) return ADKF_ERR_BADARG;
+    if (mask != nullptr && (act != 0 || bias != nullptr || (mask_act != 1 && mask_act != 2) || ldm < N)) return ADKF_ERR_BADARG;
+    cudaStream_t s = (cudaStream_t)stream;
+    (void)cudaGetLastError();
+    CUtensorMap ma, mb, mc;
+    int rc = make_map_2d(&ma, A, M, K, lda, 0);
+    if (rc) return rc;
+    if ((rc = make_map_2d(&mb, B_hi, N, K, K, 0, kBN / 2))) return rc;
+    if ((rc = make_map_2d(&mc, B_co, N, K, K, 0, kBN / 2))) return rc;
+    const int eact = mask != nullptr ? 3 + mask_act : act;
+    GemmEpilogue ep = {};
+    ep.mode = 0; ep.M = M; ep.N = N; ep.K = K; ep.bias = bias; ep.act = eact; ep.mask = mask; ep.ldm = ldm;
+    ep.kb_per_split = K / kBK; ep.splits = 1; ep.out = D; ep.ldo = ldd;
+    ep.gx = (N + kBN - 1) / kBN; ep.gy = (int)((M + 2 * kBM - 1) / (2 * kBM));
+    const int64_t ntiles64 = (int64_t)ep.gx * ep.gy;
+    if (ntiles64 > 0x7fffffff) return ADKF_ERR_BADARG;
+    ep.ntiles = (int)ntiles64;
+    CUtensorMap mo = ma, mm = ma;
+    const bool bias_ok = bias == nullptr || (reinterpret_cast<uintptr_t>(bias) & 15) == 0;
+    const bool mask_ok = mask == nullptr || (ldm % 4 == 0 && (reinterpret_cast<uintptr_t>(mask) & 15) == 0);
+    if (N % 32 == 0 && bias_ok && mask_ok && N <= ldd && make_out_map_2d(&mo, D, M, ldd, ldd) == 0 &&
+        (mask == nullptr || make_out_map_2d(&mm, const_cast<float*>(mask), M, N, ldm) == 0))
+        ep.tma_store = 1;
+    if ((rc = adkf::gemm_pair_launch_pre(ma, mb, mc, mo, mm, ep, corr, s))) return rc;
+    adkf_count_launches(1);
+    ADKF_LAUNCH_CHECK();
+    return 0;
 }
 
 extern "C" int64_t adkf_gemm_batched_splitk_ws_floats(int64_t M, int32_t N, int32_t K, int32_t batch) {

@@ -791,12 +791,81 @@ def gp_ift(layout: TaskLayout, D2, y, kernel, noise_prior_loc: float, ls_prior: 
 ACT_IDS = {None: 0, "none": 0, "relu": 1, "leaky_relu": 2}
 
 
+# pre-split weight images (adkf_gemm_presplit): built once per weight VERSION and kept on the parameter object itself, so they live
+# and die with the model; ADKF_GEMM_PRESPLIT=0 switches the path off (A/B runs)
+_PRESPLIT = os.environ.get("ADKF_GEMM_PRESPLIT", "1") != "0"
+_PRE_MIN_ROWS, _PRE_MIN_K = 2048, 256
+
+
+def _presplit_mode() -> bool:
+    """Pre-split images follow the default correction scheme only (scaled fp16 forward / bf16 backward on CTA pairs)."""
+    if not _PRESPLIT:
+        return False
+    prev = int(_cabi.load().adkf_gemm_configure(-1, -1))
+    return (prev & 0xff) == 2 and (prev >> 8) == 3
+
+
+def weight_images(w: torch.Tensor, transposed: bool):
+    """(hi, co, corr) images of a weight for adkf_gemm_tf32x3_pre: of w [N,K] itself (forward, scaled-fp16 corrections) or of w^T
+    (input gradient, bf16 corrections).  Cached on the tensor object, keyed by its version counter and data pointer."""
+    corr = 1 if transposed else 2
+    cache = getattr(w, "_adkf_images", None)
+    if cache is None:
+        cache = {}
+        try:
+            w._adkf_images = cache
+        except AttributeError:
+            pass
+    key = (transposed, w.data_ptr(), w._version, tuple(w.shape))
+    ent = cache.get(transposed)
+    if ent is not None and ent[0] == key:
+        return ent[1], ent[2], corr
+    src = w.detach()
+    src = src.t().contiguous() if transposed else (src if src.stride(1) == 1 and src.stride(0) % 2 == 0 else src.contiguous())
+    rows, K = src.shape
+    if ent is not None and ent[1].shape == (rows, K):
+        hi, co = ent[1], ent[2]                      # same stream order as the GEMMs that read them: safe to overwrite
+    else:
+        hi = torch.empty(rows, K, dtype=torch.float32, device=w.device)
+        co = torch.empty(rows, K, dtype=torch.float32, device=w.device)
+    check(_cabi.load().adkf_gemm_presplit(ctypes.c_void_p(src.data_ptr()), rows, K, src.stride(0), corr, dptr(hi), dptr(co), stream_ptr()),
+          "adkf_gemm_presplit")
+    cache[transposed] = (key, hi, co)
+    return hi, co, corr
+
+
+def _pre_eligible(a: torch.Tensor, w: torch.Tensor, transposed: bool) -> bool:
+    K = w.shape[0] if transposed else w.shape[1]
+    return (a.dim() == 2 and a.shape[0] >= _PRE_MIN_ROWS and K % 32 == 0 and K >= _PRE_MIN_K and w.dim() == 2
+            and a.stride(1) == 1 and a.stride(0) % 4 == 0 and a.data_ptr() % 16 == 0 and _presplit_mode())
+
+
+def gemm_weight_pre(a: torch.Tensor, w: torch.Tensor, transposed: bool, bias: Optional[torch.Tensor] = None, act=None,
+                    mask: Optional[torch.Tensor] = None, mask_act: int = 0) -> torch.Tensor:
+    """act(a @ w.T + bias) (transposed False: w [N,K]) or a @ w (transposed True: w [K_gemm, N]), optionally times act'(mask), with the
+    weight's pre-split images as B operand (adkf_gemm_tf32x3_pre)."""
+    lib = _cabi.load()
+    hi, co, corr = weight_images(w, transposed)
+    M, K = a.shape
+    N = hi.shape[0]
+    out = torch.empty(M, N, dtype=torch.float32, device=a.device)
+    null = ctypes.c_void_p(0)
+    rc = lib.adkf_gemm_tf32x3_pre(ctypes.c_void_p(a.data_ptr()), a.stride(0), dptr(hi), dptr(co), corr, M, N, K,
+                                  dptr(bias.contiguous(), torch.float32) if bias is not None else null, ACT_IDS[act],
+                                  ctypes.c_void_p(mask.data_ptr()) if mask is not None else null, mask.stride(0) if mask is not None else 0,
+                                  int(mask_act), dptr(out), N, stream_ptr())
+    check(rc, "adkf_gemm_tf32x3_pre")
+    return out
+
+
 def gemm_tf32x3(a: torch.Tensor, trans_a: bool, b: torch.Tensor, trans_b: bool, bias: Optional[torch.Tensor] = None,
-                act=None, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+                act=None, out: Optional[torch.Tensor] = None, weight_b: bool = False) -> torch.Tensor:
     """D[M,N] = act(opA(a) @ opB(b).T + bias) on the tensor cores with fp32-class accuracy.
     a is [M,K] (trans_a False) or [K,M]; b is [N,K] (trans_b False) or [K,N]; both may be row-strided views
     (last dim contiguous, row stride a multiple of 4 floats, 16-byte aligned)."""
     lib = _cabi.load()
+    if weight_b and not trans_a and out is None and a.is_cuda and b.is_cuda and _pre_eligible(a, b, trans_b):
+        return gemm_weight_pre(a, b, trans_b, bias, act)      # B is a weight matrix: its pre-split images feed the MMA directly
     for t in (a, b):
         if not t.is_cuda or t.dtype != torch.float32 or t.dim() != 2 or t.stride(1) != 1:
             raise RuntimeError("gemm_tf32x3 needs 2-D fp32 CUDA operands with a contiguous last dimension (no CPU fallback)")
@@ -825,7 +894,7 @@ def gemm_tf32x3(a: torch.Tensor, trans_a: bool, b: torch.Tensor, trans_b: bool, 
     return out
 
 
-def gemm_tf32x3_masked(a: torch.Tensor, b: torch.Tensor, mask: torch.Tensor, mask_act: int) -> torch.Tensor:
+def gemm_tf32x3_masked(a: torch.Tensor, b: torch.Tensor, mask: torch.Tensor, mask_act: int, weight_b: bool = False) -> torch.Tensor:
     """(a [M,K] @ b [K,N]) * act'(mask [M,N]) -- the (K,T) input-gradient form with the activation derivative of the layer
     below applied in the epilogue (mask_act 1 relu, 2 leaky_relu(0.01))."""
     lib = _cabi.load()
@@ -833,6 +902,9 @@ def gemm_tf32x3_masked(a: torch.Tensor, b: torch.Tensor, mask: torch.Tensor, mas
     N = b.shape[1]
     if b.shape[0] != K or tuple(mask.shape) != (M, N):
         raise ValueError(f"shape mismatch: a {tuple(a.shape)} b {tuple(b.shape)} mask {tuple(mask.shape)}")
+    if (weight_b and a.is_cuda and mask.is_cuda and mask.stride(1) == 1 and mask.stride(0) % 4 == 0 and mask.data_ptr() % 16 == 0
+            and _pre_eligible(a, b, True)):
+        return gemm_weight_pre(a, b, True, mask=mask, mask_act=mask_act)
     for t in (a, b, mask):
         if not t.is_cuda or t.dtype != torch.float32 or t.stride(1) != 1 or t.stride(0) % 4 or t.data_ptr() % 16:
             raise RuntimeError("gemm_tf32x3_masked needs 16-byte aligned 2-D fp32 CUDA operands (no CPU fallback)")
@@ -929,7 +1001,7 @@ class _LinearTC(torch.autograd.Function):
 
     @staticmethod
     def forward(ctx, x, weight, bias, act):
-        y = gemm_tf32x3(x, False, weight, False, bias, act)
+        y = gemm_tf32x3(x, False, weight, False, bias, act, weight_b=True)
         ctx.act = ACT_IDS[act]
         ctx.has_bias = bias is not None
         ctx.save_for_backward(x, weight, y if ctx.act else None)
@@ -942,7 +1014,7 @@ class _LinearTC(torch.autograd.Function):
         dy, db = act_bwd_colsum(dy.contiguous(), y, ctx.act, ctx.has_bias and ctx.needs_input_grad[2])
         dx = dw = None
         if ctx.needs_input_grad[0]:
-            dx = gemm_tf32x3(dy, False, weight, True)          # dX[M,K] = dY[M,N] W[N,K]
+            dx = gemm_tf32x3(dy, False, weight, True, weight_b=True)          # dX[M,K] = dY[M,N] W[N,K]
         if ctx.needs_input_grad[1]:
             dw = gemm_tf32x3(dy, True, x, True)                # dW[N,K] = dY^T[N,M] X[M,K]
         return dx, dw, db, None
@@ -956,8 +1028,8 @@ class _MLP2TC(torch.autograd.Function):
 
     @staticmethod
     def forward(ctx, x, w1, b1, act, w2, b2):
-        hid = gemm_tf32x3(x, False, w1, False, b1, act)
-        y = gemm_tf32x3(hid, False, w2, False, b2, None)
+        hid = gemm_tf32x3(x, False, w1, False, b1, act, weight_b=True)
+        y = gemm_tf32x3(hid, False, w2, False, b2, None, weight_b=True)
         ctx.act = ACT_IDS[act]
         ctx.has_b = (b1 is not None, b2 is not None)
         ctx.save_for_backward(x, w1, hid, w2)
@@ -970,10 +1042,10 @@ class _MLP2TC(torch.autograd.Function):
         need = ctx.needs_input_grad
         db2 = act_bwd_colsum(dy, None, 0, True)[1] if (ctx.has_b[1] and need[5]) else None
         dw2 = gemm_tf32x3(dy, True, hid, True) if need[4] else None          # dW2[N,H] = dY^T hid
-        dz1 = gemm_tf32x3_masked(dy, w2, hid, ctx.act)                        # dZ1[M,H] = (dY W2) * act'(hid)
+        dz1 = gemm_tf32x3_masked(dy, w2, hid, ctx.act, weight_b=True)                        # dZ1[M,H] = (dY W2) * act'(hid)
         db1 = act_bwd_colsum(dz1, None, 0, True)[1] if (ctx.has_b[0] and need[2]) else None
         dw1 = gemm_tf32x3(dz1, True, x, True) if need[1] else None
-        dx = gemm_tf32x3(dz1, False, w1, True) if need[0] else None
+        dx = gemm_tf32x3(dz1, False, w1, True, weight_b=True) if need[0] else None
         return dx, dw1, db1, None, dw2, db2
 
 

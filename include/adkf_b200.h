@@ -330,6 +330,19 @@ int adkf_ard_wsqdist(const float* Z, int32_t d, int32_t T, const int32_t* z_off,
 int adkf_ard_pairquad(const float* Z, int32_t d, int32_t T, const int32_t* z_off, const int32_t* n_sup, const int64_t* d2_off,
                       const float* G, int32_t support_only, float* q, void* stream);
 
+/* Pre-split weight images for the forward / input-gradient GEMMs (gemm_pair.cu, PRE variant).  The B operand of those products is
+ * a weight matrix (nn.Linear: y = x W^T, fs_mol/modules/gnn.py:79-95, graph_readout.py:224-259; its autograd dX = dY W) that every
+ * one of the ~1000 M-tiles would split into (hi, lo) again.  adkf_gemm_presplit writes, once per optimizer step, for W [rows, K]
+ * (K % 32 == 0, K-major): hi [rows, K] = tf32-rounded values and co [rows, K] 32-bit words = per 32-wide k-block the 16-bit pairs of
+ * hi then of lo (corr 1: bf16; corr 2: fp16 with lo x 2^11 -- see adkf_gemm_configure).  adkf_gemm_tf32x3_pre computes
+ *   D [M,N] = act(A [M,K] . W^T + bias)       or, with mask != NULL,   D = (A . W^T) * act'(mask)   (mask_act 1 relu | 2 leaky_relu)
+ * from the images of W [N,K] (for dX pass the images of the TRANSPOSED weight): TMA loads the image tiles straight into the MMA's
+ * B stages, the B-splitter warps split half of the A rows instead.  M > 128; `corr` must be the flavour the images were built with. */
+int adkf_gemm_presplit(const float* W, int64_t rows, int32_t K, int64_t ldw, int32_t corr, float* hi, float* co, void* stream);
+int adkf_gemm_tf32x3_pre(const float* A, int64_t lda, const float* B_hi, const float* B_co, int32_t corr, int64_t M, int32_t N, int32_t K,
+                         const float* bias, int32_t act, const float* mask, int64_t ldm, int32_t mask_act, float* D, int64_t ldd,
+                         void* stream);
+
 /* Process-wide GEMM variant (development / A-B measurements; initialised from ADKF_GEMM_IMPL / ADKF_GEMM_CORR):
  *   impl   1 = one CTA per 128 x 128 tile (gemm_tf32x3.cu), 2 = CTA pairs on 256 x 128 tiles (gemm_pair.cu, default); other: keep
  *   corr16 correction products of the pair kernel: 0 = tf32, 1 = bf16, 2 = tf32 forward / bf16 for the backward operand forms

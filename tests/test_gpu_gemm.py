@@ -253,3 +253,39 @@ def test_mlp2_tc_fused_backward(cuda_device, act, M, K, H, N):
         e, eu = rel(a, r), rel(u, r)
         print(f"mlp2_tc {act} {name}: rel err fused {e:.3e} unfused {eu:.3e}")
         assert e < 5e-6, name
+
+
+@pytest.mark.parametrize("M,N,K", [(5000, 768, 1408), (4100, 200, 256), (2304, 1024, 384)])
+def test_presplit_weight_images_equal_the_in_kernel_split(cuda_device, M, N, K):
+    """adkf_gemm_presplit + adkf_gemm_tf32x3_pre (B operand = pre-split images of the weight, TMA-loaded straight into the MMA's B
+    stages) against the kernel that splits B itself: same operand bits, same MMA order -> bit-identical outputs for the forward
+    form (scaled-fp16 corrections), the input-gradient form (images of W^T, bf16 corrections) and the masked input gradient; the
+    image cache follows the weight's version counter."""
+    from adkf_ift_b200 import ops
+    g = torch.Generator().manual_seed(M + N + K)
+    x = torch.randn(M, K, generator=g).to(cuda_device)
+    w = (torch.randn(N, K, generator=g) / K ** 0.5).to(cuda_device)
+    b = torch.randn(N, generator=g).to(cuda_device)
+    # forward: y = relu(x w^T + b)
+    plain = ops.gemm_tf32x3(x, False, w, False, b, "relu")
+    pre = ops.gemm_weight_pre(x, w, False, b, "relu")
+    assert torch.equal(pre, plain)
+    ref = (x.double() @ w.double().t() + b.double()).clamp_min(0)
+    assert rel(pre, ref) < 2e-6
+    # input gradient: dx = dy w  (contraction over the weight's rows: images of w^T), plain and masked
+    if N % 32 == 0 and N >= 256:
+        dy = torch.randn(M, N, generator=g).to(cuda_device)
+        plain = ops.gemm_tf32x3(dy, False, w, True)                  # (may run split-K at small M: same products, other summation order)
+        pre = ops.gemm_weight_pre(dy, w, True)
+        assert rel(pre, plain) < 1e-6
+        assert rel(pre, dy.double() @ w.double()) < 4e-6
+        mask = torch.randn(M, K, generator=g).to(cuda_device)
+        plain = ops.gemm_tf32x3_masked(dy, w, mask, 2)
+        pre = ops.gemm_weight_pre(dy, w, True, mask=mask, mask_act=2)
+        assert torch.equal(pre, plain)
+    # the cache is keyed by the version counter: an in-place update of the weight rebuilds the images
+    hi0 = ops.weight_images(w, False)[0]
+    assert ops.weight_images(w, False)[0] is hi0
+    w.mul_(2.0)
+    pre2 = ops.gemm_weight_pre(x, w, False, b, "relu")
+    assert torch.equal(pre2, ops.gemm_tf32x3(x, False, w, False, b, "relu"))

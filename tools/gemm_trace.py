@@ -32,13 +32,13 @@ def main():
             return out
         setattr(ops, name, inner)
 
-    def d_plain(a, ta, b, tb_, bias=None, act=None, out=None):
+    def d_plain(a, ta, b, tb_, bias=None, act=None, out=None, weight_b=False):
         K, M = (a.shape if ta else a.shape[::-1])
         N = b.shape[1] if tb_ else b.shape[0]
         form = "(T,T) dW" if ta else ("(K,T) dX" if tb_ else "(K,K) fwd")
         return f"{form:10s} M={M:<7d} N={N:<5d} K={K:<7d} {'bias ' if bias is not None else ''}{act or ''}"
 
-    def d_masked(a, b, mask, mask_act):
+    def d_masked(a, b, mask, mask_act, weight_b=False):
         return f"(K,T) dX   M={a.shape[0]:<7d} N={b.shape[1]:<5d} K={a.shape[1]:<7d} masked"
 
     def d_batched(a, ta, ams, aks, b, tb_, bms, bks, M, N, K, batch, out, ldd, d_stride, bias=None, bias_stride=0, act=None, allow_splitk=False):
