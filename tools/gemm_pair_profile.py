@@ -29,6 +29,7 @@ def main():
     dyT, xT = rnd(V, 768), rnd(V, 1408)
     cases = [
         ("fwd readout hidden  M=V N=768 K=1408 (K,K)", 44, lambda: ops.gemm_tf32x3(x1408, False, wr, False, br, "relu")),
+        ("fwd readout hidden  PRE-SPLIT weight images   ", 44, lambda: ops.gemm_weight_pre(x1408, wr, False, br, "relu")),
         ("fwd boom1           M=V N=1024 K=128 (K,K)", 4, lambda: ops.gemm_tf32x3(x128, False, w1, False, b1, "leaky_relu")),
         ("dX  proj-like       M=V N=3072 K=128 (K,T)", 4, lambda: ops.gemm_tf32x3(dy384, False, wT, True)),
         ("fwd pna type0 4x    M=E N=192 K=64 batched", 2, lambda: ops.gemm_tf32x3_batched(XG, False, 0, 64, W2, False, 3 * 192, 0, E, 192, 64, 4, pre, 768, 192,
