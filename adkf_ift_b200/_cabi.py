@@ -120,7 +120,15 @@ def load():
     return lib
 
 
+_RAW_STREAM = getattr(torch._C, "_cuda_getCurrentRawStream", None)
+_GET_DEVICE = getattr(torch._C, "_cuda_getDevice", None)
+
+
 def stream_ptr():
+    """cudaStream_t of torch's current stream on the current device.  One C call: torch.cuda.current_stream() builds a Stream object
+    through several Python layers (is_available, device-index parsing, os.environ) -- 15 us, ~400 times per training step."""
+    if _RAW_STREAM is not None and _GET_DEVICE is not None:
+        return c_void_p(_RAW_STREAM(_GET_DEVICE()))
     return c_void_p(torch.cuda.current_stream().cuda_stream)
 
 

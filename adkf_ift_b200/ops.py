@@ -794,7 +794,7 @@ ACT_IDS = {None: 0, "none": 0, "relu": 1, "leaky_relu": 2}
 # pre-split weight images (adkf_gemm_presplit): built once per weight VERSION and kept on the parameter object itself, so they live
 # and die with the model; ADKF_GEMM_PRESPLIT=0 switches the path off (A/B runs)
 _PRESPLIT = os.environ.get("ADKF_GEMM_PRESPLIT", "1") != "0"
-_PRE_MIN_ROWS, _PRE_MIN_K = 2048, 256
+_PRE_MIN_ROWS, _PRE_MIN_K = 32768, 256   # (below ~32k rows a step is host-launch bound: the image kernels cost more than they save)
 
 
 def _presplit_mode() -> bool:
