@@ -52,3 +52,14 @@ def test_product_never_imports_oracle():
             src = open(os.path.join(pkg, fn)).read()
             assert not re.search(r"^\s*(from|import)\s+oracle\b", src, flags=re.M), fn
             assert "/root/reference" not in src, fn
+
+
+def test_torch_library_registration_has_no_cpu_kernels():
+    """torch.ops.adkf.* (adkf_ift_b200/torch_ops.py) are registered for the CUDA key only: a CPU tensor reaches no kernel."""
+    import torch
+    import adkf_ift_b200.torch_ops as tops
+    assert set(tops.registered_ops()) == set(tops.OPS)
+    with pytest.raises(NotImplementedError):
+        torch.ops.adkf.gemm_tf32x3(torch.zeros(4, 4), False, torch.zeros(4, 4), False, None, 0)
+    with pytest.raises(NotImplementedError):
+        torch.ops.adkf.linear(torch.zeros(4, 4), torch.zeros(4, 4), None, 0)
