@@ -505,6 +505,7 @@ class ADKTModelTrainer(ADKTModel):
             if self.config.clip_value is not None or pre_scale is not None:
                 flat.clip_(self.config.clip_value, pre_scale)
             self.optimizer.step()
+            ops.weights_changed()       # Adam wrote the parameters through the flat buffer: their version counters did not move
         if self.lr_scheduler is not None:
             self.lr_scheduler.step()
         self._step += 1

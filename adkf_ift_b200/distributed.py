@@ -72,6 +72,8 @@ class FlatParams:
             self.flat[off:off + n].copy_(p.data.reshape(-1))
             p.data = self.flat[off:off + n].view_as(p.data)
             p.grad = self.grad[off:off + n].view_as(p.data)
+        from . import ops
+        ops.weights_changed()           # (every parameter moved: cached weight images are stale)
 
     def zero_grad(self):
         self.gbuf.zero_()

@@ -253,6 +253,7 @@ class DKTModelTrainer(DKTModel):
         if self.config.clip_value is not None:
             torch.nn.utils.clip_grad_norm_(self.parameters(), self.config.clip_value)
         self.optimizer.step()
+        ops.weights_changed()
         if self.lr_scheduler is not None:
             self.lr_scheduler.step()
         return losses.mean(), status

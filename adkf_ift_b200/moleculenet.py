@@ -548,4 +548,5 @@ class ADKF_Meta_Trainer(nn.Module):
             res = run_on_mol_task_batch(self.model, mb, train=True)
             torch.nn.utils.clip_grad_norm_(self.model.feature_extractor_params(), 1.0)
             self.optimizer.step()
+            ops.weights_changed()
         return res

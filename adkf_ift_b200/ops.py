@@ -797,6 +797,17 @@ _PRESPLIT = os.environ.get("ADKF_GEMM_PRESPLIT", "1") != "0"
 _PRE_MIN_ROWS, _PRE_MIN_K = 32768, 256   # (below ~32k rows a step is host-launch bound: the image kernels cost more than they save)
 
 
+# Weights that are updated THROUGH AN ALIAS do not bump their own version counter: FlatParams re-seats every parameter's .data on
+# a view of one flat buffer and Adam updates that buffer in place (p._version stays put).  Whoever updates weights that way calls
+# weights_changed(); the epoch is part of every image's key.
+_WEIGHT_EPOCH = [0]
+
+
+def weights_changed() -> None:
+    """Invalidate every cached weight image (call after an optimizer step that wrote parameters through an aliasing buffer)."""
+    _WEIGHT_EPOCH[0] += 1
+
+
 def _presplit_mode() -> bool:
     """Pre-split images follow the default correction scheme only (scaled fp16 forward / bf16 backward on CTA pairs)."""
     if not _PRESPLIT:
@@ -816,7 +827,7 @@ def weight_images(w: torch.Tensor, transposed: bool):
             w._adkf_images = cache
         except AttributeError:
             pass
-    key = (transposed, w.data_ptr(), w._version, tuple(w.shape))
+    key = (transposed, w.data_ptr(), w._version, tuple(w.shape), _WEIGHT_EPOCH[0])
     ent = cache.get(transposed)
     if ent is not None and ent[0] == key:
         return ent[1], ent[2], corr

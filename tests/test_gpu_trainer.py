@@ -196,3 +196,40 @@ def test_optimizer_state_round_trip(cuda_device, tmp_path):
     # and into the reference's own optimiser class (per-parameter Adam)
     ref_opt = torch.optim.Adam(small_model(cuda_device).feature_extractor_params(), 1e-4)
     ref_opt.load_state_dict(sd)
+
+
+def test_weight_images_follow_the_flat_buffer_optimizer(cuda_device):
+    """Regression test: ADKTModelTrainer re-seats every parameter on a view of one flat buffer and Adam updates that buffer in place,
+    which does NOT move the parameters' own version counters.  The cached pre-split weight images (ops.weight_images) must still
+    be rebuilt after every optimizer step: after two training steps the extractor's features computed through the images equal
+    the features computed with the in-kernel split of the CURRENT weights, bit for bit."""
+    from adkf_ift_b200 import dkt, ops, synthetic, task_batch
+    from adkf_ift_b200.adaptive_dkt import ADKTModelTrainerConfig
+    from adkf_ift_b200.adaptive_dkt_utils import ADKTModelTrainer
+    from adkf_ift_b200.feature_extractor import cli_default_config
+    cfg = ADKTModelTrainerConfig(graph_feature_extractor_config=cli_default_config(2), learning_rate=1e-2)
+    model = ADKTModelTrainer(cfg)
+    synthetic.deterministic_init_(model, seed=0, alpha=0.5)
+    model.to(cuda_device)
+    hosts = [dkt.task_sample_to_dkt_task_sample(synthetic.make_task_sample(300 + i, 16, 24), dkt.get_dkt_batcher(max_num_graphs=320),
+                                                False).batches[0] for i in range(2)]
+    tb = task_batch.to_device(task_batch.collate_tasks(hosts, False), cuda_device)
+    old_rows, old_on = ops._PRE_MIN_ROWS, ops._PRESPLIT
+    ops._PRE_MIN_ROWS = 256                      # small test graphs: let the image path run (it is reserved for >= 32k rows otherwise)
+    try:
+        assert ops._presplit_mode()
+        w = model.graph_feature_extractor.readout._weighted_mean_pooler._transformation_mlp._layers[0].weight
+        before = w.detach().clone()
+        for _ in range(2):
+            model.train_step(tb)
+        assert not torch.equal(w.detach(), before)                       # the optimizer moved the weight ...
+        with torch.no_grad():
+            z_img = model.embed(tb)
+            assert getattr(w, "_adkf_images", None), "the image path did not run"
+            hi = ops.weight_images(w, False)[0]
+            ops._PRESPLIT = False
+            z_plain = model.embed(tb)
+        assert torch.equal(z_img, z_plain)                                # ... and the images followed it
+        assert float((hi - w.detach()).abs().max()) <= float(w.detach().abs().max()) * 2 ** -10     # hi image = tf32(current weight)
+    finally:
+        ops._PRE_MIN_ROWS, ops._PRESPLIT = old_rows, old_on
