@@ -42,6 +42,9 @@ SIGNATURES = {
     "adkf_act_bwd_colsum": ([_P, c_int64, _P, c_int64, c_int64, c_int32, c_int32, _P, c_int64, _P, _P, c_int64, _P], ctypes.c_int),
     "adkf_act_bwd_colsum_noalloc_max_floats": ([], c_int64),
     "adkf_act_bwd_colsum_noalloc": ([_P, c_int64, _P, c_int64, c_int64, c_int32, c_int32, _P, c_int64, _P, _P], ctypes.c_int),
+    "adkf_rezero_bwd_ws_doubles": ([], c_int64),
+    "adkf_rezero_fwd": ([_P, _P, _P, c_int64, _P, _P], ctypes.c_int),
+    "adkf_rezero_bwd": ([_P, _P, _P, c_int64, _P, _P, _P, _P], ctypes.c_int),
     "adkf_pna_degree_scalers": ([_P, c_int32, _P, _P, _P], ctypes.c_int),
     "adkf_pna_combine_fwd": ([_P, _P, _P, _P, c_int64, _P, _P], ctypes.c_int),
     "adkf_pna_combine_bwd_ws_floats": ([c_int64], c_int64),

@@ -6,7 +6,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libadkf_b200.so")
-SOURCES = ["capi.cu", "gram.cu", "gp_core.cu", "gp_ard.cu", "graph.cu", "readout_ecfp.cu", "gemm_tf32x3.cu", "gemm_pair.cu", "chol_blocked.cu", "gin.cu", "pna_gemm.cu", "pna_fused.cu", "dense_bwd.cu", "mha_mp.cu", "layernorm.cu", "pna_combine.cu"]
+SOURCES = ["capi.cu", "gram.cu", "gp_core.cu", "gp_ard.cu", "graph.cu", "readout_ecfp.cu", "gemm_tf32x3.cu", "gemm_pair.cu", "chol_blocked.cu", "gin.cu", "pna_gemm.cu", "pna_fused.cu", "dense_bwd.cu", "mha_mp.cu", "layernorm.cu", "pna_combine.cu", "rezero.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-Xcompiler", "-fPIC", "--expt-relaxed-constexpr"] + os.environ.get("ADKF_NVCC_EXTRA", "").split()   # e.g. -DADKF_PAIR_PROFILE
 

@@ -129,20 +129,20 @@ class RelationalMultiHeadAttentionMP(nn.Module):
 
 
 class _ReZeroResidual(torch.autograd.Function):
-    """h + alpha * x (gnn.py:497-498, 512-513) as ONE elementwise launch forward and two backward (alpha * g, <g, x>)
-    instead of the five of the unfused expression; every tensor is [V,128] and purely HBM-bound."""
+    """h + alpha * x (gnn.py:497-498, 512-513): one streaming kernel forward; backward alpha * g and <g, x> in ONE pass over g
+    (csrc/rezero.cu; torch needed addcmul with a broadcast scalar -- its slow non-vectorised path --, a mul and a cuBLAS dot).
+    Every tensor is [V,128] and purely HBM-bound."""
 
     @staticmethod
     def forward(ctx, h, x, alpha):
         ctx.save_for_backward(x, alpha)
-        return torch.addcmul(h, x, alpha)
+        return ops.rezero_fwd(h, x, alpha)
 
     @staticmethod
     def backward(ctx, g):
         x, alpha = ctx.saved_tensors
-        g = g.contiguous()
-        dalpha = torch.dot(g.view(-1), x.contiguous().view(-1)).reshape(alpha.shape) if ctx.needs_input_grad[2] else None
-        return g, (g * alpha if ctx.needs_input_grad[1] else None), dalpha
+        dx, dalpha = ops.rezero_bwd(g, x, alpha, ctx.needs_input_grad[1], ctx.needs_input_grad[2])
+        return g, dx, dalpha
 
 
 class GNNBlock(nn.Module):

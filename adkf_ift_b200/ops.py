@@ -968,6 +968,34 @@ def act_bwd_colsum(dy: torch.Tensor, y: Optional[torch.Tensor], act: int, want_d
     return dz, db
 
 
+def rezero_fwd(h: torch.Tensor, x: torch.Tensor, alpha: torch.Tensor) -> torch.Tensor:
+    """h + alpha * x, alpha a 1-element device tensor (adkf_rezero_fwd)."""
+    lib = _cabi.load()
+    if not (h.is_cuda and x.is_cuda and alpha.is_cuda):
+        raise RuntimeError("rezero_fwd needs CUDA tensors (no CPU fallback)")
+    h, x = h.contiguous(), x.contiguous()
+    if h.shape != x.shape or h.numel() % 4 or alpha.numel() != 1:
+        raise ValueError(f"rezero_fwd: shapes {tuple(h.shape)} / {tuple(x.shape)} / alpha {tuple(alpha.shape)}")
+    out = torch.empty_like(h)
+    check(lib.adkf_rezero_fwd(dptr(h, torch.float32), dptr(x, torch.float32), dptr(alpha.contiguous(), torch.float32), h.numel(), dptr(out),
+                              stream_ptr()), "adkf_rezero_fwd")
+    return out
+
+
+def rezero_bwd(g: torch.Tensor, x: torch.Tensor, alpha: torch.Tensor, want_dx: bool = True, want_dalpha: bool = True):
+    """(dx = alpha * g, dalpha = <g, x> shaped like alpha) in one pass over g (adkf_rezero_bwd); None for what is not wanted."""
+    lib = _cabi.load()
+    g, x = g.contiguous(), x.contiguous()
+    null = ctypes.c_void_p(0)
+    dx = torch.empty_like(g) if want_dx else None
+    dalpha = torch.empty(alpha.shape, dtype=torch.float32, device=g.device) if want_dalpha else None
+    ws = torch.empty(int(lib.adkf_rezero_bwd_ws_doubles()), dtype=torch.float64, device=g.device) if want_dalpha else None
+    check(lib.adkf_rezero_bwd(dptr(g, torch.float32), dptr(x, torch.float32), dptr(alpha.contiguous(), torch.float32), g.numel(),
+                              dptr(dx) if want_dx else null, dptr(dalpha) if want_dalpha else null,
+                              ctypes.c_void_p(ws.data_ptr()) if want_dalpha else null, stream_ptr()), "adkf_rezero_bwd")
+    return dx, dalpha
+
+
 class _LayerNorm128(torch.autograd.Function):
     """nn.LayerNorm(128) on [V,128] node states (gnn.py:504): warp-per-row kernels, deterministic dgamma / dbeta."""
 

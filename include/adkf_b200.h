@@ -133,6 +133,15 @@ int adkf_act_bwd_colsum_noalloc(const float* dY, int64_t ldy, const float* Y, in
                                 float* dZ, int64_t ldz, float* db, void* stream);
 
 /* ---------------------------------------------------------------------------------------------
+ * ReZero residual of a GNN block (fs_mol/modules/gnn.py:497-498, 512-513): out = h + alpha * x with a learned scalar alpha read
+ * from the device; backward in one pass over g: dx = alpha * g (dx may be NULL) and dalpha = <g, x> (dalpha may be NULL;
+ * deterministic, fp64 partials in ws[adkf_rezero_bwd_ws_doubles()]).  n % 4 == 0, 16-byte aligned arrays.
+ * ------------------------------------------------------------------------------------------- */
+int64_t adkf_rezero_bwd_ws_doubles(void);
+int adkf_rezero_fwd(const float* h, const float* x, const float* alpha, int64_t n, float* out, void* stream);
+int adkf_rezero_bwd(const float* g, const float* x, const float* alpha, int64_t n, float* dx, float* dalpha, double* ws, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
  * PNA degree scalers folded out of the aggregate (gnn.py:242-263 + msg_out_projection, gnn.py:492-495; pna_combine.cu):
  * out[v] = P[v,0:128] + amp(v) P[v,128:256] + att(v) P[v,256:384] + bias, where P = agg_unscaled [V,1024] @ [W_1;W_amp;W_att]^T.
  *   adkf_pna_degree_scalers: amp = log(deg+1)/1.1515, att = 1.1515/(log(deg+1)+1e-7) from the type-sorted tptr [3V+1]

@@ -359,3 +359,23 @@ def test_pna_scalers_folded_into_projection(cuda_device, n_mol):
     # ... and the no-gradient pass (fused message-passing kernel where the graph allows it) agrees with it to rounding
     out3 = ops.pna_message_passing_projected(*[c.detach() for c in cs], gi)
     assert rel(out3, out) < 5e-5
+
+
+def test_rezero_residual_fwd_bwd(cuda_device):
+    """csrc/rezero.cu against torch: out = h + alpha x; dx = alpha g; dalpha = <g, x> (fp64 accumulation, deterministic)."""
+    from adkf_ift_b200 import ops
+    from adkf_ift_b200.feature_extractor import _ReZeroResidual
+    gen = torch.Generator().manual_seed(5)
+    V = 70001
+    h, x, g = (torch.randn(V, 128, generator=gen).to(cuda_device) for _ in range(3))
+    alpha = torch.tensor([0.37], device=cuda_device)
+    hc, xc, ac = h.clone().requires_grad_(True), x.clone().requires_grad_(True), alpha.clone().requires_grad_(True)
+    out = _ReZeroResidual.apply(hc, xc, ac)
+    assert rel(out, h.double() + 0.37 * x.double()) < 1e-6
+    out.backward(g)
+    assert torch.equal(hc.grad, g)
+    assert rel(xc.grad, 0.37 * g.double()) < 1e-6
+    want = float((g.double() * x.double()).sum())
+    assert abs(float(ac.grad) - want) <= 1e-6 * abs(want) + 1e-3 and ac.grad.shape == alpha.shape
+    dx2, da2 = ops.rezero_bwd(g, x, alpha)
+    assert torch.equal(da2, ac.grad) and torch.equal(dx2, xc.grad)          # run-to-run bit stability
