@@ -1035,6 +1035,24 @@ def layernorm128(x: torch.Tensor, gamma: torch.Tensor, beta: torch.Tensor, eps: 
     return _LayerNorm128.apply(x, gamma, beta, eps)
 
 
+def _padded_tile_area(m: int, n: int) -> int:
+    """Output area the GEMM kernels actually compute for an [m, n] product: 256 x 128 tiles on CTA pairs (m > 128), else 128 x 128."""
+    bm = 256 if m > 128 else 128
+    return -(-m // bm) * bm * (-(-n // 128) * 128)
+
+
+def weight_grad_gemm(dy: torch.Tensor, x: torch.Tensor) -> torch.Tensor:
+    """dW [N_out, K_in] = dy^T x (the (T,T) form, contraction over the rows).  The kernels tile the OUTPUT in 256 x 128 (pairs) or
+    128 x 128 (M <= 128: one CTA per tile, slower per flop), so the orientation matters: [384, 1024] pads to 512 x 1024, its
+    transpose [1024, 384] fits exactly (25% less tensor work), and [128, 1024] runs on pairs as [1024, 128].  The transposed
+    product is returned as a strided view (no copy)."""
+    m, n = dy.shape[1], x.shape[1]
+    direct, swapped = _padded_tile_area(m, n), _padded_tile_area(n, m)
+    if swapped < direct or (swapped == direct and m <= 128 < n):
+        return gemm_tf32x3(x, True, dy, True).t()
+    return gemm_tf32x3(dy, True, x, True)
+
+
 class _LinearTC(torch.autograd.Function):
     """nn.Linear (+ optional ReLU / LeakyReLU(0.01)) with all three GEMMs on the tcgen05 3xTF32 kernel."""
 
@@ -1055,7 +1073,7 @@ class _LinearTC(torch.autograd.Function):
         if ctx.needs_input_grad[0]:
             dx = gemm_tf32x3(dy, False, weight, True, weight_b=True)          # dX[M,K] = dY[M,N] W[N,K]
         if ctx.needs_input_grad[1]:
-            dw = gemm_tf32x3(dy, True, x, True)                # dW[N,K] = dY^T[N,M] X[M,K]
+            dw = weight_grad_gemm(dy, x)                       # dW[N,K] = dY^T[N,M] X[M,K]
         return dx, dw, db, None
 
 
@@ -1080,10 +1098,10 @@ class _MLP2TC(torch.autograd.Function):
         dy = dy.contiguous()
         need = ctx.needs_input_grad
         db2 = act_bwd_colsum(dy, None, 0, True)[1] if (ctx.has_b[1] and need[5]) else None
-        dw2 = gemm_tf32x3(dy, True, hid, True) if need[4] else None          # dW2[N,H] = dY^T hid
+        dw2 = weight_grad_gemm(dy, hid) if need[4] else None                 # dW2[N,H] = dY^T hid
         dz1 = gemm_tf32x3_masked(dy, w2, hid, ctx.act, weight_b=True)                        # dZ1[M,H] = (dY W2) * act'(hid)
         db1 = act_bwd_colsum(dz1, None, 0, True)[1] if (ctx.has_b[0] and need[2]) else None
-        dw1 = gemm_tf32x3(dz1, True, x, True) if need[1] else None
+        dw1 = weight_grad_gemm(dz1, x) if need[1] else None
         dx = gemm_tf32x3(dz1, False, w1, True, weight_b=True) if need[0] else None
         return dx, dw1, db1, None, dw2, db2
 
