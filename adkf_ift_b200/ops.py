@@ -888,6 +888,9 @@ def gemm_tf32x3(a: torch.Tensor, trans_a: bool, b: torch.Tensor, trans_b: bool, 
         raise ValueError(f"contraction mismatch: {tuple(a.shape)} vs {tuple(b.shape)}")
     if out is None:
         out = torch.empty(M, N, dtype=torch.float32, device=a.device)
+    elif (not out.is_cuda or out.dtype != torch.float32 or tuple(out.shape) != (M, N) or out.stride(1) != 1 or out.stride(0) % 4
+          or out.data_ptr() % 16):
+        raise ValueError("gemm_tf32x3: `out` must be an [M, N] fp32 CUDA tensor (or row-strided view) with 16-byte aligned rows")
     ws, nws = None, 0
     # split-K only for the backward operand forms: a forward (K,K) product must give every output row the same bits whatever the
     # number of rows in the launch (the split plan depends on the shape), so that a task's features -- and with them every
@@ -899,7 +902,7 @@ def gemm_tf32x3(a: torch.Tensor, trans_a: bool, b: torch.Tensor, trans_b: bool, 
     rc = lib.adkf_gemm_tf32x3(ctypes.c_void_p(a.data_ptr()), 1 if trans_a else 0, a.stride(0),
                               ctypes.c_void_p(b.data_ptr()), 1 if trans_b else 0, b.stride(0), M, N, K,
                               dptr(bias.contiguous(), torch.float32) if bias is not None else ctypes.c_void_p(0),
-                              ACT_IDS[act], dptr(out, torch.float32), out.stride(0),
+                              ACT_IDS[act], ctypes.c_void_p(out.data_ptr()), out.stride(0),
                               dptr(ws) if ws is not None else ctypes.c_void_p(0), nws, stream_ptr())
     check(rc, "adkf_gemm_tf32x3")
     return out

@@ -289,3 +289,35 @@ def test_presplit_weight_images_equal_the_in_kernel_split(cuda_device, M, N, K):
     w.mul_(2.0)
     pre2 = ops.gemm_weight_pre(x, w, False, b, "relu")
     assert torch.equal(pre2, ops.gemm_tf32x3(x, False, w, False, b, "relu"))
+
+
+@pytest.mark.parametrize("M", [129, 257, 1000, 4099])
+@pytest.mark.parametrize("N,K", [(32, 32), (64, 100), (96, 192), (160, 64), (384, 36)])
+def test_tma_store_epilogue_clipping_and_strided_outputs(cuda_device, M, N, K):
+    """The TMA-store epilogue of the pair kernel (N % 32 == 0): partial row tiles are clipped by the tensor map, 32-column passes
+    past N are skipped, and an output that is a column block of a wider buffer (ldd > N) leaves its neighbours untouched; K tails
+    (K % 32 != 0) are zero-filled by the loads.  Checked against fp64 for plain, bias + relu and the masked form."""
+    from adkf_ift_b200 import ops
+    g = torch.Generator().manual_seed(1000 * M + 10 * N + K)
+    a = torch.randn(M, K, generator=g).to(cuda_device)
+    w = (torch.randn(N, K, generator=g) / max(K, 1) ** 0.5).to(cuda_device)
+    b = torch.randn(N, generator=g).to(cuda_device)
+    ref = a.double() @ w.double().t()
+    y = ops.gemm_tf32x3(a, False, w, False)
+    assert y.shape == (M, N) and rel(y, ref) < 2e-6
+    y = ops.gemm_tf32x3(a, False, w, False, b, "relu")
+    assert rel(y, (ref + b.double()).clamp_min(0)) < 2e-6
+    # output = columns [32, 32 + N) of a wider buffer filled with a sentinel
+    wide = torch.full((M + 3, N + 96), 7.0, device=cuda_device)
+    view = wide[:M, 32:32 + N]
+    ops.gemm_tf32x3(a, False, w, False, b, None, out=view)
+    assert rel(view, ref + b.double()) < 2e-6
+    wide[:M, 32:32 + N] = 7.0
+    assert float(wide.min()) == 7.0 and float(wide.max()) == 7.0, "the epilogue wrote outside its column block / past row M"
+    # masked input-gradient form (K,T): (dy @ w2) * leaky_relu'(mask), N_out = K here
+    if K % 4 == 0:
+        dy = torch.randn(M, N, generator=g).to(cuda_device)
+        mask = torch.randn(M, K, generator=g).to(cuda_device)
+        got = ops.gemm_tf32x3_masked(dy, w, mask, 2)
+        want = (dy.double() @ w.double()) * torch.where(mask > 0, 1.0, 0.01).double()
+        assert rel(got, want) < 4e-6
