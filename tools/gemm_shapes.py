@@ -80,7 +80,7 @@ def pna(count):
 
 
 pna(10)
-layer("proj", 10, V, 3072, 128)
+layer("proj (degree scalers folded: [384,1024])", 10, V, 1024, 384)
 layer("boom1", 10, V, 128, 1024, "leaky_relu")
 layer("boom2", 10, V, 1024, 128)
 layer("readout hidden", 4, V, 1408, 768, "relu")
