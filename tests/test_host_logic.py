@@ -374,3 +374,15 @@ def test_host_pipeline_workers_equal_inline():
     r1 = HostBatchPipeline(spec, num_workers=0, emulate_workers=1, rank=1, world=2)
     f0, f1 = next(r0).fingerprints, next(r1).fingerprints
     assert f0.shape != f1.shape or not torch.equal(f0, f1)
+
+
+def test_weight_gradient_orientation_rule():
+    """ops.weight_grad_gemm computes dW in the orientation whose padded tile area (256 x 128 pair tiles above 128 rows, 128 x 128
+    below) is smaller: the [384, 1024] projection gradient goes transposed, square and already-fitting shapes stay."""
+    from adkf_ift_b200 import ops
+    assert ops._padded_tile_area(384, 1024) == 512 * 1024 and ops._padded_tile_area(1024, 384) == 1024 * 384
+    assert ops._padded_tile_area(128, 1024) == ops._padded_tile_area(1024, 128) == 128 * 1024
+    assert ops._padded_tile_area(768, 1408) == 768 * 1408 and ops._padded_tile_area(1408, 768) == 1536 * 768
+    e0 = ops._WEIGHT_EPOCH[0]
+    ops.weights_changed()
+    assert ops._WEIGHT_EPOCH[0] == e0 + 1
