@@ -340,20 +340,24 @@ class _PNAMessagePassingFused(torch.autograd.Function):
         return d_h, d_W, d_b, None
 
 
-# Which path runs (measured on the C2 graph batch, tools/pna_fused_probe.py, profiles/r2p_pna_fused_probe.txt): the fused forward
-# is 0.93 ms against 0.99 ms for the chain, but a backward pass that has to RECOMPUTE the pre-activations costs 2.09 ms against
-# 1.46 ms for the chain that saved them (the recompute repeats the gather + MMA work of the forward; the d-pre arithmetic per node is
-# latency-bound).  So by default the fused kernel serves the passes that need no gradient (meta-test, evaluation, prediction) and
-# meta-training keeps the chain.  ADKF_PNA_FUSED=0: never fused; =2: fused in training as well (A/B runs).
+# Which path runs (measured on the C2 graph batch, tools/pna_fused_probe.py, profiles/r2z_pna_fused_probe.txt): the fused forward
+# takes 0.94 ms; the chain took 0.99 ms when the fused kernel was written and takes 0.78 ms since its GEMM got the TMA-store epilogue.
+# A backward pass that has to RECOMPUTE the pre-activations costs 1.93 ms against 1.29 ms for the chain that saved them.  What the
+# fused kernel still buys is MEMORY: the chain materialises XG [2E,256] + pre [2E,768] (4 KB per message: 1.2 GB at C2, 19 GB for
+# the 256-task meta-test pass) and moves 3.0 GB through HBM per block where the fused kernel moves 0.8 GB.  So it serves the passes
+# without gradient whose transient buffers would exceed _FUSED_MIN_BYTES; everything else runs the chain.
+# ADKF_PNA_FUSED=0: never fused; =2: fused whenever the graph allows it, training included (A/B runs).
 _FUSED_MODE = int(os.environ.get("ADKF_PNA_FUSED", "1"))
+_FUSED_MIN_BYTES = 32 << 30
 
 
 def multiaggr_message_passing(h, W, b, gi: GraphIndex, fused: Optional[bool] = None):
-    """Unscaled [V,1024] aggregate of the 4 towers: the fused kernel when the graph allows it (in-degree <= 16) and no gradient is
-    wanted (see above; `fused` overrides the choice), else the three-kernel chain."""
+    """Unscaled [V,1024] aggregate of the 4 towers: the three-kernel chain, or the fused kernel (in-degree <= 16) for no-gradient
+    passes whose XG / pre buffers would be larger than _FUSED_MIN_BYTES (see above; `fused` overrides the choice)."""
     if fused is None:
         needs_grad = torch.is_grad_enabled() and (h.requires_grad or W.requires_grad or b.requires_grad)
-        fused = _FUSED_MODE == 2 or (_FUSED_MODE == 1 and not needs_grad)
+        big = gi.num_edges * 4096 > _FUSED_MIN_BYTES
+        fused = _FUSED_MODE == 2 or (_FUSED_MODE == 1 and not needs_grad and big)
     if fused and gi.fused_ok and gi.num_edges > 0:
         return _PNAMessagePassingFused.apply(h, W, b, gi)
     return _PNAMessagePassingTC.apply(h, W, b, gi, MP_MULTIAGGR)
