@@ -45,12 +45,13 @@ constexpr int kBH = 64;                              // B rows held by one CTA
 // NS = number of split stages (B tiles in smem, A operand in TMEM).  NS = 2: hi.hi and the corrections in separate TMEM
 // accumulators (big[2] + small + 2 operand stages = 512 columns).  NS = 4: the corrections go to the hi.hi accumulator of their
 // drain group (big[2] + 4 operand stages): twice the pipeline depth for the cross-CTA hand-offs, one more rounding per product.
-// Staging tiles per drain warp / raw ring depth by operand form: the (K,T) instantiation (input gradients -- the only form with
-// masked outputs) has two staging tiles per warp (TMA-fetched mask boxes, both passes in flight) and a 5-deep raw ring; the other
-// forms keep one staging tile and the 6-deep ring (A/B on one box, profiles/r2s_gemm_trace_*.txt: depth 5 costs the long-K forward
-// launches 4%, the masked TMA epilogue saves 1.9 ms per step).
-constexpr int stage_bufs(bool TA, bool TB) { return (!TA && TB) ? 2 : 1; }
-constexpr int raw_depth(int NS, int bufs) { return (NS == 4 || bufs == 2) ? 5 : 6; }
+// Staging tiles per drain warp / raw ring depth by operand form: the forms with M-long outputs -- (K,K) forward and (K,T) input
+// gradients, the latter the only one with masked outputs -- have two staging tiles per warp (both 32-column passes in flight, TMA-fetched
+// mask boxes) and a 5-deep raw ring; the weight-gradient form (T,T), whose outputs are small, keeps one tile and the 6-deep ring.
+// (A/B on one box, profiles/r2s_gemm_trace_*.txt: depth 5 costs a long-K in-kernel-split forward launch 4% -- those now run the
+// pre-split variant -- and the second tile is what the epilogue-bound short-K launches need.)
+constexpr int stage_bufs(bool TA, bool TB) { return TA ? 1 : 2; }
+constexpr int raw_depth(int NS, int bufs) { return NS == 4 ? (bufs == 2 ? 4 : 5) : (bufs == 2 ? 5 : 6); }   // (every variant <= 227 KB)
 constexpr int kBHalfBytes = kBH * kBK * 4;           // 8 KB
 constexpr int kRawBytes = kTileBytes + kBHalfBytes;  // A 16 KB + B half 8 KB
 constexpr int kSplitBytes = 2 * kBHalfBytes;         // B_hi 8 KB + B_cat (or B_lo) 8 KB
@@ -495,6 +496,7 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     constexpr int kRaw = Cfg::kRaw, kSplit = NS, kRingBytes = Cfg::kRingBytes, kAopCol = aop_col(NS);
     constexpr bool kMerged = NS == 4;
     static_assert(!PRE || (!TA && !TB && NS == 2 && CORR16 != 0), "pre-split B: forward operand forms, 16-bit corrections");
+    static_assert(Cfg::kSmem <= 227 * 1024, "shared memory of this variant exceeds the 227 KB a CTA can have");
     extern __shared__ unsigned char smem_raw[];
     const uint32_t raw = smem_u32(smem_raw);
     const uint32_t base = (raw + 1023u) & ~1023u;
