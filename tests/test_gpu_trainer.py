@@ -233,3 +233,46 @@ def test_weight_images_follow_the_flat_buffer_optimizer(cuda_device):
         assert float((hi - w.detach()).abs().max()) <= float(w.detach().abs().max()) * 2 ** -10     # hi image = tf32(current weight)
     finally:
         ops._PRE_MIN_ROWS, ops._PRESPLIT = old_rows, old_on
+
+
+def test_training_trajectory_same_on_the_one_cta_gemm_without_round2_paths(cuda_device):
+    """Regression guard over everything the GEMM gained in round 2 (CTA pairs, 16-bit correction operands, TMA-store epilogue, pre-split
+    weight images rebuilt after every optimizer step, weight-gradient orientation): four training steps from the same initial model
+    on the default path and with adkf_gemm_configure(impl=1) -- every product on the round-1 one-CTA kernel (in-kernel split, tf32
+    corrections, LDS/STG epilogue, no images) -- give the same loss trajectory.  (Parameters are not compared entry by entry: Adam's
+    first updates are lr * sign(g), so an entry whose gradient is ~0 may legitimately move the other way.)"""
+    from adkf_ift_b200 import _cabi, dkt, ops, synthetic, task_batch
+    from adkf_ift_b200.adaptive_dkt import ADKTModelTrainerConfig
+    from adkf_ift_b200.adaptive_dkt_utils import ADKTModelTrainer
+    from adkf_ift_b200.feature_extractor import cli_default_config
+    lib = _cabi.load()
+    hosts = [dkt.task_sample_to_dkt_task_sample(synthetic.make_task_sample(500 + i, 16, 24), dkt.get_dkt_batcher(max_num_graphs=320),
+                                                False).batches[0] for i in range(3)]
+    old_rows = ops._PRE_MIN_ROWS
+    ops._PRE_MIN_ROWS = 256                       # let the image path run on the small test graphs
+
+    def run(impl):
+        prev = lib.adkf_gemm_configure(impl, -1)
+        try:
+            cfg = ADKTModelTrainerConfig(graph_feature_extractor_config=cli_default_config(2), learning_rate=1e-3)
+            model = ADKTModelTrainer(cfg)
+            synthetic.deterministic_init_(model, seed=0, alpha=0.5)
+            model.to(cuda_device)
+            tb = task_batch.to_device(task_batch.collate_tasks(hosts, False), cuda_device)
+            losses = [float(model.train_step(tb).loss_per_sample.mean()) for _ in range(4)]
+            used_images = any(getattr(p, "_adkf_images", None) for p in model.parameters())
+            return losses, used_images
+        finally:
+            lib.adkf_gemm_configure(prev & 0xff, prev >> 8)
+
+    try:
+        new, img_new = run(2)
+        old, img_old = run(1)
+    finally:
+        ops._PRE_MIN_ROWS = old_rows
+    print("loss trajectories: default", new, "| one-CTA round-1 path", old)
+    assert img_new and not img_old
+    assert new[-1] != new[0]                                        # the model moved
+    scale = max(abs(x) for x in old)                               # (the loss crosses zero on the way down: judge on the trajectory's scale)
+    for a, b in zip(new, old):
+        assert abs(a - b) <= 2e-4 * scale, (new, old)
